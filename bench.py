@@ -1,0 +1,299 @@
+#!/usr/bin/env python
+"""bench.py — CG iterations/sec of the LS-SVM hot path (BASELINE.json metric) on N B200s of one node.
+
+A "step" is one CG iteration (implicit matvec Abar*d + the fused vector updates / dot products) on the BASELINE
+configs[1] workload: RBF kernel, 65536 points x 1024 dense features, float, gamma = 1/F, C = 1 — run in fixed-iteration
+mode (eps = 0) because at the configured eps = 1e-3 CG converges after 1-2 iterations.  A timed solve of K
+steps therefore contains K + 1 applications of the implicit matrix (the initial residual, csvm.cpp:94) plus one more per
+50 iterations (csvm.cpp:130-135) — they are inside the timed region, nothing is skipped.
+
+  value : K / t, t = device time (CUDA events on the launching stream, max over ranks) of one b200svm_cg_solve call with
+          the training matrix already resident in HBM.
+  e2e   : K / t_e2e through the C ABI with HOST buffers: b200svm_set_data_dense (H2D of X from pinned memory) +
+          b200svm_generate_q + b200svm_cg_solve (H2D of b, D2H of alpha) inside the timed region.
+  roofline : the O(m^2 F) Gram-tile kernel; algorithmic flops per launch = F * m * (m+1), duration =
+          CUDA events recorded around each launch inside libb200svm (b200svm_stats.matvec_ms / matvecs).
+  cpu_baseline / --impl reference : the UNMODIFIED reference OpenMP backend (oracle/_ref, built from /root/reference) or,
+          if absent, the oracle port, timed on the host cores on a bounded row-subset of the same workload and scaled by
+          the pair count to one full CG iteration.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "cg_iterations_per_sec"
+UNIT = "iterations/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--points", type=int, default=65536)
+    ap.add_argument("--features", type=int, default=1024)
+    ap.add_argument("--kernel", default="rbf", choices=["linear", "polynomial", "rbf"])
+    ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
+    ap.add_argument("--path", type=int, default=0, help="matvec path: 0 auto, 1 SIMT, 2 tcgen05")
+    ap.add_argument("--cpu-sample-points", type=int, default=0, help="row subset for the CPU baseline (0 = calibrate to ~10 s)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--seed", type=int, default=43)
+    return ap.parse_args()
+
+
+def workload_config(a):
+    return {
+        "workload": f"configs[1]: {a.kernel} kernel, {a.points} points x {a.features} dense features, {a.dtype}, gamma=1/F, C=1, "
+                    "fixed-iteration CG (eps=0)",
+        "points": a.points, "features": a.features, "kernel": a.kernel,
+        "l2": "inputs larger than L2 (X = %.0f MB > 126 MB); vectors are rewritten every step" % (a.points * a.features * (4 if a.dtype == "f32" else 8) / 1e6),
+    }
+
+
+def alg_flops_per_matvec(n, F):
+    m = n - 1
+    return float(F) * m * (m + 1)  # 2 F P, P = m(m+1)/2 unordered pairs incl. diagonal
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# CPU arm: reference OpenMP backend (oracle/_ref) or the oracle port, on a bounded sample
+# ----------------------------------------------------------------------------------------------------------------------
+def cpu_reference_iteration_rate(a, steps, warmup, X, sample_points=0, budget_s=10.0):
+    """Times the reference's run_device_kernel on the first n_s points (all F features) and scales by the pair count."""
+    from oracle import port, ref
+    dt = np.float32 if a.dtype == "f32" else np.float64
+    use_ref = ref.available()
+    cores = os.cpu_count() or 1
+    if use_ref:
+        ref.set_num_threads(cores)
+
+    def one(ns):
+        Xs = np.ascontiguousarray(X[:ns].astype(dt))
+        d = np.ones(ns - 1, dt)
+        q = np.zeros(ns - 1, dt)
+        t0 = time.perf_counter()
+        if use_ref:
+            ref.matvec(Xs, q, d, 1.0, 1.0, a.kernel)
+        else:
+            port.matvec(Xs, q, d, 1.0, 1.0, a.kernel, rows=(0, ns - 1))
+        return time.perf_counter() - t0
+
+    ns = sample_points
+    if ns <= 0:
+        t_probe = one(1024)
+        per_pair = t_probe / (1023 * 1024 / 2 if use_ref else 1023 * 1023)
+        ns = int(min(a.points, max(1024, (2 * (budget_s / max(steps + warmup, 1)) / per_pair) ** 0.5 if use_ref
+                                   else (budget_s / max(steps + warmup, 1) / per_pair) ** 0.5)))
+        ns = max(1024, ns // 256 * 256)
+    for _ in range(warmup):
+        one(ns)
+    ts = [one(ns) for _ in range(steps)]
+    t = float(np.sum(ts))
+    m_s, m = ns - 1, a.points - 1
+    pairs_s = m_s * (m_s + 1) / 2 if use_ref else float(m_s) * m_s
+    pairs_full = m * (m + 1) / 2 if use_ref else float(m) * m
+    t_iter_full = (t / steps) * pairs_full / pairs_s  # one CG iteration = one matvec (+ O(m) vector ops, ignored)
+    return {
+        "value": 1.0 / t_iter_full, "unit": UNIT, "cores": cores, "kind": "reference" if use_ref else "port",
+        "sample": f"run_device_kernel on the first {ns} of {a.points} points (all {a.features} features), {steps} timed calls "
+                  f"({t:.1f} s CPU wall), scaled by the pair count to one full iteration",
+        "ms_per_step": 1e3 * t_iter_full, "seconds_measured": t,
+    }
+
+
+def run_reference_arm(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from plssvm_sparse_fp22_b200 import datagen
+    X, _ = datagen.make_dense(min(a.points, 16384), a.features, seed=a.seed, problem="blobs", dtype=np.float32 if a.dtype == "f32" else np.float64)
+    res = cpu_reference_iteration_rate(a, a.steps, a.warmup, X, a.cpu_sample_points, budget_s=60.0)
+    line = {
+        "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": a.dtype, "data": "synthetic", "config": workload_config(a), "impl": "reference",
+        "cpu_baseline": {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": res["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# GPU arm
+# ----------------------------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples = []
+        self.stop_flag = threading.Event()
+
+    def run(self):
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([s.strip() for s in out.split(",")])
+            except Exception:
+                pass
+            self.stop_flag.wait(0.1)
+
+    def summary(self):
+        sm = [float(s[0]) for s in self.samples if s and s[0].replace(".", "").isdigit()]
+        mx = [float(s[1]) for s in self.samples if len(s) > 1 and s[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [nm for k, nm in enumerate(names) if any(len(s) > 3 + k and s[3 + k].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.samples)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d, "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+def run_b200_arm(a):
+    import torch
+    import torch.distributed as dist
+
+    from plssvm_sparse_fp22_b200 import capi, datagen
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the B200 arm has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dt = np.float32 if a.dtype == "f32" else np.float64
+    n, F, K, W = a.points, a.features, a.steps, a.warmup
+
+    X, y = datagen.make_dense(n, F, seed=a.seed, problem="blobs", dtype=dt)
+    # pinned host staging for the e2e leg
+    Xp = torch.empty((n, F), dtype=torch.float32 if dt == np.float32 else torch.float64, pin_memory=True)
+    Xp.numpy()[:] = X
+    Xh = Xp.numpy()
+    b = (y[:-1] - y[-1]).astype(dt)
+
+    h = capi.Handle(dt, a.kernel, 3, 1.0 / F, 0.0, 1.0, device=local_rank)
+    stream = torch.cuda.current_stream()
+    h.set_stream(stream.cuda_stream)
+    if a.path:
+        h.set_option(capi.OPT_MATVEC_PATH, a.path)
+    if world > 1:
+        idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idbuf.copy_(torch.frombuffer(bytearray(capi.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idbuf, 0)
+        h.comm_init(bytes(idbuf.cpu().numpy().tobytes()), rank, world)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- resident leg (value) ----
+    h.set_data(Xh)
+    q = h.generate_q()
+    QA = h.kxx_last() + 1.0
+    h.solver_cg(b, None, QA, max(W, 3), 0.0)  # warm-up steps (untimed)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    h.reset_stats()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    alpha, iters, delta = h.solver_cg(b, None, QA, K, 0.0)
+    e1.record(stream)
+    barrier()
+    t_ms = e0.elapsed_time(e1)
+    st = h.stats()
+    assert iters == K, (iters, K)
+    launches = int(st.kernel_launches)
+    matvec_ms = st.matvec_ms / max(st.matvecs, 1)
+    n_matvecs = int(st.matvecs)
+    path = int(st.matvec_path)
+
+    # ---- e2e leg: host buffers through the C ABI ----
+    def e2e_once():
+        h.set_data(Xh)
+        h.generate_q()
+        return h.solver_cg(b, None, QA, K, 0.0)
+
+    e2e_once()  # warm-up (allocations)
+    barrier()
+    h.reset_stats()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record(stream)
+    e2e_once()
+    f1.record(stream)
+    barrier()
+    t_e2e_ms = f0.elapsed_time(f1)
+    st2 = h.stats()
+    sampler.stop_flag.set()
+    sampler.join(timeout=2)
+
+    if world > 1:
+        tt = torch.tensor([t_ms, t_e2e_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t_ms, t_e2e_ms = float(tt[0]), float(tt[1])
+
+    if rank == 0:
+        peaks, peak_kind = measured_peaks()
+        flops = alg_flops_per_matvec(n, F)
+        achieved = flops / (matvec_ms * 1e-3) / 1e12 if matvec_ms > 0 else 0.0
+        # the kernel is timed inside a multi-second solve -> sustained tensor figure
+        peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops")))
+        roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": f"{peak_kind} bf16 dense (sustained)", "kernel": {1: "k_kmv_tile (SIMT fp32)", 2: "k_gram_tc (tcgen05 fp16x2-split)", 3: "gemv pair"}.get(path, "?"),
+                "alg_flops_per_launch": flops, "ms_per_launch": matvec_ms, "launches_timed": n_matvecs}
+        line = {
+            "metric": METRIC, "value": K / (t_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(W, 3),
+            "ms_per_step": t_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": a.dtype, "data": "synthetic", "config": workload_config(a),
+            "matvec_gflops": flops / (matvec_ms * 1e-3) / 1e9 if matvec_ms > 0 else None,
+            "clocks": sampler.summary(),
+            "e2e": {"value": K / (t_e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": st2.h2d_bytes / K, "d2h_bytes_per_step": st2.d2h_bytes / K,
+                    "ms_total": t_e2e_ms},
+            "gpu_launches": launches,
+            "roofline": roof,
+        }
+        if world == 1 and not a.no_cpu_baseline:
+            res = cpu_reference_iteration_rate(a, 1, 0, X, a.cpu_sample_points, budget_s=12.0)
+            line["cpu_baseline"] = {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line), flush=True)
+    h.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference_arm(a)
+    else:
+        run_b200_arm(a)
+
+
+if __name__ == "__main__":
+    main()

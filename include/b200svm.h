@@ -1,0 +1,127 @@
+/*
+ * b200svm.h — C ABI of the B200-native LS-SVM hot path (libb200svm.so).
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types, no exceptions.  Every entry point returns
+ * B200SVM_OK (0) or an error code; the message is available through b200svm_last_error().  The entry points are what a
+ * PLSSVM backend (a subclass of plssvm::csvm<T>, reference include/plssvm/csvm.hpp:33-278) calls from its five protected
+ * pure virtuals; each declaration cites the reference interface it replaces (paths relative to the reference tree).
+ * There is no CPU fallback: every compute entry point fails with B200SVM_ERR_CUDA when no sm_100 device is usable.
+ *
+ * Host pointers unless a parameter is named *_dev.  `n` = number of data points, `F` = number of features,
+ * m = n - 1 = size of the reduced system ("dept" in the reference).  Real type is selected per handle (dtype).
+ */
+#ifndef B200SVM_H
+#define B200SVM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200SVM_OK 0
+#define B200SVM_ERR_INVALID 1  /* bad argument / call order                           */
+#define B200SVM_ERR_CUDA 2     /* CUDA runtime / driver error, or no usable device    */
+#define B200SVM_ERR_NCCL 3     /* NCCL error                                          */
+#define B200SVM_ERR_ALLOC 4    /* host or device allocation failure                   */
+
+/* real type of the handle: plssvm::csvm<float> / plssvm::csvm<double> (include/plssvm/csvm.hpp:33-39) */
+#define B200SVM_F32 0
+#define B200SVM_F64 1
+/* plssvm::kernel_type (include/plssvm/kernel_types.hpp:27-34) */
+#define B200SVM_LINEAR 0
+#define B200SVM_POLYNOMIAL 1
+#define B200SVM_RBF 2
+/* value storage of CSR data (the reference stores dense vector<vector<real>> only) */
+#define B200SVM_VAL_F32 0
+#define B200SVM_VAL_F64 1
+#define B200SVM_VAL_FP22 2 /* packed 32-bit entries: (fp22 << 10) | column_delta, see DESIGN.md "FP22" */
+
+typedef struct b200svm_ctx *b200svm_handle;
+
+/* Error text of the last failing call on this handle (or of the last failing b200svm_create when h == NULL). */
+const char *b200svm_last_error(b200svm_handle h);
+
+/* Library/ABI version (major * 1000 + minor). */
+int b200svm_version(void);
+
+/* Replaces the backend constructor: plssvm::csvm<T>::csvm(const parameter<T>&) (src/plssvm/csvm.cpp:39-57) +
+ * plssvm::cuda::csvm ctor device selection (src/plssvm/backends/CUDA/csvm.cu:38-80).  `device` = CUDA ordinal.
+ * gamma must be > 0 for polynomial / rbf (the caller resolves the 1/F default, src/plssvm/parameter.cpp:150-152). */
+int b200svm_create(b200svm_handle *h, int dtype, int kernel, int degree, double gamma, double coef0, double cost, int device);
+int b200svm_destroy(b200svm_handle h);
+
+/* Launch all work of this handle on an existing CUDA stream (cudaStream_t passed as void*); NULL = the handle's own
+ * stream.  Lets a harness time the kernels with events recorded on the launching stream. */
+int b200svm_set_stream(b200svm_handle h, void *cuda_stream);
+
+/* Replaces setup_data_on_device() (include/plssvm/csvm.hpp:188; GPU analogue src/plssvm/backends/gpu_csvm.cpp:129-157):
+ * copies the n x F training matrix (row-major, leading dimension ld elements) to HBM and prepares device-side layouts.
+ * The last row is the reference's "last point" x_n; rows 0..n-2 span the reduced system. */
+int b200svm_set_data_dense(b200svm_handle h, const void *X, int64_t n, int64_t F, int64_t ld);
+/* Same for CSR rows (sorted, unique column indices per row).  rowptr int64[n+1], colidx int32[nnz];
+ * values: float[nnz] / double[nnz] for VAL_F32 / VAL_F64, or uint32 packed entries for VAL_FP22 (colidx ignored). */
+int b200svm_set_data_csr(b200svm_handle h, const int64_t *rowptr, const int32_t *colidx, const void *values, int64_t n, int64_t F,
+                         int64_t nnz, int value_format);
+
+/* Replaces generate_q() (include/plssvm/csvm.hpp:193; src/plssvm/backends/OpenMP/q_kernel.cpp:19-50):
+ * q[i] = k(x_i, x_n), i < m.  Keeps q resident on the device; q_out (m reals) may be NULL.
+ * Also evaluates k(x_n, x_n) (src/plssvm/csvm.cpp:243) — see b200svm_get_kxx_last. */
+int b200svm_generate_q(b200svm_handle h, void *q_out);
+int b200svm_get_kxx_last(b200svm_handle h, double *kxx);
+/* Test hook: overwrite the device-resident q and QA_cost (mirrors mock_csvm::set_QA_cost, tests/backends/OpenMP/mock_openmp_csvm.hpp:38). */
+int b200svm_set_q(b200svm_handle h, const void *q, double QA_cost);
+
+/* Replaces run_device_kernel (src/plssvm/backends/OpenMP/csvm.cpp:67-79 -> svm_kernel.cpp:21-47):
+ * ret += add * Abar * d, Abar_ij = k(x_i,x_j) + QA_cost - q_i - q_j + delta_ij / C.  d, ret: m reals. */
+int b200svm_matvec(b200svm_handle h, const void *d, double add, void *ret_inout);
+
+/* Replaces solver_CG (include/plssvm/csvm.hpp:204; src/plssvm/backends/OpenMP/csvm.cpp:82-170): alpha_0 = 1, residual
+ * refresh every 50th iteration, stop when delta <= eps^2 delta_0, at most imax iterations; all vectors stay on the device.
+ * b: m reals; q: m reals or NULL (use the device-resident q); alpha_out: m reals.  iters = iterations executed
+ * (the value the reference prints, csvm.cpp:162-167); delta = final residual r.r (may be NULL). */
+int b200svm_cg_solve(b200svm_handle h, const void *b, const void *q, double QA_cost, int64_t imax, double eps, void *alpha_out,
+                     int64_t *iters, double *delta);
+
+/* Whole csvm::learn() numeric path (src/plssvm/csvm.cpp:228-258) on the device: q, b = y - y_n, QA_cost, CG (imax = F),
+ * bias, alpha_n = -sum(alpha).  y: n reals (+-1).  alpha_out: n reals; rho_out = -bias. */
+int b200svm_learn(b200svm_handle h, const void *y, double eps, void *alpha_out, double *rho_out, int64_t *iters);
+
+/* Replaces update_w() (include/plssvm/csvm.hpp:208; src/plssvm/backends/OpenMP/csvm.cpp:173-188): w[f] = sum_i alpha_i x_i[f]
+ * over the data set by set_data_*; alpha: n reals; w_out: F reals. */
+int b200svm_update_w(b200svm_handle h, const void *alpha, void *w_out);
+
+/* Replaces predict(points) (include/plssvm/csvm.hpp:214; src/plssvm/backends/OpenMP/csvm.cpp:191-244): decision values
+ * out[p] = -rho + sum_i alpha_i k(x_i, p) over the support vectors set by set_data_* (alpha: n reals). */
+int b200svm_predict_dense(b200svm_handle h, const void *alpha, double rho, const void *points, int64_t P, int64_t ld, void *out);
+int b200svm_predict_csr(b200svm_handle h, const void *alpha, double rho, const int64_t *rowptr, const int32_t *colidx, const void *values,
+                        int64_t P, int64_t nnz, int value_format, void *out);
+
+/* Multi-GPU (one process per GPU): rows/tiles of the implicit matrix are partitioned over `world` ranks; the CG loop
+ * exchanges with NCCL on the handle's stream.  The unique id (128 bytes) is created on rank 0 and distributed by the
+ * caller (e.g. torch.distributed broadcast).  Replaces the reference's host-staged device_reduction
+ * (src/plssvm/backends/gpu_csvm.cpp:365-386). */
+int b200svm_comm_unique_id(void *id128);
+int b200svm_comm_init(b200svm_handle h, const void *id128, int rank, int world);
+
+/* Tuning / introspection. */
+#define B200SVM_OPT_MATVEC_PATH 1 /* 0 = auto, 1 = SIMT full-square, 2 = tcgen05 symmetric tiles (f32 dense only) */
+#define B200SVM_OPT_SYNC_EVERY 2  /* CG: host polls the convergence flag every k iterations (default 1)            */
+int b200svm_set_option(b200svm_handle h, int option, int64_t value);
+
+typedef struct b200svm_stats {
+    int64_t kernel_launches;  /* CUDA kernels launched by this handle since creation / last reset */
+    int64_t matvecs;          /* applications of Abar                                              */
+    double matvec_ms;         /* accumulated device time of the O(m^2) kernel (CUDA events)       */
+    int64_t matvec_path;      /* path used by the last matvec (B200SVM_OPT_MATVEC_PATH values)    */
+    int64_t h2d_bytes;        /* host->device bytes copied                                        */
+    int64_t d2h_bytes;        /* device->host bytes copied                                        */
+} b200svm_stats;
+int b200svm_get_stats(b200svm_handle h, b200svm_stats *out);
+int b200svm_reset_stats(b200svm_handle h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SVM_H */

@@ -1,0 +1,407 @@
+// C ABI of libb200svm.so (see include/b200svm.h for the contract and the reference interfaces each entry replaces).
+#include "internal.cuh"
+
+#include <cstring>
+#include <exception>
+#include <new>
+
+using namespace b200;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+template <typename Fn>
+int guarded(ctx *c, Fn &&fn) {
+    try {
+        if (c != nullptr) { B200_CUDA_CHECK(cudaSetDevice(c->device)); }  // callers may hop threads (src/plssvm/csvm.cpp:230-235)
+        fn();
+        return B200SVM_OK;
+    } catch (const error &e) {
+        (c != nullptr ? c->last_error : g_create_error) = e.msg;
+        return e.code;
+    } catch (const std::bad_alloc &) {
+        (c != nullptr ? c->last_error : g_create_error) = "host allocation failed";
+        return B200SVM_ERR_ALLOC;
+    } catch (const std::exception &e) {
+        (c != nullptr ? c->last_error : g_create_error) = e.what();
+        return B200SVM_ERR_INVALID;
+    }
+}
+
+#define DISPATCH_T(c, expr_f32, expr_f64)   \
+    do {                                    \
+        if ((c)->dtype == B200SVM_F32) {    \
+            using T = float;                \
+            expr_f32;                       \
+        } else {                            \
+            using T = double;               \
+            expr_f64;                       \
+        }                                   \
+    } while (0)
+
+void h2d(ctx &c, void *dst, const void *src, size_t bytes) {
+    if (bytes == 0) { return; }
+    B200_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c.stream));
+    c.stats.h2d_bytes += (int64_t) bytes;
+}
+void d2h(ctx &c, void *dst, const void *src, size_t bytes) {
+    if (bytes == 0) { return; }
+    B200_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c.stream));
+    c.stats.d2h_bytes += (int64_t) bytes;
+}
+
+// copy a host row-major matrix (rows x F, leading dimension ld) into a zero-padded device matrix (rows x ldd)
+void stage_matrix(ctx &c, void *dst, int64_t ldd, const void *src, int64_t rows, int64_t F, int64_t ld) {
+    const size_t es = c.esize();
+    B200_CUDA_CHECK(cudaMemsetAsync(dst, 0, (size_t) rows * ldd * es, c.stream));
+    B200_CUDA_CHECK(cudaMemcpy2DAsync(dst, (size_t) ldd * es, src, (size_t) ld * es, (size_t) F * es, (size_t) rows, cudaMemcpyHostToDevice, c.stream));
+    c.stats.h2d_bytes += (int64_t) ((size_t) rows * F * es);
+}
+
+void require_data(const ctx &c) { B200_REQUIRE(c.has_data, "no data set: call b200svm_set_data_dense / b200svm_set_data_csr first"); }
+void require_q(const ctx &c) { B200_REQUIRE(c.has_q, "q vector missing: call b200svm_generate_q or b200svm_set_q first"); }
+
+template <typename T>
+void do_generate_q(ctx &c, void *q_out) {
+    require_data(c);
+    B200_REQUIRE(c.n >= 2, "at least two data points are required");
+    c.q.reserve((size_t) c.m() * sizeof(T));
+    generate_q<T>(c);
+    c.has_q = true;
+    if (q_out != nullptr) { d2h(c, q_out, c.q.p, (size_t) c.m() * sizeof(T)); }
+    sync_stream(c);
+}
+
+template <typename T>
+T read_scalar(ctx &c, int idx) {
+    T *mb = static_cast<T *>(c.pinned);
+    B200_CUDA_CHECK(cudaMemcpyAsync(mb, c.scal.as<T>() + idx, sizeof(T), cudaMemcpyDeviceToHost, c.stream));
+    sync_stream(c);
+    return mb[0];
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200svm_version(void) { return 1000; }
+
+const char *b200svm_last_error(b200svm_handle h) {
+    return h != nullptr ? reinterpret_cast<ctx *>(h)->last_error.c_str() : g_create_error.c_str();
+}
+
+int b200svm_create(b200svm_handle *h, int dtype, int kernel, int degree, double gamma, double coef0, double cost, int device) {
+    if (h == nullptr) {
+        g_create_error = "null handle pointer";
+        return B200SVM_ERR_INVALID;
+    }
+    *h = nullptr;
+    ctx *c = nullptr;
+    const int rc = guarded(nullptr, [&]() {
+        B200_REQUIRE(dtype == B200SVM_F32 || dtype == B200SVM_F64, "dtype must be B200SVM_F32 or B200SVM_F64");
+        B200_REQUIRE(kernel >= B200SVM_LINEAR && kernel <= B200SVM_RBF, "unknown kernel type");
+        B200_REQUIRE(cost != 0.0, "cost must not be 0");
+        int count = 0;
+        const cudaError_t e = cudaGetDeviceCount(&count);
+        if (e != cudaSuccess || count == 0) {
+            fail(B200SVM_ERR_CUDA, std::string("no CUDA device available (") + cudaGetErrorString(e) + "): libb200svm has no CPU fallback");
+        }
+        B200_REQUIRE(device >= 0 && device < count, "device ordinal out of range");
+        cudaDeviceProp prop{};
+        B200_CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+        if (prop.major != 10) {
+            fail(B200SVM_ERR_CUDA, std::string("device '") + prop.name + "' is sm_" + std::to_string(prop.major) + std::to_string(prop.minor) +
+                                       "; libb200svm is built for sm_100a (B200) only");
+        }
+        B200_CUDA_CHECK(cudaSetDevice(device));
+        c = new ctx();
+        c->dtype = dtype;
+        c->kernel = kernel;
+        c->degree = degree;
+        c->gamma = gamma;
+        c->coef0 = coef0;
+        c->cost = cost;
+        c->device = device;
+        B200_CUDA_CHECK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+        c->stream = c->own_stream;
+        for (auto &ev : c->ev) { B200_CUDA_CHECK(cudaEventCreate(&ev)); }
+        B200_CUDA_CHECK(cudaMallocHost(&c->pinned, 256));
+        c->scal.reserve(S_COUNT * sizeof(double));
+        c->partials.reserve(4 * MAX_PARTIAL_BLOCKS * sizeof(double));
+        c->counters.reserve(8 * sizeof(unsigned int));
+        B200_CUDA_CHECK(cudaMemsetAsync(c->scal.p, 0, c->scal.bytes, c->stream));
+        B200_CUDA_CHECK(cudaMemsetAsync(c->counters.p, 0, c->counters.bytes, c->stream));
+        B200_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    });
+    if (rc != B200SVM_OK) {
+        delete c;
+        return rc;
+    }
+    *h = reinterpret_cast<b200svm_handle>(c);
+    return B200SVM_OK;
+}
+
+int b200svm_destroy(b200svm_handle h) {
+    if (h == nullptr) { return B200SVM_OK; }
+    ctx *c = reinterpret_cast<ctx *>(h);
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    comm_destroy(*c);
+    for (auto &ev : c->ev) {
+        if (ev != nullptr) { cudaEventDestroy(ev); }
+    }
+    if (c->pinned != nullptr) { cudaFreeHost(c->pinned); }
+    if (c->own_stream != nullptr) { cudaStreamDestroy(c->own_stream); }
+    delete c;
+    return B200SVM_OK;
+}
+
+int b200svm_set_stream(b200svm_handle h, void *cuda_stream) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() {
+        B200_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+        c->stream = cuda_stream != nullptr ? static_cast<cudaStream_t>(cuda_stream) : c->own_stream;
+    });
+}
+
+int b200svm_set_option(b200svm_handle h, int option, int64_t value) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() {
+        switch (option) {
+            case B200SVM_OPT_MATVEC_PATH:
+                B200_REQUIRE(value >= 0 && value <= 2, "matvec path must be 0 (auto), 1 (SIMT) or 2 (tcgen05)");
+                c->opt_matvec_path = value;
+                break;
+            case B200SVM_OPT_SYNC_EVERY:
+                B200_REQUIRE(value >= 1, "sync interval must be >= 1");
+                c->opt_sync_every = value;
+                break;
+            default: fail(B200SVM_ERR_INVALID, "unknown option");
+        }
+    });
+}
+
+int b200svm_get_stats(b200svm_handle h, b200svm_stats *out) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() {
+        B200_REQUIRE(out != nullptr, "null stats pointer");
+        *out = c->stats;
+    });
+}
+
+int b200svm_reset_stats(b200svm_handle h) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() { c->stats = b200svm_stats{}; });
+}
+
+int b200svm_set_data_dense(b200svm_handle h, const void *X, int64_t n, int64_t F, int64_t ld) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() {
+        B200_REQUIRE(X != nullptr, "No data points provided!");               // src/plssvm/csvm.cpp:42
+        B200_REQUIRE(n > 0, "Data set is empty!");                             // src/plssvm/csvm.cpp:44
+        B200_REQUIRE(F > 0, "No features provided for the data points!");      // src/plssvm/csvm.cpp:48
+        B200_REQUIRE(ld >= F, "leading dimension smaller than the number of features");
+        const size_t es = c->esize();
+        c->is_csr = false;
+        c->has_data = false;
+        c->has_q = false;
+        c->has_split = false;
+        c->n = n;
+        c->F = F;
+        c->ldx = (F + 15) / 16 * 16;
+        c->X.reserve((size_t) n * c->ldx * es);
+        c->norms.reserve((size_t) n * es);
+        stage_matrix(*c, c->X.p, c->ldx, X, n, F, ld);
+        DISPATCH_T(c, compute_norms<T>(*c, c->X.as<T>(), n, c->ldx, F, c->norms.as<T>()), compute_norms<T>(*c, c->X.as<T>(), n, c->ldx, F, c->norms.as<T>()));
+        c->has_data = true;
+        if (c->dtype == B200SVM_F32 && c->kernel != B200SVM_LINEAR && c->opt_matvec_path != 1) { tc_prepare_split(*c); }
+        sync_stream(*c);
+    });
+}
+
+int b200svm_generate_q(b200svm_handle h, void *q_out) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() { DISPATCH_T(c, do_generate_q<T>(*c, q_out), do_generate_q<T>(*c, q_out)); });
+}
+
+int b200svm_get_kxx_last(b200svm_handle h, double *kxx) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() {
+        require_q(*c);
+        B200_REQUIRE(kxx != nullptr, "null output pointer");
+        DISPATCH_T(c, *kxx = (double) read_scalar<T>(*c, S_KXX), *kxx = (double) read_scalar<T>(*c, S_KXX));
+    });
+}
+
+int b200svm_set_q(b200svm_handle h, const void *q, double QA_cost) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() {
+        require_data(*c);
+        B200_REQUIRE(c->n >= 2, "at least two data points are required");
+        if (q != nullptr) {
+            c->q.reserve((size_t) c->m() * c->esize());
+            h2d(*c, c->q.p, q, (size_t) c->m() * c->esize());
+            c->has_q = true;
+        }
+        c->QA_cost = QA_cost;
+        sync_stream(*c);
+    });
+}
+
+int b200svm_matvec(b200svm_handle h, const void *d, double add, void *ret_inout) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() {
+        require_data(*c);
+        require_q(*c);
+        B200_REQUIRE(d != nullptr && ret_inout != nullptr, "null vector");
+        const size_t vb = (size_t) c->m() * c->esize();
+        c->v_tmp.reserve(vb);
+        c->v_b.reserve(vb);
+        h2d(*c, c->v_tmp.p, d, vb);
+        h2d(*c, c->v_b.p, ret_inout, vb);
+        DISPATCH_T(c, apply_abar<T>(*c, c->v_tmp.as<T>(), (T) add, c->v_b.as<T>()), apply_abar<T>(*c, c->v_tmp.as<T>(), (T) add, c->v_b.as<T>()));
+        d2h(*c, ret_inout, c->v_b.p, vb);
+        sync_stream(*c);
+    });
+}
+
+int b200svm_cg_solve(b200svm_handle h, const void *b, const void *q, double QA_cost, int64_t imax, double eps, void *alpha_out, int64_t *iters,
+                     double *delta) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() {
+        require_data(*c);
+        B200_REQUIRE(b != nullptr && alpha_out != nullptr, "null vector");
+        B200_REQUIRE(c->n >= 2, "at least two data points are required");
+        const size_t vb = (size_t) c->m() * c->esize();
+        if (q != nullptr) {
+            c->q.reserve(vb);
+            h2d(*c, c->q.p, q, vb);
+            c->has_q = true;
+        }
+        require_q(*c);
+        c->QA_cost = QA_cost;
+        c->v_b.reserve(vb);
+        c->v_x.reserve(vb);
+        h2d(*c, c->v_b.p, b, vb);
+        int64_t it = 0;
+        DISPATCH_T(c, it = cg_solve<T>(*c, c->v_b.as<T>(), imax, (T) eps, c->v_x.as<T>(), delta),
+                   it = cg_solve<T>(*c, c->v_b.as<T>(), imax, (T) eps, c->v_x.as<T>(), delta));
+        d2h(*c, alpha_out, c->v_x.p, vb);
+        sync_stream(*c);
+        if (iters != nullptr) { *iters = it; }
+    });
+}
+
+}  // extern "C"
+
+namespace {
+
+// csvm::learn() numeric path (src/plssvm/csvm.cpp:228-258)
+template <typename T>
+void do_learn(ctx &c, const void *y_host, double eps, void *alpha_out, double *rho_out, int64_t *iters) {
+    require_data(c);
+    B200_REQUIRE(y_host != nullptr, "No labels given for training! Maybe the data is only usable for prediction?");  // csvm.cpp:214
+    B200_REQUIRE(alpha_out != nullptr && rho_out != nullptr, "null output pointer");
+    B200_REQUIRE(c.n >= 2, "at least two data points are required");
+    const int64_t n = c.n, m = c.m();
+    const T *y = static_cast<const T *>(y_host);
+    // q = generate_q() ; QA_cost = k(x_n, x_n) + 1 / C   (csvm.cpp:232-243)
+    c.q.reserve((size_t) m * sizeof(T));
+    generate_q<T>(c);
+    c.has_q = true;
+    // b = y[0..m) - y_n  (csvm.cpp:238-239)
+    std::vector<T> b((size_t) m);
+    for (int64_t i = 0; i < m; ++i) { b[(size_t) i] = y[i] - y[n - 1]; }
+    c.v_b.reserve((size_t) m * sizeof(T));
+    c.v_x.reserve((size_t) n * sizeof(T));
+    h2d(c, c.v_b.p, b.data(), (size_t) m * sizeof(T));
+    const T kxx = read_scalar<T>(c, S_KXX);  // syncs: b may go out of scope afterwards
+    const T QA_cost = kxx + T(1) / (T) c.cost;
+    c.QA_cost = (double) QA_cost;
+    // alpha = solver_CG(b, num_features, epsilon, q)   (csvm.cpp:256)
+    const int64_t it = cg_solve<T>(c, c.v_b.as<T>(), c.F, (T) eps, c.v_x.as<T>(), nullptr);
+    // bias = y_n + QA_cost * sum(alpha) - q.alpha ; alpha_n = -sum(alpha)   (csvm.cpp:257-258)
+    sums2<T>(c, c.v_x.as<T>(), S_SUM_X, S_Q_X);
+    T *mb = static_cast<T *>(c.pinned);
+    B200_CUDA_CHECK(cudaMemcpyAsync(mb, c.scal.as<T>() + S_SUM_X, 2 * sizeof(T), cudaMemcpyDeviceToHost, c.stream));
+    d2h(c, alpha_out, c.v_x.p, (size_t) m * sizeof(T));
+    sync_stream(c);
+    const T sum_alpha = mb[0], q_alpha = mb[1];
+    const T bias = y[n - 1] + QA_cost * sum_alpha - q_alpha;
+    static_cast<T *>(alpha_out)[m] = -sum_alpha;
+    *rho_out = -(double) bias;
+    if (iters != nullptr) { *iters = it; }
+}
+
+template <typename T>
+void do_update_w(ctx &c, const void *alpha, void *w_out) {
+    require_data(c);
+    B200_REQUIRE(!c.is_csr, "update_w on CSR data is not available in this build");
+    B200_REQUIRE(alpha != nullptr && w_out != nullptr, "No alphas provided for prediction!");
+    c.alpha_dev.reserve((size_t) c.n * sizeof(T));
+    c.wvec.reserve((size_t) c.ldx * sizeof(T));
+    h2d(c, c.alpha_dev.p, alpha, (size_t) c.n * sizeof(T));
+    update_w<T>(c, c.alpha_dev.as<T>(), c.wvec.as<T>());
+    d2h(c, w_out, c.wvec.p, (size_t) c.F * sizeof(T));
+    sync_stream(c);
+}
+
+template <typename T>
+void do_predict_dense(ctx &c, const void *alpha, double rho, const void *points, int64_t P, int64_t ld, void *out) {
+    require_data(c);
+    B200_REQUIRE(!c.is_csr, "dense predict against CSR support vectors is not available in this build");
+    B200_REQUIRE(alpha != nullptr, "No alphas provided for prediction!");  // src/plssvm/backends/OpenMP/csvm.cpp:207
+    if (P == 0) { return; }                                                // csvm.cpp:198-200
+    B200_REQUIRE(points != nullptr && out != nullptr, "null pointer");
+    B200_REQUIRE(ld >= c.F, "Number of features per data point must match the number of features per predict point!");
+    c.alpha_dev.reserve((size_t) c.n * sizeof(T));
+    h2d(c, c.alpha_dev.p, alpha, (size_t) c.n * sizeof(T));
+    // stage the points in chunks of at most ~1 GiB
+    int64_t chunk = (int64_t) ((size_t(1) << 30) / ((size_t) c.ldx * sizeof(T)));
+    if (chunk < 1024) { chunk = 1024; }
+    if (chunk > P) { chunk = P; }
+    c.pts.reserve((size_t) chunk * c.ldx * sizeof(T));
+    c.pred_out.reserve((size_t) chunk * sizeof(T));
+    const T bias = (T) (-rho);  // src/plssvm/csvm.cpp:42
+    for (int64_t p0 = 0; p0 < P; p0 += chunk) {
+        const int64_t rows = P - p0 < chunk ? P - p0 : chunk;
+        stage_matrix(c, c.pts.p, c.ldx, static_cast<const T *>(points) + p0 * ld, rows, c.F, ld);
+        predict_dense<T>(c, c.alpha_dev.as<T>(), bias, c.pts.as<T>(), rows, c.ldx, c.pred_out.as<T>());
+        d2h(c, static_cast<T *>(out) + p0, c.pred_out.p, (size_t) rows * sizeof(T));
+        sync_stream(c);
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200svm_learn(b200svm_handle h, const void *y, double eps, void *alpha_out, double *rho_out, int64_t *iters) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() { DISPATCH_T(c, do_learn<T>(*c, y, eps, alpha_out, rho_out, iters), do_learn<T>(*c, y, eps, alpha_out, rho_out, iters)); });
+}
+
+int b200svm_update_w(b200svm_handle h, const void *alpha, void *w_out) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() { DISPATCH_T(c, do_update_w<T>(*c, alpha, w_out), do_update_w<T>(*c, alpha, w_out)); });
+}
+
+int b200svm_predict_dense(b200svm_handle h, const void *alpha, double rho, const void *points, int64_t P, int64_t ld, void *out) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() {
+        DISPATCH_T(c, do_predict_dense<T>(*c, alpha, rho, points, P, ld, out), do_predict_dense<T>(*c, alpha, rho, points, P, ld, out));
+    });
+}
+
+int b200svm_set_data_csr(b200svm_handle h, const int64_t *, const int32_t *, const void *, int64_t, int64_t, int64_t, int) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() { fail(B200SVM_ERR_INVALID, "CSR data path is not available in this build"); });
+}
+
+int b200svm_predict_csr(b200svm_handle h, const void *, double, const int64_t *, const int32_t *, const void *, int64_t, int64_t, int, void *) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() { fail(B200SVM_ERR_INVALID, "CSR predict path is not available in this build"); });
+}
+
+}  // extern "C"

@@ -1,0 +1,299 @@
+// Device-resident Conjugate Gradient (restates src/plssvm/backends/OpenMP/csvm.cpp:82-170; the reference's GPU variant keeps
+// the vector algebra on the host with 4-5 PCIe round trips per iteration, src/plssvm/backends/gpu_csvm.cpp:259-309).
+//
+// All vectors and scalars live in HBM.  Per iteration: [sums of d] -> [K d] -> [Abar epilogue + d.Ad] -> [x, r update + r.r]
+// -> [d update + sums of d]; every reduction is a fused two-stage deterministic grid sum (device_utils.cuh: grid_sum).
+// The host only reads one scalar (delta) per iteration for the stop test `delta <= eps^2 delta0` (csvm.cpp:145).
+#include "device_utils.cuh"
+
+namespace b200 {
+
+constexpr int VEC_THREADS = 256;
+
+static int vec_grid(int64_t m) {
+    int64_t g = (m + VEC_THREADS * 4 - 1) / (VEC_THREADS * 4);
+    if (g > MAX_PARTIAL_BLOCKS) { g = MAX_PARTIAL_BLOCKS; }
+    if (g < 1) { g = 1; }
+    return (int) g;
+}
+
+// scal[idx_sum] = sum v ; scal[idx_qv] = q . v
+template <typename T>
+__global__ void __launch_bounds__(VEC_THREADS) k_sums2(const T *__restrict__ v, const T *__restrict__ q, int64_t m, T *__restrict__ scal,
+                                                       int idx_sum, int idx_qv, T *partials, unsigned int *ticket) {
+    __shared__ T red[32];
+    T acc[2] = { T(0), T(0) };
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (int64_t) gridDim.x * blockDim.x) {
+        const T vi = v[i];
+        acc[0] += vi;
+        acc[1] = fma(q[i], vi, acc[1]);
+    }
+    T out[2];
+    if (grid_sum<T, 2>(acc, partials, ticket, red, out)) {
+        scal[idx_sum] = out[0];
+        scal[idx_qv] = out[1];
+    }
+}
+
+// Rank-1 epilogue of the implicit matrix (svm_kernel.cpp:32-34 rewritten):
+//   (Abar d)_i = (K d)_i + (QA_cost - q_i) sum(d) - q.d + d_i / C,   (K d)_i = sum_s P[s][i]
+// MODE 0: out = Abar d,            scal[S_DAD] = d . out                                  (CG:  Ad, d.Ad)
+// MODE 1: out += add * Abar d,     delta_old = delta, delta = out.out, beta = delta/old   (CG:  residual refresh, csvm.cpp:130-135)
+// MODE 2: out += add * Abar d,     delta = delta0 = out.out                               (CG:  initial residual, csvm.cpp:94-98)
+// MODE 3: out += add * Abar d                                                             (run_device_kernel test hook)
+template <typename T, int MODE>
+__global__ void __launch_bounds__(VEC_THREADS) k_abar_finish(const T *__restrict__ P, int64_t ldP, int splits, const T *__restrict__ d,
+                                                             const T *__restrict__ q, int64_t m, T QA_cost, T inv_cost, T add,
+                                                             T *__restrict__ out, T *__restrict__ scal, T *partials, unsigned int *ticket) {
+    __shared__ T red[32];
+    const T sum_d = scal[S_SUM_D], q_d = scal[S_Q_D];
+    T acc[1] = { T(0) };
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (int64_t) gridDim.x * blockDim.x) {
+        T kd = T(0);
+        for (int s = 0; s < splits; ++s) { kd += P[(int64_t) s * ldP + i]; }
+        const T di = d[i];
+        const T val = kd + (QA_cost - q[i]) * sum_d - q_d + di * inv_cost;
+        if constexpr (MODE == 0) {
+            out[i] = val;
+            acc[0] = fma(di, val, acc[0]);
+        } else {
+            const T r = fma(add, val, out[i]);
+            out[i] = r;
+            acc[0] = fma(r, r, acc[0]);
+        }
+    }
+    if constexpr (MODE != 3) {
+        T res[1];
+        if (grid_sum<T, 1>(acc, partials, ticket, red, res)) {
+            if constexpr (MODE == 0) {
+                scal[S_DAD] = res[0];
+            } else if constexpr (MODE == 1) {
+                const T old = scal[S_DELTA];
+                scal[S_DELTA_OLD] = old;
+                scal[S_DELTA] = res[0];
+                scal[S_BETA] = res[0] / old;
+            } else {
+                scal[S_DELTA] = res[0];
+                scal[S_DELTA0] = res[0];
+            }
+        }
+    }
+}
+
+// alpha_cd = delta / d.Ad ; x += alpha_cd d ; (REFRESH == 0:) r -= alpha_cd Ad, delta_old = delta, delta = r.r, beta = delta / delta_old
+template <typename T, int REFRESH>
+__global__ void __launch_bounds__(VEC_THREADS) k_cg_update(T *__restrict__ x, T *__restrict__ r, const T *__restrict__ d,
+                                                           const T *__restrict__ Ad, int64_t m, T *__restrict__ scal, T *partials,
+                                                           unsigned int *ticket) {
+    __shared__ T red[32];
+    const T delta = scal[S_DELTA];
+    const T alpha_cd = delta / scal[S_DAD];  // csvm.cpp:125
+    T acc[1] = { T(0) };
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (int64_t) gridDim.x * blockDim.x) {
+        x[i] = fma(alpha_cd, d[i], x[i]);  // csvm.cpp:128
+        if constexpr (REFRESH == 0) {
+            const T ri = fma(-alpha_cd, Ad[i], r[i]);  // csvm.cpp:138
+            r[i] = ri;
+            acc[0] = fma(ri, ri, acc[0]);
+        }
+    }
+    if constexpr (REFRESH == 0) {
+        T res[1];
+        if (grid_sum<T, 1>(acc, partials, ticket, red, res)) {
+            scal[S_ALPHA_CD] = alpha_cd;
+            scal[S_DELTA_OLD] = delta;         // csvm.cpp:142
+            scal[S_DELTA] = res[0];            // csvm.cpp:143
+            scal[S_BETA] = res[0] / delta;     // csvm.cpp:153
+        }
+    }
+}
+
+// d = beta d + r (csvm.cpp:155) ; scal[S_SUM_D] = sum d ; scal[S_Q_D] = q.d (for the next matvec's rank-1 epilogue)
+template <typename T>
+__global__ void __launch_bounds__(VEC_THREADS) k_cg_direction(T *__restrict__ d, const T *__restrict__ r, const T *__restrict__ q, int64_t m,
+                                                              T *__restrict__ scal, T *partials, unsigned int *ticket) {
+    __shared__ T red[32];
+    const T beta = scal[S_BETA];
+    T acc[2] = { T(0), T(0) };
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (int64_t) gridDim.x * blockDim.x) {
+        const T di = fma(beta, d[i], r[i]);
+        d[i] = di;
+        acc[0] += di;
+        acc[1] = fma(q[i], di, acc[1]);
+    }
+    T out[2];
+    if (grid_sum<T, 2>(acc, partials, ticket, red, out)) {
+        scal[S_SUM_D] = out[0];
+        scal[S_Q_D] = out[1];
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(VEC_THREADS) k_fill(T *__restrict__ v, int64_t m, T value) {
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (int64_t) gridDim.x * blockDim.x) { v[i] = value; }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------------------
+void drain_matvec_events(ctx &c) {
+    for (int k = 0; k < c.ev_pending; ++k) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, c.ev[2 * k], c.ev[2 * k + 1]) == cudaSuccess) { c.stats.matvec_ms += ms; }
+    }
+    c.ev_pending = 0;
+}
+
+void sync_stream(ctx &c) {
+    B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));
+    drain_matvec_events(c);
+}
+
+template <typename T>
+void sums2(ctx &c, const T *v, int idx_sum, int idx_qv) {
+    const int64_t m = c.m();
+    k_sums2<T><<<vec_grid(m), VEC_THREADS, 0, c.stream>>>(v, c.q.as<T>(), m, c.scal.as<T>(), idx_sum, idx_qv, c.partials.as<T>(),
+                                                          c.counters.as<unsigned int>());
+    count_launch(c);
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+template void sums2<float>(ctx &, const float *, int, int);
+template void sums2<double>(ctx &, const double *, int, int);
+
+namespace {
+
+struct kd_result {
+    int64_t ldP;
+    int splits;
+};
+
+// K d for the reduced system (rows/cols 0..m-1) into c.P as `splits` partial vectors.
+template <typename T>
+kd_result kernel_times_vector(ctx &c, const T *d) {
+    const int64_t m = c.m();
+    const int64_t ldP = (m + 255) / 256 * 256;
+    constexpr int MAXS = 64;
+    kd_result res{ ldP, 1 };
+    const bool timed = c.ev_pending < 4;
+    if (timed) { B200_CUDA_CHECK(cudaEventRecord(c.ev[2 * c.ev_pending], c.stream)); }
+    if (c.is_csr) {
+        fail(B200SVM_ERR_INVALID, "CSR matvec is not available in this build");
+    } else if (c.kernel == B200SVM_LINEAR) {
+        // K d = X (X^T d): two GEMVs (HBM bound) instead of m^2 F flops
+        c.P.reserve((size_t) ldP * sizeof(T));
+        c.wvec.reserve((size_t) c.ldx * sizeof(T));
+        xt_v<T>(c, c.X.as<T>(), m, c.ldx, d, c.wvec.as<T>());
+        x_w<T>(c, c.X.as<T>(), m, c.ldx, c.wvec.as<T>(), T(0), c.P.as<T>());
+        c.stats.matvec_path = 3;
+    } else {
+        bool use_tc = false;
+        if constexpr (sizeof(T) == 4) { use_tc = (c.opt_matvec_path == 2) || (c.opt_matvec_path == 0 && tc_available(c)); }
+        if (use_tc) {
+            if constexpr (sizeof(T) == 4) {
+                c.P.reserve((size_t) ldP * sizeof(T));
+                tc_kernel_matvec(c, reinterpret_cast<const float *>(d), c.P.as<float>());
+            }
+            c.stats.matvec_path = 2;
+        } else {
+            c.P.reserve((size_t) (MAXS * ldP) * sizeof(T));
+            res.splits = kmv_simt_launch<T>(c, c.X.as<T>(), c.norms.as<T>(), m, c.ldx, c.X.as<T>(), c.norms.as<T>(), m, c.ldx, d, c.P.as<T>(),
+                                            ldP, MAXS);
+            c.stats.matvec_path = 1;
+        }
+    }
+    if (timed) {
+        B200_CUDA_CHECK(cudaEventRecord(c.ev[2 * c.ev_pending + 1], c.stream));
+        ++c.ev_pending;
+    }
+    ++c.stats.matvecs;
+    return res;
+}
+
+template <typename T, int MODE>
+void abar_finish(ctx &c, const kd_result &kd, const T *d, T add, T *out) {
+    const int64_t m = c.m();
+    k_abar_finish<T, MODE><<<vec_grid(m), VEC_THREADS, 0, c.stream>>>(c.P.as<T>(), kd.ldP, kd.splits, d, c.q.as<T>(), m, (T) c.QA_cost,
+                                                                       T(1) / (T) c.cost, add, out, c.scal.as<T>(), c.partials.as<T>(),
+                                                                       c.counters.as<unsigned int>());
+    count_launch(c);
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace
+
+// ret += add * Abar d (test hook for run_device_kernel; d and ret are device vectors of m reals)
+template <typename T>
+void apply_abar(ctx &c, const T *d, T add, T *ret) {
+    sums2<T>(c, d, S_SUM_D, S_Q_D);
+    const kd_result kd = kernel_times_vector<T>(c, d);
+    abar_finish<T, 3>(c, kd, d, add, ret);
+}
+template void apply_abar<float>(ctx &, const float *, float, float *);
+template void apply_abar<double>(ctx &, const double *, double, double *);
+
+template <typename T>
+int64_t cg_solve(ctx &c, const T *b, int64_t imax, T eps, T *x, double *delta_out) {
+    const int64_t m = c.m();
+    const size_t vb = (size_t) m * sizeof(T);
+    c.v_r.reserve(vb);
+    c.v_d.reserve(vb);
+    c.v_Ad.reserve(vb);
+    T *r = c.v_r.as<T>(), *d = c.v_d.as<T>(), *Ad = c.v_Ad.as<T>();
+    T *scal = c.scal.as<T>();
+    T *mailbox = static_cast<T *>(c.pinned);
+    const int g = vec_grid(m);
+    unsigned int *ticket = c.counters.as<unsigned int>();
+    T *partials = c.partials.as<T>();
+
+    // alpha = 1 (csvm.cpp:85), r = b (:91), r -= Abar alpha (:94), delta0 = delta = r.r (:97-98), d = r (:101)
+    k_fill<T><<<g, VEC_THREADS, 0, c.stream>>>(x, m, T(1));
+    count_launch(c);
+    B200_CUDA_CHECK(cudaMemcpyAsync(r, b, vb, cudaMemcpyDeviceToDevice, c.stream));
+    sums2<T>(c, x, S_SUM_D, S_Q_D);
+    {
+        const kd_result kd = kernel_times_vector<T>(c, x);
+        abar_finish<T, 2>(c, kd, x, T(-1), r);
+    }
+    B200_CUDA_CHECK(cudaMemcpyAsync(d, r, vb, cudaMemcpyDeviceToDevice, c.stream));
+    sums2<T>(c, d, S_SUM_D, S_Q_D);
+    B200_CUDA_CHECK(cudaMemcpyAsync(mailbox, scal + S_DELTA0, sizeof(T), cudaMemcpyDeviceToHost, c.stream));
+    sync_stream(c);
+    const T delta0 = mailbox[0];
+    T delta = delta0;
+    const T target = eps * eps * delta0;
+
+    int64_t run = 0;
+    for (; run < imax; ++run) {
+        // Ad = Abar d (:121-122) and d.Ad
+        const kd_result kd = kernel_times_vector<T>(c, d);
+        abar_finish<T, 0>(c, kd, d, T(1), Ad);
+        if (run % 50 == 49) {
+            // x += alpha_cd d ; r = b - Abar x (:130-135)
+            k_cg_update<T, 1><<<g, VEC_THREADS, 0, c.stream>>>(x, r, d, Ad, m, scal, partials, ticket);
+            count_launch(c);
+            B200_CUDA_CHECK(cudaMemcpyAsync(r, b, vb, cudaMemcpyDeviceToDevice, c.stream));
+            sums2<T>(c, x, S_SUM_D, S_Q_D);
+            const kd_result kx = kernel_times_vector<T>(c, x);
+            abar_finish<T, 1>(c, kx, x, T(-1), r);
+        } else {
+            k_cg_update<T, 0><<<g, VEC_THREADS, 0, c.stream>>>(x, r, d, Ad, m, scal, partials, ticket);
+            count_launch(c);
+        }
+        B200_CUDA_CHECK(cudaGetLastError());
+        // stop test on the host (:145) — one scalar per iteration
+        B200_CUDA_CHECK(cudaMemcpyAsync(mailbox, scal + S_DELTA, sizeof(T), cudaMemcpyDeviceToHost, c.stream));
+        // speculatively queue the direction update; it is only *used* if the loop continues
+        k_cg_direction<T><<<g, VEC_THREADS, 0, c.stream>>>(d, r, c.q.as<T>(), m, scal, partials, ticket);
+        count_launch(c);
+        B200_CUDA_CHECK(cudaGetLastError());
+        sync_stream(c);
+        delta = mailbox[0];
+        if (delta <= target) { break; }
+    }
+    if (delta_out != nullptr) { *delta_out = (double) delta; }
+    return run + 1 < imax ? run + 1 : imax;  // std::min(run + 1, imax), csvm.cpp:162-167
+}
+template int64_t cg_solve<float>(ctx &, const float *, int64_t, float, float *, double *);
+template int64_t cg_solve<double>(ctx &, const double *, int64_t, double, double *, double *);
+
+}  // namespace b200

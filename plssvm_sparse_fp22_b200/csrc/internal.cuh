@@ -1,0 +1,182 @@
+// Internal declarations shared by the translation units of libb200svm.so (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+#include <vector>
+
+#include "../../include/b200svm.h"
+
+namespace b200 {
+
+// ---------------------------------------------------------------------------------------------------------------------
+// error handling: C-ABI functions catch `error` and turn it into a status code + message
+// ---------------------------------------------------------------------------------------------------------------------
+struct error {
+    int code;
+    std::string msg;
+};
+
+[[noreturn]] inline void fail(int code, const std::string &msg) { throw error{ code, msg }; }
+
+#define B200_CUDA_CHECK(expr)                                                                                                \
+    do {                                                                                                                     \
+        const cudaError_t err__ = (expr);                                                                                    \
+        if (err__ != cudaSuccess) {                                                                                          \
+            ::b200::fail(B200SVM_ERR_CUDA, std::string("CUDA error '") + cudaGetErrorString(err__) + "' in " #expr " (" +    \
+                                               __FILE__ + ":" + std::to_string(__LINE__) + ")");                             \
+        }                                                                                                                    \
+    } while (0)
+
+#define B200_REQUIRE(cond, text)                                            \
+    do {                                                                    \
+        if (!(cond)) { ::b200::fail(B200SVM_ERR_INVALID, std::string(text)); } \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------------------------------
+// RAII device buffer (replaces the reference's detail::gpu_device_ptr, include/plssvm/backends/gpu_device_ptr.hpp)
+// ---------------------------------------------------------------------------------------------------------------------
+struct dbuf {
+    void *p{ nullptr };
+    size_t bytes{ 0 };
+    dbuf() = default;
+    dbuf(const dbuf &) = delete;
+    dbuf &operator=(const dbuf &) = delete;
+    ~dbuf() { release(); }
+    void release() {
+        if (p != nullptr) { cudaFree(p); }
+        p = nullptr;
+        bytes = 0;
+    }
+    // (re)allocate if too small; contents are not preserved
+    void reserve(size_t nbytes) {
+        if (nbytes <= bytes) { return; }
+        release();
+        const cudaError_t e = cudaMalloc(&p, nbytes);
+        if (e != cudaSuccess) {
+            p = nullptr;
+            fail(B200SVM_ERR_ALLOC, std::string("cudaMalloc of ") + std::to_string(nbytes) + " bytes failed: " + cudaGetErrorString(e));
+        }
+        bytes = nbytes;
+    }
+    template <typename T>
+    T *as() const { return static_cast<T *>(p); }
+};
+
+constexpr int NUM_SMS = 148;          // B200
+constexpr int MAX_PARTIAL_BLOCKS = 1024;  // upper bound of blocks in a fused vector-op + reduction launch
+
+// device scalars of the CG loop (index into ctx.scal, element type = real type of the handle)
+enum scal_index : int {
+    S_DELTA = 0,
+    S_DELTA_OLD,
+    S_DELTA0,
+    S_DAD,
+    S_SUM_D,
+    S_Q_D,
+    S_ALPHA_CD,
+    S_BETA,
+    S_SUM_X,  // sum(alpha) for the bias
+    S_Q_X,    // q . alpha for the bias
+    S_KXX,    // k(x_n, x_n)
+    S_TMP0,
+    S_TMP1,
+    S_COUNT
+};
+
+struct comm_state;  // NCCL communicator wrapper (comm.cu)
+
+struct ctx {
+    // configuration
+    int dtype{ B200SVM_F64 };
+    int kernel{ B200SVM_LINEAR };
+    int degree{ 3 };
+    double gamma{ 0 }, coef0{ 0 }, cost{ 1 };
+    int device{ 0 };
+    cudaStream_t own_stream{ nullptr };
+    cudaStream_t stream{ nullptr };
+    std::string last_error;
+
+    // options
+    int64_t opt_matvec_path{ 0 };
+    int64_t opt_sync_every{ 1 };
+
+    // data
+    bool has_data{ false };
+    bool is_csr{ false };
+    int64_t n{ 0 }, F{ 0 }, ldx{ 0 };  // ldx in elements
+    dbuf X;                            // dense n x ldx, row-major, real type
+    dbuf norms;                        // n squared norms (real type)
+    // CSR
+    int64_t nnz{ 0 };
+    int value_format{ 0 };
+    dbuf csr_rowptr, csr_colidx, csr_vals;
+    dbuf csc_colptr, csc_rowidx, csc_vals;  // transpose (for X^T d)
+    // fp16 hi/lo split of X for the tcgen05 path (f32 dense only)
+    dbuf Xh_hi, Xh_lo;
+    int64_t ldh{ 0 };     // leading dimension (elements) of the split operands
+    int64_t n_pad{ 0 };   // rows padded to the tile size
+    float split_scale{ 1.f };
+    bool has_split{ false };
+
+    // hot-path state
+    dbuf q;        // m
+    bool has_q{ false };
+    double QA_cost{ 0 };
+    dbuf scal;     // S_COUNT reals
+    dbuf partials; // reduction partials: 4 * MAX_PARTIAL_BLOCKS reals
+    dbuf counters; // unsigned int[8] "last block" tickets
+    dbuf P;        // matvec partial buffer [splits][m_pad]
+    dbuf wvec;     // F reals (linear path: X^T d) + split partials
+    dbuf wpart;
+    dbuf v_x, v_r, v_d, v_Ad, v_b, v_tmp;  // CG vectors (m reals)
+    dbuf pts, pts_norms, pred_out, alpha_dev;  // predict staging
+    void *pinned{ nullptr };                   // small pinned host mailbox (scalars / flags)
+
+    // multi-GPU
+    comm_state *comm{ nullptr };
+    int rank{ 0 }, world{ 1 };
+
+    // stats
+    b200svm_stats stats{};
+    cudaEvent_t ev[8]{};   // 4 (start, stop) pairs around the O(m^2) kernel, drained at the next stream sync
+    int ev_pending{ 0 };
+
+    size_t esize() const { return dtype == B200SVM_F32 ? 4 : 8; }
+    int64_t m() const { return n - 1; }
+};
+
+// ---------------------------------------------------------------------------------------------------------------------
+// entry points implemented per translation unit (T = float / double)
+// ---------------------------------------------------------------------------------------------------------------------
+template <typename T> void compute_norms(ctx &c, const T *X, int64_t rows, int64_t ld, int64_t F, T *out);
+template <typename T> void generate_q(ctx &c);                                              // q + k(x_n,x_n) -> c.q, scal[S_KXX]
+template <typename T> void kernel_matvec(ctx &c, const T *d, T *out_Kd);                    // out = K d (m), poly/rbf O(m^2) or linear X(X^T d)
+template <typename T> void apply_abar(ctx &c, const T *d, T add, T *ret);                   // ret += add * Abar d  (device vectors)
+template <typename T> int64_t cg_solve(ctx &c, const T *b_dev, int64_t imax, T eps, T *alpha_dev, double *delta_out);
+template <typename T> void update_w(ctx &c, const T *alpha_dev, T *w_dev);
+template <typename T> int kmv_simt_launch(ctx &c, const T *A, const T *normA, int64_t rowsA, int64_t ldA, const T *B, const T *normB, int64_t rowsB,
+                                          int64_t ldB, const T *v, T *P, int64_t ldP, int max_splits);
+template <typename T> void xt_v(ctx &c, const T *X, int64_t rows, int64_t ld, const T *v, T *w);
+template <typename T> void x_w(ctx &c, const T *X, int64_t rows, int64_t ld, const T *w, T bias, T *out);
+template <typename T> void predict_dense(ctx &c, const T *alpha_dev, T bias, const T *pts_dev, int64_t P, int64_t ld, T *out_dev);
+
+// tcgen05 path (gram_tc.cu), f32 dense only
+void tc_prepare_split(ctx &c);                                   // build fp16 hi/lo operands + TMA descriptors
+bool tc_available(const ctx &c);
+void tc_kernel_matvec(ctx &c, const float *d, float *out_Kd);    // out = K d via symmetric tcgen05 tiles
+
+// multi-GPU (comm.cu)
+void comm_destroy(ctx &c);
+void comm_allreduce_sum(ctx &c, void *buf, int64_t count);  // in place, real type of the handle
+
+inline void count_launch(ctx &c, int k = 1) { c.stats.kernel_launches += k; }
+void drain_matvec_events(ctx &c);   // call after a stream synchronisation
+void sync_stream(ctx &c);           // cudaStreamSynchronize + drain
+template <typename T> void sums2(ctx &c, const T *v, int idx_sum, int idx_qv);
+
+}  // namespace b200

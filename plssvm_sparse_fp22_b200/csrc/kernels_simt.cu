@@ -1,0 +1,385 @@
+// SIMT kernels (sm_100a): squared norms, q-vector, the generic tiled "kernel-matrix x vector" product used by the
+// O(m^2) matvec (double, and float when the tcgen05 path is not selected) and by predict, and the two-GEMV linear path.
+//
+// Reference behaviour restated (not ported): src/plssvm/backends/OpenMP/svm_kernel.cpp:21-47 (matvec),
+// q_kernel.cpp:19-50 (q), csvm.cpp:173-244 (w, predict); CUDA analogues src/plssvm/backends/CUDA/{svm,q,predict}_kernel.cu.
+// Differences by design: Gram form for all kernels (rbf via |a|^2 + |b|^2 - 2<a,b>), full rows without atomics
+// (deterministic), rank-1 terms (QA_cost, q) applied in an O(m) epilogue, linear kernel as X (X^T d).
+#include "device_utils.cuh"
+
+namespace b200 {
+
+// ---------------------------------------------------------------------------------------------------------------------
+// squared norms: one warp per row
+// ---------------------------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) k_row_norms(const T *__restrict__ X, int64_t rows, int64_t ld, T *__restrict__ out) {
+    const int64_t row = (int64_t) blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= rows) { return; }
+    const int lane = threadIdx.x & 31;
+    const T *x = X + row * ld;
+    T s = 0;
+    for (int64_t k = lane; k < ld; k += 32) { s = fma(x[k], x[k], s); }
+    s = warp_sum(s);
+    if (lane == 0) { out[row] = s; }
+}
+
+template <typename T>
+void compute_norms(ctx &c, const T *X, int64_t rows, int64_t ld, int64_t, T *out) {
+    if (rows == 0) { return; }
+    k_row_norms<T><<<(unsigned) ((rows + 7) / 8), 256, 0, c.stream>>>(X, rows, ld, out);
+    count_launch(c);
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+template void compute_norms<float>(ctx &, const float *, int64_t, int64_t, int64_t, float *);
+template void compute_norms<double>(ctx &, const double *, int64_t, int64_t, int64_t, double *);
+
+// ---------------------------------------------------------------------------------------------------------------------
+// q[i] = k(x_i, x_last), i < m ; also k(x_last, x_last) -> scal[S_KXX]       (one warp per row)
+// ---------------------------------------------------------------------------------------------------------------------
+template <typename T, int KERNEL>
+__global__ void __launch_bounds__(256) k_generate_q(const T *__restrict__ X, const T *__restrict__ norms, int64_t n, int64_t ld,
+                                                    int degree, T gamma, T coef0, T *__restrict__ q, T *__restrict__ scal) {
+    const int64_t row = (int64_t) blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= n) { return; }
+    const int lane = threadIdx.x & 31;
+    const T *x = X + row * ld;
+    const T *xl = X + (n - 1) * ld;
+    T s = 0;
+    for (int64_t k = lane; k < ld; k += 32) { s = fma(x[k], xl[k], s); }
+    s = warp_sum(s);
+    if (lane == 0) {
+        const T v = kernel_value<T, KERNEL>(s, norms[row], norms[n - 1], degree, gamma, coef0);
+        if (row < n - 1) {
+            q[row] = v;
+        } else {
+            scal[S_KXX] = KERNEL == B200SVM_RBF ? T(1) : v;  // exp(-gamma * 0) is exactly 1 in the reference
+        }
+    }
+}
+
+template <typename T>
+void generate_q(ctx &c) {
+    const unsigned grid = (unsigned) ((c.n + 7) / 8);
+    const T *X = c.X.as<T>();
+    const T *nr = c.norms.as<T>();
+    T *q = c.q.as<T>();
+    T *sc = c.scal.as<T>();
+    switch (c.kernel) {
+        case B200SVM_LINEAR: k_generate_q<T, B200SVM_LINEAR><<<grid, 256, 0, c.stream>>>(X, nr, c.n, c.ldx, c.degree, (T) c.gamma, (T) c.coef0, q, sc); break;
+        case B200SVM_POLYNOMIAL: k_generate_q<T, B200SVM_POLYNOMIAL><<<grid, 256, 0, c.stream>>>(X, nr, c.n, c.ldx, c.degree, (T) c.gamma, (T) c.coef0, q, sc); break;
+        default: k_generate_q<T, B200SVM_RBF><<<grid, 256, 0, c.stream>>>(X, nr, c.n, c.ldx, c.degree, (T) c.gamma, (T) c.coef0, q, sc); break;
+    }
+    count_launch(c);
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+template void generate_q<float>(ctx &);
+template void generate_q<double>(ctx &);
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Generic tiled kernel-matrix x vector:  P[s][i] = sum_{j in column split s} k(A_i, B_j) v_j
+//   A: rowsA x ldA, B: rowsB x ldB (row-major, zero padded to a multiple of 16 features), squared norms precomputed.
+//   256 threads = 16 x 16, each owning a TM x TN register micro-tile of the BM x BN Gram tile (BM = 16 TM, BN = 16 TN);
+//   K is streamed in BK = 16 slices through double-buffered shared memory (register prefetch of the next slice).
+//   The Gram tile never leaves registers: kernel function + multiply by v_j + row reduction happen in the epilogue.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int BK = 16;
+
+template <typename T>
+struct vec16;
+template <>
+struct vec16<float> {
+    using type = float4;
+    static constexpr int N = 4;
+};
+template <>
+struct vec16<double> {
+    using type = double2;
+    static constexpr int N = 2;
+};
+
+template <typename T, int KERNEL, int TM, int TN>
+__global__ void __launch_bounds__(256)
+    k_kmv_tile(const T *__restrict__ A, const T *__restrict__ normA, int64_t rowsA, int64_t ldA, const T *__restrict__ B,
+               const T *__restrict__ normB, int64_t rowsB, int64_t ldB, int64_t K, const T *__restrict__ v, int degree, T gamma, T coef0,
+               T *__restrict__ P, int64_t ldP, int col_tiles) {
+    constexpr int BM = 16 * TM, BN = 16 * TN;
+    using V = typename vec16<T>::type;
+    constexpr int VN = vec16<T>::N;
+    constexpr int EA = BM * BK / 256, TPRA = BK / EA;  // elements per thread / threads per row when loading the A slice
+    constexpr int EB = BN * BK / 256, TPRB = BK / EB;
+    static_assert(EA % VN == 0 && EB % VN == 0, "slice loads are 16-byte vectors");
+
+    __shared__ __align__(16) T As[2][BK][BM];
+    __shared__ __align__(16) T Bs[2][BK][BN];
+
+    const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
+    const int64_t row0 = (int64_t) blockIdx.x * BM;
+    const int ct0 = (int) ((int64_t) blockIdx.y * col_tiles / gridDim.y);
+    const int ct1 = (int) ((int64_t) (blockIdx.y + 1) * col_tiles / gridDim.y);
+
+    const int la_row = t / TPRA, la_k = (t % TPRA) * EA;
+    const int lb_row = t / TPRB, lb_k = (t % TPRB) * EB;
+    const int64_t a_row = min(row0 + la_row, rowsA - 1);  // out-of-range rows re-read the last row; masked in the epilogue
+    const T *a_ptr = A + a_row * ldA + la_k;
+
+    T rowsum[TM];
+    T na[TM];
+#pragma unroll
+    for (int r = 0; r < TM; ++r) {
+        rowsum[r] = T(0);
+        const int64_t row = row0 + (r >> 2) * 64 + ty * 4 + (r & 3);
+        na[r] = row < rowsA ? normA[row] : T(0);
+    }
+
+    const int nk = (int) (K / BK);
+    for (int ct = ct0; ct < ct1; ++ct) {
+        const int64_t col0 = (int64_t) ct * BN;
+        const int64_t b_row = min(col0 + lb_row, rowsB - 1);
+        const T *b_ptr = B + b_row * ldB + lb_k;
+
+        T acc[TM][TN];
+#pragma unroll
+        for (int r = 0; r < TM; ++r) {
+#pragma unroll
+            for (int cc = 0; cc < TN; ++cc) { acc[r][cc] = T(0); }
+        }
+
+        V ra[EA / VN], rb[EB / VN];
+#pragma unroll
+        for (int e = 0; e < EA / VN; ++e) { ra[e] = __ldg(reinterpret_cast<const V *>(a_ptr) + e); }
+#pragma unroll
+        for (int e = 0; e < EB / VN; ++e) { rb[e] = __ldg(reinterpret_cast<const V *>(b_ptr) + e); }
+#pragma unroll
+        for (int e = 0; e < EA; ++e) { As[0][la_k + e][la_row] = reinterpret_cast<const T *>(ra)[e]; }
+#pragma unroll
+        for (int e = 0; e < EB; ++e) { Bs[0][lb_k + e][lb_row] = reinterpret_cast<const T *>(rb)[e]; }
+        __syncthreads();
+
+        for (int kt = 0; kt < nk; ++kt) {
+            const int cur = kt & 1;
+            if (kt + 1 < nk) {
+#pragma unroll
+                for (int e = 0; e < EA / VN; ++e) { ra[e] = __ldg(reinterpret_cast<const V *>(a_ptr + (int64_t) (kt + 1) * BK) + e); }
+#pragma unroll
+                for (int e = 0; e < EB / VN; ++e) { rb[e] = __ldg(reinterpret_cast<const V *>(b_ptr + (int64_t) (kt + 1) * BK) + e); }
+            }
+#pragma unroll
+            for (int k = 0; k < BK; ++k) {
+                T a[TM], b[TN];
+#pragma unroll
+                for (int r4 = 0; r4 < TM / 4; ++r4) {
+#pragma unroll
+                    for (int e = 0; e < 4 / VN; ++e) {
+                        const V val = *reinterpret_cast<const V *>(&As[cur][k][r4 * 64 + ty * 4 + e * VN]);
+#pragma unroll
+                        for (int u = 0; u < VN; ++u) { a[r4 * 4 + e * VN + u] = reinterpret_cast<const T *>(&val)[u]; }
+                    }
+                }
+#pragma unroll
+                for (int c4 = 0; c4 < TN / 4; ++c4) {
+#pragma unroll
+                    for (int e = 0; e < 4 / VN; ++e) {
+                        const V val = *reinterpret_cast<const V *>(&Bs[cur][k][c4 * 64 + tx * 4 + e * VN]);
+#pragma unroll
+                        for (int u = 0; u < VN; ++u) { b[c4 * 4 + e * VN + u] = reinterpret_cast<const T *>(&val)[u]; }
+                    }
+                }
+#pragma unroll
+                for (int r = 0; r < TM; ++r) {
+#pragma unroll
+                    for (int cc = 0; cc < TN; ++cc) { acc[r][cc] = fma(a[r], b[cc], acc[r][cc]); }
+                }
+            }
+            if (kt + 1 < nk) {
+#pragma unroll
+                for (int e = 0; e < EA; ++e) { As[cur ^ 1][la_k + e][la_row] = reinterpret_cast<const T *>(ra)[e]; }
+#pragma unroll
+                for (int e = 0; e < EB; ++e) { Bs[cur ^ 1][lb_k + e][lb_row] = reinterpret_cast<const T *>(rb)[e]; }
+            }
+            __syncthreads();
+        }
+
+        // epilogue of this Gram tile: kernel function, times v_j, row reduction in registers
+#pragma unroll
+        for (int cc = 0; cc < TN; ++cc) {
+            const int64_t col = col0 + (cc >> 2) * 64 + tx * 4 + (cc & 3);
+            const bool valid = col < rowsB;
+            const T vj = valid ? v[col] : T(0);
+            const T nb = valid ? normB[col] : T(0);
+#pragma unroll
+            for (int r = 0; r < TM; ++r) {
+                const T kv = kernel_value<T, KERNEL>(acc[r][cc], na[r], nb, degree, gamma, coef0);
+                rowsum[r] = valid ? fma(kv, vj, rowsum[r]) : rowsum[r];
+            }
+        }
+    }
+
+    // reduce over the 16 threads (tx) sharing a row; lanes of one row group are contiguous within a half-warp
+#pragma unroll
+    for (int r = 0; r < TM; ++r) {
+        T s = rowsum[r];
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); }
+        const int64_t row = row0 + (r >> 2) * 64 + ty * 4 + (r & 3);
+        if (tx == 0 && row < rowsA) { P[(int64_t) blockIdx.y * ldP + row] = s; }
+    }
+}
+
+template <typename T>
+struct simt_tile {
+    static constexpr int TM = sizeof(T) == 4 ? 8 : 4;
+    static constexpr int TN = sizeof(T) == 4 ? 8 : 4;
+};
+
+// Launch: returns the number of column splits written to P ([splits][ldP]).
+template <typename T>
+int kmv_simt_launch(ctx &c, const T *A, const T *normA, int64_t rowsA, int64_t ldA, const T *B, const T *normB, int64_t rowsB, int64_t ldB,
+                    const T *v, T *P, int64_t ldP, int max_splits) {
+    constexpr int TM = simt_tile<T>::TM, TN = simt_tile<T>::TN;
+    constexpr int BM = 16 * TM, BN = 16 * TN;
+    const int64_t row_tiles = (rowsA + BM - 1) / BM;
+    const int col_tiles = (int) ((rowsB + BN - 1) / BN);
+    // at least ~3 waves of CTAs when the problem allows it
+    int64_t splits = (3 * 2 * NUM_SMS + row_tiles - 1) / row_tiles;
+    if (splits > col_tiles) { splits = col_tiles; }
+    if (splits > max_splits) { splits = max_splits; }
+    if (splits < 1) { splits = 1; }
+    const int64_t K = ldA < ldB ? ldA : ldB;
+    const dim3 grid((unsigned) row_tiles, (unsigned) splits);
+#define B200_LAUNCH_KMV(KN)                                                                                                              \
+    k_kmv_tile<T, KN, TM, TN><<<grid, 256, 0, c.stream>>>(A, normA, rowsA, ldA, B, normB, rowsB, ldB, K, v, c.degree, (T) c.gamma,       \
+                                                           (T) c.coef0, P, ldP, col_tiles)
+    switch (c.kernel) {
+        case B200SVM_LINEAR: B200_LAUNCH_KMV(B200SVM_LINEAR); break;
+        case B200SVM_POLYNOMIAL: B200_LAUNCH_KMV(B200SVM_POLYNOMIAL); break;
+        default: B200_LAUNCH_KMV(B200SVM_RBF); break;
+    }
+#undef B200_LAUNCH_KMV
+    count_launch(c);
+    B200_CUDA_CHECK(cudaGetLastError());
+    return (int) splits;
+}
+template int kmv_simt_launch<float>(ctx &, const float *, const float *, int64_t, int64_t, const float *, const float *, int64_t, int64_t,
+                                    const float *, float *, int64_t, int);
+template int kmv_simt_launch<double>(ctx &, const double *, const double *, int64_t, int64_t, const double *, const double *, int64_t, int64_t,
+                                     const double *, double *, int64_t, int);
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Linear kernel: K d = X (X^T d) — two HBM-bound GEMVs instead of an O(m^2 F) pairwise pass.
+//   k_xt_v : wpart[chunk][f] = sum_{i in row chunk} v_i X[i][f]     (thread per feature: coalesced across f)
+//   k_sum_chunks : w[f] = sum_chunk wpart[chunk][f]                  (fixed order => deterministic)
+//   k_x_w  : out[i] = X[i] . w                                       (warp per row)
+// The same kernels implement update_w (w = X^T alpha over all n rows; reference src/plssvm/backends/OpenMP/csvm.cpp:173-188).
+// ---------------------------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) k_xt_v(const T *__restrict__ X, int64_t rows, int64_t ld, const T *__restrict__ v,
+                                              T *__restrict__ wpart, int64_t rows_per_chunk) {
+    const int64_t f = (int64_t) blockIdx.x * 256 + threadIdx.x;
+    if (f >= ld) { return; }
+    const int64_t r0 = (int64_t) blockIdx.y * rows_per_chunk;
+    const int64_t r1 = min(rows, r0 + rows_per_chunk);
+    T s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+    int64_t i = r0;
+    for (; i + 3 < r1; i += 4) {
+        s0 = fma(v[i], X[i * ld + f], s0);
+        s1 = fma(v[i + 1], X[(i + 1) * ld + f], s1);
+        s2 = fma(v[i + 2], X[(i + 2) * ld + f], s2);
+        s3 = fma(v[i + 3], X[(i + 3) * ld + f], s3);
+    }
+    for (; i < r1; ++i) { s0 = fma(v[i], X[i * ld + f], s0); }
+    wpart[(int64_t) blockIdx.y * ld + f] = (s0 + s1) + (s2 + s3);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_sum_chunks(const T *__restrict__ wpart, int64_t ld, int chunks, T *__restrict__ w) {
+    const int64_t f = (int64_t) blockIdx.x * 256 + threadIdx.x;
+    if (f >= ld) { return; }
+    T s = 0;
+    for (int ch = 0; ch < chunks; ++ch) { s += wpart[(int64_t) ch * ld + f]; }
+    w[f] = s;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_x_w(const T *__restrict__ X, int64_t rows, int64_t ld, const T *__restrict__ w, T bias,
+                                             T *__restrict__ out) {
+    const int64_t row = (int64_t) blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= rows) { return; }
+    const int lane = threadIdx.x & 31;
+    const T *x = X + row * ld;
+    T s = 0;
+    for (int64_t k = lane; k < ld; k += 32) { s = fma(x[k], w[k], s); }
+    s = warp_sum(s);
+    if (lane == 0) { out[row] = bias + s; }
+}
+
+// w = X[0:rows]^T v   (w: ld reals)
+template <typename T>
+void xt_v(ctx &c, const T *X, int64_t rows, int64_t ld, const T *v, T *w) {
+    const int64_t fblocks = (ld + 255) / 256;
+    int64_t chunks = (4 * NUM_SMS + fblocks - 1) / fblocks;
+    if (chunks > (rows + 63) / 64) { chunks = (rows + 63) / 64; }
+    if (chunks < 1) { chunks = 1; }
+    const int64_t rpc = (rows + chunks - 1) / chunks;
+    chunks = (rows + rpc - 1) / rpc;
+    c.wpart.reserve((size_t) (chunks * ld) * sizeof(T));
+    k_xt_v<T><<<dim3((unsigned) fblocks, (unsigned) chunks), 256, 0, c.stream>>>(X, rows, ld, v, c.wpart.as<T>(), rpc);
+    k_sum_chunks<T><<<(unsigned) fblocks, 256, 0, c.stream>>>(c.wpart.as<T>(), ld, (int) chunks, w);
+    count_launch(c, 2);
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+// out[i] = bias + X[i] . w
+template <typename T>
+void x_w(ctx &c, const T *X, int64_t rows, int64_t ld, const T *w, T bias, T *out) {
+    if (rows == 0) { return; }
+    k_x_w<T><<<(unsigned) ((rows + 7) / 8), 256, 0, c.stream>>>(X, rows, ld, w, bias, out);
+    count_launch(c);
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+template void xt_v<float>(ctx &, const float *, int64_t, int64_t, const float *, float *);
+template void xt_v<double>(ctx &, const double *, int64_t, int64_t, const double *, double *);
+template void x_w<float>(ctx &, const float *, int64_t, int64_t, const float *, float, float *);
+template void x_w<double>(ctx &, const double *, int64_t, int64_t, const double *, double, double *);
+
+template <typename T>
+void update_w(ctx &c, const T *alpha_dev, T *w_dev) {
+    xt_v<T>(c, c.X.as<T>(), c.n, c.ldx, alpha_dev, w_dev);
+}
+template void update_w<float>(ctx &, const float *, float *);
+template void update_w<double>(ctx &, const double *, double *);
+
+// out[p] = bias + sum_s P[s][p]
+template <typename T>
+__global__ void __launch_bounds__(256) k_sum_splits_bias(const T *__restrict__ P, int64_t ldP, int splits, int64_t rows, T bias, T *__restrict__ out) {
+    const int64_t i = (int64_t) blockIdx.x * 256 + threadIdx.x;
+    if (i >= rows) { return; }
+    T s = 0;
+    for (int sp = 0; sp < splits; ++sp) { s += P[(int64_t) sp * ldP + i]; }
+    out[i] = bias + s;
+}
+
+// predict (reference src/plssvm/backends/OpenMP/csvm.cpp:191-244): decision values for dense points already on the device
+template <typename T>
+void predict_dense(ctx &c, const T *alpha_dev, T bias, const T *pts_dev, int64_t P, int64_t ld, T *out_dev) {
+    if (P == 0) { return; }
+    if (c.kernel == B200SVM_LINEAR) {
+        c.wvec.reserve((size_t) c.ldx * sizeof(T));
+        update_w<T>(c, alpha_dev, c.wvec.as<T>());
+        x_w<T>(c, pts_dev, P, ld, c.wvec.as<T>(), bias, out_dev);
+        return;
+    }
+    c.pts_norms.reserve((size_t) P * sizeof(T));
+    compute_norms<T>(c, pts_dev, P, ld, c.F, c.pts_norms.as<T>());
+    constexpr int MAXS = 64;
+    const int64_t ldP = (P + 63) / 64 * 64;
+    c.P.reserve((size_t) (MAXS * ldP) * sizeof(T));
+    const int splits = kmv_simt_launch<T>(c, pts_dev, c.pts_norms.as<T>(), P, ld, c.X.as<T>(), c.norms.as<T>(), c.n, c.ldx, alpha_dev,
+                                          c.P.as<T>(), ldP, MAXS);
+    k_sum_splits_bias<T><<<(unsigned) ((P + 255) / 256), 256, 0, c.stream>>>(c.P.as<T>(), ldP, splits, P, bias, out_dev);
+    count_launch(c);
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+template void predict_dense<float>(ctx &, const float *, float, const float *, int64_t, int64_t, float *);
+template void predict_dense<double>(ctx &, const double *, double, const double *, int64_t, int64_t, double *);
+
+}  // namespace b200

@@ -1,0 +1,195 @@
+"""GPU parity tests (run with -m gpu on a B200): every call goes through the C ABI (libb200svm.so via ctypes) and is
+compared with the oracle (oracle/lssvm_oracle.c, pinned to the reference by tests/test_oracle.py) on the same seeded
+inputs, and with the golden vectors the unmodified reference produced (tests/golden/).
+
+Tolerances (floating point path, stated per BASELINE.json north_star and SURVEY.md F4/H2):
+  * q, matvec: the reference's own test tolerance 128 eps (|a|+|b|) per element (tests/utility.hpp:117-136), with a factor for
+    the different (tree/tile) summation order; float additionally norm-wise.
+  * CG: identical iteration count; alpha norm-wise <= 1e-10 (double) at the BASELINE epsilon 1e-3, or 10x the reference's own
+    1-vs-8-thread spread where that is larger; float against 10x the reference's measured float spread (its float noise floor
+    is 1e-5..1e-3, tests/golden/make_golden.py output) and never worse than the f64 truth distance of the reference float.
+  * rho: cancellation-aware, tol * (|y_n| + |QA_cost sum(alpha)| + |q.alpha|).
+  * predicted labels: bit-identical.
+"""
+import numpy as np
+import pytest
+
+from conftest import nrm_rel
+from oracle import port
+from plssvm_sparse_fp22_b200 import capi, datagen
+
+pytestmark = pytest.mark.gpu
+KERNELS = ["linear", "polynomial", "rbf"]
+DTYPES = [np.float64, np.float32]
+
+
+def near(a, b, dt, scale):
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    eps = 128 * np.finfo(dt).eps * scale
+    return bool(np.all(np.abs(a - b) <= np.maximum(eps * (np.abs(a) + np.abs(b)), np.finfo(dt).tiny)))
+
+
+@pytest.mark.parametrize("dt", DTYPES)
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_generate_q_and_matvec_kat(golden, kernel, dt):
+    g = golden("kernel_kat.npz")
+    name = "f64" if dt == np.float64 else "f32"
+    X, _ = datagen.make_dense(193, 57, seed=11, problem="planes")
+    X = X.astype(dt)
+    degree, gamma, coef0, cost = 3, 1.0 / X.shape[1], 0.5 if kernel == "polynomial" else 0.0, 2.0
+    with capi.Handle(dt, kernel, degree, gamma, coef0, cost) as h:
+        h.set_data(X)
+        q = h.generate_q()
+        assert near(q, g[f"{name}/{kernel}/q"], dt, 8.0), np.max(np.abs(q - g[f"{name}/{kernel}/q"]))
+        qa = float(g[f"{name}/{kernel}/QA_cost"])
+        kxx = h.kxx_last()
+        assert abs((kxx + 1.0 / cost) - qa) <= 1e3 * np.finfo(dt).eps * abs(qa)
+        h.set_q(g[f"{name}/{kernel}/q"], qa)
+        d = g["d"].astype(dt)
+        for add in (1.0, -1.0):
+            want = g[f"{name}/{kernel}/matvec{int(add):+d}"]
+            got = h.matvec(d, add)
+            assert nrm_rel(want, got) < (1e-13 if dt == np.float64 else 2e-6), (kernel, name, add, nrm_rel(want, got))
+            # accumulate into a non-zero ret (ret += add * A d)
+            base = np.linspace(-1, 1, want.shape[0]).astype(dt)
+            got2 = h.matvec(d, add, ret=base)
+            assert nrm_rel(want + base, got2) < (1e-13 if dt == np.float64 else 2e-6)
+
+
+@pytest.mark.parametrize("dt", DTYPES)
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("shape", [(2, 1), (3, 5), (65, 17), (129, 200), (700, 130)])
+def test_matvec_vs_oracle_shapes(kernel, dt, shape):
+    """Ragged / tiny / tile-edge sizes against the oracle's full-row operator."""
+    n, F = shape
+    X, _ = datagen.make_dense(n, F, seed=100 + n, problem="blobs", dtype=dt)
+    rng = np.random.default_rng(n)
+    d = rng.uniform(-1, 2, n - 1).astype(dt)
+    with capi.Handle(dt, kernel, 3, 1.0 / F, 0.25 if kernel == "polynomial" else 0.0, 1.5) as h:
+        h.set_data(X)
+        q = h.generate_q()
+        q_o = port.generate_q(X, kernel, 3, 1.0 / F, 0.25 if kernel == "polynomial" else 0.0)
+        assert nrm_rel(q_o, q) < (1e-13 if dt == np.float64 else 5e-6)
+        qa = h.kxx_last() + 1.0 / 1.5
+        h.set_q(q_o, qa)
+        got = h.matvec(d, 1.0)
+        want = port.matvec(X.astype(np.float64), q_o.astype(np.float64), d.astype(np.float64), qa, 1.0, kernel, 3, 1.0 / F,
+                           0.25 if kernel == "polynomial" else 0.0, 1.5, rows=(0, n - 1))
+        assert nrm_rel(want, got) < (1e-12 if dt == np.float64 else 5e-5), nrm_rel(want, got)
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_learn_reference_fixture_f64(golden, kernel):
+    """The reference's own 500x200 training fixture, double, epsilon 1e-3 (BASELINE config-1 setting):
+    identical CG iteration count, alpha <= 1e-10 norm-wise (or 10x the reference's own thread spread), rho cancellation-aware."""
+    g = golden("train_500x200.npz")
+    X, y = g["X"], g["y"]
+    key = f"f64/{kernel}/0.001"
+    with capi.Handle(np.float64, kernel) as h:
+        h.set_data(X)
+        alpha, rho, it = h.learn(y, eps=1e-3)
+    assert it == int(g[key + "/iters"])
+    tol = max(1e-10, 10 * float(g[key + "/spread_alpha"]))
+    assert nrm_rel(g[key + "/alpha"], alpha) < tol, (nrm_rel(g[key + "/alpha"], alpha), tol)
+    a_ref = g[key + "/alpha"]
+    q = port.generate_q(X, kernel)
+    qa = port.kernel_function(X[-1], X[-1], kernel, gamma=1.0 / X.shape[1]) + 1.0
+    scale = abs(y[-1]) + abs(qa * a_ref[:-1].sum()) + abs(q @ a_ref[:-1])
+    assert abs(rho - float(g[key + "/rho"])) <= 1e-10 * scale + 10 * float(g[key + "/spread_rho"]) * abs(float(g[key + "/rho"]))
+
+
+@pytest.mark.parametrize("eps", [1e-3, 1e-6])
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("case", ["blobs_257x33_s7", "planes_384x64_s8", "blobs_1000x256_s43"])
+def test_learn_synth_golden(golden, case, kernel, eps):
+    g = golden("cg_synth.npz")
+    problem, shape, seed = case.split("_")
+    n, F = map(int, shape.split("x"))
+    X, y = datagen.make_dense(n, F, seed=int(seed[1:]), problem=problem)
+    for name, dt in (("f64", np.float64), ("f32", np.float32)):
+        key = f"{case}/{name}/{kernel}/{eps:g}"
+        with capi.Handle(dt, kernel) as h:
+            h.set_data(X.astype(dt))
+            alpha, rho, it = h.learn(y.astype(dt), eps=eps)
+        it_ref, it_ref8 = int(g[key + "/iters"]), int(g[key + "/iters8"])
+        spread = float(g[key + "/spread_alpha"])
+        if dt == np.float64 and eps == 1e-3:
+            assert it == it_ref
+            assert nrm_rel(g[key + "/alpha"], alpha) < max(1e-10, 10 * spread)
+        elif dt == np.float64:
+            # tight epsilon: the reference itself is not reproducible across thread counts
+            assert abs(it - it_ref) <= max(1, abs(it_ref - it_ref8))
+            assert nrm_rel(g[key + "/alpha"], alpha) < max(1e-8, 20 * spread)
+        else:
+            # float: compare with the f64 truth; must be at least as close as the reference's float result (x2 slack)
+            truth = g[f"{case}/f64/{kernel}/{eps:g}/alpha"]
+            err_ref = nrm_rel(truth, g[key + "/alpha"])
+            err_ours = nrm_rel(truth, alpha)
+            assert abs(it - it_ref) <= max(2, abs(it_ref - it_ref8), it_ref // 4), (it, it_ref)
+            assert err_ours <= max(2 * err_ref, 20 * spread, 1e-4), (err_ours, err_ref, spread)
+
+
+@pytest.mark.parametrize("dt", DTYPES)
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_solver_cg_direct_and_refresh(kernel, dt):
+    """solver_CG called directly with imax large and eps tiny so the every-50th-iteration residual refresh
+    (src/plssvm/backends/OpenMP/csvm.cpp:130-135) is exercised; compared with the oracle's CG."""
+    n, F = 300, 20
+    X, y = datagen.make_dense(n, F, seed=77, problem="planes", dtype=dt)
+    q = port.generate_q(X, kernel)
+    qa = port.kernel_function(X[-1], X[-1], kernel, gamma=1.0 / F) + 1.0
+    b = (y[:-1] - y[-1]).astype(dt)
+    imax = 60
+    a_o, it_o, delta_o = port.solver_cg(X, b, q, qa, imax, 0.0, kernel, use_rows=True)
+    with capi.Handle(dt, kernel) as h:
+        h.set_data(X)
+        a, it, delta = h.solver_cg(b, q, qa, imax, 0.0)
+    assert it == it_o == imax
+    if dt == np.float64:
+        assert nrm_rel(a_o, a) < 1e-6, nrm_rel(a_o, a)  # 60 CG steps amplify rounding-order differences
+    else:
+        assert nrm_rel(a_o, a) < 0.2
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_predict_golden_labels(golden, kernel):
+    """Reference golden fixture (tests/backends/generic_tests.hpp:229-258): bit-identical labels, label * decision > 0."""
+    g = golden("predict_500x200.npz")
+    degree, gamma, coef0, rho = g[f"{kernel}/params"]
+    for dt in DTYPES:
+        with capi.Handle(dt, kernel, int(degree), gamma if gamma > 0 else 1.0 / 200, coef0) as h:
+            h.set_data(g[f"{kernel}/X"].astype(dt))
+            dec = h.predict(g[f"{kernel}/alpha"].astype(dt), rho, g["points"].astype(dt))
+            labels = h.predict_label(dec)
+            assert np.array_equal(labels, g["expected_labels"].astype(dt))
+            assert np.all(g["point_labels"] * dec > 0)
+            assert nrm_rel(g[f"{kernel}/decision"], dec) < (1e-12 if dt == np.float64 else 1e-4)
+            if kernel == "linear":
+                w = h.update_w(g[f"{kernel}/alpha"].astype(dt))
+                w_o = port.update_w(g[f"{kernel}/X"], g[f"{kernel}/alpha"])
+                assert nrm_rel(w_o, w) < (1e-13 if dt == np.float64 else 1e-5)
+
+
+def test_predict_edge_cases():
+    X, y = datagen.make_dense(50, 8, seed=5)
+    with capi.Handle(np.float64, "rbf") as h:
+        h.set_data(X)
+        alpha = np.linspace(-1, 1, 50)
+        out = h.predict(alpha, 0.3, np.empty((0, 8)))
+        assert out.shape == (0,)
+        one = h.predict(alpha, 0.3, X[:1])
+        want = port.predict(X, alpha, 0.3, X[:1], "rbf")
+        assert abs(one[0] - want[0]) < 1e-12
+        # 0 decision -> label -1 (operators::sign)
+        assert h.predict_label(np.array([0.0, 1e-300, -0.0]))[0] == -1.0
+
+
+def test_errors_are_loud():
+    with capi.Handle(np.float64, "linear", gamma=1.0) as h:
+        with pytest.raises(capi.B200Error, match="no data set"):
+            h.n, h.F = 3, 2
+            h.matvec(np.ones(2))
+        with pytest.raises(capi.B200Error, match="Data set is empty"):
+            h.L.b200svm_set_data_dense.restype = int
+            h._chk(h.L.b200svm_set_data_dense(h.h, np.zeros(1).ctypes.data, 0, 4, 4))
