@@ -148,6 +148,7 @@ int b200svm_destroy(b200svm_handle h) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     comm_destroy(*c);
+    if (c->tc_opaque != nullptr && c->tc_opaque_free != nullptr) { c->tc_opaque_free(c->tc_opaque); }
     for (auto &ev : c->ev) {
         if (ev != nullptr) { cudaEventDestroy(ev); }
     }
@@ -207,6 +208,7 @@ int b200svm_set_data_dense(b200svm_handle h, const void *X, int64_t n, int64_t F
         c->has_data = false;
         c->has_q = false;
         c->has_split = false;
+        c->has_Z = false;
         c->n = n;
         c->F = F;
         c->ldx = (F + 15) / 16 * 16;

@@ -35,24 +35,25 @@ __global__ void __launch_bounds__(VEC_THREADS) k_sums2(const T *__restrict__ v, 
     }
 }
 
-// Rank-1 epilogue of the implicit matrix (svm_kernel.cpp:32-34 rewritten):
-//   (Abar d)_i = (K d)_i + (QA_cost - q_i) sum(d) - q.d + d_i / C,   (K d)_i = sum_s P[s][i]
+// Final O(m) pass of the implicit matrix.  The O(m^2) kernels deliver, per entry, the reference's centred value
+// k(x_i,x_j) + QA_cost - q_i - q_j (svm_kernel.cpp:32) times d_j, summed into partial vectors P[s][i]; here the diagonal
+// term of svm_kernel.cpp:33-34 is added:  (Abar d)_i = sum_s P[s][i] + d_i / C  (+ sum(d) / C for the linear Z Z^T form).
 // MODE 0: out = Abar d,            scal[S_DAD] = d . out                                  (CG:  Ad, d.Ad)
 // MODE 1: out += add * Abar d,     delta_old = delta, delta = out.out, beta = delta/old   (CG:  residual refresh, csvm.cpp:130-135)
 // MODE 2: out += add * Abar d,     delta = delta0 = out.out                               (CG:  initial residual, csvm.cpp:94-98)
 // MODE 3: out += add * Abar d                                                             (run_device_kernel test hook)
 template <typename T, int MODE>
 __global__ void __launch_bounds__(VEC_THREADS) k_abar_finish(const T *__restrict__ P, int64_t ldP, int splits, const T *__restrict__ d,
-                                                             const T *__restrict__ q, int64_t m, T QA_cost, T inv_cost, T add,
+                                                             int64_t m, T inv_cost, int linear, T add,
                                                              T *__restrict__ out, T *__restrict__ scal, T *partials, unsigned int *ticket) {
     __shared__ T red[32];
-    const T sum_d = scal[S_SUM_D], q_d = scal[S_Q_D];
+    const T rank1 = linear ? scal[S_SUM_D] * inv_cost : T(0);
     T acc[1] = { T(0) };
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (int64_t) gridDim.x * blockDim.x) {
         T kd = T(0);
         for (int s = 0; s < splits; ++s) { kd += P[(int64_t) s * ldP + i]; }
         const T di = d[i];
-        const T val = kd + (QA_cost - q[i]) * sum_d - q_d + di * inv_cost;
+        const T val = kd + rank1 + di * inv_cost;
         if constexpr (MODE == 0) {
             out[i] = val;
             acc[0] = fma(di, val, acc[0]);
@@ -179,11 +180,17 @@ kd_result kernel_times_vector(ctx &c, const T *d) {
     if (c.is_csr) {
         fail(B200SVM_ERR_INVALID, "CSR matvec is not available in this build");
     } else if (c.kernel == B200SVM_LINEAR) {
-        // K d = X (X^T d): two GEMVs (HBM bound) instead of m^2 F flops
+        // centred linear kernel: sum_j (K_ij + K_nn - K_in - K_nj) d_j = Z (Z^T d), Z = X - 1 x_n^T : two GEMVs (HBM bound)
+        if (!c.has_Z) {
+            c.Z.reserve((size_t) m * c.ldx * sizeof(T));
+            center_rows<T>(c, c.X.as<T>(), m, c.ldx, c.X.as<T>() + m * c.ldx, c.Z.as<T>());
+            c.has_Z = true;
+        }
         c.P.reserve((size_t) ldP * sizeof(T));
         c.wvec.reserve((size_t) c.ldx * sizeof(T));
-        xt_v<T>(c, c.X.as<T>(), m, c.ldx, d, c.wvec.as<T>());
-        x_w<T>(c, c.X.as<T>(), m, c.ldx, c.wvec.as<T>(), T(0), c.P.as<T>());
+        sums2<T>(c, d, S_SUM_D, S_Q_D);
+        xt_v<T>(c, c.Z.as<T>(), m, c.ldx, d, c.wvec.as<T>());
+        x_w<T>(c, c.Z.as<T>(), m, c.ldx, c.wvec.as<T>(), T(0), c.P.as<T>());
         c.stats.matvec_path = 3;
     } else {
         bool use_tc = false;
@@ -197,7 +204,7 @@ kd_result kernel_times_vector(ctx &c, const T *d) {
         } else {
             c.P.reserve((size_t) (MAXS * ldP) * sizeof(T));
             res.splits = kmv_simt_launch<T>(c, c.X.as<T>(), c.norms.as<T>(), m, c.ldx, c.X.as<T>(), c.norms.as<T>(), m, c.ldx, d, c.P.as<T>(),
-                                            ldP, MAXS);
+                                            ldP, MAXS, c.q.as<T>(), (T) c.QA_cost);
             c.stats.matvec_path = 1;
         }
     }
@@ -212,9 +219,9 @@ kd_result kernel_times_vector(ctx &c, const T *d) {
 template <typename T, int MODE>
 void abar_finish(ctx &c, const kd_result &kd, const T *d, T add, T *out) {
     const int64_t m = c.m();
-    k_abar_finish<T, MODE><<<vec_grid(m), VEC_THREADS, 0, c.stream>>>(c.P.as<T>(), kd.ldP, kd.splits, d, c.q.as<T>(), m, (T) c.QA_cost,
-                                                                       T(1) / (T) c.cost, add, out, c.scal.as<T>(), c.partials.as<T>(),
-                                                                       c.counters.as<unsigned int>());
+    k_abar_finish<T, MODE><<<vec_grid(m), VEC_THREADS, 0, c.stream>>>(c.P.as<T>(), kd.ldP, kd.splits, d, m, T(1) / (T) c.cost,
+                                                                       c.kernel == B200SVM_LINEAR ? 1 : 0, add, out, c.scal.as<T>(),
+                                                                       c.partials.as<T>(), c.counters.as<unsigned int>());
     count_launch(c);
     B200_CUDA_CHECK(cudaGetLastError());
 }
@@ -224,7 +231,6 @@ void abar_finish(ctx &c, const kd_result &kd, const T *d, T add, T *out) {
 // ret += add * Abar d (test hook for run_device_kernel; d and ret are device vectors of m reals)
 template <typename T>
 void apply_abar(ctx &c, const T *d, T add, T *ret) {
-    sums2<T>(c, d, S_SUM_D, S_Q_D);
     const kd_result kd = kernel_times_vector<T>(c, d);
     abar_finish<T, 3>(c, kd, d, add, ret);
 }
@@ -249,13 +255,11 @@ int64_t cg_solve(ctx &c, const T *b, int64_t imax, T eps, T *x, double *delta_ou
     k_fill<T><<<g, VEC_THREADS, 0, c.stream>>>(x, m, T(1));
     count_launch(c);
     B200_CUDA_CHECK(cudaMemcpyAsync(r, b, vb, cudaMemcpyDeviceToDevice, c.stream));
-    sums2<T>(c, x, S_SUM_D, S_Q_D);
     {
         const kd_result kd = kernel_times_vector<T>(c, x);
         abar_finish<T, 2>(c, kd, x, T(-1), r);
     }
     B200_CUDA_CHECK(cudaMemcpyAsync(d, r, vb, cudaMemcpyDeviceToDevice, c.stream));
-    sums2<T>(c, d, S_SUM_D, S_Q_D);
     B200_CUDA_CHECK(cudaMemcpyAsync(mailbox, scal + S_DELTA0, sizeof(T), cudaMemcpyDeviceToHost, c.stream));
     sync_stream(c);
     const T delta0 = mailbox[0];
@@ -272,7 +276,6 @@ int64_t cg_solve(ctx &c, const T *b, int64_t imax, T eps, T *x, double *delta_ou
             k_cg_update<T, 1><<<g, VEC_THREADS, 0, c.stream>>>(x, r, d, Ad, m, scal, partials, ticket);
             count_launch(c);
             B200_CUDA_CHECK(cudaMemcpyAsync(r, b, vb, cudaMemcpyDeviceToDevice, c.stream));
-            sums2<T>(c, x, S_SUM_D, S_Q_D);
             const kd_result kx = kernel_times_vector<T>(c, x);
             abar_finish<T, 1>(c, kx, x, T(-1), r);
         } else {

@@ -1,11 +1,591 @@
-// tcgen05 / TMA Gram-tile path (f32 dense).  Placeholder translation unit: the path reports "unavailable" so the
-// dispatcher in cg.cu selects the SIMT kernel.
+// tcgen05 / TMA / TMEM Gram-tile path for dense float data (BASELINE configs[1]: rbf, 65536 x 1024, float).
+//
+// What it computes (reference semantics: src/plssvm/backends/OpenMP/svm_kernel.cpp:21-47, lower triangle mirrored):
+//   for every 128 x 256 tile (I, J) of the lower block triangle of the implicit matrix
+//       G    = X_I X_J^T                         (tensor cores, fp32 accumulation in TMEM)
+//       t_ij = k(G_ij) + QA_cost - q_i - q_j     (kernel function + the reference's per-entry centring, svm_kernel.cpp:32)
+//       Pr[J][i] = sum_j t_ij d_j                (row contribution,   i >= j)
+//       Pc[I][j] = sum_i t_ij d_i                (mirrored contribution, i > j)
+//   a small deterministic pass (k_tc_reduce) then sums the partial vectors in a fixed order — no atomics.
+//
+// Precision: X is split once into two fp16 planes, x * s = hi + lo (s = power of two placing max|x| in [2^13, 2^14)), and
+//   G = (hi hi^T + hi lo^T + lo hi^T) / s^2 — three kind::f16 MMAs per K-slice, 22 significant bits per operand
+//   (the dropped lo lo^T term is 2^-22 relative).  See DESIGN.md "fp16x2 split" for the measured error.
+//
+// Structure (one persistent CTA per SM, 192 threads):
+//   warp 0 / lane 0 : TMA producer  — cp.async.bulk.tensor 2-D boxes (64 fp16 x 128 rows, SWIZZLE_128B) into a 2-stage ring
+//   warp 1 / lane 0 : MMA issuer    — tcgen05.mma.cta_group::1.kind::f16, M=128 N=256 K=16, accumulator double-buffered in TMEM
+//   warps 2..5      : epilogue      — tcgen05.ld 32x32b, exp2 / pow, centring, row sums in registers, column sums by a
+//                                     warp-shuffle butterfly + shared memory
 #include "internal.cuh"
+
+#include <cuda.h>
+#include <cuda_fp16.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
 
 namespace b200 {
 
-void tc_prepare_split(ctx &) {}
-bool tc_available(const ctx &) { return false; }
-void tc_kernel_matvec(ctx &, const float *, float *) { fail(B200SVM_ERR_INVALID, "tcgen05 matvec path is not available in this build"); }
+namespace tc {
+
+constexpr int BM = 128;       // tile rows   (A operand, "i")
+constexpr int BN = 256;       // tile cols   (B operand, "j")
+constexpr int BK = 64;        // fp16 elements per K block = 128 bytes = one SWIZZLE_128B row
+constexpr int STAGES = 2;
+constexpr int UMMA_K = 16;
+constexpr int A_BYTES = BM * BK * 2;                      // 16 KB per plane
+constexpr int B_BYTES = BN * BK * 2;                      // 32 KB per plane
+constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;    // hi + lo planes: 96 KB
+constexpr int NUM_THREADS = 192;
+constexpr int EPI_THREADS = 128;
+constexpr int TMEM_COLS = 512;                            // two 256-column fp32 accumulators
+
+struct smem_layout {
+    // operand ring (1024-byte aligned for SWIZZLE_128B): per stage [A_hi | A_lo | B_hi | B_lo]
+    static constexpr int OPERANDS = 0;
+    static constexpr int COLBUF = STAGES * STAGE_BYTES;              // float4[2][BN]   per-column {c_j, q_j, d_j, -}
+    static constexpr int COLRED = COLBUF + 2 * BN * 16;              // float[2][4][BN] per-warp column partial sums
+    static constexpr int BARRIERS = COLRED + 2 * 4 * BN * 4;         // uint64: full[S], empty[S], tmem_full[2], tmem_empty[2]
+    static constexpr int TMEM_PTR = BARRIERS + (2 * STAGES + 4) * 8;
+    static constexpr int TOTAL = TMEM_PTR + 16;
+};
+constexpr int SMEM_BYTES = smem_layout::TOTAL + 1024;  // + slack for the manual 1024-byte alignment
+
+struct params {
+    const int2 *tiles;
+    int num_tiles;
+    int num_k_blocks;
+    const float4 *pk;  // [n_pad] {c_i, q_i, d_i, 0}; rows >= m are all-zero (d = 0 masks them)
+    float *Pr;         // [T_c][ldP]
+    float *Pc;         // [T_r][ldP]
+    int64_t ldP;
+    float w;           // rbf: 2 gamma log2(e) / s^2 ; polynomial: gamma / s^2
+    float coef0;
+    float qa;          // QA_cost
+    int degree;
+    int kernel;
+};
+
+// ---------------------------------------------------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra WAIT_DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "WAIT_DONE:\n\t"
+        "}" ::"r"(bar),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+                 "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+          "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+          "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// K-major SWIZZLE_128B shared-memory matrix descriptor (sm_100 "version 1"): rows of 128 bytes, 8-row groups 1024 bytes apart.
+__device__ __forceinline__ uint64_t make_desc_sw128(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((saddr & 0x3FFFF) >> 4);   // start address, bits [0,14)
+    d |= static_cast<uint64_t>(1) << 16;                  // leading byte offset (unused for swizzled K-major), bits [16,30)
+    d |= static_cast<uint64_t>(1024 >> 4) << 32;          // stride byte offset between 8-row groups, bits [32,46)
+    d |= static_cast<uint64_t>(1) << 46;                  // descriptor version (Blackwell), bits [46,48)
+    d |= static_cast<uint64_t>(2) << 61;                  // layout type SWIZZLE_128B, bits [61,64)
+    return d;
+}
+// instruction descriptor: D = f32, A = B = f16, both K-major, N at bits [17,23) (N >> 3), M at bits [24,29) (M >> 4)
+__host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
+    return (1u << 4) | (0u << 7) | (0u << 10) | (0u << 15) | (0u << 16) | (static_cast<uint32_t>(N >> 3) << 17) |
+           (static_cast<uint32_t>(M >> 4) << 24);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// epilogue math
+// ---------------------------------------------------------------------------------------------------------------------
+template <int KERNEL>
+__device__ __forceinline__ float kernel_from_gram(float g, float ci, float cj, float w, float coef0, int degree) {
+    if constexpr (KERNEL == B200SVM_RBF) {
+        // exp(-gamma (n_i + n_j - 2 G)) = 2^(c_i + c_j + w G), c = -gamma log2(e) n, w = 2 gamma log2(e) / s^2 ; clamp d2 >= 0
+        const float a = fminf(fmaf(w, g, ci) + cj, 0.f);
+        return ex2_approx(a);
+    } else {
+        float base = fmaf(w, g, coef0);
+        const bool neg = degree < 0;
+        unsigned int u = neg ? static_cast<unsigned int>(-degree) : static_cast<unsigned int>(degree);
+        float r = 1.f;
+        while (u != 0u) {
+            if (u & 1u) { r *= base; }
+            base *= base;
+            u >>= 1;
+        }
+        return neg ? 1.f / r : r;
+    }
+}
+
+// Sum v[c] over the 32 lanes of the warp for each of the 32 columns c; lane l returns the total of column l.
+// Fixed exchange pattern => bit-reproducible.
+__device__ __forceinline__ float warp_column_sums(float (&v)[32], int lane) {
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) {
+        const bool up = (lane & o) != 0;
+#pragma unroll
+        for (int k = 0; k < o; ++k) {
+            const float send = up ? v[k] : v[k + o];
+            const float keep = up ? v[k + o] : v[k];
+            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
+    }
+    return v[0];
+}
+
+template <int KERNEL>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+    k_gram_tc(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo, const params p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    const uint32_t sbase = smem_u32(smem);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    const uint32_t bar_full = sbase + smem_layout::BARRIERS;          // [STAGES]
+    const uint32_t bar_empty = bar_full + STAGES * 8;                  // [STAGES]
+    const uint32_t bar_tfull = bar_empty + STAGES * 8;                 // [2]
+    const uint32_t bar_tempty = bar_tfull + 2 * 8;                     // [2]
+    uint32_t *tmem_ptr_smem = reinterpret_cast<uint32_t *>(smem + smem_layout::TMEM_PTR);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(bar_full + s * 8, 1);
+            mbar_init(bar_empty + s * 8, 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(bar_tfull + b * 8, 1);
+            mbar_init(bar_tempty + b * 8, 4);  // one arrival per epilogue warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(TMEM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    const int first_tile = blockIdx.x, tile_step = gridDim.x;
+
+    if (warp == 0) {
+        // ============================== TMA producer ==============================
+        if (lane == 0) {
+            asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_hi)) : "memory");
+            asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_lo)) : "memory");
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = first_tile; t < p.num_tiles; t += tile_step) {
+                const int2 tile = p.tiles[t];
+                const int row_a = tile.x * BM, row_b = tile.y * BN;
+                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                    mbar_wait(bar_empty + stage * 8, phase ^ 1);
+                    const uint32_t full = bar_full + stage * 8;
+                    mbar_arrive_expect_tx(full, STAGE_BYTES);
+                    const uint32_t s0 = sbase + smem_layout::OPERANDS + stage * STAGE_BYTES;
+                    const int kc = kb * BK;
+                    tma_load_2d(s0, &map_hi, full, kc, row_a);                                  // A_hi  128 rows
+                    tma_load_2d(s0 + A_BYTES, &map_lo, full, kc, row_a);                        // A_lo
+                    tma_load_2d(s0 + 2 * A_BYTES, &map_hi, full, kc, row_b);                    // B_hi  rows 0..127
+                    tma_load_2d(s0 + 2 * A_BYTES + A_BYTES, &map_hi, full, kc, row_b + 128);    // B_hi  rows 128..255
+                    tma_load_2d(s0 + 2 * A_BYTES + B_BYTES, &map_lo, full, kc, row_b);          // B_lo
+                    tma_load_2d(s0 + 2 * A_BYTES + B_BYTES + A_BYTES, &map_lo, full, kc, row_b + 128);
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ============================== MMA issuer ==============================
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_f16(BM, BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int t = first_tile; t < p.num_tiles; t += tile_step, ++it) {
+                const int buf = it & 1;
+                const uint32_t use = static_cast<uint32_t>(it >> 1);
+                mbar_wait(bar_tempty + buf * 8, (use & 1) ^ 1);  // epilogue has drained this accumulator
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + buf * BN;
+                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                    mbar_wait(bar_full + stage * 8, phase);
+                    tc_fence_after();
+                    const uint32_t s0 = sbase + smem_layout::OPERANDS + stage * STAGE_BYTES;
+                    const uint64_t a_hi = make_desc_sw128(s0), a_lo = make_desc_sw128(s0 + A_BYTES);
+                    const uint64_t b_hi = make_desc_sw128(s0 + 2 * A_BYTES), b_lo = make_desc_sw128(s0 + 2 * A_BYTES + B_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) {
+                        const uint64_t adv = static_cast<uint64_t>((k * UMMA_K * 2) >> 4);  // +32 bytes per K step inside the swizzle row
+                        tc_mma_f16(tmem_d, a_hi + adv, b_hi + adv, idesc, (kb | k) != 0 ? 1u : 0u);
+                        tc_mma_f16(tmem_d, a_hi + adv, b_lo + adv, idesc, 1u);
+                        tc_mma_f16(tmem_d, a_lo + adv, b_hi + adv, idesc, 1u);
+                    }
+                    tc_commit(bar_empty + stage * 8);  // frees the smem stage when these MMAs retire
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                tc_commit(bar_tfull + buf * 8);  // accumulator complete -> epilogue
+            }
+        }
+    } else {
+        // ============================== epilogue warps (2..5) ==============================
+        const int q = warp & 3;                 // TMEM lane quadrant this warp may access
+        const int et = threadIdx.x - 64;        // 0..127
+        float4 *colbuf = reinterpret_cast<float4 *>(smem + smem_layout::COLBUF);
+        float *colred = reinterpret_cast<float *>(smem + smem_layout::COLRED);
+        int it = 0;
+        for (int t = first_tile; t < p.num_tiles; t += tile_step, ++it) {
+            const int buf = it & 1;
+            const uint32_t use = static_cast<uint32_t>(it >> 1);
+            const int2 tile = p.tiles[t];
+            const int64_t row0 = static_cast<int64_t>(tile.x) * BM, col0 = static_cast<int64_t>(tile.y) * BN;
+            // stage the per-column data of this tile
+            colbuf[buf * BN + et] = __ldg(&p.pk[col0 + et]);
+            colbuf[buf * BN + 128 + et] = __ldg(&p.pk[col0 + 128 + et]);
+            const int r = q * 32 + lane;
+            const int64_t gi = row0 + r;
+            const float4 mine = __ldg(&p.pk[gi]);  // {c_i, q_i, d_i, -}
+            const float ai = p.qa - mine.y;
+            const float di = mine.z;
+            const bool diag_tile = (row0 < col0 + BN);  // tile touches or crosses the diagonal
+
+            mbar_wait(bar_tfull + buf * 8, use & 1);
+            tc_fence_after();
+            asm volatile("bar.sync 1, 128;" ::: "memory");  // colbuf visible to the 4 epilogue warps
+
+            float rowsum = 0.f;
+            float *cr = colred + (buf * 4 + q) * BN;
+#pragma unroll 1
+            for (int g = 0; g < BN / 32; ++g) {
+                uint32_t u[32];
+                tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * BN + g * 32), u);
+                tmem_ld_wait();
+                float v[32];
+                if (!diag_tile) {
+#pragma unroll
+                    for (int cc = 0; cc < 32; ++cc) {
+                        const float4 cj = colbuf[buf * BN + g * 32 + cc];
+                        const float kv = kernel_from_gram<KERNEL>(__uint_as_float(u[cc]), mine.x, cj.x, p.w, p.coef0, p.degree);
+                        const float tv = kv + (ai - cj.y);
+                        rowsum = fmaf(tv, cj.z, rowsum);
+                        v[cc] = tv * di;
+                    }
+                } else {
+#pragma unroll
+                    for (int cc = 0; cc < 32; ++cc) {
+                        const float4 cj = colbuf[buf * BN + g * 32 + cc];
+                        const int64_t gj = col0 + g * 32 + cc;
+                        const float kv = kernel_from_gram<KERNEL>(__uint_as_float(u[cc]), mine.x, cj.x, p.w, p.coef0, p.degree);
+                        const float tv = kv + (ai - cj.y);
+                        rowsum = gi >= gj ? fmaf(tv, cj.z, rowsum) : rowsum;  // lower triangle incl. diagonal -> row i
+                        v[cc] = gi > gj ? tv * di : 0.f;                        // strictly lower -> mirrored into column j
+                    }
+                }
+                const float cs = warp_column_sums(v, lane);
+                cr[g * 32 + lane] = cs;
+            }
+            // accumulator fully read: hand the TMEM buffer back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) { mbar_arrive(bar_tempty + buf * 8); }
+            p.Pr[static_cast<int64_t>(tile.y) * p.ldP + gi] = rowsum;
+            asm volatile("bar.sync 1, 128;" ::: "memory");  // colred complete
+            {
+                const float *c0 = colred + buf * 4 * BN;
+                const float s_lo = (c0[et] + c0[BN + et]) + (c0[2 * BN + et] + c0[3 * BN + et]);
+                const float s_hi = (c0[128 + et] + c0[BN + 128 + et]) + (c0[2 * BN + 128 + et] + c0[3 * BN + 128 + et]);
+                float *pc = p.Pc + static_cast<int64_t>(tile.x) * p.ldP + col0;
+                pc[et] = s_lo;
+                pc[128 + et] = s_hi;
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// helper kernels: max |x|, fp16 hi/lo split, per-index pack, partial-vector reduction
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_absmax(const float *__restrict__ X, int64_t count, unsigned int *__restrict__ out) {
+    float mx = 0.f;
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t) gridDim.x * blockDim.x) {
+        mx = fmaxf(mx, fabsf(X[i]));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o)); }
+    if ((threadIdx.x & 31) == 0) { atomicMax(out, __float_as_uint(mx)); }  // non-negative floats order like their bit patterns
+}
+
+// hi = fp16(x s), lo = fp16(x s - hi); rows >= n and columns >= ldx are zero
+__global__ void __launch_bounds__(256) k_split_fp16(const float *__restrict__ X, int64_t n, int64_t ldx, float s, __half *__restrict__ hi,
+                                                    __half *__restrict__ lo, int64_t n_pad, int64_t ldh) {
+    const int64_t total = n_pad * ldh;
+    for (int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t row = e / ldh, col = e - row * ldh;
+        float x = 0.f;
+        if (row < n && col < ldx) { x = X[row * ldx + col] * s; }
+        const __half h = __float2half_rn(x);
+        hi[e] = h;
+        lo[e] = __float2half_rn(x - __half2float(h));
+    }
+}
+
+// pk[i] = {c_i, q_i, d_i, 0} for i < m, zeros above; c_i = -gamma log2(e) |x_i|^2 (rbf) or 0
+__global__ void __launch_bounds__(256) k_pack(const float *__restrict__ norms, const float *__restrict__ q, const float *__restrict__ d,
+                                              int64_t m, int64_t n_pad, float cscale, float4 *__restrict__ pk) {
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pad) { return; }
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < m) { v = make_float4(cscale * norms[i], q[i], d[i], 0.f); }
+    pk[i] = v;
+}
+
+// out[i] = sum_{J <= I_i / 2} Pr[J][i] + sum_{I' >= 2 J_i} Pc[I'][i]   (fixed order; slots of tiles owned by other ranks are zero)
+__global__ void __launch_bounds__(256) k_tc_reduce(const float *__restrict__ Pr, const float *__restrict__ Pc, int64_t ldP, int64_t m, int T_r,
+                                                   float *__restrict__ out) {
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) { return; }
+    const int Ii = (int) (i / BM), Ji = (int) (i / BN);
+    float s0 = 0.f, s1 = 0.f;
+    for (int J = 0; J <= Ii / 2; ++J) { s0 += Pr[(int64_t) J * ldP + i]; }
+    for (int I = 2 * Ji; I < T_r; ++I) { s1 += Pc[(int64_t) I * ldP + i]; }
+    out[i] = s0 + s1;
+}
+
+}  // namespace tc
+
+// ---------------------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+
+struct tc_state {
+    CUtensorMap map_hi{}, map_lo{};
+    dbuf tiles, pk, Pr, Pc, amax;
+    int num_tiles{ 0 };
+    int T_r{ 0 }, T_c{ 0 };
+    int64_t ldP{ 0 };
+    bool ready{ false };
+};
+
+// one tc_state per handle, owned through ctx::tc_opaque
+tc_state &state_of(ctx &c) {
+    if (c.tc_opaque == nullptr) {
+        c.tc_opaque = new tc_state();
+        c.tc_opaque_free = [](void *p) { delete static_cast<tc_state *>(p); };
+    }
+    return *static_cast<tc_state *>(c.tc_opaque);
+}
+
+using encode_fn = CUresult (*)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                               const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+encode_fn get_encode() {
+    static encode_fn fn = nullptr;
+    if (fn == nullptr) {
+        void *sym = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        B200_CUDA_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres));
+        if (sym == nullptr || qres != cudaDriverEntryPointSuccess) { fail(B200SVM_ERR_CUDA, "cuTensorMapEncodeTiled is not available in this driver"); }
+        fn = reinterpret_cast<encode_fn>(sym);
+    }
+    return fn;
+}
+
+void make_map(CUtensorMap *map, void *base, int64_t rows, int64_t ld_elems) {
+    const cuuint64_t dims[2] = { (cuuint64_t) ld_elems, (cuuint64_t) rows };
+    const cuuint64_t strides[1] = { (cuuint64_t) ld_elems * 2 };
+    const cuuint32_t box[2] = { (cuuint32_t) tc::BK, 128u };
+    const cuuint32_t estr[2] = { 1u, 1u };
+    const CUresult r = get_encode()(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { fail(B200SVM_ERR_CUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string((int) r)); }
+}
+
+// lower block triangle, grouped in super-tiles of GI x GJ block tiles so that one wave of CTAs shares its operands in L2
+std::vector<int2> build_tiles(int T_r, int T_c, int rank, int world) {
+    constexpr int GI = 32, GJ = 16;
+    std::vector<int2> all;
+    for (int sj = 0; sj < T_c; sj += GJ) {
+        for (int si = 2 * sj; si < T_r; si += GI) {
+            for (int j = sj; j < std::min(sj + GJ, T_c); ++j) {
+                for (int i = std::max(si, 2 * j); i < std::min(si + GI, T_r); ++i) { all.push_back(make_int2(i, j)); }
+            }
+        }
+    }
+    if (world <= 1) { return all; }
+    // contiguous slice of the (uniform-cost) tile list per rank: balanced to within one tile
+    const size_t lo = all.size() * (size_t) rank / (size_t) world, hi = all.size() * (size_t) (rank + 1) / (size_t) world;
+    return std::vector<int2>(all.begin() + (std::ptrdiff_t) lo, all.begin() + (std::ptrdiff_t) hi);
+}
+
+}  // namespace
+
+bool tc_available(const ctx &c) {
+    return c.has_split && c.tc_opaque != nullptr && static_cast<const tc_state *>(c.tc_opaque)->ready;
+}
+
+void tc_prepare_split(ctx &c) {
+    if (c.dtype != B200SVM_F32 || c.is_csr || c.kernel == B200SVM_LINEAR) { return; }
+    const int64_t m = c.m();
+    if (m < 1) { return; }
+    tc_state &st = state_of(c);
+    st.ready = false;
+    c.n_pad = (c.n + tc::BN - 1) / tc::BN * tc::BN;
+    c.ldh = (c.ldx + tc::BK - 1) / tc::BK * tc::BK;
+    // scale: place max |x| in [2^13, 2^14) so that the low plane keeps 11 bits down to |x| = max / 2^13
+    st.amax.reserve(sizeof(unsigned int));
+    B200_CUDA_CHECK(cudaMemsetAsync(st.amax.p, 0, sizeof(unsigned int), c.stream));
+    tc::k_absmax<<<4 * NUM_SMS, 256, 0, c.stream>>>(c.X.as<float>(), c.n * c.ldx, st.amax.as<unsigned int>());
+    count_launch(c);
+    unsigned int *mb = static_cast<unsigned int *>(c.pinned);
+    B200_CUDA_CHECK(cudaMemcpyAsync(mb, st.amax.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, c.stream));
+    B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));
+    float amax;
+    std::memcpy(&amax, mb, 4);
+    float s = 1.f;
+    if (amax > 0.f && std::isfinite(amax)) {
+        int e = 0;
+        std::frexp(amax, &e);  // amax = f * 2^e, f in [0.5, 1)  ->  amax * 2^(14 - e) in [2^13, 2^14)
+        s = std::ldexp(1.f, 14 - e);
+    }
+    c.split_scale = s;
+    const size_t plane = (size_t) c.n_pad * c.ldh * sizeof(__half);
+    c.Xh_hi.reserve(plane);
+    c.Xh_lo.reserve(plane);
+    tc::k_split_fp16<<<8 * NUM_SMS, 256, 0, c.stream>>>(c.X.as<float>(), c.n, c.ldx, s, c.Xh_hi.as<__half>(), c.Xh_lo.as<__half>(), c.n_pad, c.ldh);
+    count_launch(c);
+    B200_CUDA_CHECK(cudaGetLastError());
+    make_map(&st.map_hi, c.Xh_hi.p, c.n_pad, c.ldh);
+    make_map(&st.map_lo, c.Xh_lo.p, c.n_pad, c.ldh);
+
+    st.T_r = (int) (c.n_pad / tc::BM);
+    st.T_c = (int) (c.n_pad / tc::BN);
+    st.ldP = c.n_pad;
+    const std::vector<int2> tiles = build_tiles(st.T_r, st.T_c, c.rank, c.world);
+    st.num_tiles = (int) tiles.size();
+    st.tiles.reserve(std::max<size_t>(tiles.size(), 1) * sizeof(int2));
+    B200_CUDA_CHECK(cudaMemcpyAsync(st.tiles.p, tiles.data(), tiles.size() * sizeof(int2), cudaMemcpyHostToDevice, c.stream));
+    st.pk.reserve((size_t) c.n_pad * sizeof(float4));
+    st.Pr.reserve((size_t) st.T_c * st.ldP * sizeof(float));
+    st.Pc.reserve((size_t) st.T_r * st.ldP * sizeof(float));
+    B200_CUDA_CHECK(cudaMemsetAsync(st.Pr.p, 0, (size_t) st.T_c * st.ldP * sizeof(float), c.stream));
+    B200_CUDA_CHECK(cudaMemsetAsync(st.Pc.p, 0, (size_t) st.T_r * st.ldP * sizeof(float), c.stream));
+    B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));  // `tiles` (host vector) must outlive the copy
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200_CUDA_CHECK(cudaFuncSetAttribute(tc::k_gram_tc<B200SVM_RBF>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+        B200_CUDA_CHECK(cudaFuncSetAttribute(tc::k_gram_tc<B200SVM_POLYNOMIAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+        attr_set = true;
+    }
+    c.has_split = true;
+    st.ready = true;
+}
+
+// out[i] = sum_j (k(x_i, x_j) + QA_cost - q_i - q_j) d_j  over the tiles owned by this rank (all tiles when world == 1)
+void tc_kernel_matvec(ctx &c, const float *d, float *out) {
+    if (!tc_available(c)) { fail(B200SVM_ERR_INVALID, "tcgen05 matvec path requested but the fp16 operand planes are not prepared"); }
+    tc_state &st = state_of(c);
+    const int64_t m = c.m();
+    constexpr float LOG2E = 1.4426950408889634f;
+    const float s2 = c.split_scale * c.split_scale;
+    tc::params p{};
+    p.tiles = st.tiles.as<int2>();
+    p.num_tiles = st.num_tiles;
+    p.num_k_blocks = (int) (c.ldh / tc::BK);
+    p.pk = st.pk.as<float4>();
+    p.Pr = st.Pr.as<float>();
+    p.Pc = st.Pc.as<float>();
+    p.ldP = st.ldP;
+    p.coef0 = (float) c.coef0;
+    p.qa = (float) c.QA_cost;
+    p.degree = c.degree;
+    p.kernel = c.kernel;
+    float cscale = 0.f;
+    if (c.kernel == B200SVM_RBF) {
+        p.w = (float) (2.0 * c.gamma * (double) LOG2E / (double) s2);
+        cscale = (float) (-c.gamma * (double) LOG2E);
+    } else {
+        p.w = (float) (c.gamma / (double) s2);
+    }
+    tc::k_pack<<<(unsigned) ((c.n_pad + 255) / 256), 256, 0, c.stream>>>(c.norms.as<float>(), c.q.as<float>(), d, m, c.n_pad, cscale, st.pk.as<float4>());
+    const int grid = std::min(NUM_SMS, std::max(st.num_tiles, 1));
+    if (c.kernel == B200SVM_RBF) {
+        tc::k_gram_tc<B200SVM_RBF><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_lo, p);
+    } else {
+        tc::k_gram_tc<B200SVM_POLYNOMIAL><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_lo, p);
+    }
+    tc::k_tc_reduce<<<(unsigned) ((m + 255) / 256), 256, 0, c.stream>>>(st.Pr.as<float>(), st.Pc.as<float>(), st.ldP, m, st.T_r, out);
+    count_launch(c, 3);
+    B200_CUDA_CHECK(cudaGetLastError());
+}
 
 }  // namespace b200

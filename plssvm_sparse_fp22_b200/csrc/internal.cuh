@@ -111,6 +111,8 @@ struct ctx {
     int64_t n{ 0 }, F{ 0 }, ldx{ 0 };  // ldx in elements
     dbuf X;                            // dense n x ldx, row-major, real type
     dbuf norms;                        // n squared norms (real type)
+    dbuf Z;                            // linear kernel: rows 0..m-1 of X minus the last row
+    bool has_Z{ false };
     // CSR
     int64_t nnz{ 0 };
     int value_format{ 0 };
@@ -137,6 +139,9 @@ struct ctx {
     dbuf pts, pts_norms, pred_out, alpha_dev;  // predict staging
     void *pinned{ nullptr };                   // small pinned host mailbox (scalars / flags)
 
+    void *tc_opaque{ nullptr };                 // tcgen05 path state (gram_tc.cu)
+    void (*tc_opaque_free)(void *){ nullptr };
+
     // multi-GPU
     comm_state *comm{ nullptr };
     int rank{ 0 }, world{ 1 };
@@ -160,7 +165,8 @@ template <typename T> void apply_abar(ctx &c, const T *d, T add, T *ret);       
 template <typename T> int64_t cg_solve(ctx &c, const T *b_dev, int64_t imax, T eps, T *alpha_dev, double *delta_out);
 template <typename T> void update_w(ctx &c, const T *alpha_dev, T *w_dev);
 template <typename T> int kmv_simt_launch(ctx &c, const T *A, const T *normA, int64_t rowsA, int64_t ldA, const T *B, const T *normB, int64_t rowsB,
-                                          int64_t ldB, const T *v, T *P, int64_t ldP, int max_splits);
+                                          int64_t ldB, const T *v, T *P, int64_t ldP, int max_splits, const T *qv, T qa);
+template <typename T> void center_rows(ctx &c, const T *X, int64_t rows, int64_t ld, const T *xlast, T *Z);
 template <typename T> void xt_v(ctx &c, const T *X, int64_t rows, int64_t ld, const T *v, T *w);
 template <typename T> void x_w(ctx &c, const T *X, int64_t rows, int64_t ld, const T *w, T bias, T *out);
 template <typename T> void predict_dense(ctx &c, const T *alpha_dev, T bias, const T *pts_dev, int64_t P, int64_t ld, T *out_dev);

@@ -78,6 +78,7 @@ template void generate_q<double>(ctx &);
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Generic tiled kernel-matrix x vector:  P[s][i] = sum_{j in column split s} k(A_i, B_j) v_j
+//   (CENTER: k(A_i, B_j) + QA_cost - q_i - q_j, the entry of the reduced system without its 1/C diagonal)
 //   A: rowsA x ldA, B: rowsB x ldB (row-major, zero padded to a multiple of 16 features), squared norms precomputed.
 //   256 threads = 16 x 16, each owning a TM x TN register micro-tile of the BM x BN Gram tile (BM = 16 TM, BN = 16 TN);
 //   K is streamed in BK = 16 slices through double-buffered shared memory (register prefetch of the next slice).
@@ -98,11 +99,11 @@ struct vec16<double> {
     static constexpr int N = 2;
 };
 
-template <typename T, int KERNEL, int TM, int TN>
+template <typename T, int KERNEL, int TM, int TN, bool CENTER>
 __global__ void __launch_bounds__(256)
     k_kmv_tile(const T *__restrict__ A, const T *__restrict__ normA, int64_t rowsA, int64_t ldA, const T *__restrict__ B,
                const T *__restrict__ normB, int64_t rowsB, int64_t ldB, int64_t K, const T *__restrict__ v, int degree, T gamma, T coef0,
-               T *__restrict__ P, int64_t ldP, int col_tiles) {
+               const T *__restrict__ qv, T qa, T *__restrict__ P, int64_t ldP, int col_tiles) {
     constexpr int BM = 16 * TM, BN = 16 * TN;
     using V = typename vec16<T>::type;
     constexpr int VN = vec16<T>::N;
@@ -125,11 +126,14 @@ __global__ void __launch_bounds__(256)
 
     T rowsum[TM];
     T na[TM];
+    T ai[TM];  // CENTER: QA_cost - q_i (the reference's per-entry centring, svm_kernel.cpp:32)
 #pragma unroll
     for (int r = 0; r < TM; ++r) {
         rowsum[r] = T(0);
         const int64_t row = row0 + (r >> 2) * 64 + ty * 4 + (r & 3);
         na[r] = row < rowsA ? normA[row] : T(0);
+        ai[r] = T(0);
+        if constexpr (CENTER) { ai[r] = row < rowsA ? qa - qv[row] : T(0); }
     }
 
     const int nk = (int) (K / BK);
@@ -207,9 +211,12 @@ __global__ void __launch_bounds__(256)
             const bool valid = col < rowsB;
             const T vj = valid ? v[col] : T(0);
             const T nb = valid ? normB[col] : T(0);
+            T qj = T(0);
+            if constexpr (CENTER) { qj = valid ? qv[col] : T(0); }
 #pragma unroll
             for (int r = 0; r < TM; ++r) {
-                const T kv = kernel_value<T, KERNEL>(acc[r][cc], na[r], nb, degree, gamma, coef0);
+                T kv = kernel_value<T, KERNEL>(acc[r][cc], na[r], nb, degree, gamma, coef0);
+                if constexpr (CENTER) { kv += ai[r] - qj; }
                 rowsum[r] = valid ? fma(kv, vj, rowsum[r]) : rowsum[r];
             }
         }
@@ -235,7 +242,7 @@ struct simt_tile {
 // Launch: returns the number of column splits written to P ([splits][ldP]).
 template <typename T>
 int kmv_simt_launch(ctx &c, const T *A, const T *normA, int64_t rowsA, int64_t ldA, const T *B, const T *normB, int64_t rowsB, int64_t ldB,
-                    const T *v, T *P, int64_t ldP, int max_splits) {
+                    const T *v, T *P, int64_t ldP, int max_splits, const T *qv, T qa) {
     constexpr int TM = simt_tile<T>::TM, TN = simt_tile<T>::TN;
     constexpr int BM = 16 * TM, BN = 16 * TN;
     const int64_t row_tiles = (rowsA + BM - 1) / BM;
@@ -248,8 +255,15 @@ int kmv_simt_launch(ctx &c, const T *A, const T *normA, int64_t rowsA, int64_t l
     const int64_t K = ldA < ldB ? ldA : ldB;
     const dim3 grid((unsigned) row_tiles, (unsigned) splits);
 #define B200_LAUNCH_KMV(KN)                                                                                                              \
-    k_kmv_tile<T, KN, TM, TN><<<grid, 256, 0, c.stream>>>(A, normA, rowsA, ldA, B, normB, rowsB, ldB, K, v, c.degree, (T) c.gamma,       \
-                                                           (T) c.coef0, P, ldP, col_tiles)
+    do {                                                                                                                                 \
+        if (qv != nullptr) {                                                                                                             \
+            k_kmv_tile<T, KN, TM, TN, true><<<grid, 256, 0, c.stream>>>(A, normA, rowsA, ldA, B, normB, rowsB, ldB, K, v, c.degree,      \
+                                                                         (T) c.gamma, (T) c.coef0, qv, qa, P, ldP, col_tiles);           \
+        } else {                                                                                                                         \
+            k_kmv_tile<T, KN, TM, TN, false><<<grid, 256, 0, c.stream>>>(A, normA, rowsA, ldA, B, normB, rowsB, ldB, K, v, c.degree,     \
+                                                                          (T) c.gamma, (T) c.coef0, qv, qa, P, ldP, col_tiles);          \
+        }                                                                                                                                \
+    } while (0)
     switch (c.kernel) {
         case B200SVM_LINEAR: B200_LAUNCH_KMV(B200SVM_LINEAR); break;
         case B200SVM_POLYNOMIAL: B200_LAUNCH_KMV(B200SVM_POLYNOMIAL); break;
@@ -261,9 +275,9 @@ int kmv_simt_launch(ctx &c, const T *A, const T *normA, int64_t rowsA, int64_t l
     return (int) splits;
 }
 template int kmv_simt_launch<float>(ctx &, const float *, const float *, int64_t, int64_t, const float *, const float *, int64_t, int64_t,
-                                    const float *, float *, int64_t, int);
+                                    const float *, float *, int64_t, int, const float *, float);
 template int kmv_simt_launch<double>(ctx &, const double *, const double *, int64_t, int64_t, const double *, const double *, int64_t, int64_t,
-                                     const double *, double *, int64_t, int);
+                                     const double *, double *, int64_t, int, const double *, double);
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Linear kernel: K d = X (X^T d) — two HBM-bound GEMVs instead of an O(m^2 F) pairwise pass.
@@ -341,6 +355,25 @@ template void xt_v<double>(ctx &, const double *, int64_t, int64_t, const double
 template void x_w<float>(ctx &, const float *, int64_t, int64_t, const float *, float, float *);
 template void x_w<double>(ctx &, const double *, int64_t, int64_t, const double *, double, double *);
 
+// Z[i] = X[i] - X[last]  (linear kernel: K_ij + K_nn - K_in - K_nj = <x_i - x_n, x_j - x_n>, so the reduced system is
+// Z Z^T + 1/C (1 1^T + I) — no cancellation of large terms)
+template <typename T>
+__global__ void __launch_bounds__(256) k_center_rows(const T *__restrict__ X, int64_t rows, int64_t ld, const T *__restrict__ xlast,
+                                                     T *__restrict__ Z) {
+    const int64_t total = rows * ld;
+    for (int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t) gridDim.x * blockDim.x) {
+        Z[e] = X[e] - xlast[e % ld];
+    }
+}
+template <typename T>
+void center_rows(ctx &c, const T *X, int64_t rows, int64_t ld, const T *xlast, T *Z) {
+    k_center_rows<T><<<8 * NUM_SMS, 256, 0, c.stream>>>(X, rows, ld, xlast, Z);
+    count_launch(c);
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+template void center_rows<float>(ctx &, const float *, int64_t, int64_t, const float *, float *);
+template void center_rows<double>(ctx &, const double *, int64_t, int64_t, const double *, double *);
+
 template <typename T>
 void update_w(ctx &c, const T *alpha_dev, T *w_dev) {
     xt_v<T>(c, c.X.as<T>(), c.n, c.ldx, alpha_dev, w_dev);
@@ -374,7 +407,7 @@ void predict_dense(ctx &c, const T *alpha_dev, T bias, const T *pts_dev, int64_t
     const int64_t ldP = (P + 63) / 64 * 64;
     c.P.reserve((size_t) (MAXS * ldP) * sizeof(T));
     const int splits = kmv_simt_launch<T>(c, pts_dev, c.pts_norms.as<T>(), P, ld, c.X.as<T>(), c.norms.as<T>(), c.n, c.ldx, alpha_dev,
-                                          c.P.as<T>(), ldP, MAXS);
+                                          c.P.as<T>(), ldP, MAXS, static_cast<const T *>(nullptr), T(0));
     k_sum_splits_bias<T><<<(unsigned) ((P + 255) / 256), 256, 0, c.stream>>>(c.P.as<T>(), ldP, splits, P, bias, out_dev);
     count_launch(c);
     B200_CUDA_CHECK(cudaGetLastError());
