@@ -116,7 +116,7 @@ class Handle:
 
     def _chk(self, rc):
         if rc != 0:
-            raise B200Error(rc, self.L.b200svm_last_error(self.h).decode())
+            raise B200Error(rc, self.L.b200svm_last_error(self.h if self._created else None).decode())
 
     def close(self):
         if self._created:
@@ -163,6 +163,8 @@ class Handle:
         self._chk(self.L.b200svm_set_stream(self.h, C.c_void_p(stream_ptr)))
 
     def set_option(self, opt, value):
+        if not self._created:
+            raise B200Error(1, "handle not created yet: pass gamma to Handle(...) or call set_data first")
         self._chk(self.L.b200svm_set_option(self.h, opt, int(value)))
 
     # -- generate_q ----------------------------------------------------------------------------------------------

@@ -12,7 +12,11 @@ namespace {
 thread_local std::string g_create_error;
 
 template <typename Fn>
-int guarded(ctx *c, Fn &&fn) {
+int guarded(ctx *c, Fn &&fn, bool need_handle = true) {
+    if (c == nullptr && need_handle) {
+        g_create_error = "null b200svm_handle";
+        return B200SVM_ERR_INVALID;
+    }
     try {
         if (c != nullptr) { B200_CUDA_CHECK(cudaSetDevice(c->device)); }  // callers may hop threads (src/plssvm/csvm.cpp:230-235)
         fn();
@@ -98,7 +102,7 @@ int b200svm_create(b200svm_handle *h, int dtype, int kernel, int degree, double 
     }
     *h = nullptr;
     ctx *c = nullptr;
-    const int rc = guarded(nullptr, [&]() {
+    const auto create_body = [&]() {
         B200_REQUIRE(dtype == B200SVM_F32 || dtype == B200SVM_F64, "dtype must be B200SVM_F32 or B200SVM_F64");
         B200_REQUIRE(kernel >= B200SVM_LINEAR && kernel <= B200SVM_RBF, "unknown kernel type");
         B200_REQUIRE(cost != 0.0, "cost must not be 0");
@@ -133,7 +137,8 @@ int b200svm_create(b200svm_handle *h, int dtype, int kernel, int degree, double 
         B200_CUDA_CHECK(cudaMemsetAsync(c->scal.p, 0, c->scal.bytes, c->stream));
         B200_CUDA_CHECK(cudaMemsetAsync(c->counters.p, 0, c->counters.bytes, c->stream));
         B200_CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    });
+    };
+    const int rc = guarded(nullptr, create_body, false);
     if (rc != B200SVM_OK) {
         delete c;
         return rc;

@@ -120,7 +120,8 @@ def test_learn_synth_golden(golden, case, kernel, eps):
         elif dt == np.float64:
             # tight epsilon: the reference itself is not reproducible across thread counts
             assert abs(it - it_ref) <= max(1, abs(it_ref - it_ref8))
-            assert nrm_rel(g[key + "/alpha"], alpha) < max(1e-8, 20 * spread)
+            # CG stops at |r| <= eps |r0|: two rounding-different runs may legitimately differ by O(cond * eps)
+            assert nrm_rel(g[key + "/alpha"], alpha) < max(1e-8, 20 * spread, 100 * eps)
         else:
             # float: compare with the f64 truth; must be at least as close as the reference's float result (x2 slack)
             truth = g[f"{case}/f64/{kernel}/{eps:g}/alpha"]
@@ -140,7 +141,8 @@ def test_solver_cg_direct_and_refresh(kernel, dt):
     q = port.generate_q(X, kernel)
     qa = port.kernel_function(X[-1], X[-1], kernel, gamma=1.0 / F) + 1.0
     b = (y[:-1] - y[-1]).astype(dt)
-    imax = 60
+    # float: the recursively updated residual underflows to 0 after ~18 iterations (oracle and GPU alike) -> stay below that
+    imax = 60 if dt == np.float64 else 8
     a_o, it_o, delta_o = port.solver_cg(X, b, q, qa, imax, 0.0, kernel, use_rows=True)
     with capi.Handle(dt, kernel) as h:
         h.set_data(X)
@@ -149,7 +151,7 @@ def test_solver_cg_direct_and_refresh(kernel, dt):
     if dt == np.float64:
         assert nrm_rel(a_o, a) < 1e-6, nrm_rel(a_o, a)  # 60 CG steps amplify rounding-order differences
     else:
-        assert nrm_rel(a_o, a) < 0.2
+        assert nrm_rel(a_o, a) < 1e-3
 
 
 @pytest.mark.parametrize("kernel", KERNELS)
@@ -185,6 +187,12 @@ def test_predict_edge_cases():
         assert h.predict_label(np.array([0.0, 1e-300, -0.0]))[0] == -1.0
 
 
+def test_null_handle_is_rejected():
+    L = capi.load()
+    assert L.b200svm_set_option(None, capi.OPT_MATVEC_PATH, 1) == 1
+    assert b"null" in L.b200svm_last_error(None)
+
+
 def test_errors_are_loud():
     with capi.Handle(np.float64, "linear", gamma=1.0) as h:
         with pytest.raises(capi.B200Error, match="no data set"):
@@ -193,3 +201,45 @@ def test_errors_are_loud():
         with pytest.raises(capi.B200Error, match="Data set is empty"):
             h.L.b200svm_set_data_dense.restype = int
             h._chk(h.L.b200svm_set_data_dense(h.h, np.zeros(1).ctypes.data, 0, 4, 4))
+
+
+@pytest.mark.parametrize("kernel", ["rbf", "polynomial"])
+@pytest.mark.parametrize("shape", [(2, 3), (130, 64), (257, 33), (513, 100), (1000, 200), (2049, 1024)])
+def test_tcgen05_path_vs_simt_and_oracle(kernel, shape):
+    """The tcgen05/TMA path (fp16x2-split Gram tiles, symmetric) against the SIMT fp32 path and the f64 oracle on ragged sizes
+    (rows not a multiple of the 128x256 tile, features not a multiple of the 64-wide K block)."""
+    n, F = shape
+    X, _ = datagen.make_dense(n, F, seed=n + F, problem="blobs", dtype=np.float32)
+    d = np.random.default_rng(1).uniform(-1, 2, n - 1).astype(np.float32)
+    coef0 = 0.5 if kernel == "polynomial" else 0.0
+    outs = {}
+    for path in (capi.PATH_SIMT, capi.PATH_TC):
+        with capi.Handle(np.float32, kernel, 3, 1.0 / F, coef0, 1.0) as h:
+            h.set_option(capi.OPT_MATVEC_PATH, path)
+            h.set_data(X)
+            q = h.generate_q()
+            h.set_q(q, h.kxx_last() + 1.0)
+            outs[path] = h.matvec(d, 1.0)
+            assert h.stats().matvec_path == path
+            outs[(path, "neg")] = h.matvec(d, -1.0, ret=np.ones(n - 1, np.float32))
+    X64 = X.astype(np.float64)
+    q64 = port.generate_q(X64, kernel, 3, 1.0 / F, coef0)
+    qa64 = port.kernel_function(X64[-1], X64[-1], kernel, 3, 1.0 / F, coef0) + 1.0
+    want = port.matvec(X64, q64, d.astype(np.float64), qa64, 1.0, kernel, 3, 1.0 / F, coef0, 1.0, rows=(0, n - 1))
+    assert nrm_rel(want, outs[capi.PATH_SIMT]) < 2e-6
+    assert nrm_rel(want, outs[capi.PATH_TC]) < 5e-6, nrm_rel(want, outs[capi.PATH_TC])
+    assert nrm_rel(1.0 - want, outs[(capi.PATH_TC, "neg")]) < 5e-6
+
+
+def test_tcgen05_path_is_deterministic():
+    n, F = 1500, 96
+    X, _ = datagen.make_dense(n, F, seed=3, dtype=np.float32)
+    d = np.random.default_rng(2).standard_normal(n - 1).astype(np.float32)
+    with capi.Handle(np.float32, "rbf", gamma=1.0 / F) as h:
+        h.set_option(capi.OPT_MATVEC_PATH, capi.PATH_TC)
+        h.set_data(X)
+        q = h.generate_q()
+        h.set_q(q, h.kxx_last() + 1.0)
+        a = h.matvec(d)
+        for _ in range(3):
+            assert np.array_equal(a, h.matvec(d))
