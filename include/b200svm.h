@@ -104,6 +104,11 @@ int b200svm_predict_csr(b200svm_handle h, const void *alpha, double rho, const i
  * (src/plssvm/backends/gpu_csvm.cpp:365-386). */
 int b200svm_comm_unique_id(void *id128);
 int b200svm_comm_init(b200svm_handle h, const void *id128, int rank, int world);
+/* Host-only helpers (no device needed): the ownership rules the ranks use, exposed so that the sharding can be tested on
+ * CPU-only machines.  Rows [lo, hi) of the m rows of the implicit matrix (full-row paths: SIMT, sparse), and the slice
+ * [first, first + count) of the `total` lower-triangle 128 x 256 tiles of an n-point problem (tcgen05 path). */
+int b200svm_partition_rows(int64_t m, int rank, int world, int64_t *lo, int64_t *hi);
+int b200svm_partition_tiles(int64_t n, int rank, int world, int64_t *first, int64_t *count, int64_t *total);
 
 /* Tuning / introspection. */
 #define B200SVM_OPT_MATVEC_PATH 1 /* 0 = auto, 1 = SIMT full-square, 2 = tcgen05 symmetric tiles (f32 dense only) */
@@ -117,6 +122,8 @@ typedef struct b200svm_stats {
     int64_t matvec_path;      /* path used by the last matvec (B200SVM_OPT_MATVEC_PATH values)    */
     int64_t h2d_bytes;        /* host->device bytes copied                                        */
     int64_t d2h_bytes;        /* device->host bytes copied                                        */
+    int64_t collectives;      /* NCCL collectives enqueued                                        */
+    int64_t collective_bytes; /* payload bytes of those collectives (per rank)                    */
 } b200svm_stats;
 int b200svm_get_stats(b200svm_handle h, b200svm_stats *out);
 int b200svm_reset_stats(b200svm_handle h);

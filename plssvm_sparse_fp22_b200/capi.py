@@ -25,7 +25,7 @@ SYMBOLS = [
     "b200svm_set_data_dense", "b200svm_set_data_csr", "b200svm_generate_q", "b200svm_get_kxx_last", "b200svm_set_q",
     "b200svm_matvec", "b200svm_cg_solve", "b200svm_learn", "b200svm_update_w", "b200svm_predict_dense",
     "b200svm_predict_csr", "b200svm_comm_unique_id", "b200svm_comm_init", "b200svm_set_option", "b200svm_get_stats",
-    "b200svm_reset_stats",
+    "b200svm_reset_stats", "b200svm_partition_rows", "b200svm_partition_tiles",
 ]
 
 
@@ -37,6 +37,8 @@ class Stats(C.Structure):
         ("matvec_path", C.c_int64),
         ("h2d_bytes", C.c_int64),
         ("d2h_bytes", C.c_int64),
+        ("collectives", C.c_int64),
+        ("collective_bytes", C.c_int64),
     ]
 
 
@@ -82,6 +84,8 @@ def load():
     L.b200svm_set_option.argtypes = [vp, i, i64]
     L.b200svm_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.b200svm_reset_stats.argtypes = [vp]
+    L.b200svm_partition_rows.argtypes = [i64, i, i, pi64, pi64]
+    L.b200svm_partition_tiles.argtypes = [i64, i, i, pi64, pi64, pi64]
     _LIB = L
     return L
 
@@ -256,6 +260,22 @@ class Handle:
 
     def reset_stats(self):
         self._chk(self.L.b200svm_reset_stats(self.h))
+
+
+def partition_rows(m: int, rank: int, world: int):
+    lo, hi = C.c_int64(0), C.c_int64(0)
+    rc = load().b200svm_partition_rows(m, rank, world, C.byref(lo), C.byref(hi))
+    if rc != 0:
+        raise B200Error(rc, "invalid partition request")
+    return lo.value, hi.value
+
+
+def partition_tiles(n: int, rank: int, world: int):
+    first, count, total = C.c_int64(0), C.c_int64(0), C.c_int64(0)
+    rc = load().b200svm_partition_tiles(n, rank, world, C.byref(first), C.byref(count), C.byref(total))
+    if rc != 0:
+        raise B200Error(rc, "invalid partition request")
+    return first.value, count.value, total.value
 
 
 def comm_unique_id() -> bytes:

@@ -129,6 +129,19 @@ __global__ void __launch_bounds__(VEC_THREADS) k_cg_direction(T *__restrict__ d,
     }
 }
 
+// Multi-GPU: fold this rank's column-split partials into one full-length vector, zero outside its row range [lo, hi)
+// (the vector is then summed over ranks with one ncclAllReduce):  P[0][i] = lo <= i < hi ? sum_s P[s][i] : 0
+template <typename T>
+__global__ void __launch_bounds__(VEC_THREADS) k_fold_splits(T *__restrict__ P, int64_t ldP, int splits, int64_t m, int64_t lo, int64_t hi) {
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (int64_t) gridDim.x * blockDim.x) {
+        T s = T(0);
+        if (i >= lo && i < hi) {
+            for (int k = 0; k < splits; ++k) { s += P[(int64_t) k * ldP + i]; }
+        }
+        P[i] = s;
+    }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(VEC_THREADS) k_fill(T *__restrict__ v, int64_t m, T value) {
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (int64_t) gridDim.x * blockDim.x) { v[i] = value; }
@@ -198,13 +211,27 @@ kd_result kernel_times_vector(ctx &c, const T *d) {
         if (use_tc) {
             if constexpr (sizeof(T) == 4) {
                 c.P.reserve((size_t) ldP * sizeof(T));
-                tc_kernel_matvec(c, reinterpret_cast<const float *>(d), c.P.as<float>());
+                tc_kernel_matvec(c, reinterpret_cast<const float *>(d), c.P.as<float>());  // partial over this rank's tiles
             }
+            comm_allreduce_sum(c, c.P.p, m);
             c.stats.matvec_path = 2;
         } else {
+            // full rows [lo, hi) of the implicit matrix on this rank (all rows when world == 1)
+            int64_t lo = 0, hi = m;
+            partition_rows(m, c.rank, c.world, &lo, &hi);
             c.P.reserve((size_t) (MAXS * ldP) * sizeof(T));
-            res.splits = kmv_simt_launch<T>(c, c.X.as<T>(), c.norms.as<T>(), m, c.ldx, c.X.as<T>(), c.norms.as<T>(), m, c.ldx, d, c.P.as<T>(),
-                                            ldP, MAXS, c.q.as<T>(), (T) c.QA_cost);
+            res.splits = 0;
+            if (hi > lo) {
+                res.splits = kmv_simt_launch<T>(c, c.X.as<T>() + lo * c.ldx, c.norms.as<T>() + lo, hi - lo, c.ldx, c.X.as<T>(), c.norms.as<T>(), m,
+                                                c.ldx, d, c.P.as<T>() + lo, ldP, MAXS, c.q.as<T>() + lo, c.q.as<T>(), (T) c.QA_cost);
+            }
+            if (c.world > 1) {
+                k_fold_splits<T><<<vec_grid(m), VEC_THREADS, 0, c.stream>>>(c.P.as<T>(), ldP, res.splits, m, lo, hi);
+                count_launch(c);
+                B200_CUDA_CHECK(cudaGetLastError());
+                comm_allreduce_sum(c, c.P.p, m);
+                res.splits = 1;
+            }
             c.stats.matvec_path = 1;
         }
     }

@@ -589,3 +589,15 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out) {
 }
 
 }  // namespace b200
+
+extern "C" int b200svm_partition_tiles(int64_t n, int rank, int world, int64_t *first, int64_t *count, int64_t *total) {
+    if (first == nullptr || count == nullptr || total == nullptr || world < 1 || rank < 0 || rank >= world || n < 1) { return B200SVM_ERR_INVALID; }
+    const int64_t n_pad = (n + b200::tc::BN - 1) / b200::tc::BN * b200::tc::BN;
+    const int T_r = (int) (n_pad / b200::tc::BM), T_c = (int) (n_pad / b200::tc::BN);
+    const size_t all = b200::build_tiles(T_r, T_c, 0, 1).size();
+    const size_t lo = all * (size_t) rank / (size_t) world, hi = all * (size_t) (rank + 1) / (size_t) world;
+    *first = (int64_t) lo;
+    *count = (int64_t) (hi - lo);
+    *total = (int64_t) all;
+    return B200SVM_OK;
+}

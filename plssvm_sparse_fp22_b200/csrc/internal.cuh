@@ -164,8 +164,9 @@ template <typename T> void kernel_matvec(ctx &c, const T *d, T *out_Kd);        
 template <typename T> void apply_abar(ctx &c, const T *d, T add, T *ret);                   // ret += add * Abar d  (device vectors)
 template <typename T> int64_t cg_solve(ctx &c, const T *b_dev, int64_t imax, T eps, T *alpha_dev, double *delta_out);
 template <typename T> void update_w(ctx &c, const T *alpha_dev, T *w_dev);
+// qrow / qcol: q indexed like the rows of A / rows of B (both nullptr = no centring)
 template <typename T> int kmv_simt_launch(ctx &c, const T *A, const T *normA, int64_t rowsA, int64_t ldA, const T *B, const T *normB, int64_t rowsB,
-                                          int64_t ldB, const T *v, T *P, int64_t ldP, int max_splits, const T *qv, T qa);
+                                          int64_t ldB, const T *v, T *P, int64_t ldP, int max_splits, const T *qrow, const T *qcol, T qa);
 template <typename T> void center_rows(ctx &c, const T *X, int64_t rows, int64_t ld, const T *xlast, T *Z);
 template <typename T> void xt_v(ctx &c, const T *X, int64_t rows, int64_t ld, const T *v, T *w);
 template <typename T> void x_w(ctx &c, const T *X, int64_t rows, int64_t ld, const T *w, T bias, T *out);
@@ -179,6 +180,7 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out_Kd);    // out = K d vi
 // multi-GPU (comm.cu)
 void comm_destroy(ctx &c);
 void comm_allreduce_sum(ctx &c, void *buf, int64_t count);  // in place, real type of the handle
+void partition_rows(int64_t m, int rank, int world, int64_t *lo, int64_t *hi);
 
 inline void count_launch(ctx &c, int k = 1) { c.stats.kernel_launches += k; }
 void drain_matvec_events(ctx &c);   // call after a stream synchronisation

@@ -103,7 +103,7 @@ template <typename T, int KERNEL, int TM, int TN, bool CENTER>
 __global__ void __launch_bounds__(256)
     k_kmv_tile(const T *__restrict__ A, const T *__restrict__ normA, int64_t rowsA, int64_t ldA, const T *__restrict__ B,
                const T *__restrict__ normB, int64_t rowsB, int64_t ldB, int64_t K, const T *__restrict__ v, int degree, T gamma, T coef0,
-               const T *__restrict__ qv, T qa, T *__restrict__ P, int64_t ldP, int col_tiles) {
+               const T *__restrict__ qrow, const T *__restrict__ qcol, T qa, T *__restrict__ P, int64_t ldP, int col_tiles) {
     constexpr int BM = 16 * TM, BN = 16 * TN;
     using V = typename vec16<T>::type;
     constexpr int VN = vec16<T>::N;
@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(256)
         const int64_t row = row0 + (r >> 2) * 64 + ty * 4 + (r & 3);
         na[r] = row < rowsA ? normA[row] : T(0);
         ai[r] = T(0);
-        if constexpr (CENTER) { ai[r] = row < rowsA ? qa - qv[row] : T(0); }
+        if constexpr (CENTER) { ai[r] = row < rowsA ? qa - qrow[row] : T(0); }
     }
 
     const int nk = (int) (K / BK);
@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(256)
             const T vj = valid ? v[col] : T(0);
             const T nb = valid ? normB[col] : T(0);
             T qj = T(0);
-            if constexpr (CENTER) { qj = valid ? qv[col] : T(0); }
+            if constexpr (CENTER) { qj = valid ? qcol[col] : T(0); }
 #pragma unroll
             for (int r = 0; r < TM; ++r) {
                 T kv = kernel_value<T, KERNEL>(acc[r][cc], na[r], nb, degree, gamma, coef0);
@@ -242,7 +242,7 @@ struct simt_tile {
 // Launch: returns the number of column splits written to P ([splits][ldP]).
 template <typename T>
 int kmv_simt_launch(ctx &c, const T *A, const T *normA, int64_t rowsA, int64_t ldA, const T *B, const T *normB, int64_t rowsB, int64_t ldB,
-                    const T *v, T *P, int64_t ldP, int max_splits, const T *qv, T qa) {
+                    const T *v, T *P, int64_t ldP, int max_splits, const T *qrow, const T *qcol, T qa) {
     constexpr int TM = simt_tile<T>::TM, TN = simt_tile<T>::TN;
     constexpr int BM = 16 * TM, BN = 16 * TN;
     const int64_t row_tiles = (rowsA + BM - 1) / BM;
@@ -256,12 +256,12 @@ int kmv_simt_launch(ctx &c, const T *A, const T *normA, int64_t rowsA, int64_t l
     const dim3 grid((unsigned) row_tiles, (unsigned) splits);
 #define B200_LAUNCH_KMV(KN)                                                                                                              \
     do {                                                                                                                                 \
-        if (qv != nullptr) {                                                                                                             \
+        if (qrow != nullptr) {                                                                                                           \
             k_kmv_tile<T, KN, TM, TN, true><<<grid, 256, 0, c.stream>>>(A, normA, rowsA, ldA, B, normB, rowsB, ldB, K, v, c.degree,      \
-                                                                         (T) c.gamma, (T) c.coef0, qv, qa, P, ldP, col_tiles);           \
+                                                                         (T) c.gamma, (T) c.coef0, qrow, qcol, qa, P, ldP, col_tiles);   \
         } else {                                                                                                                         \
             k_kmv_tile<T, KN, TM, TN, false><<<grid, 256, 0, c.stream>>>(A, normA, rowsA, ldA, B, normB, rowsB, ldB, K, v, c.degree,     \
-                                                                          (T) c.gamma, (T) c.coef0, qv, qa, P, ldP, col_tiles);          \
+                                                                          (T) c.gamma, (T) c.coef0, qrow, qcol, qa, P, ldP, col_tiles);  \
         }                                                                                                                                \
     } while (0)
     switch (c.kernel) {
@@ -275,9 +275,9 @@ int kmv_simt_launch(ctx &c, const T *A, const T *normA, int64_t rowsA, int64_t l
     return (int) splits;
 }
 template int kmv_simt_launch<float>(ctx &, const float *, const float *, int64_t, int64_t, const float *, const float *, int64_t, int64_t,
-                                    const float *, float *, int64_t, int, const float *, float);
+                                    const float *, float *, int64_t, int, const float *, const float *, float);
 template int kmv_simt_launch<double>(ctx &, const double *, const double *, int64_t, int64_t, const double *, const double *, int64_t, int64_t,
-                                     const double *, double *, int64_t, int, const double *, double);
+                                     const double *, double *, int64_t, int, const double *, const double *, double);
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Linear kernel: K d = X (X^T d) — two HBM-bound GEMVs instead of an O(m^2 F) pairwise pass.
@@ -407,7 +407,7 @@ void predict_dense(ctx &c, const T *alpha_dev, T bias, const T *pts_dev, int64_t
     const int64_t ldP = (P + 63) / 64 * 64;
     c.P.reserve((size_t) (MAXS * ldP) * sizeof(T));
     const int splits = kmv_simt_launch<T>(c, pts_dev, c.pts_norms.as<T>(), P, ld, c.X.as<T>(), c.norms.as<T>(), c.n, c.ldx, alpha_dev,
-                                          c.P.as<T>(), ldP, MAXS, static_cast<const T *>(nullptr), T(0));
+                                          c.P.as<T>(), ldP, MAXS, static_cast<const T *>(nullptr), static_cast<const T *>(nullptr), T(0));
     k_sum_splits_bias<T><<<(unsigned) ((P + 255) / 256), 256, 0, c.stream>>>(c.P.as<T>(), ldP, splits, P, bias, out_dev);
     count_launch(c);
     B200_CUDA_CHECK(cudaGetLastError());

@@ -1,0 +1,66 @@
+"""Multi-GPU parity check, one process per GPU:  python -m torch.distributed.run --nproc-per-node N tests/multi_gpu_check.py
+
+Every rank trains the same problems through the C ABI with the NCCL communicator initialised (rows / tiles of the implicit
+matrix partitioned over the ranks, one allreduce per matvec) and compares with the oracle: identical CG iteration count,
+alpha within tolerance, and bit-identical alpha across ranks.  Exit code 0 = all green.
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+
+    from oracle import port
+    from plssvm_sparse_fp22_b200 import capi, datagen
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
+    if rank == 0:
+        idbuf.copy_(torch.frombuffer(bytearray(capi.comm_unique_id()), dtype=torch.uint8))
+    dist.broadcast(idbuf, 0)
+    uid = bytes(idbuf.cpu().numpy().tobytes())
+    ok = True
+    cases = [("rbf", np.float32, capi.PATH_TC, 1500, 96), ("polynomial", np.float32, capi.PATH_TC, 1100, 70),
+             ("rbf", np.float32, capi.PATH_SIMT, 900, 64), ("rbf", np.float64, capi.PATH_AUTO, 1200, 80),
+             ("polynomial", np.float64, capi.PATH_AUTO, 700, 33), ("linear", np.float64, capi.PATH_AUTO, 1000, 50)]
+    for kernel, dt, path, n, F in cases:
+        X, y = datagen.make_dense(n, F, seed=n, problem="planes", dtype=dt)
+        with capi.Handle(dt, kernel, gamma=1.0 / F, device=local) as h:
+            if path:
+                h.set_option(capi.OPT_MATVEC_PATH, path)
+            h.comm_init(uid, rank, world)
+            h.set_data(X)
+            alpha, rho, it = h.learn(y, eps=1e-3)
+            st = h.stats()
+        a_o, rho_o, it_o = port.learn(X.astype(np.float64), y.astype(np.float64), kernel, eps=1e-3, use_rows=True)
+        err = float(np.linalg.norm(alpha.astype(np.float64) - a_o) / np.linalg.norm(a_o))
+        tol = 1e-10 if dt == np.float64 else 1e-3
+        # bit-identical across ranks
+        t = torch.from_numpy(alpha.astype(np.float64)).cuda()
+        ref = t.clone()
+        dist.broadcast(ref, 0)
+        same = bool(torch.equal(t, ref))
+        good = it == it_o and err < tol and same and (world == 1 or st.collectives > 0 or kernel == "linear")
+        ok &= good
+        if rank == 0:
+            print(f"[{world} ranks] {kernel:10s} {np.dtype(dt).name} path={st.matvec_path} iters={it}/{it_o} alpha_relerr={err:.2e} "
+                  f"identical_across_ranks={same} collectives={st.collectives} -> {'OK' if good else 'FAIL'}", flush=True)
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    dist.destroy_process_group()
+    sys.exit(0 if int(flag.item()) == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -247,3 +247,19 @@ def test_tcgen05_path_is_deterministic():
         a = h.matvec(d)
         for _ in range(3):
             assert np.array_equal(a, h.matvec(d))
+
+
+def test_multi_gpu_row_and_tile_partition():
+    """N >= 2 GPUs only (skipped on a 1-GPU box): tests/multi_gpu_check.py under torchrun — NCCL allreduce of the per-rank partial
+    K d, identical iteration counts and bit-identical alpha on every rank."""
+    import subprocess
+    import sys
+    import torch
+    ngpu = torch.cuda.device_count()
+    if ngpu < 2:
+        pytest.skip("needs >= 2 GPUs")
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={min(ngpu, 8)}", "--master-addr", "127.0.0.1",
+                        "--master-port", "29541", os.path.join(root, "tests", "multi_gpu_check.py")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
