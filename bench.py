@@ -260,7 +260,7 @@ def run_b200_arm(a):
 
     if rank == 0:
         peaks, peak_kind = measured_peaks()
-        flops = alg_flops_per_matvec(n, F)
+        flops = alg_flops_per_matvec(n, F) / world  # per launch on ONE GPU: the tile list is split evenly over the ranks
         achieved = flops / (matvec_ms * 1e-3) / 1e12 if matvec_ms > 0 else 0.0
         # the kernel is timed inside a multi-second solve -> sustained tensor figure
         peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops")))
@@ -271,7 +271,7 @@ def run_b200_arm(a):
             "metric": METRIC, "value": K / (t_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(W, 3),
             "ms_per_step": t_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": a.dtype, "data": "synthetic", "config": workload_config(a),
-            "matvec_gflops": flops / (matvec_ms * 1e-3) / 1e9 if matvec_ms > 0 else None,
+            "matvec_gflops": world * flops / (matvec_ms * 1e-3) / 1e9 if matvec_ms > 0 else None,
             "clocks": sampler.summary(),
             "e2e": {"value": K / (t_e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": st2.h2d_bytes / K, "d2h_bytes_per_step": st2.d2h_bytes / K,
                     "ms_total": t_e2e_ms},

@@ -25,11 +25,15 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
-    if rank == 0:
-        idbuf.copy_(torch.frombuffer(bytearray(capi.comm_unique_id()), dtype=torch.uint8))
-    dist.broadcast(idbuf, 0)
-    uid = bytes(idbuf.cpu().numpy().tobytes())
+
+    def fresh_uid():
+        # an ncclUniqueId is single-use: one per communicator, created on rank 0 and broadcast
+        idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idbuf.copy_(torch.frombuffer(bytearray(capi.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idbuf, 0)
+        return bytes(idbuf.cpu().numpy().tobytes())
+
     ok = True
     cases = [("rbf", np.float32, capi.PATH_TC, 1500, 96), ("polynomial", np.float32, capi.PATH_TC, 1100, 70),
              ("rbf", np.float32, capi.PATH_SIMT, 900, 64), ("rbf", np.float64, capi.PATH_AUTO, 1200, 80),
@@ -39,7 +43,7 @@ def main():
         with capi.Handle(dt, kernel, gamma=1.0 / F, device=local) as h:
             if path:
                 h.set_option(capi.OPT_MATVEC_PATH, path)
-            h.comm_init(uid, rank, world)
+            h.comm_init(fresh_uid(), rank, world)
             h.set_data(X)
             alpha, rho, it = h.learn(y, eps=1e-3)
             st = h.stats()
