@@ -113,13 +113,14 @@ int b200svm_partition_tiles(int64_t n, int rank, int world, int64_t *first, int6
 /* Tuning / introspection. */
 #define B200SVM_OPT_MATVEC_PATH 1 /* 0 = auto, 1 = SIMT full-square, 2 = tcgen05 symmetric tiles (f32 dense only) */
 #define B200SVM_OPT_SYNC_EVERY 2  /* CG: host polls the convergence flag every k iterations (default 1)            */
+#define B200SVM_OPT_SPARSE_BLOCK 3 /* CSR paths: columns of the implicit matrix per block (power of two, 128..4096; set before set_data_csr) */
 int b200svm_set_option(b200svm_handle h, int option, int64_t value);
 
 typedef struct b200svm_stats {
     int64_t kernel_launches;  /* CUDA kernels launched by this handle since creation / last reset */
     int64_t matvecs;          /* applications of Abar                                              */
     double matvec_ms;         /* accumulated device time of the O(m^2) kernel (CUDA events)       */
-    int64_t matvec_path;      /* path used by the last matvec (B200SVM_OPT_MATVEC_PATH values)    */
+    int64_t matvec_path;      /* path used by the last matvec: 1 SIMT, 2 tcgen05, 3 dense GEMV pair, 4 sparse */
     int64_t h2d_bytes;        /* host->device bytes copied                                        */
     int64_t d2h_bytes;        /* device->host bytes copied                                        */
     int64_t collectives;      /* NCCL collectives enqueued                                        */

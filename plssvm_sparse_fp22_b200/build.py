@@ -19,7 +19,7 @@ SOURCES = ["api.cu", "cg.cu", "kernels_simt.cu", "gram_tc.cu", "sparse.cu", "com
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
-    "-Xcompiler", "-fPIC",
+    "-Xcompiler", "-fPIC,-fopenmp",
 ]
 
 
@@ -70,7 +70,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     with ThreadPoolExecutor(max_workers=min(8, max(1, len(todo)))) as ex:
         list(ex.map(compile_one, todo))
-    cmd = [nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB, *[_obj(s) for s in sources()], "-ldl"]
+    cmd = [nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB, *[_obj(s) for s in sources()], "-ldl", "-lgomp"]
     if verbose:
         print(" ".join(cmd), file=sys.stderr)
     subprocess.check_call(cmd)

@@ -71,7 +71,11 @@ void do_generate_q(ctx &c, void *q_out) {
     require_data(c);
     B200_REQUIRE(c.n >= 2, "at least two data points are required");
     c.q.reserve((size_t) c.m() * sizeof(T));
-    generate_q<T>(c);
+    if (c.is_csr) {
+        sp_generate_q<T>(c);
+    } else {
+        generate_q<T>(c);
+    }
     c.has_q = true;
     if (q_out != nullptr) { d2h(c, q_out, c.q.p, (size_t) c.m() * sizeof(T)); }
     sync_stream(c);
@@ -154,6 +158,7 @@ int b200svm_destroy(b200svm_handle h) {
     cudaStreamSynchronize(c->stream);
     comm_destroy(*c);
     if (c->tc_opaque != nullptr && c->tc_opaque_free != nullptr) { c->tc_opaque_free(c->tc_opaque); }
+    if (c->sp_opaque != nullptr && c->sp_opaque_free != nullptr) { c->sp_opaque_free(c->sp_opaque); }
     for (auto &ev : c->ev) {
         if (ev != nullptr) { cudaEventDestroy(ev); }
     }
@@ -182,6 +187,10 @@ int b200svm_set_option(b200svm_handle h, int option, int64_t value) {
             case B200SVM_OPT_SYNC_EVERY:
                 B200_REQUIRE(value >= 1, "sync interval must be >= 1");
                 c->opt_sync_every = value;
+                break;
+            case B200SVM_OPT_SPARSE_BLOCK:
+                B200_REQUIRE(value == 0 || (value >= 128 && value <= 4096 && (value & (value - 1)) == 0), "sparse block width must be 0 or a power of two in [128, 4096]");
+                c->opt_sparse_block = value;
                 break;
             default: fail(B200SVM_ERR_INVALID, "unknown option");
         }
@@ -315,7 +324,11 @@ void do_learn(ctx &c, const void *y_host, double eps, void *alpha_out, double *r
     const T *y = static_cast<const T *>(y_host);
     // q = generate_q() ; QA_cost = k(x_n, x_n) + 1 / C   (csvm.cpp:232-243)
     c.q.reserve((size_t) m * sizeof(T));
-    generate_q<T>(c);
+    if (c.is_csr) {
+        sp_generate_q<T>(c);
+    } else {
+        generate_q<T>(c);
+    }
     c.has_q = true;
     // b = y[0..m) - y_n  (csvm.cpp:238-239)
     std::vector<T> b((size_t) m);
@@ -344,12 +357,15 @@ void do_learn(ctx &c, const void *y_host, double eps, void *alpha_out, double *r
 template <typename T>
 void do_update_w(ctx &c, const void *alpha, void *w_out) {
     require_data(c);
-    B200_REQUIRE(!c.is_csr, "update_w on CSR data is not available in this build");
     B200_REQUIRE(alpha != nullptr && w_out != nullptr, "No alphas provided for prediction!");
     c.alpha_dev.reserve((size_t) c.n * sizeof(T));
     c.wvec.reserve((size_t) c.ldx * sizeof(T));
     h2d(c, c.alpha_dev.p, alpha, (size_t) c.n * sizeof(T));
-    update_w<T>(c, c.alpha_dev.as<T>(), c.wvec.as<T>());
+    if (c.is_csr) {
+        sp_update_w<T>(c, c.alpha_dev.as<T>(), c.wvec.as<T>());
+    } else {
+        update_w<T>(c, c.alpha_dev.as<T>(), c.wvec.as<T>());
+    }
     d2h(c, w_out, c.wvec.p, (size_t) c.F * sizeof(T));
     sync_stream(c);
 }
@@ -357,7 +373,7 @@ void do_update_w(ctx &c, const void *alpha, void *w_out) {
 template <typename T>
 void do_predict_dense(ctx &c, const void *alpha, double rho, const void *points, int64_t P, int64_t ld, void *out) {
     require_data(c);
-    B200_REQUIRE(!c.is_csr, "dense predict against CSR support vectors is not available in this build");
+    B200_REQUIRE(!c.is_csr, "dense points against CSR support vectors: pass the points as CSR (b200svm_predict_csr)");
     B200_REQUIRE(alpha != nullptr, "No alphas provided for prediction!");  // src/plssvm/backends/OpenMP/csvm.cpp:207
     if (P == 0) { return; }                                                // csvm.cpp:198-200
     B200_REQUIRE(points != nullptr && out != nullptr, "null pointer");
@@ -401,14 +417,39 @@ int b200svm_predict_dense(b200svm_handle h, const void *alpha, double rho, const
     });
 }
 
-int b200svm_set_data_csr(b200svm_handle h, const int64_t *, const int32_t *, const void *, int64_t, int64_t, int64_t, int) {
+int b200svm_set_data_csr(b200svm_handle h, const int64_t *rowptr, const int32_t *colidx, const void *values, int64_t n, int64_t F, int64_t nnz,
+                         int value_format) {
     ctx *c = reinterpret_cast<ctx *>(h);
-    return guarded(c, [&]() { fail(B200SVM_ERR_INVALID, "CSR data path is not available in this build"); });
+    return guarded(c, [&]() {
+        B200_REQUIRE(rowptr != nullptr, "No data points provided!");        // src/plssvm/csvm.cpp:42
+        B200_REQUIRE(n > 0, "Data set is empty!");                           // src/plssvm/csvm.cpp:44
+        B200_REQUIRE(F > 0, "No features provided for the data points!");    // src/plssvm/csvm.cpp:48
+        c->has_data = false;
+        c->has_q = false;
+        c->has_split = false;
+        c->has_Z = false;
+        sp_set_data(*c, rowptr, colidx, values, n, F, nnz, value_format);
+        c->is_csr = true;
+        c->has_data = true;
+        sync_stream(*c);
+    });
 }
 
-int b200svm_predict_csr(b200svm_handle h, const void *, double, const int64_t *, const int32_t *, const void *, int64_t, int64_t, int, void *) {
+int b200svm_predict_csr(b200svm_handle h, const void *alpha, double rho, const int64_t *rowptr, const int32_t *colidx, const void *values, int64_t P,
+                        int64_t nnz, int value_format, void *out) {
     ctx *c = reinterpret_cast<ctx *>(h);
-    return guarded(c, [&]() { fail(B200SVM_ERR_INVALID, "CSR predict path is not available in this build"); });
+    return guarded(c, [&]() {
+        require_data(*c);
+        B200_REQUIRE(c->is_csr, "CSR predict needs CSR support vectors (b200svm_set_data_csr)");
+        B200_REQUIRE(alpha != nullptr, "No alphas provided for prediction!");  // src/plssvm/backends/OpenMP/csvm.cpp:207
+        if (P == 0) { return; }                                                // csvm.cpp:198-200
+        B200_REQUIRE(rowptr != nullptr && out != nullptr, "null pointer");
+        c->alpha_dev.reserve((size_t) c->n * c->esize());
+        h2d(*c, c->alpha_dev.p, alpha, (size_t) c->n * c->esize());
+        DISPATCH_T(c, sp_predict<T>(*c, c->alpha_dev.as<T>(), (T) (-rho), rowptr, colidx, values, P, nnz, value_format, static_cast<T *>(out)),
+                   sp_predict<T>(*c, c->alpha_dev.as<T>(), (T) (-rho), rowptr, colidx, values, P, nnz, value_format, static_cast<T *>(out)));
+        sync_stream(*c);
+    });
 }
 
 }  // extern "C"

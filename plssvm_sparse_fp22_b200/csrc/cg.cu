@@ -42,17 +42,23 @@ __global__ void __launch_bounds__(VEC_THREADS) k_sums2(const T *__restrict__ v, 
 // MODE 1: out += add * Abar d,     delta_old = delta, delta = out.out, beta = delta/old   (CG:  residual refresh, csvm.cpp:130-135)
 // MODE 2: out += add * Abar d,     delta = delta0 = out.out                               (CG:  initial residual, csvm.cpp:94-98)
 // MODE 3: out += add * Abar d                                                             (run_device_kernel test hook)
+// CENTER 0: P already holds the per-entry centred sums (dense tile kernels)
+//        1: dense linear Z Z^T form: + sum(d) / C
+//        2: P holds the un-centred K d (sparse paths): + (QA_cost - q_i) sum(d) - q.d   (the rank-1 part of svm_kernel.cpp:32)
 template <typename T, int MODE>
 __global__ void __launch_bounds__(VEC_THREADS) k_abar_finish(const T *__restrict__ P, int64_t ldP, int splits, const T *__restrict__ d,
-                                                             int64_t m, T inv_cost, int linear, T add,
+                                                             int64_t m, T inv_cost, int center, const T *__restrict__ q, T qa, T add,
                                                              T *__restrict__ out, T *__restrict__ scal, T *partials, unsigned int *ticket) {
     __shared__ T red[32];
-    const T rank1 = linear ? scal[S_SUM_D] * inv_cost : T(0);
+    const T sum_d = center != 0 ? scal[S_SUM_D] : T(0);
+    const T q_d = center == 2 ? scal[S_Q_D] : T(0);
+    const T rank1 = center == 1 ? sum_d * inv_cost : T(0);
     T acc[1] = { T(0) };
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (int64_t) gridDim.x * blockDim.x) {
         T kd = T(0);
         for (int s = 0; s < splits; ++s) { kd += P[(int64_t) s * ldP + i]; }
         const T di = d[i];
+        if (center == 2) { kd += fma(qa - q[i], sum_d, -q_d); }
         const T val = kd + rank1 + di * inv_cost;
         if constexpr (MODE == 0) {
             out[i] = val;
@@ -179,6 +185,7 @@ namespace {
 struct kd_result {
     int64_t ldP;
     int splits;
+    int center;  // see k_abar_finish
 };
 
 // K d for the reduced system (rows/cols 0..m-1) into c.P as `splits` partial vectors.
@@ -187,11 +194,17 @@ kd_result kernel_times_vector(ctx &c, const T *d) {
     const int64_t m = c.m();
     const int64_t ldP = (m + 255) / 256 * 256;
     constexpr int MAXS = 64;
-    kd_result res{ ldP, 1 };
+    kd_result res{ ldP, 1, 0 };
     const bool timed = c.ev_pending < 4;
     if (timed) { B200_CUDA_CHECK(cudaEventRecord(c.ev[2 * c.ev_pending], c.stream)); }
     if (c.is_csr) {
-        fail(B200SVM_ERR_INVALID, "CSR matvec is not available in this build");
+        // sparse rows: un-centred K d of this rank's rows, rank-1 centring in the O(m) epilogue
+        c.P.reserve((size_t) ldP * sizeof(T));
+        sums2<T>(c, d, S_SUM_D, S_Q_D);
+        sp_kernel_matvec<T>(c, d, c.P.as<T>());
+        comm_allreduce_sum(c, c.P.p, m);
+        res.center = 2;
+        c.stats.matvec_path = 4;
     } else if (c.kernel == B200SVM_LINEAR) {
         // centred linear kernel: sum_j (K_ij + K_nn - K_in - K_nj) d_j = Z (Z^T d), Z = X - 1 x_n^T : two GEMVs (HBM bound)
         if (!c.has_Z) {
@@ -204,6 +217,7 @@ kd_result kernel_times_vector(ctx &c, const T *d) {
         sums2<T>(c, d, S_SUM_D, S_Q_D);
         xt_v<T>(c, c.Z.as<T>(), m, c.ldx, d, c.wvec.as<T>());
         x_w<T>(c, c.Z.as<T>(), m, c.ldx, c.wvec.as<T>(), T(0), c.P.as<T>());
+        res.center = 1;
         c.stats.matvec_path = 3;
     } else {
         bool use_tc = false;
@@ -246,8 +260,8 @@ kd_result kernel_times_vector(ctx &c, const T *d) {
 template <typename T, int MODE>
 void abar_finish(ctx &c, const kd_result &kd, const T *d, T add, T *out) {
     const int64_t m = c.m();
-    k_abar_finish<T, MODE><<<vec_grid(m), VEC_THREADS, 0, c.stream>>>(c.P.as<T>(), kd.ldP, kd.splits, d, m, T(1) / (T) c.cost,
-                                                                       c.kernel == B200SVM_LINEAR ? 1 : 0, add, out, c.scal.as<T>(),
+    k_abar_finish<T, MODE><<<vec_grid(m), VEC_THREADS, 0, c.stream>>>(c.P.as<T>(), kd.ldP, kd.splits, d, m, T(1) / (T) c.cost, kd.center,
+                                                                       c.q.as<T>(), (T) c.QA_cost, add, out, c.scal.as<T>(),
                                                                        c.partials.as<T>(), c.counters.as<unsigned int>());
     count_launch(c);
     B200_CUDA_CHECK(cudaGetLastError());

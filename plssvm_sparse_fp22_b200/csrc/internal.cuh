@@ -104,6 +104,7 @@ struct ctx {
     // options
     int64_t opt_matvec_path{ 0 };
     int64_t opt_sync_every{ 1 };
+    int64_t opt_sparse_block{ 0 };  // 0 = default
 
     // data
     bool has_data{ false };
@@ -141,6 +142,8 @@ struct ctx {
 
     void *tc_opaque{ nullptr };                 // tcgen05 path state (gram_tc.cu)
     void (*tc_opaque_free)(void *){ nullptr };
+    void *sp_opaque{ nullptr };                 // sparse path state (sparse.cu)
+    void (*sp_opaque_free)(void *){ nullptr };
 
     // multi-GPU
     comm_state *comm{ nullptr };
@@ -176,6 +179,14 @@ template <typename T> void predict_dense(ctx &c, const T *alpha_dev, T bias, con
 void tc_prepare_split(ctx &c);                                   // build fp16 hi/lo operands + TMA descriptors
 bool tc_available(const ctx &c);
 void tc_kernel_matvec(ctx &c, const float *d, float *out_Kd);    // out = K d via symmetric tcgen05 tiles
+
+// sparse path (sparse.cu)
+void sp_set_data(ctx &c, const int64_t *rowptr, const int32_t *colidx, const void *values, int64_t n, int64_t F, int64_t nnz, int fmt);
+template <typename T> void sp_generate_q(ctx &c);
+template <typename T> void sp_kernel_matvec(ctx &c, const T *d, T *out);  // out[0..m) = K d (un-centred), this rank's rows
+template <typename T> void sp_update_w(ctx &c, const T *alpha_dev, T *w_dev);
+template <typename T> void sp_predict(ctx &c, const T *alpha_dev, T bias, const int64_t *rowptr, const int32_t *colidx, const void *values, int64_t P,
+                                      int64_t nnz, int fmt, T *out_host);
 
 // multi-GPU (comm.cu)
 void comm_destroy(ctx &c);

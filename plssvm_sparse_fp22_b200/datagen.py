@@ -139,3 +139,49 @@ def fp22_decode(v22: np.ndarray) -> np.ndarray:
 
 def fp22_round(x: np.ndarray) -> np.ndarray:
     return fp22_decode(fp22_encode(x))
+
+
+def pack_fp22_csr(rowptr: np.ndarray, colidx: np.ndarray, values: np.ndarray):
+    """CSR -> FP22-packed CSR: one uint32 per stored entry, ``(fp22(value) << 10) | column_delta`` with col_0 = delta_0 and
+    col_k = col_{k-1} + delta_k; gaps > 1023 are bridged by padding entries (value +0, delta 1023).
+    Returns (rowptr_packed int64[n+1], packed uint32[...])."""
+    rowptr = np.ascontiguousarray(rowptr, np.int64)
+    n = rowptr.shape[0] - 1
+    nnz = int(rowptr[-1])
+    if nnz == 0:
+        return rowptr.copy(), np.zeros(0, np.uint32)
+    cols = np.ascontiguousarray(colidx, np.int64)
+    prev = np.empty(nnz, np.int64)
+    prev[1:] = cols[:-1]
+    starts = rowptr[:-1][np.diff(rowptr) > 0]
+    prev[starts] = 0
+    delta = cols - prev
+    npad = np.maximum((delta - 1) // 1023, 0)
+    last = delta - 1023 * npad
+    code = fp22_encode(np.asarray(values, np.float32)).astype(np.uint32)
+    out_counts = npad + 1
+    total = int(out_counts.sum())
+    packed = np.full(total, np.uint32(1023), np.uint32)  # padding: value +0, delta 1023
+    pos = np.cumsum(out_counts) - 1  # position of the real entry of each nnz
+    packed[pos] = (code << np.uint32(10)) | last.astype(np.uint32)
+    rows = np.repeat(np.arange(n, dtype=np.int64), np.diff(rowptr))
+    per_row = np.bincount(rows, weights=out_counts, minlength=n).astype(np.int64)
+    rp = np.zeros(n + 1, np.int64)
+    np.cumsum(per_row, out=rp[1:])
+    return rp, packed
+
+
+def unpack_fp22_csr(rowptr_packed: np.ndarray, packed: np.ndarray):
+    """Inverse of pack_fp22_csr (padding entries dropped): (rowptr, colidx int32, values float32)."""
+    n = rowptr_packed.shape[0] - 1
+    rp = np.zeros(n + 1, np.int64)
+    cols, vals = [], []
+    for i in range(n):
+        w = packed[rowptr_packed[i]:rowptr_packed[i + 1]]
+        c = np.cumsum((w & np.uint32(1023)).astype(np.int64))
+        v = (w & np.uint32(0xFFFFFC00)).view(np.float32)
+        keep = (w & np.uint32(0x7FFFFC00)) != 0
+        cols.append(c[keep].astype(np.int32))
+        vals.append(v[keep])
+        rp[i + 1] = rp[i] + int(keep.sum())
+    return rp, (np.concatenate(cols) if cols else np.zeros(0, np.int32)), (np.concatenate(vals) if vals else np.zeros(0, np.float32))

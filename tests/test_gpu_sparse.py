@@ -1,0 +1,162 @@
+"""GPU parity tests of the sparse (CSR / FP22-packed) path through the C ABI, against the oracle's CSR restatement
+(oracle/lssvm_oracle.c lssvm_csr_*, itself checked against the dense restatement and the reference build in
+tests/test_oracle.py) on the same seeded inputs.  The reference stores data dense, so the semantics are the
+dense ones applied to rows whose zeros are not stored.
+
+Tolerances: double 1e-10 norm-wise on alpha with identical iteration count (north star); q / matvec 1e-12 (double), 2e-5 (float):
+the sparse path evaluates K_ij = u_i u_j (1 + expm1(2 gamma G_ij)) instead of exp(-gamma |x_i - x_j|^2) — same value, different
+rounding.  FP22: the oracle is fed decode(encode(x)), so the register-decoded values must match to float tolerance.
+"""
+import numpy as np
+import pytest
+
+from conftest import nrm_rel
+from oracle import port
+from plssvm_sparse_fp22_b200 import capi, datagen
+
+pytestmark = pytest.mark.gpu
+KERNELS = ["linear", "polynomial", "rbf"]
+
+
+def make(n, F, density, seed, dt, min_nnz=1):
+    rp, ci, v, y = datagen.make_sparse_csr(n, F, density, seed=seed, dtype=dt, min_nnz=min_nnz)
+    return rp, ci, v, y
+
+
+@pytest.mark.parametrize("dt", [np.float64, np.float32])
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("shape", [(2, 7, 0.5, 0), (67, 40, 0.2, 128), (300, 1000, 0.01, 128), (1100, 300, 0.05, 256), (700, 5000, 0.004, 0)])
+def test_csr_q_and_matvec_vs_oracle(kernel, dt, shape):
+    n, F, density, W = shape
+    rp, ci, v, _ = make(n, F, density, seed=n + F, dt=dt, min_nnz=0 if n > 2 else 1)
+    coef0 = 0.5 if kernel == "polynomial" else 0.0
+    d = np.random.default_rng(n).uniform(-1, 2, n - 1).astype(dt)
+    with capi.Handle(dt, kernel, 3, 1.0 / F, coef0, 1.5) as h:
+        if W:
+            h.set_option(capi.OPT_SPARSE_BLOCK, W)
+        h.set_data_csr(rp, ci, v, F)
+        q = h.generate_q()
+        q_o = port.csr_generate_q(rp, ci, v, F, kernel, 3, 1.0 / F, coef0)
+        assert nrm_rel(q_o, q) < (1e-13 if dt == np.float64 else 5e-6)
+        X = datagen.csr_to_dense(rp, ci, v, F)
+        kxx = port.kernel_function(X[-1], X[-1], kernel, 3, 1.0 / F, coef0)
+        assert abs(h.kxx_last() - kxx) <= 1e3 * np.finfo(dt).eps * max(abs(kxx), 1.0)
+        qa = float(kxx) + 1.0 / 1.5
+        h.set_q(q_o, qa)
+        got = h.matvec(d, 1.0)
+        assert h.stats().matvec_path == 4
+        rp64, ci64, v64 = rp, ci, v.astype(np.float64)
+        want = port.csr_matvec(rp64, ci64, v64, F, q_o.astype(np.float64), d.astype(np.float64), qa, 1.0, kernel, 3, 1.0 / F, coef0, 1.5)
+        assert nrm_rel(want, got) < (1e-12 if dt == np.float64 else 2e-5), nrm_rel(want, got)
+        base = np.linspace(-1, 1, n - 1).astype(dt)
+        got2 = h.matvec(d, -1.0, ret=base)
+        assert nrm_rel(base - want, got2) < (1e-12 if dt == np.float64 else 2e-5)
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("shape", [(400, 600, 0.02), (1500, 4000, 0.005)])
+def test_csr_learn_f64_matches_dense_oracle(kernel, shape):
+    """Full learn() on CSR rows == the oracle's learn() on the densified rows: identical CG iteration count, alpha <= 1e-10."""
+    n, F, density = shape
+    rp, ci, v, y = make(n, F, density, seed=3 * n, dt=np.float64)
+    X = datagen.csr_to_dense(rp, ci, v, F)
+    a_o, rho_o, it_o = port.learn(X, y, kernel, eps=1e-3, use_rows=True)
+    with capi.Handle(np.float64, kernel) as h:
+        h.set_data_csr(rp, ci, v, F)
+        alpha, rho, it = h.learn(y, eps=1e-3)
+    assert it == it_o
+    assert nrm_rel(a_o, alpha) < 1e-10, nrm_rel(a_o, alpha)
+    q = port.generate_q(X, kernel)
+    qa = port.kernel_function(X[-1], X[-1], kernel, gamma=1.0 / F) + 1.0
+    scale = abs(y[-1]) + abs(qa * a_o[:-1].sum()) + abs(q @ a_o[:-1])
+    assert abs(rho - rho_o) <= 1e-10 * scale
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_csr_matches_dense_device_path(kernel):
+    """Same data through set_data_dense and set_data_csr: the two device paths agree (double)."""
+    n, F = 500, 300
+    rp, ci, v, y = make(n, F, 0.05, seed=9, dt=np.float64)
+    X = datagen.csr_to_dense(rp, ci, v, F)
+    with capi.Handle(np.float64, kernel) as hd, capi.Handle(np.float64, kernel) as hs:
+        hd.set_data(X)
+        hs.set_data_csr(rp, ci, v, F)
+        ad, rd, itd = hd.learn(y, eps=1e-3)
+        as_, rs, its = hs.learn(y, eps=1e-3)
+        assert itd == its
+        assert nrm_rel(ad, as_) < 1e-9
+        # tight epsilon: more iterations amplify the rounding-order difference of the two paths (O(cond * eps))
+        ad, rd, itd = hd.learn(y, eps=1e-6)
+        as_, rs, its = hs.learn(y, eps=1e-6)
+        assert abs(itd - its) <= 1
+        assert nrm_rel(ad, as_) < 1e-4
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_fp22_packed_path(kernel):
+    """FP22-packed CSR (decoded in registers) against the oracle fed with decode(encode(x)) — float."""
+    n, F = 900, 6000   # gaps > 1023 occur -> padding entries are exercised
+    rp, ci, v, y = make(n, F, 0.004, seed=21, dt=np.float32, min_nnz=0)
+    prp, packed = datagen.pack_fp22_csr(rp, ci, v)
+    assert packed.shape[0] > rp[-1]
+    vq = datagen.fp22_round(v)
+    coef0 = 0.25 if kernel == "polynomial" else 0.0
+    d = np.random.default_rng(5).uniform(-1, 2, n - 1).astype(np.float32)
+    with capi.Handle(np.float32, kernel, 3, 1.0 / F, coef0, 1.0) as h:
+        h.set_data_csr(prp, None, packed, F, value_format=capi.VAL_FP22)
+        q = h.generate_q()
+        q_o = port.csr_generate_q(rp, ci, vq, F, kernel, 3, 1.0 / F, coef0)
+        assert nrm_rel(q_o, q) < 5e-6
+        X = datagen.csr_to_dense(rp, ci, vq, F)
+        qa = float(port.kernel_function(X[-1], X[-1], kernel, 3, 1.0 / F, coef0)) + 1.0
+        h.set_q(q_o, qa)
+        got = h.matvec(d, 1.0)
+        want = port.csr_matvec(rp, ci, vq.astype(np.float64), F, q_o.astype(np.float64), d.astype(np.float64), qa, 1.0, kernel, 3, 1.0 / F, coef0, 1.0)
+        assert nrm_rel(want, got) < 2e-5, nrm_rel(want, got)
+        # the same rows as plain float CSR of the rounded values give the same operator
+        with capi.Handle(np.float32, kernel, 3, 1.0 / F, coef0, 1.0) as h2:
+            h2.set_option(capi.OPT_SPARSE_BLOCK, 1024)
+            h2.set_data_csr(rp, ci, vq, F)
+            h2.set_q(q_o, qa)
+            assert nrm_rel(h2.matvec(d, 1.0), got) < 2e-6
+        # predict with packed points
+        alpha = np.random.default_rng(6).standard_normal(n).astype(np.float32) * 0.1
+        dec = h.predict_csr(alpha, 0.1, prp, None, packed, value_format=capi.VAL_FP22)
+        dec_o = port.csr_predict(rp, ci, vq.astype(np.float64), alpha.astype(np.float64), 0.1, rp, ci, vq.astype(np.float64), F, kernel, 3, 1.0 / F, coef0)
+        assert nrm_rel(dec_o, dec) < 2e-5
+        safe = np.abs(dec_o) > 1e-4 * np.abs(dec_o).max()
+        assert np.array_equal(np.sign(dec[safe]), np.sign(dec_o[safe]))
+
+
+@pytest.mark.parametrize("dt", [np.float64, np.float32])
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_csr_predict_and_update_w(kernel, dt):
+    n, F, P = 600, 800, 1300
+    rp, ci, v, y = make(n, F, 0.02, seed=31, dt=dt)
+    prp, pci, pv, _ = make(P, F, 0.02, seed=32, dt=dt, min_nnz=0)
+    alpha = (np.random.default_rng(7).standard_normal(n) * 0.1).astype(dt)
+    with capi.Handle(dt, kernel, gamma=1.0 / F) as h:
+        h.set_option(capi.OPT_SPARSE_BLOCK, 256)
+        h.set_data_csr(rp, ci, v, F)
+        dec = h.predict_csr(alpha, -0.2, prp, pci, pv)
+        dec_o = port.csr_predict(rp, ci, v.astype(np.float64), alpha.astype(np.float64), -0.2, prp, pci, pv.astype(np.float64), F, kernel)
+        assert nrm_rel(dec_o, dec) < (1e-12 if dt == np.float64 else 2e-5)
+        if dt == np.float64:
+            assert np.array_equal(h.predict_label(dec), port.sign(dec_o))  # bit-identical labels
+        empty = h.predict_csr(alpha, -0.2, np.zeros(1, np.int64), np.zeros(0, np.int32), np.zeros(0, dt))
+        assert empty.shape == (0,)
+        if kernel == "linear":
+            w = h.update_w(alpha)
+            w_o = port.update_w(datagen.csr_to_dense(rp, ci, v, F).astype(np.float64), alpha.astype(np.float64))
+            assert nrm_rel(w_o, w) < (1e-13 if dt == np.float64 else 1e-5)
+
+
+def test_csr_errors_are_loud():
+    with capi.Handle(np.float64, "rbf", gamma=0.5) as h:
+        rp = np.array([0, 2, 3], np.int64)
+        with pytest.raises(capi.B200Error, match="sorted and unique"):
+            h.set_data_csr(rp, np.array([1, 1, 0], np.int32), np.ones(3), 4)
+        with pytest.raises(capi.B200Error, match="out of range"):
+            h.set_data_csr(rp, np.array([0, 9, 0], np.int32), np.ones(3), 4)
+        with pytest.raises(capi.B200Error, match="float handle"):
+            h.set_data_csr(rp, None, np.ones(3, np.uint32), 4, value_format=capi.VAL_FP22)
