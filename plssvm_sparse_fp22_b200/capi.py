@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(HERE, "libb200svm.so")
 F32, F64 = 0, 1
 KERNELS = {"linear": 0, "polynomial": 1, "rbf": 2}
 VAL_F32, VAL_F64, VAL_FP22 = 0, 1, 2
-OPT_MATVEC_PATH, OPT_SYNC_EVERY, OPT_SPARSE_BLOCK = 1, 2, 3
+OPT_MATVEC_PATH, OPT_SYNC_EVERY, OPT_SPARSE_BLOCK, OPT_SPARSE_GROUP, OPT_SPARSE_LANES = 1, 2, 3, 4, 5
 PATH_AUTO, PATH_SIMT, PATH_TC = 0, 1, 2
 
 # every symbol include/b200svm.h declares

@@ -192,6 +192,14 @@ int b200svm_set_option(b200svm_handle h, int option, int64_t value) {
                 B200_REQUIRE(value == 0 || (value >= 128 && value <= 4096 && (value & (value - 1)) == 0), "sparse block width must be 0 or a power of two in [128, 4096]");
                 c->opt_sparse_block = value;
                 break;
+            case B200SVM_OPT_SPARSE_LANES:
+                B200_REQUIRE(value == 0 || value == 1 || value == 8, "lanes per segment must be 0, 1 or 8");
+                c->opt_sparse_lanes = value;
+                break;
+            case B200SVM_OPT_SPARSE_GROUP:
+                B200_REQUIRE(value >= 0, "blocks per group must be >= 0");
+                c->opt_sparse_group = value;
+                break;
             default: fail(B200SVM_ERR_INVALID, "unknown option");
         }
     });

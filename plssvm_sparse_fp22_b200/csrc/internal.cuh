@@ -105,6 +105,8 @@ struct ctx {
     int64_t opt_matvec_path{ 0 };
     int64_t opt_sync_every{ 1 };
     int64_t opt_sparse_block{ 0 };  // 0 = default
+    int64_t opt_sparse_group{ 0 };  // 0 = auto
+    int64_t opt_sparse_lanes{ 0 };  // 0 = auto
 
     // data
     bool has_data{ false };

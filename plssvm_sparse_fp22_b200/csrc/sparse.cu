@@ -16,6 +16,7 @@
 #include "device_utils.cuh"
 
 #include <algorithm>
+#include <cmath>
 #include <cstring>
 
 namespace b200 {
@@ -32,14 +33,20 @@ struct csr_view {
     int64_t rows;
 };
 
-struct blk_view {
-    const uint32_t *ptr;     // [nb][F + 1] entry offsets relative to blk[b]
-    const int64_t *blk;      // [nb + 1] first entry of each column block
-    const uint16_t *j;       // [nnzB] local column (row of X) inside its block   (unused for FP22)
-    const void *val;         // T[nnzB] or uint32 packed (fp22 << 10 | j_local), W = 1024
+// Transpose of X (CSC, rows ascending inside a column) cut into column blocks of the implicit matrix:
+//   block b  = rows [b W, (b+1) W) of X  -> one pass of the warp-private accumulator
+//   group g  = G consecutive blocks      -> one kernel launch (its slice of the transpose stays L2-resident)
+// A lane that owns feature f walks column f sequentially across the blocks of a group, so its loads are contiguous; the
+// per-(feature, block) end pointers give every segment a known trip count (loads issue back to back, no pointer chasing).
+struct csc_view {
+    const uint32_t *ptrT;    // [F][nb + 1] index of the first entry of column f inside block b; ptrT[f][nb] = end of the column
+    const uint16_t *j;       // [entries] row of X relative to its block (plain formats)
+    const void *val;         // T[entries], or uint32 packed (fp22 << 10 | row_in_block), W <= 1024
     int64_t F;
-    int W;                   // columns of the implicit matrix per block (power of two, <= 4096; 1024 for FP22)
-    int nb;
+    int W;                   // rows of X per block (power of two, 128..4096; <= 1024 for FP22)
+    int nb;                  // blocks
+    int G;                   // blocks per group
+    int ng;                  // groups
 };
 
 __device__ __forceinline__ float fp22_value(uint32_t w) { return __uint_as_float(w & 0xFFFFFC00u); }
@@ -140,17 +147,16 @@ __global__ void __launch_bounds__(256) k_sp_row_dot(csr_view A, const T *__restr
     }
 }
 
-// w[f] = sum_j x_jf v_j  via the blocked transpose (thread per feature, fixed order => deterministic); v is zero-extended to nb * W
+// w[f] = sum_j x_jf v_j  via the transpose (thread per feature, fixed order => deterministic); v has nb * W entries
 template <typename T, bool FP22>
-__global__ void __launch_bounds__(256) k_sp_xt_v(blk_view B, const T *__restrict__ v, T *__restrict__ w) {
+__global__ void __launch_bounds__(256) k_sp_xt_v(csc_view B, const T *__restrict__ v, T *__restrict__ w) {
     const int64_t f = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (f >= B.F) { return; }
+    const uint32_t *pt = B.ptrT + f * (B.nb + 1);
     T s = 0;
     for (int b = 0; b < B.nb; ++b) {
-        const uint32_t *ptr = B.ptr + (int64_t) b * (B.F + 1);
-        const int64_t base = B.blk[b];
         const T *vb = v + (int64_t) b * B.W;
-        for (int64_t e = base + ptr[f], e1 = base + ptr[f + 1]; e < e1; ++e) {
+        for (uint32_t e = pt[b], e1 = pt[b + 1]; e < e1; ++e) {
             if constexpr (FP22) {
                 const uint32_t wd = __ldg(static_cast<const uint32_t *>(B.val) + e);
                 s = fma((T) fp22_value(wd), vb[wd & 1023u], s);
@@ -193,6 +199,7 @@ struct kfun {
     double a;       // rbf: 2 gamma ; polynomial: gamma
     double coef0;
     double c0pow;   // coef0^degree
+    double fx_scale, fx_inv;  // 2^s and 2^-s of the fixed-point Gram accumulation
 };
 
 template <typename T, int KERNEL>
@@ -200,84 +207,192 @@ __device__ __forceinline__ T s_value(T g, const kfun &k) {
     if constexpr (KERNEL == B200SVM_RBF) {
         return expm1_fast((T) k.a * g);
     } else {
-        return ipow(fma((T) k.a, g, (T) k.coef0), k.degree) - (T) k.c0pow;
+        const T base = fma((T) k.a, g, (T) k.coef0);
+        T r;
+        switch (k.degree) {  // warp-uniform
+            case 1: r = base; break;
+            case 2: r = base * base; break;
+            case 3: r = base * base * base; break;
+            case 4: r = (base * base) * (base * base); break;
+            default: r = ipow(base, k.degree); break;
+        }
+        return r - (T) k.c0pow;
     }
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// out[row] += sum_{j in blocks [b0, b1)} S(G_row,j) v_j      rows [row_lo, row_hi) of A, grid-strided over warps
+// out[row] += sum_{j in group g} S(G_row,j) v_j      rows [row_lo, row_hi) of A, grid-strided over warps
 //   per-warp shared memory: acc T[W] | touched bitmap uint32[W/32] | touched list uint16[W]
+//   A lane keeps up to K features of the row in registers (value, feature, cursor into the feature's column) and, block after
+//   block, consumes the entries whose row falls into the block (segment end from ptrT: known trip count, loads batched by 4).
+//   COMPACT: touched slots are recorded in a bitmap and compacted, the kernel function runs on those only (sparse fill);
+//   otherwise all W slots are evaluated (S(0) = 0), which is cheaper when most slots are hit.
 // ---------------------------------------------------------------------------------------------------------------------
-template <typename T, int KERNEL, bool FP22>
-__global__ void __launch_bounds__(1024, 1)
-    k_sp_kmv(csr_view A, int64_t row_lo, int64_t row_hi, blk_view B, int b0, int b1, const T *__restrict__ v, kfun kf, T *__restrict__ out) {
+// Fixed-point accumulation of the Gram entries in 32-bit limbs: shared-memory floating-point atomics are CAS loops on sm_100,
+// 32-bit integer atomics are single fire-and-forget instructions.  A product p is scaled by 2^s (s chosen from the largest
+// squared row norm, which bounds every partial sum by Cauchy-Schwarz), rounded to an integer q and split into limbs with 10 bits
+// of head-room each, so up to 1024 products can be added per slot without a carry; limbs are recombined in the epilogue.
+// The sum is exact in the fixed-point grid (2^-42 / 2^-61 of the bound for float / double) and independent of the order of the
+// additions => bit-reproducible.
+template <typename T>
+struct fixp;
+template <>
+struct fixp<float> {
+    static constexpr int LIMBS = 2;
+    static constexpr int BITS = 42;  // |q| <= 2^42
+    static __device__ __forceinline__ void add(uint32_t *acc, int W, int jl, float p, float scale) {
+        const long long q = __float2ll_rn(p * scale);
+        atomicAdd(&acc[jl], (uint32_t) (q & 0x3FFFFFll));
+        atomicAdd(reinterpret_cast<int *>(&acc[W + jl]), (int) (q >> 22));
+    }
+    static __device__ __forceinline__ float take(uint32_t *acc, int W, int jl, double inv_scale) {
+        const uint32_t lo = acc[jl];
+        const int hi = (int) acc[W + jl];
+        acc[jl] = 0u;
+        acc[W + jl] = 0u;
+        const long long q = ((long long) hi << 22) + (long long) lo;
+        return (float) q * (float) inv_scale;  // 2^-s: exact scaling, one rounding of q to 24 bits
+    }
+};
+template <>
+struct fixp<double> {
+    static constexpr int LIMBS = 3;
+    static constexpr int BITS = 61;  // |q| <= 2^61
+    static __device__ __forceinline__ void add(uint32_t *acc, int W, int jl, double p, double scale) {
+        const long long q = __double2ll_rn(p * scale);
+        atomicAdd(&acc[jl], (uint32_t) (q & 0x1FFFFFll));
+        atomicAdd(&acc[W + jl], (uint32_t) ((q >> 21) & 0x1FFFFFll));
+        atomicAdd(reinterpret_cast<int *>(&acc[2 * W + jl]), (int) (q >> 42));
+    }
+    static __device__ __forceinline__ double take(uint32_t *acc, int W, int jl, double inv_scale) {
+        const uint32_t lo = acc[jl], mid = acc[W + jl];
+        const int hi = (int) acc[2 * W + jl];
+        acc[jl] = 0u;
+        acc[W + jl] = 0u;
+        acc[2 * W + jl] = 0u;
+        const long long q = ((long long) hi << 42) + ((long long) mid << 21) + (long long) lo;
+        return (double) q * inv_scale;
+    }
+};
+
+template <typename T, bool FP22>
+__device__ __forceinline__ void load_b_entry(const csc_view &B, uint32_t e, int &jl, T &xv) {
+    if constexpr (FP22) {
+        const uint32_t wd = __ldg(static_cast<const uint32_t *>(B.val) + e);
+        jl = (int) (wd & 1023u);
+        xv = (T) fp22_value(wd);
+    } else {
+        jl = (int) __ldg(B.j + e);
+        xv = __ldg(static_cast<const T *>(B.val) + e);
+    }
+}
+
+template <typename T, int KERNEL, bool FP22, int K, int MAXT, bool COMPACT, int GS>
+__global__ void __launch_bounds__(MAXT, 1)
+    k_sp_kmv(csr_view A, int64_t row_lo, int64_t row_hi, csc_view B, int g, const T *__restrict__ v, kfun kf, T *__restrict__ out) {
     extern __shared__ __align__(16) unsigned char sp_smem[];
+    using FX = fixp<T>;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     const int W = B.W, words = W >> 5;
-    const size_t per_warp = (size_t) W * sizeof(T) + (size_t) words * 4 + (size_t) W * 2;
+    const size_t per_warp = (size_t) W * 4 * FX::LIMBS + (size_t) words * 4 + (size_t) W * 2;
     unsigned char *mine = sp_smem + (size_t) warp * per_warp;
-    T *acc = reinterpret_cast<T *>(mine);
-    uint32_t *bits = reinterpret_cast<uint32_t *>(mine + (size_t) W * sizeof(T));
-    uint16_t *list = reinterpret_cast<uint16_t *>(mine + (size_t) W * sizeof(T) + (size_t) words * 4);
-    for (int k = lane; k < W; k += 32) { acc[k] = T(0); }
-    for (int k = lane; k < words; k += 32) { bits[k] = 0u; }
+    uint32_t *acc = reinterpret_cast<uint32_t *>(mine);
+    uint32_t *bits = acc + (size_t) W * FX::LIMBS;
+    uint16_t *list = reinterpret_cast<uint16_t *>(bits + words);
+    for (int k = lane; k < W * FX::LIMBS + words; k += 32) { acc[k] = 0u; }
+    const T fx_scale = (T) kf.fx_scale;
+    const double fx_inv = kf.fx_inv;
     __syncwarp();
 
+    constexpr int UNR = K <= 8 ? K : 1;  // the 32-features-per-lane fallback keeps its state in local memory
+    const int b0 = g * B.G, b1 = min(B.nb, b0 + B.G);
     const int64_t gwarp = (int64_t) blockIdx.x * nwarps + warp, twarps = (int64_t) gridDim.x * nwarps;
     for (int64_t row = row_lo + gwarp; row < row_hi; row += twarps) {
         const int64_t p0 = A.rowptr[row], p1 = A.rowptr[row + 1];
+        // ---- this lane's features: value, end-pointer row of ptrT, cursor
+        T x[K];
+        const uint32_t *pt[K];
+        uint32_t cur[K];
+        int colrun = 0;
+#pragma unroll UNR
+        for (int k = 0; k < K; ++k) {
+            int f = 0;
+            x[k] = T(0);
+            pt[k] = nullptr;
+            cur[k] = 0u;
+            if (p0 + (int64_t) k * 32 < p1) {  // warp-uniform
+                const bool valid = load_entry<T, FP22>(A, p0 + (int64_t) k * 32, p1, lane, colrun, f, x[k]);
+                if (valid && x[k] != T(0)) {
+                    pt[k] = B.ptrT + (int64_t) f * (B.nb + 1) + b0;
+                    cur[k] = __ldg(pt[k]);
+                }
+            }
+        }
         T rowsum = T(0);
         for (int b = b0; b < b1; ++b) {
-            const uint32_t *ptr = B.ptr + (int64_t) b * (B.F + 1);
-            const int64_t base = B.blk[b];
-            // ---- scatter: lane <-> feature of the row, each lane walks that feature's segment of block b
-            int colrun = 0;
-            for (int64_t p = p0; p < p1; p += 32) {
-                int f;
-                T x;
-                const bool valid = load_entry<T, FP22>(A, p, p1, lane, colrun, f, x);
-                if (valid && x != T(0)) {
-                    const int64_t e0 = base + __ldg(ptr + f), e1 = base + __ldg(ptr + f + 1);
-                    for (int64_t e = e0; e < e1; ++e) {
+            // ---- segment ends of this block (independent loads), then the products
+            uint32_t e1[K];
+#pragma unroll UNR
+            for (int k = 0; k < K; ++k) { e1[k] = pt[k] != nullptr ? __ldg(pt[k] + (b - b0) + 1) : cur[k]; }
+            // GS lanes share one feature's segment (GS = 1: a lane walks its own features; larger GS for longer segments)
+            constexpr int NG = 32 / GS;
+#pragma unroll UNR
+            for (int k = 0; k < K; ++k) {
+                if (p0 + (int64_t) k * 32 >= p1) { break; }  // warp-uniform: no more stored entries in this row
+                for (int l0 = 0; l0 < 32; l0 += NG) {
+                    if (p0 + (int64_t) k * 32 + l0 >= p1) { break; }
+                    uint32_t e, ee;
+                    T xs;
+                    if constexpr (GS == 1) {
+                        e = cur[k];
+                        ee = e1[k];
+                        xs = x[k];
+                    } else {
+                        const int src = l0 + lane / GS;
+                        e = __shfl_sync(0xffffffffu, cur[k], src) + (uint32_t) (lane % GS);
+                        ee = __shfl_sync(0xffffffffu, e1[k], src);
+                        xs = __shfl_sync(0xffffffffu, x[k], src);
+                    }
+                    for (; e < ee; e += GS) {
                         int jl;
                         T xv;
-                        if constexpr (FP22) {
-                            const uint32_t wd = __ldg(static_cast<const uint32_t *>(B.val) + e);
-                            jl = (int) (wd & 1023u);
-                            xv = (T) fp22_value(wd);
-                        } else {
-                            jl = (int) __ldg(B.j + e);
-                            xv = __ldg(static_cast<const T *>(B.val) + e);
-                        }
-                        atomicAdd(&acc[jl], x * xv);                 // lanes of one warp may meet on a slot
-                        atomicOr(&bits[jl >> 5], 1u << (jl & 31));
+                        load_b_entry<T, FP22>(B, e, jl, xv);
+                        FX::add(acc, W, jl, xs * xv, fx_scale);  // lanes of one warp may meet on a slot
+                        if constexpr (COMPACT) { atomicOr(&bits[jl >> 5], 1u << (jl & 31)); }
                     }
                 }
+                cur[k] = e1[k];
             }
             __syncwarp();
-            // ---- compact the touched slots (bitmap -> list), fixed order
-            int cnt = 0;
-            for (int w0 = 0; w0 < words; w0 += 32) {
-                uint32_t word = (w0 + lane < words) ? bits[w0 + lane] : 0u;
-                const int c = __popc(word);
-                const int incl = warp_incl_scan(c, lane);
-                int pos = cnt + incl - c;
-                if (word != 0u) { bits[w0 + lane] = 0u; }
-                while (word != 0u) {
-                    const int bit = __ffs((int) word) - 1;
-                    list[pos++] = (uint16_t) (((w0 + lane) << 5) + bit);
-                    word &= word - 1u;
-                }
-                cnt += __shfl_sync(0xffffffffu, incl, 31);
-            }
-            __syncwarp();
-            // ---- kernel function on the touched slots only, times v_j
             const T *vb = v + (int64_t) b * W;
-            for (int t = lane; t < cnt; t += 32) {
-                const int jl = list[t];
-                const T g = acc[jl];
-                acc[jl] = T(0);
-                rowsum = fma(s_value<T, KERNEL>(g, kf), __ldg(vb + jl), rowsum);
+            if constexpr (COMPACT) {
+                // ---- compact the touched slots (bitmap -> list), fixed order
+                int cnt = 0;
+                for (int w0 = 0; w0 < words; w0 += 32) {
+                    uint32_t word = (w0 + lane < words) ? bits[w0 + lane] : 0u;
+                    const int c = __popc(word);
+                    const int incl = warp_incl_scan(c, lane);
+                    int pos = cnt + incl - c;
+                    if (word != 0u) { bits[w0 + lane] = 0u; }
+                    while (word != 0u) {
+                        const int bit = __ffs((int) word) - 1;
+                        list[pos++] = (uint16_t) (((w0 + lane) << 5) + bit);
+                        word &= word - 1u;
+                    }
+                    cnt += __shfl_sync(0xffffffffu, incl, 31);
+                }
+                __syncwarp();
+                // ---- kernel function on the touched slots only, times v_j
+                for (int t = lane; t < cnt; t += 32) {
+                    const int jl = list[t];
+                    const T gv = FX::take(acc, W, jl, fx_inv);
+                    rowsum = fma(s_value<T, KERNEL>(gv, kf), __ldg(vb + jl), rowsum);
+                }
+            } else {
+                for (int jl = lane; jl < W; jl += 32) {
+                    const T gv = FX::take(acc, W, jl, fx_inv);
+                    rowsum = fma(s_value<T, KERNEL>(gv, kf), __ldg(vb + jl), rowsum);
+                }
             }
             __syncwarp();
         }
@@ -330,16 +445,19 @@ struct sparse_state {
     // rows (A side)
     dbuf a_rowptr, a_col, a_val;
     int64_t a_entries{ 0 };
-    // column-blocked transpose (B side)
-    dbuf b_ptr, b_blk, b_j, b_val;
-    int W{ 0 }, nb{ 0 };
+    int64_t a_max_row{ 0 };  // longest row (stored entries)
+    double max_norm2{ 0 };   // largest squared row norm (bounds every Gram entry)
+    // transpose (B side): CSC + per-group column pointers
+    dbuf b_ptrT, b_j, b_val;
+    int W{ 0 }, nb{ 0 }, G{ 1 }, ng{ 1 };
     int64_t b_entries{ 0 };
+    double avg_seg{ 0 };     // mean stored entries per (feature, block) segment
+    double fill{ 0 };  // expected fraction of accumulator slots hit per (row, block) visit
     // per-row data and work vectors
     dbuf norms, u, v, xl, wvec;
     // launch geometry of k_sp_kmv
     int warps{ 0 };
     size_t smem{ 0 };
-    int blocks_per_launch{ 1 };
     // predict staging
     dbuf p_rowptr, p_col, p_val, p_norms, p_u, p_out;
 };
@@ -355,8 +473,8 @@ sparse_state &state_of(ctx &c) {
 sp::csr_view view_rows(const sparse_state &st, int64_t lo, int64_t hi) {
     return sp::csr_view{ st.a_rowptr.as<int64_t>() + lo, st.a_col.as<int32_t>(), st.a_val.p, hi - lo };
 }
-sp::blk_view view_blocks(const sparse_state &st) {
-    return sp::blk_view{ st.b_ptr.as<uint32_t>(), st.b_blk.as<int64_t>(), st.b_j.as<uint16_t>(), st.b_val.p, st.F, st.W, st.nb };
+sp::csc_view view_blocks(const sparse_state &st) {
+    return sp::csc_view{ st.b_ptrT.as<uint32_t>(), st.b_j.as<uint16_t>(), st.b_val.p, st.F, st.W, st.nb, st.G, st.ng };
 }
 
 void upload(ctx &c, dbuf &dst, const void *src, size_t bytes) {
@@ -415,72 +533,100 @@ host_csr<T> decode_input(const int64_t *rowptr, const int32_t *colidx, const voi
     return h;
 }
 
-// Column-blocked transpose: for block b (rows [bW, (b+1)W) of X) and feature f the entries (j_local, x_jf), j ascending.
+// Transpose (CSC, rows ascending) + per-(feature, block) pointers.  FP22: entries are re-packed as (fp22 << 10 | row_in_block).
 template <typename T>
-void build_blocks(ctx &c, sparse_state &st, const host_csr<T> &h) {
+void build_transpose(ctx &c, sparse_state &st, const host_csr<T> &h) {
     const int64_t n = st.n, F = st.F;
-    const int W = st.W, nb = st.nb;
-    std::vector<uint32_t> ptr((size_t) nb * (size_t) (F + 1), 0u);
-    std::vector<int64_t> blk((size_t) nb + 1, 0);
-    for (int b = 0; b < nb; ++b) {
-        const int64_t r0 = (int64_t) b * W, r1 = std::min<int64_t>(n, r0 + W);
-        blk[(size_t) b + 1] = blk[(size_t) b] + (h.rowptr[(size_t) r1] - h.rowptr[(size_t) r0]);
+    const int64_t nnz = (int64_t) h.col.size();
+    const int nb = st.nb, W = st.W;
+    B200_REQUIRE(nnz < (int64_t) 0xFFFFFFFFll, "more than 2^32 - 1 stored entries are not supported by the sparse path");
+    std::vector<int64_t> colptr((size_t) F + 1, 0);
+    for (int64_t p = 0; p < nnz; ++p) { ++colptr[(size_t) h.col[(size_t) p] + 1]; }
+    double sumsq = 0;
+    for (int64_t f = 0; f < F; ++f) {
+        sumsq += (double) colptr[(size_t) f + 1] * (double) colptr[(size_t) f + 1];
+        colptr[(size_t) f + 1] += colptr[(size_t) f];
     }
-    const int64_t total = blk[(size_t) nb];
-    std::vector<uint16_t> bj;
-    std::vector<T> bval;
-    std::vector<uint32_t> bpack;
+    st.fill = n > 0 ? std::min(1.0, sumsq / ((double) n * (double) n)) : 0.0;  // products per visit / W (upper bound of the hit fraction)
+    std::vector<uint16_t> tj;
+    std::vector<T> tval;
+    std::vector<uint32_t> pack;
+    std::vector<int32_t> trow((size_t) nnz);  // global row of every transposed entry (for the block pointers)
     if (st.fp22) {
-        bpack.resize((size_t) total);
+        pack.resize((size_t) nnz);
     } else {
-        bj.resize((size_t) total);
-        bval.resize((size_t) total);
+        tj.resize((size_t) nnz);
+        tval.resize((size_t) nnz);
     }
-#pragma omp parallel
     {
-        std::vector<uint32_t> cursor((size_t) F);
-#pragma omp for schedule(dynamic, 1)
-        for (int b = 0; b < nb; ++b) {
-            uint32_t *pb = ptr.data() + (size_t) b * (size_t) (F + 1);
-            const int64_t r0 = (int64_t) b * W, r1 = std::min<int64_t>(n, r0 + W);
-            for (int64_t p = h.rowptr[(size_t) r0]; p < h.rowptr[(size_t) r1]; ++p) { ++pb[(size_t) h.col[(size_t) p] + 1]; }
-            for (int64_t f = 0; f < F; ++f) { pb[f + 1] += pb[f]; }
-            std::copy(pb, pb + F, cursor.begin());
-            const int64_t base = blk[(size_t) b];
-            for (int64_t j = r0; j < r1; ++j) {
-                for (int64_t p = h.rowptr[(size_t) j]; p < h.rowptr[(size_t) j + 1]; ++p) {
-                    const size_t e = (size_t) (base + cursor[(size_t) h.col[(size_t) p]]++);
-                    if (st.fp22) {
-                        bpack[e] = h.bits[(size_t) p] | (uint32_t) (j - r0);
-                    } else {
-                        bj[e] = (uint16_t) (j - r0);
-                        bval[e] = h.val[(size_t) p];
-                    }
+        std::vector<int64_t> cursor(colptr.begin(), colptr.end() - 1);
+        for (int64_t j = 0; j < n; ++j) {
+            const uint32_t jl = (uint32_t) (j % W);
+            for (int64_t p = h.rowptr[(size_t) j]; p < h.rowptr[(size_t) j + 1]; ++p) {
+                const size_t e = (size_t) cursor[(size_t) h.col[(size_t) p]]++;
+                trow[e] = (int32_t) j;
+                if (st.fp22) {
+                    pack[e] = h.bits[(size_t) p] | jl;
+                } else {
+                    tj[e] = (uint16_t) jl;
+                    tval[e] = h.val[(size_t) p];
                 }
             }
         }
     }
-    st.b_entries = total;
-    upload(c, st.b_ptr, ptr.data(), ptr.size() * sizeof(uint32_t));
-    upload(c, st.b_blk, blk.data(), blk.size() * sizeof(int64_t));
-    if (st.fp22) {
-        upload(c, st.b_val, bpack.data(), bpack.size() * sizeof(uint32_t));
-    } else {
-        upload(c, st.b_j, bj.data(), bj.size() * sizeof(uint16_t));
-        upload(c, st.b_val, bval.data(), bval.size() * sizeof(T));
+    std::vector<uint32_t> ptrT((size_t) F * (size_t) (nb + 1));
+#pragma omp parallel for schedule(static)
+    for (int64_t f = 0; f < F; ++f) {
+        uint32_t *pt = ptrT.data() + (size_t) f * (size_t) (nb + 1);
+        int64_t e = colptr[(size_t) f];
+        const int64_t e1 = colptr[(size_t) f + 1];
+        for (int b = 0; b < nb; ++b) {
+            pt[b] = (uint32_t) e;
+            const int64_t limit = (int64_t) (b + 1) * W;
+            while (e < e1 && trow[(size_t) e] < limit) { ++e; }
+        }
+        pt[nb] = (uint32_t) e1;
     }
+    st.b_entries = nnz;
+    st.avg_seg = (double) nnz / std::max(1.0, (double) F * (double) nb);
+    if (st.fp22) {
+        st.b_j.reserve(16);
+        upload(c, st.b_val, pack.data(), pack.size() * sizeof(uint32_t));
+    } else {
+        upload(c, st.b_j, tj.data(), tj.size() * sizeof(uint16_t));
+        upload(c, st.b_val, tval.data(), tval.size() * sizeof(T));
+    }
+    upload(c, st.b_ptrT, ptrT.data(), ptrT.size() * sizeof(uint32_t));
     B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));  // host vectors go out of scope
+}
+
+// k_sp_kmv variants: K features per lane in registers -> rows of up to 32 K stored entries
+template <typename T, int KERNEL, bool FP22>
+void kmv_set_smem(int smem) {
+#define B200_SP_ATTR(KK, MT, CP, GG) \
+    B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, KERNEL, FP22, KK, MT, CP, GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))
+#define B200_SP_ATTR_G(KK, MT, CP) \
+    B200_SP_ATTR(KK, MT, CP, 1);   \
+    B200_SP_ATTR(KK, MT, CP, 8)
+    B200_SP_ATTR_G(4, 1024, true);
+    B200_SP_ATTR_G(8, 512, true);
+    B200_SP_ATTR_G(32, 256, true);
+    B200_SP_ATTR_G(4, 1024, false);
+    B200_SP_ATTR_G(8, 512, false);
+    B200_SP_ATTR_G(32, 256, false);
+#undef B200_SP_ATTR_G
+#undef B200_SP_ATTR
 }
 
 template <typename T>
 void set_kmv_attributes(size_t smem) {
     static size_t configured = 0;
     if (smem <= configured) { return; }
-    B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, B200SVM_RBF, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-    B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, B200SVM_POLYNOMIAL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    kmv_set_smem<T, B200SVM_RBF, false>((int) smem);
+    kmv_set_smem<T, B200SVM_POLYNOMIAL, false>((int) smem);
     if constexpr (sizeof(T) == 4) {
-        B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, B200SVM_RBF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, B200SVM_POLYNOMIAL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        kmv_set_smem<T, B200SVM_RBF, true>((int) smem);
+        kmv_set_smem<T, B200SVM_POLYNOMIAL, true>((int) smem);
     }
     configured = smem;
 }
@@ -518,19 +664,33 @@ void set_data_typed(ctx &c, const int64_t *rowptr, const int32_t *colidx, const 
         upload(c, st.a_col, h.col.data(), h.col.size() * sizeof(int32_t));
         upload(c, st.a_val, h.val.data(), h.val.size() * sizeof(T));
     }
-    // block width: FP22 packs a 10-bit local column; otherwise the option or a default sized for >= 11 resident warps per SM
-    int W = st.fp22 ? 1024 : (c.opt_sparse_block > 0 ? (int) c.opt_sparse_block : 2048);
+    st.max_norm2 = 0;
+    for (int64_t i = 0; i < n; ++i) {
+        double nrm = 0;
+        for (int64_t p = h.rowptr[(size_t) i]; p < h.rowptr[(size_t) i + 1]; ++p) { nrm += (double) h.val[(size_t) p] * (double) h.val[(size_t) p]; }
+        st.max_norm2 = std::max(st.max_norm2, nrm);
+    }
+    st.a_max_row = 0;
+    {
+        const int64_t *rpx = st.fp22 ? rowptr : h.rowptr.data();
+        for (int64_t i = 0; i < n; ++i) { st.a_max_row = std::max(st.a_max_row, rpx[i + 1] - rpx[i]); }
+    }
+    // block width (rows of X per accumulator pass): option or default; shared memory per warp = W (sizeof(T) + 2) + W / 8
+    const int W = c.opt_sparse_block > 0 ? (int) c.opt_sparse_block : 1024;
     B200_REQUIRE(W >= 128 && W <= 4096 && (W & (W - 1)) == 0, "sparse block width must be a power of two in [128, 4096]");
+    B200_REQUIRE(!st.fp22 || W <= 1024, "FP22 storage packs a 10-bit row-in-block index: sparse block width must be <= 1024");
     st.W = W;
     st.nb = (int) ((n + W - 1) / W);
-    build_blocks<T>(c, st, h);
-    const size_t per_warp = (size_t) W * sizeof(T) + (size_t) W / 8 + (size_t) W * 2;
+    // blocks per launch group: keep the group's slice of the transpose L2-resident (~48 MB)
+    const double bytes_per_block = (double) h.col.size() / std::max(1, st.nb) * (st.fp22 ? 4.0 : 2.0 + sizeof(T)) + 4.0 * (double) F;
+    st.G = (int) std::max(1.0, std::min((double) st.nb, 48.0e6 / std::max(1.0, bytes_per_block)));
+    if (c.opt_sparse_group > 0) { st.G = (int) std::min<int64_t>(c.opt_sparse_group, st.nb); }
+    st.ng = (st.nb + st.G - 1) / st.G;
+    build_transpose<T>(c, st, h);
+    const size_t per_warp = (size_t) W * 4 * (sizeof(T) == 4 ? 2 : 3) + (size_t) W / 8 + (size_t) W * 2;
     st.warps = (int) std::min<size_t>(32, (size_t) (220 * 1024) / per_warp);
     st.smem = per_warp * (size_t) st.warps;
     set_kmv_attributes<T>(st.smem);
-    // keep the B slices of one launch L2-resident (~64 MB)
-    const double bytes_per_block = (double) st.b_entries / std::max(1, st.nb) * (st.fp22 ? 4.0 : 2.0 + sizeof(T)) + 4.0 * (double) (F + 1);
-    st.blocks_per_launch = (int) std::max(1.0, std::min((double) st.nb, 64.0e6 / std::max(1.0, bytes_per_block)));
     // per-row norms, u = exp(-gamma |x|^2), work vectors
     st.norms.reserve((size_t) n * sizeof(T));
     st.u.reserve((size_t) n * sizeof(T));
@@ -571,8 +731,16 @@ namespace {
         }                                                   \
     } while (0)
 
-sp::kfun make_kfun(const ctx &c) {
+// max_norm2 bounds |G_ij| and every partial sum of its products (Cauchy-Schwarz): scale = 2^(BITS - ceil(log2 bound))
+sp::kfun make_kfun(const ctx &c, double max_norm2 = 1.0) {
     sp::kfun k{};
+    {
+        const int bits = c.dtype == B200SVM_F32 ? 42 : 61;
+        int e = 0;
+        if (max_norm2 > 0 && std::isfinite(max_norm2)) { std::frexp(max_norm2, &e); }  // max_norm2 < 2^e
+        k.fx_scale = std::ldexp(1.0, bits - e);
+        k.fx_inv = std::ldexp(1.0, e - bits);
+    }
     k.degree = c.degree;
     k.coef0 = c.coef0;
     if (c.kernel == B200SVM_RBF) {
@@ -585,27 +753,62 @@ sp::kfun make_kfun(const ctx &c) {
     return k;
 }
 
-// out[row] (rows [lo, hi) of A, zero on entry) += sum_j S(G_row,j) v_j over all column blocks
-template <typename T>
-void launch_kmv(ctx &c, const sparse_state &st, const sp::csr_view &A, int64_t lo, int64_t hi, const T *v, T *out) {
-    if (hi <= lo) { return; }
-    const sp::blk_view B = view_blocks(st);
-    const sp::kfun kf = make_kfun(c);
+// out[row] (rows [lo, hi) of A, zero on entry) += sum_j S(G_row,j) v_j over all column groups; max_row = longest row of A
+template <typename T, int KERNEL, bool FP22>
+void launch_kmv_variant(ctx &c, const sparse_state &st, const sp::csr_view &A, int64_t lo, int64_t hi, int64_t max_row, double max_norm2,
+                        const T *v, T *out) {
+    const sp::csc_view B = view_blocks(st);
+    const sp::kfun kf = make_kfun(c, max_norm2);
     const int64_t rows = hi - lo;
-    const int grid = (int) std::min<int64_t>(NUM_SMS, (rows + st.warps - 1) / st.warps);
-    const int threads = st.warps * 32;
-    for (int b0 = 0; b0 < st.nb; b0 += st.blocks_per_launch) {
-        const int b1 = std::min(st.nb, b0 + st.blocks_per_launch);
-        if (c.kernel == B200SVM_RBF) {
-            B200_SP_DISPATCH_FP22(st, T, (sp::k_sp_kmv<T, B200SVM_RBF, true><<<grid, threads, st.smem, c.stream>>>(A, lo, hi, B, b0, b1, v, kf, out)),
-                                  (sp::k_sp_kmv<T, B200SVM_RBF, false><<<grid, threads, st.smem, c.stream>>>(A, lo, hi, B, b0, b1, v, kf, out)));
+    B200_REQUIRE(max_row <= 1024, "rows with more than 1024 stored entries are not supported by the sparse path: pass the data dense");
+    const int K = max_row <= 128 ? 4 : (max_row <= 256 ? 8 : 32);
+    const int warps = std::min(st.warps, K == 4 ? 32 : (K == 8 ? 16 : 8));
+    const int grid = (int) std::min<int64_t>(NUM_SMS, (rows + warps - 1) / warps);
+    const size_t smem = st.smem / (size_t) st.warps * (size_t) warps;
+    const bool compact = st.fill < 0.5;
+    // lanes per (feature, block) segment: one lane walks its own features unless the segments are long (measured on B200:
+    // 8 lanes per segment only pays beyond ~64 entries per segment)
+    const int gs = c.opt_sparse_lanes > 0 ? (int) c.opt_sparse_lanes : (st.avg_seg < 64.0 ? 1 : 8);
+    for (int g = 0; g < st.ng; ++g) {
+#define B200_SP_LAUNCH_G(KK, MT, CP)                                                                                               \
+    do {                                                                                                                           \
+        if (gs == 1) {                                                                                                             \
+            sp::k_sp_kmv<T, KERNEL, FP22, KK, MT, CP, 1><<<grid, warps * 32, smem, c.stream>>>(A, lo, hi, B, g, v, kf, out);       \
+        } else {                                                                                                                   \
+            sp::k_sp_kmv<T, KERNEL, FP22, KK, MT, CP, 8><<<grid, warps * 32, smem, c.stream>>>(A, lo, hi, B, g, v, kf, out);       \
+        }                                                                                                                          \
+    } while (0)
+#define B200_SP_LAUNCH(KK, MT)                \
+    do {                                      \
+        if (compact) {                        \
+            B200_SP_LAUNCH_G(KK, MT, true);   \
+        } else {                              \
+            B200_SP_LAUNCH_G(KK, MT, false);  \
+        }                                     \
+    } while (0)
+        if (K == 4) {
+            B200_SP_LAUNCH(4, 1024);
+        } else if (K == 8) {
+            B200_SP_LAUNCH(8, 512);
         } else {
-            B200_SP_DISPATCH_FP22(st, T,
-                                  (sp::k_sp_kmv<T, B200SVM_POLYNOMIAL, true><<<grid, threads, st.smem, c.stream>>>(A, lo, hi, B, b0, b1, v, kf, out)),
-                                  (sp::k_sp_kmv<T, B200SVM_POLYNOMIAL, false><<<grid, threads, st.smem, c.stream>>>(A, lo, hi, B, b0, b1, v, kf, out)));
+            B200_SP_LAUNCH(32, 256);
         }
+#undef B200_SP_LAUNCH_G
+#undef B200_SP_LAUNCH
         count_launch(c);
         B200_CUDA_CHECK(cudaGetLastError());
+    }
+}
+
+template <typename T>
+void launch_kmv(ctx &c, const sparse_state &st, const sp::csr_view &A, int64_t lo, int64_t hi, int64_t max_row, double max_norm2, const T *v, T *out) {
+    if (hi <= lo) { return; }
+    if (c.kernel == B200SVM_RBF) {
+        B200_SP_DISPATCH_FP22(st, T, (launch_kmv_variant<T, B200SVM_RBF, true>(c, st, A, lo, hi, max_row, max_norm2, v, out)),
+                              (launch_kmv_variant<T, B200SVM_RBF, false>(c, st, A, lo, hi, max_row, max_norm2, v, out)));
+    } else {
+        B200_SP_DISPATCH_FP22(st, T, (launch_kmv_variant<T, B200SVM_POLYNOMIAL, true>(c, st, A, lo, hi, max_row, max_norm2, v, out)),
+                              (launch_kmv_variant<T, B200SVM_POLYNOMIAL, false>(c, st, A, lo, hi, max_row, max_norm2, v, out)));
     }
 }
 
@@ -631,7 +834,7 @@ void row_dot(ctx &c, const sparse_state &st, const sp::csr_view &A, const T *w, 
 
 template <typename T>
 void xt_v_blocks(ctx &c, const sparse_state &st, const T *v, T *w) {
-    const sp::blk_view B = view_blocks(st);
+    const sp::csc_view B = view_blocks(st);
     const unsigned grid = (unsigned) ((st.F + 255) / 256);
     B200_SP_DISPATCH_FP22(st, T, (sp::k_sp_xt_v<T, true><<<grid, 256, 0, c.stream>>>(B, v, w)), (sp::k_sp_xt_v<T, false><<<grid, 256, 0, c.stream>>>(B, v, w)));
     count_launch(c);
@@ -689,7 +892,7 @@ void sp_kernel_matvec(ctx &c, const T *d, T *out) {
     const bool rbf = c.kernel == B200SVM_RBF;
     weights<T>(c, d, rbf ? st.u.as<T>() : static_cast<const T *>(nullptr), m, nbW, v);
     B200_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t) m * sizeof(T), c.stream));
-    launch_kmv<T>(c, st, view_rows(st, 0, st.n), lo, hi, v, out);
+    launch_kmv<T>(c, st, view_rows(st, 0, st.n), lo, hi, st.a_max_row, st.max_norm2, v, out);
     const sp::kfun kf = make_kfun(c);
     int64_t g = std::max<int64_t>(1, std::min<int64_t>((m + 1023) / 1024, 8 * NUM_SMS));
     sp::k_sp_finish<T><<<(unsigned) g, 256, 0, c.stream>>>(out, st.u.as<T>(), m, lo, hi, rbf ? 1 : 0, (T) kf.c0pow, c.scal.as<T>(), S_TMP0, T(0),
@@ -759,7 +962,26 @@ void sp_predict(ctx &c, const T *alpha_dev, T bias, const int64_t *rowptr, const
             st.p_u.reserve((size_t) rows * sizeof(T));
             norms_and_u<T>(c, st, A, st.p_norms.as<T>(), st.p_u.as<T>());
             B200_CUDA_CHECK(cudaMemsetAsync(st.p_out.p, 0, (size_t) rows * sizeof(T), c.stream));
-            launch_kmv<T>(c, st, A, 0, rows, st.v.as<T>(), st.p_out.as<T>());
+            int64_t max_row = 0;
+            double max_norm2 = st.max_norm2;
+            for (int64_t i = 0; i < rows; ++i) {
+                max_row = std::max(max_row, rp[(size_t) i + 1] - rp[(size_t) i]);
+                double nrm = 0;
+                for (int64_t p = rowptr[r0 + i]; p < rowptr[r0 + i + 1]; ++p) {
+                    double x;
+                    if (st.fp22) {
+                        const uint32_t vb = static_cast<const uint32_t *>(values)[p] & 0xFFFFFC00u;
+                        float xf;
+                        std::memcpy(&xf, &vb, 4);
+                        x = xf;
+                    } else {
+                        x = fmt == B200SVM_VAL_F32 ? (double) static_cast<const float *>(values)[p] : static_cast<const double *>(values)[p];
+                    }
+                    nrm += x * x;
+                }
+                max_norm2 = std::max(max_norm2, nrm);
+            }
+            launch_kmv<T>(c, st, A, 0, rows, max_row, max_norm2, st.v.as<T>(), st.p_out.as<T>());
             const sp::kfun kf = make_kfun(c);
             int64_t g = std::max<int64_t>(1, std::min<int64_t>((rows + 1023) / 1024, 8 * NUM_SMS));
             sp::k_sp_finish<T><<<(unsigned) g, 256, 0, c.stream>>>(st.p_out.as<T>(), st.p_u.as<T>(), rows, 0, rows, rbf ? 1 : 0, (T) kf.c0pow,

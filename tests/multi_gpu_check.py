@@ -38,13 +38,22 @@ def main():
     cases = [("rbf", np.float32, capi.PATH_TC, 1500, 96), ("polynomial", np.float32, capi.PATH_TC, 1100, 70),
              ("rbf", np.float32, capi.PATH_SIMT, 900, 64), ("rbf", np.float64, capi.PATH_AUTO, 1200, 80),
              ("polynomial", np.float64, capi.PATH_AUTO, 700, 33), ("linear", np.float64, capi.PATH_AUTO, 1000, 50)]
+    cases += [("rbf", np.float64, "csr", 1300, 900), ("polynomial", np.float64, "csr", 800, 500), ("linear", np.float64, "csr", 600, 700)]
     for kernel, dt, path, n, F in cases:
-        X, y = datagen.make_dense(n, F, seed=n, problem="planes", dtype=dt)
+        if path == "csr":
+            rp, ci, v, y = datagen.make_sparse_csr(n, F, 0.02, seed=n, dtype=dt)
+            X = datagen.csr_to_dense(rp, ci, v, F)
+        else:
+            X, y = datagen.make_dense(n, F, seed=n, problem="planes", dtype=dt)
         with capi.Handle(dt, kernel, gamma=1.0 / F, device=local) as h:
-            if path:
+            if path and path != "csr":
                 h.set_option(capi.OPT_MATVEC_PATH, path)
             h.comm_init(fresh_uid(), rank, world)
-            h.set_data(X)
+            if path == "csr":
+                h.set_option(capi.OPT_SPARSE_BLOCK, 256)
+                h.set_data_csr(rp, ci, v, F)
+            else:
+                h.set_data(X)
             alpha, rho, it = h.learn(y, eps=1e-3)
             st = h.stats()
         a_o, rho_o, it_o = port.learn(X.astype(np.float64), y.astype(np.float64), kernel, eps=1e-3, use_rows=True)
@@ -55,7 +64,7 @@ def main():
         ref = t.clone()
         dist.broadcast(ref, 0)
         same = bool(torch.equal(t, ref))
-        good = it == it_o and err < tol and same and (world == 1 or st.collectives > 0 or kernel == "linear")
+        good = it == it_o and err < tol and same and (world == 1 or st.collectives > 0 or (kernel == "linear" and path != "csr"))
         ok &= good
         if rank == 0:
             print(f"[{world} ranks] {kernel:10s} {np.dtype(dt).name} path={st.matvec_path} iters={it}/{it_o} alpha_relerr={err:.2e} "

@@ -151,6 +151,58 @@ def test_csr_predict_and_update_w(kernel, dt):
             assert nrm_rel(w_o, w) < (1e-13 if dt == np.float64 else 1e-5)
 
 
+@pytest.mark.parametrize("dt", [np.float64, np.float32])
+@pytest.mark.parametrize("kernel", ["polynomial", "rbf"])
+@pytest.mark.parametrize("shape", [(300, 2000, 0.1, 128, 1), (200, 1500, 0.4, 128, 1), (900, 500, 0.05, 128, 2), (1000, 3000, 0.01, 256, 1)])
+def test_csr_long_rows_and_launch_groups(kernel, dt, shape):
+    """Rows of > 128 / > 256 stored entries (8 / 32 features per lane) and several launch groups (cursor restart per group)."""
+    n, F, density, W, G = shape
+    rp, ci, v, _ = make(n, F, density, seed=n, dt=dt)
+    d = np.random.default_rng(n).uniform(-1, 2, n - 1).astype(dt)
+    with capi.Handle(dt, kernel, 2, 1.0 / F, 0.0, 1.0) as h:
+        h.set_option(capi.OPT_SPARSE_BLOCK, W)
+        h.set_option(capi.OPT_SPARSE_GROUP, G)
+        h.set_data_csr(rp, ci, v, F)
+        q = h.generate_q()
+        qa = h.kxx_last() + 1.0
+        h.set_q(q, qa)
+        got = h.matvec(d, 1.0)
+    want = port.csr_matvec(rp, ci, v.astype(np.float64), F, q.astype(np.float64), d.astype(np.float64), qa, 1.0, kernel, 2, 1.0 / F, 0.0, 1.0)
+    assert nrm_rel(want, got) < (1e-12 if dt == np.float64 else 2e-5), nrm_rel(want, got)
+
+
+def test_fp22_launch_groups():
+    n, F = 700, 3000
+    rp, ci, v, _ = make(n, F, 0.01, seed=77, dt=np.float32)
+    prp, packed = datagen.pack_fp22_csr(rp, ci, v)
+    vq = datagen.fp22_round(v)
+    d = np.random.default_rng(3).uniform(-1, 2, n - 1).astype(np.float32)
+    outs = []
+    for G in (1, 2, 0):
+        with capi.Handle(np.float32, "rbf", 3, 1.0 / F, 0.0, 1.0) as h:
+            h.set_option(capi.OPT_SPARSE_BLOCK, 128)
+            h.set_option(capi.OPT_SPARSE_GROUP, G)
+            h.set_data_csr(prp, None, packed, F, value_format=capi.VAL_FP22)
+            q = h.generate_q()
+            h.set_q(q, h.kxx_last() + 1.0)
+            outs.append(h.matvec(d, 1.0))
+    want = port.csr_matvec(rp, ci, vq.astype(np.float64), F, q.astype(np.float64), d.astype(np.float64), float(h.np_dtype.type(2.0)), 1.0, "rbf", 3, 1.0 / F, 0.0, 1.0)
+    for o in outs:
+        assert nrm_rel(want, o) < 2e-5
+    assert nrm_rel(outs[0], outs[2]) < 1e-6
+
+
+def test_csr_row_too_long_is_rejected():
+    n, F = 40, 3000
+    rp, ci, v, _ = make(n, F, 0.5, seed=1, dt=np.float64)
+    with capi.Handle(np.float64, "rbf", gamma=1.0 / F) as h:
+        h.set_data_csr(rp, ci, v, F)
+        q = h.generate_q()
+        h.set_q(q, 2.0)
+        with pytest.raises(capi.B200Error, match="1024 stored entries"):
+            h.matvec(np.ones(n - 1))
+
+
 def test_csr_errors_are_loud():
     with capi.Handle(np.float64, "rbf", gamma=0.5) as h:
         rp = np.array([0, 2, 3], np.int64)
