@@ -1,0 +1,126 @@
+"""Drop-in boundary: the reference's own base class (plssvm::csvm<T>::learn / predict_label / accuracy, compiled unmodified
+from /root/reference) driving libb200svm.so through the B200 backend subclass of integration/ — built by `make -C oracle backend`
+into oracle/_ref/libplssvm_b200_backend.so.
+
+CPU part: the library loads, and without a GPU the backend constructor fails loudly with plssvm::b200::backend_exception (no CPU
+fallback).  GPU part (-m gpu): learn() through the reference control flow matches the reference's OpenMP backend (oracle/_ref) and
+the golden predict labels.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from conftest import nrm_rel
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(ROOT, "oracle", "_ref", "libplssvm_b200_backend.so")
+KERNELS = {"linear": 0, "polynomial": 1, "rbf": 2}
+
+needs_lib = pytest.mark.skipif(not os.path.exists(LIB), reason="oracle/_ref/libplssvm_b200_backend.so not built (needs /root/reference at build time)")
+
+
+def load():
+    L = C.CDLL(LIB)
+    vp, i, d, l = C.c_void_p, C.c_int, C.c_double, C.c_long
+    L.b200int_last_error.restype = C.c_char_p
+    L.b200int_learn.argtypes = [i, i, i, d, d, d, d, i, vp, vp, l, l, vp, C.POINTER(d), C.POINTER(l), C.POINTER(i), C.POINTER(d)]
+    L.b200int_predict.argtypes = [i, i, i, d, d, vp, vp, l, l, d, vp, l, l, vp, vp]
+    return L
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def learn(L, X, y, kernel, eps=1e-3, gamma=None, target=0):
+    X = np.ascontiguousarray(X)
+    y = np.ascontiguousarray(y, X.dtype)
+    n, F = X.shape
+    alpha = np.empty(n, X.dtype)
+    rho, it, sp, acc = C.c_double(0), C.c_long(0), C.c_int(0), C.c_double(0)
+    rc = L.b200int_learn(0 if X.dtype == np.float32 else 1, KERNELS[kernel], 3, 1.0 / F if gamma is None else gamma, 0.0, 1.0, eps, target, _p(X), _p(y), n, F,
+                         _p(alpha), C.byref(rho), C.byref(it), C.byref(sp), C.byref(acc))
+    return rc, alpha, rho.value, it.value, sp.value, acc.value
+
+
+@needs_lib
+def test_backend_library_loads_and_fails_loudly_without_gpu():
+    L = load()
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the gpu tests")
+    X = np.random.default_rng(0).standard_normal((8, 3))
+    rc, *_ = learn(L, X, np.sign(X[:, 0]), "linear")
+    assert rc == 3  # plssvm::b200::backend_exception
+    msg = L.b200int_last_error().decode()
+    assert "b200::backend_exception" in msg and "no CPU fallback" in msg
+
+
+@needs_lib
+def test_invalid_target_platform_message():
+    """Same text shape as the reference asserts for its CUDA backend (tests/backends/CUDA/test.cpp:55)."""
+    L = load()
+    X = np.random.default_rng(0).standard_normal((8, 3))
+    rc, *_ = learn(L, X, np.sign(X[:, 0]), "linear", target=1)  # target_platform::cpu
+    assert rc == 3
+    assert "Invalid target platform 'cpu' for the B200 backend!" in L.b200int_last_error().decode()
+
+
+@needs_lib
+@pytest.mark.gpu
+@pytest.mark.parametrize("kernel", ["linear", "polynomial", "rbf"])
+def test_reference_learn_flow_on_b200_backend(golden, kernel):
+    from oracle import ref
+    L = load()
+    g = golden("train_500x200.npz")
+    X, y = g["X"], g["y"]
+    rc, alpha, rho, it, sp, acc = learn(L, X, y, kernel)
+    assert rc == 0, L.b200int_last_error()
+    key = f"f64/{kernel}/0.001"
+    assert it == int(g[key + "/iters"])
+    assert nrm_rel(g[key + "/alpha"], alpha) < max(1e-10, 10 * float(g[key + "/spread_alpha"]))
+    assert sp == 0 and acc > 0.9
+    if ref.available():
+        ref.set_num_threads(1)
+        a_r, rho_r, it_r = ref.learn(X, y, kernel, eps=1e-3)[:3]
+        assert it == it_r
+        assert nrm_rel(a_r, alpha) < 1e-10
+
+
+@needs_lib
+@pytest.mark.gpu
+def test_reference_learn_flow_picks_sparse_rows():
+    from oracle import port
+    from plssvm_sparse_fp22_b200 import datagen
+    L = load()
+    rp, ci, v, y = datagen.make_sparse_csr(700, 900, 0.01, seed=12, dtype=np.float64)
+    X = datagen.csr_to_dense(rp, ci, v, 900)
+    rc, alpha, rho, it, sp, acc = learn(L, X, y, "rbf")
+    assert rc == 0, L.b200int_last_error()
+    assert sp == 1
+    a_o, rho_o, it_o = port.learn(X, y, "rbf", eps=1e-3, use_rows=True)
+    assert it == it_o and nrm_rel(a_o, alpha) < 1e-10
+
+
+@needs_lib
+@pytest.mark.gpu
+@pytest.mark.parametrize("kernel", ["linear", "polynomial", "rbf"])
+def test_reference_predict_label_on_b200_backend(golden, kernel):
+    L = load()
+    g = golden("predict_500x200.npz")
+    degree, gamma, coef0, rho = g[f"{kernel}/params"]
+    X, alpha, pts = g[f"{kernel}/X"], g[f"{kernel}/alpha"], g["points"]
+    dec = np.empty(pts.shape[0])
+    lab = np.empty(pts.shape[0])
+    rc = L.b200int_predict(1, KERNELS[kernel], int(degree), gamma if gamma > 0 else 1.0 / 200, coef0, _p(X), _p(alpha), X.shape[0], X.shape[1], rho,
+                           _p(pts), pts.shape[0], pts.shape[1], _p(dec), _p(lab))
+    assert rc == 0, L.b200int_last_error()
+    assert np.array_equal(lab, g["expected_labels"])
+    assert nrm_rel(g[f"{kernel}/decision"], dec) < 1e-12
+    # reference error text for a feature-count mismatch (src/plssvm/backends/OpenMP/csvm.cpp:205-206)
+    bad = np.ascontiguousarray(pts[:, :-1])
+    rc = L.b200int_predict(1, KERNELS[kernel], int(degree), 0.005, coef0, _p(X), _p(alpha), X.shape[0], X.shape[1], rho, _p(bad), bad.shape[0], bad.shape[1],
+                           _p(dec), None)
+    assert rc == 2 and "must match the number of features per predict point" in L.b200int_last_error().decode()
