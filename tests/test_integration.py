@@ -81,7 +81,12 @@ def test_reference_learn_flow_on_b200_backend(golden, kernel):
     key = f"f64/{kernel}/0.001"
     assert it == int(g[key + "/iters"])
     assert nrm_rel(g[key + "/alpha"], alpha) < max(1e-10, 10 * float(g[key + "/spread_alpha"]))
-    assert sp == 0 and acc > 0.9
+    # accuracy() of the reference base class over our predict(): equal to the oracle's (the linear kernel stops after ONE CG
+    # iteration at eps = 1e-3 on this fixture and is only 42.4 % accurate in the reference as well)
+    from oracle import port
+    a_o, rho_o, _ = port.learn(X, y, kernel, eps=1e-3, use_rows=True)
+    acc_o = float((port.predict(X, a_o, rho_o, X, kernel) * y > 0).mean())
+    assert sp == 0 and abs(acc - acc_o) < 1e-12
     if ref.available():
         ref.set_num_threads(1)
         a_r, rho_r, it_r = ref.learn(X, y, kernel, eps=1e-3)[:3]
