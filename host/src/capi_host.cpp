@@ -1,0 +1,98 @@
+// Test hooks (extern "C") over the host's parsers / writer so that tests/test_host_formats.py can compare them with the
+// reference's own parsers compiled into oracle/_ref (oracle/ref_driver.cpp oref_parse_*).  Not needed by the executables.
+#include "plssvm/core.hpp"
+
+#include <cstring>
+#include <string>
+
+namespace {
+thread_local std::string g_err;
+
+template <typename T, typename F>
+int guarded(F &&f) {
+    try {
+        g_err.clear();
+        f();
+        return 0;
+    } catch (const plssvm::invalid_file_format_exception &e) {
+        g_err = e.what();
+        return 2;
+    } catch (const plssvm::file_not_found_exception &e) {
+        g_err = e.what();
+        return 3;
+    } catch (const std::exception &e) {
+        g_err = e.what();
+        return 1;
+    }
+}
+
+template <typename T>
+void copy_dense(const plssvm::csr_matrix<T> &m, void *X_out) {
+    if (X_out == nullptr) { return; }
+    T *x = static_cast<T *>(X_out);
+    std::memset(x, 0, m.rows * m.cols * sizeof(T));
+    for (std::size_t i = 0; i < m.rows; ++i) {
+        for (std::int64_t p = m.rowptr[i]; p < m.rowptr[i + 1]; ++p) { x[i * m.cols + (std::size_t) m.col[(std::size_t) p]] = m.val[(std::size_t) p]; }
+    }
+}
+
+template <typename T>
+int parse_data(const char *path, long *n, long *F, long *nnz, int *has_labels, void *X_out, void *y_out, double *gamma_out) {
+    return guarded<T>([&]() {
+        plssvm::parameter<T> p;
+        p.print_info = false;
+        const std::string file{ path };
+        if (file.size() >= 5 && file.substr(file.size() - 5) == ".arff") {
+            p.parse_arff_file(file);
+        } else {
+            p.parse_libsvm_file(file);
+        }
+        *n = (long) p.sparse_data_ptr->rows;
+        *F = (long) p.sparse_data_ptr->cols;
+        *nnz = (long) p.sparse_data_ptr->nnz();
+        *has_labels = p.value_ptr != nullptr;
+        if (gamma_out != nullptr) { *gamma_out = (double) p.gamma; }
+        copy_dense(*p.sparse_data_ptr, X_out);
+        if (y_out != nullptr && p.value_ptr != nullptr) { std::memcpy(y_out, p.value_ptr->data(), p.value_ptr->size() * sizeof(T)); }
+    });
+}
+
+template <typename T>
+int parse_model(const char *path, int *kernel, int *degree, double *gamma, double *coef0, double *rho, long *n, long *F, void *X_out, void *alpha_out,
+                void *y_out) {
+    return guarded<T>([&]() {
+        plssvm::parameter<T> p;
+        p.print_info = false;
+        p.parse_model_file(path);
+        *kernel = (int) p.kernel;
+        *degree = p.degree;
+        *gamma = (double) p.gamma;
+        *coef0 = (double) p.coef0;
+        *rho = (double) p.rho;
+        *n = (long) p.sparse_data_ptr->rows;
+        *F = (long) p.sparse_data_ptr->cols;
+        copy_dense(*p.sparse_data_ptr, X_out);
+        if (alpha_out != nullptr) { std::memcpy(alpha_out, p.alpha_ptr->data(), p.alpha_ptr->size() * sizeof(T)); }
+        if (y_out != nullptr && p.value_ptr != nullptr) { std::memcpy(y_out, p.value_ptr->data(), p.value_ptr->size() * sizeof(T)); }
+    });
+}
+}  // namespace
+
+extern "C" {
+const char *b200host_last_error() { return g_err.c_str(); }
+int b200host_parse_data_file(int dtype, const char *path, long *n, long *F, long *nnz, int *has_labels, void *X_out, void *y_out, double *gamma_out) {
+    return dtype == 0 ? parse_data<float>(path, n, F, nnz, has_labels, X_out, y_out, gamma_out) : parse_data<double>(path, n, F, nnz, has_labels, X_out, y_out, gamma_out);
+}
+int b200host_parse_model_file(int dtype, const char *path, int *kernel, int *degree, double *gamma, double *coef0, double *rho, long *n, long *F, void *X_out,
+                              void *alpha_out, void *y_out) {
+    return dtype == 0 ? parse_model<float>(path, kernel, degree, gamma, coef0, rho, n, F, X_out, alpha_out, y_out)
+                      : parse_model<double>(path, kernel, degree, gamma, coef0, rho, n, F, X_out, alpha_out, y_out);
+}
+int b200host_format_shortest(int dtype, double v, char *out, int cap) {
+    const std::string s = dtype == 0 ? plssvm::detail::format_shortest((float) v) : plssvm::detail::format_shortest(v);
+    if ((int) s.size() + 1 > cap) { return 1; }
+    std::memcpy(out, s.c_str(), s.size() + 1);
+    return 0;
+}
+unsigned b200host_fp22_encode(float x) { return plssvm::detail::fp22_encode(x); }
+}  // extern "C"

@@ -113,7 +113,7 @@ def write_libsvm(path: str, X: np.ndarray, y=None, one_based: bool = False) -> N
     with open(path, "w") as f:
         for i in range(X.shape[0]):
             nz = np.nonzero(X[i])[0]
-            feats = " ".join(f"{j + off}:{X[i, j]!r}" if X.dtype == np.float64 else f"{j + off}:{float(X[i, j]):.9g}" for j in nz)
+            feats = " ".join(f"{j + off}:{float(X[i, j])!r}" if X.dtype == np.float64 else f"{j + off}:{float(X[i, j]):.9g}" for j in nz)
             if y is not None:
                 lab = int(y[i]) if float(y[i]).is_integer() else float(y[i])
                 f.write(f"{lab} {feats}\n")
