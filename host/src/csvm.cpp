@@ -87,10 +87,7 @@ csvm<T>::csvm(const parameter<T> &params) :
         throw exception{ "Number of weights (" + std::to_string(alpha_ptr_->size()) + ") must match the number of data points (" +
                          std::to_string(num_data_points_) + ")!" };
     }
-    if (value_ptr_ != nullptr && value_ptr_->size() != num_data_points_) {
-        throw exception{ "Number of labels (" + std::to_string(value_ptr_->size()) + ") must match the number of data points (" +
-                         std::to_string(num_data_points_) + ")!" };
-    }
+    // (no label-count check here: plssvm-predict hands over the TEST labels next to the model's support vectors, src/main_predict.cpp:92-105)
     if (target_ != target_platform::automatic && target_ != target_platform::gpu_nvidia) {
         throw b200::backend_exception{ "Invalid target platform '" + to_text(target_) + "' for the B200 backend!" };
     }
@@ -144,6 +141,10 @@ void csvm<T>::setup_data_on_device() {
 template <typename T>
 void csvm<T>::learn() {
     if (value_ptr_ == nullptr) { throw exception{ "No labels given for training! Maybe the data is only usable for prediction?" }; }  // csvm.cpp:214
+    if (value_ptr_->size() != num_data_points_) {
+        throw exception{ "Number of labels (" + std::to_string(value_ptr_->size()) + ") must match the number of data points (" +
+                         std::to_string(num_data_points_) + ")!" };
+    }
     const auto t0 = std::chrono::steady_clock::now();
     setup_data_on_device();
     const auto t1 = std::chrono::steady_clock::now();
@@ -280,6 +281,9 @@ void csvm<T>::write_model(const std::string &model_name) {
         throw exception{ "No alphas given! Maybe a call to 'learn()' is missing?" };
     } else if (value_ptr_ == nullptr) {
         throw exception{ "No labels given! Maybe the data is only usable for prediction?" };
+    } else if (value_ptr_->size() != num_data_points_) {
+        throw exception{ "Number of labels (" + std::to_string(value_ptr_->size()) + ") must match the number of data points (" +
+                         std::to_string(num_data_points_) + ")!" };  // src/plssvm/csvm.cpp:69-71
     }
     unsigned long long count_pos = 0, count_neg = 0;
     for (const T v : *value_ptr_) {

