@@ -115,6 +115,7 @@ int b200svm_partition_tiles(int64_t n, int rank, int world, int64_t *first, int6
 #define B200SVM_OPT_SYNC_EVERY 2  /* CG: host polls the convergence flag every k iterations (default 1)            */
 #define B200SVM_OPT_SPARSE_GROUP 4 /* CSR paths: blocks per launch group (0 = sized so that a group's slice of the transpose fits L2) */
 #define B200SVM_OPT_SPARSE_LANES 5 /* CSR paths: lanes sharing one (feature, block) segment: 0 auto, 1 or 8 */
+#define B200SVM_OPT_TC_MODE 6 /* tcgen05 path, cross terms of the fp16x2 split: 0 = default (fp8 chain), 1 = three f16 MMAs, 2 = fp8 chain; set before set_data */
 #define B200SVM_OPT_SPARSE_BLOCK 3 /* CSR paths: columns of the implicit matrix per block (power of two, 128..4096; set before set_data_csr) */
 int b200svm_set_option(b200svm_handle h, int option, int64_t value);
 

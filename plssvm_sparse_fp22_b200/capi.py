@@ -16,7 +16,8 @@ LIB_PATH = os.path.join(HERE, "libb200svm.so")
 F32, F64 = 0, 1
 KERNELS = {"linear": 0, "polynomial": 1, "rbf": 2}
 VAL_F32, VAL_F64, VAL_FP22 = 0, 1, 2
-OPT_MATVEC_PATH, OPT_SYNC_EVERY, OPT_SPARSE_BLOCK, OPT_SPARSE_GROUP, OPT_SPARSE_LANES = 1, 2, 3, 4, 5
+OPT_MATVEC_PATH, OPT_SYNC_EVERY, OPT_SPARSE_BLOCK, OPT_SPARSE_GROUP, OPT_SPARSE_LANES, OPT_TC_MODE = 1, 2, 3, 4, 5, 6
+TC_F16X3, TC_FP8X = 1, 2
 PATH_AUTO, PATH_SIMT, PATH_TC = 0, 1, 2
 
 # every symbol include/b200svm.h declares

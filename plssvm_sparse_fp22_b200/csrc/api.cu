@@ -192,6 +192,11 @@ int b200svm_set_option(b200svm_handle h, int option, int64_t value) {
                 B200_REQUIRE(value == 0 || (value >= 128 && value <= 4096 && (value & (value - 1)) == 0), "sparse block width must be 0 or a power of two in [128, 4096]");
                 c->opt_sparse_block = value;
                 break;
+            case B200SVM_OPT_TC_MODE:
+                B200_REQUIRE(value >= 0 && value <= 2, "tcgen05 mode must be 0 (default), 1 (f16 x 3) or 2 (fp8 cross terms)");
+                c->opt_tc_mode = value;
+                if (c->has_data && c->has_split) { tc_prepare_split(*c); }
+                break;
             case B200SVM_OPT_SPARSE_LANES:
                 B200_REQUIRE(value == 0 || value == 1 || value == 8, "lanes per segment must be 0, 1 or 8");
                 c->opt_sparse_lanes = value;

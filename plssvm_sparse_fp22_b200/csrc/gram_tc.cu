@@ -9,8 +9,13 @@
 //   a small deterministic pass (k_tc_reduce) then sums the partial vectors in a fixed order — no atomics.
 //
 // Precision: X is split once into two fp16 planes, x * s = hi + lo (s = power of two placing max|x| in [2^13, 2^14)), and
-//   G = (hi hi^T + hi lo^T + lo hi^T) / s^2 — three kind::f16 MMAs per K-slice, 22 significant bits per operand
-//   (the dropped lo lo^T term is 2^-22 relative).  See DESIGN.md "fp16x2 split" for the measured error.
+//   G = (hi hi^T + hi lo^T + lo hi^T) / s^2 (the dropped lo lo^T term is 2^-22 relative).  Two ways to form the cross terms:
+//   MODE_F16X3 : three kind::f16 MMAs per K-slice (22 significant bits per operand);
+//   MODE_FP8X  : hi hi^T in kind::f16, the two cross terms as ONE kind::f8f6f4 chain over K-concatenated e4m3 planes
+//                [hi8 | lo8] x [lo8 | hi8]^T with hi8 = e4m3(hi 2^-6), lo8 = e4m3(lo 2^6) — fp8 runs at twice the f16 rate, so a
+//                K-slice costs 2 instead of 3 pass-equivalents.  The cross terms are 2^-11 of the main term, their 4-bit
+//                operands make an error of ~2^-15 of a product: the same size as the fp32 accumulation noise of a 1024-term
+//                dot product (DESIGN.md §3.1 has the measured error of both modes).
 //
 // Structure (one persistent CTA per SM, 192 threads):
 //   warp 0 / lane 0 : TMA producer  — cp.async.bulk.tensor 2-D boxes (64 fp16 x 128 rows, SWIZZLE_128B) into a 2-stage ring
@@ -21,6 +26,7 @@
 
 #include <cuda.h>
 #include <cuda_fp16.h>
+#include <cuda_fp8.h>
 
 #include <algorithm>
 #include <cmath>
@@ -115,6 +121,16 @@ __device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t desc_a, uin
         "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+__device__ __forceinline__ void tc_mma_f8(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -188,9 +204,13 @@ __device__ __forceinline__ float warp_column_sums(float (&v)[32], int lane) {
     return v[0];
 }
 
-template <int KERNEL>
+// FP8X: map_lo / map_b are the e4m3 planes [hi8 | lo8] (A role) and [lo8 | hi8] (B role), 128 bytes per 64-element K block;
+// otherwise map_lo is the fp16 lo plane and map_b is unused.  Stage layout (96 KB either way):
+//   F16X3: [A_hi 16K | A_lo 16K | B_hi 32K | B_lo 32K]        FP8X: [A_hi 16K | A_8 16K | B_hi 32K | B_8 32K]
+template <int KERNEL, bool FP8X>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-    k_gram_tc(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo, const params p) {
+    k_gram_tc(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo, const __grid_constant__ CUtensorMap map_b,
+              const params p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     const uint32_t sbase = smem_u32(smem);
@@ -230,6 +250,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         if (lane == 0) {
             asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_hi)) : "memory");
             asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_lo)) : "memory");
+            if constexpr (FP8X) { asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory"); }
             int stage = 0;
             uint32_t phase = 0;
             for (int t = first_tile; t < p.num_tiles; t += tile_step) {
@@ -242,11 +263,18 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
                     const uint32_t s0 = sbase + smem_layout::OPERANDS + stage * STAGE_BYTES;
                     const int kc = kb * BK;
                     tma_load_2d(s0, &map_hi, full, kc, row_a);                                  // A_hi  128 rows
-                    tma_load_2d(s0 + A_BYTES, &map_lo, full, kc, row_a);                        // A_lo
                     tma_load_2d(s0 + 2 * A_BYTES, &map_hi, full, kc, row_b);                    // B_hi  rows 0..127
                     tma_load_2d(s0 + 2 * A_BYTES + A_BYTES, &map_hi, full, kc, row_b + 128);    // B_hi  rows 128..255
-                    tma_load_2d(s0 + 2 * A_BYTES + B_BYTES, &map_lo, full, kc, row_b);          // B_lo
-                    tma_load_2d(s0 + 2 * A_BYTES + B_BYTES + A_BYTES, &map_lo, full, kc, row_b + 128);
+                    if constexpr (FP8X) {
+                        const int kc8 = kb * 128;  // bytes: [hi8 | lo8] of this K block
+                        tma_load_2d(s0 + A_BYTES, &map_lo, full, kc8, row_a);                               // A_8
+                        tma_load_2d(s0 + 2 * A_BYTES + B_BYTES, &map_b, full, kc8, row_b);                  // B_8
+                        tma_load_2d(s0 + 2 * A_BYTES + B_BYTES + A_BYTES, &map_b, full, kc8, row_b + 128);
+                    } else {
+                        tma_load_2d(s0 + A_BYTES, &map_lo, full, kc, row_a);                                // A_lo
+                        tma_load_2d(s0 + 2 * A_BYTES + B_BYTES, &map_lo, full, kc, row_b);                  // B_lo
+                        tma_load_2d(s0 + 2 * A_BYTES + B_BYTES + A_BYTES, &map_lo, full, kc, row_b + 128);
+                    }
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1;
@@ -277,8 +305,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
                     for (int k = 0; k < BK / UMMA_K; ++k) {
                         const uint64_t adv = static_cast<uint64_t>((k * UMMA_K * 2) >> 4);  // +32 bytes per K step inside the swizzle row
                         tc_mma_f16(tmem_d, a_hi + adv, b_hi + adv, idesc, (kb | k) != 0 ? 1u : 0u);
-                        tc_mma_f16(tmem_d, a_hi + adv, b_lo + adv, idesc, 1u);
-                        tc_mma_f16(tmem_d, a_lo + adv, b_hi + adv, idesc, 1u);
+                        if constexpr (FP8X) {
+                            // same 32-byte step: 32 e4m3 elements of [hi8 | lo8] x [lo8 | hi8]^T (idesc formats 0 = E4M3, same bit layout)
+                            tc_mma_f8(tmem_d, a_lo + adv, b_lo + adv, idesc, 1u);
+                        } else {
+                            tc_mma_f16(tmem_d, a_hi + adv, b_lo + adv, idesc, 1u);
+                            tc_mma_f16(tmem_d, a_lo + adv, b_hi + adv, idesc, 1u);
+                        }
                     }
                     tc_commit(bar_empty + stage * 8);  // frees the smem stage when these MMAs retire
                     if (++stage == STAGES) {
@@ -384,17 +417,30 @@ __global__ void __launch_bounds__(256) k_absmax(const float *__restrict__ X, int
     if ((threadIdx.x & 31) == 0) { atomicMax(out, __float_as_uint(mx)); }  // non-negative floats order like their bit patterns
 }
 
-// hi = fp16(x s), lo = fp16(x s - hi); rows >= n and columns >= ldx are zero
+// hi = fp16(x s), lo = fp16(x s - hi); rows >= n and columns >= ldx are zero.
+// FP8X planes (when pa != nullptr): per 64-element K block 128 bytes, pa = [e4m3(hi / 64) | e4m3(lo * 64)], pb = [e4m3(lo * 64) | e4m3(hi / 64)]
+// (hi < 2^14 -> hi / 64 < 256; |lo| <= 4 -> lo * 64 <= 256; e4m3 holds +-448).
 __global__ void __launch_bounds__(256) k_split_fp16(const float *__restrict__ X, int64_t n, int64_t ldx, float s, __half *__restrict__ hi,
-                                                    __half *__restrict__ lo, int64_t n_pad, int64_t ldh) {
+                                                    __half *__restrict__ lo, uint8_t *__restrict__ pa, uint8_t *__restrict__ pb, int64_t n_pad,
+                                                    int64_t ldh) {
     const int64_t total = n_pad * ldh;
     for (int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t) gridDim.x * blockDim.x) {
         const int64_t row = e / ldh, col = e - row * ldh;
         float x = 0.f;
         if (row < n && col < ldx) { x = X[row * ldx + col] * s; }
         const __half h = __float2half_rn(x);
+        const float l = x - __half2float(h);
         hi[e] = h;
-        lo[e] = __float2half_rn(x - __half2float(h));
+        if (lo != nullptr) { lo[e] = __float2half_rn(l); }
+        if (pa != nullptr) {
+            const uint8_t h8 = (uint8_t) __nv_cvt_float_to_fp8(__half2float(h) * 0.015625f, __NV_SATFINITE, __NV_E4M3);
+            const uint8_t l8 = (uint8_t) __nv_cvt_float_to_fp8(l * 64.f, __NV_SATFINITE, __NV_E4M3);
+            const int64_t base = row * (2 * ldh) + (col >> 6) * 128 + (col & 63);
+            pa[base] = h8;
+            pa[base + 64] = l8;
+            pb[base] = l8;
+            pb[base + 64] = h8;
+        }
     }
 }
 
@@ -428,8 +474,9 @@ __global__ void __launch_bounds__(256) k_tc_reduce(const float *__restrict__ Pr,
 namespace {
 
 struct tc_state {
-    CUtensorMap map_hi{}, map_lo{};
-    dbuf tiles, pk, Pr, Pc, amax;
+    CUtensorMap map_hi{}, map_lo{}, map_a8{}, map_b8{};
+    dbuf tiles, pk, Pr, Pc, amax, P8a, P8b;
+    bool fp8x{ false };
     int num_tiles{ 0 };
     int T_r{ 0 }, T_c{ 0 };
     int64_t ldP{ 0 };
@@ -460,13 +507,15 @@ encode_fn get_encode() {
     return fn;
 }
 
-void make_map(CUtensorMap *map, void *base, int64_t rows, int64_t ld_elems) {
+// 2-D map over a row-major plane, boxes of 128 bytes x 128 rows (64 fp16 or 128 e4m3 elements), SWIZZLE_128B
+void make_map(CUtensorMap *map, void *base, int64_t rows, int64_t ld_elems, bool bytes = false) {
     const cuuint64_t dims[2] = { (cuuint64_t) ld_elems, (cuuint64_t) rows };
-    const cuuint64_t strides[1] = { (cuuint64_t) ld_elems * 2 };
-    const cuuint32_t box[2] = { (cuuint32_t) tc::BK, 128u };
+    const cuuint64_t strides[1] = { (cuuint64_t) ld_elems * (bytes ? 1 : 2) };
+    const cuuint32_t box[2] = { bytes ? 128u : (cuuint32_t) tc::BK, 128u };
     const cuuint32_t estr[2] = { 1u, 1u };
-    const CUresult r = get_encode()(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    const CUresult r = get_encode()(map, bytes ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, base, dims, strides, box, estr,
+                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { fail(B200SVM_ERR_CUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string((int) r)); }
 }
 
@@ -519,13 +568,27 @@ void tc_prepare_split(ctx &c) {
     }
     c.split_scale = s;
     const size_t plane = (size_t) c.n_pad * c.ldh * sizeof(__half);
+    st.fp8x = c.opt_tc_mode != 1;  // 0 (default) / 2 = fp8 cross terms, 1 = three f16 MMAs
     c.Xh_hi.reserve(plane);
-    c.Xh_lo.reserve(plane);
-    tc::k_split_fp16<<<8 * NUM_SMS, 256, 0, c.stream>>>(c.X.as<float>(), c.n, c.ldx, s, c.Xh_hi.as<__half>(), c.Xh_lo.as<__half>(), c.n_pad, c.ldh);
+    if (st.fp8x) {
+        st.P8a.reserve(plane);  // 2 ldh bytes per row
+        st.P8b.reserve(plane);
+        tc::k_split_fp16<<<8 * NUM_SMS, 256, 0, c.stream>>>(c.X.as<float>(), c.n, c.ldx, s, c.Xh_hi.as<__half>(), nullptr, st.P8a.as<uint8_t>(),
+                                                             st.P8b.as<uint8_t>(), c.n_pad, c.ldh);
+    } else {
+        c.Xh_lo.reserve(plane);
+        tc::k_split_fp16<<<8 * NUM_SMS, 256, 0, c.stream>>>(c.X.as<float>(), c.n, c.ldx, s, c.Xh_hi.as<__half>(), c.Xh_lo.as<__half>(), nullptr, nullptr,
+                                                             c.n_pad, c.ldh);
+    }
     count_launch(c);
     B200_CUDA_CHECK(cudaGetLastError());
     make_map(&st.map_hi, c.Xh_hi.p, c.n_pad, c.ldh);
-    make_map(&st.map_lo, c.Xh_lo.p, c.n_pad, c.ldh);
+    if (st.fp8x) {
+        make_map(&st.map_a8, st.P8a.p, c.n_pad, 2 * c.ldh, true);
+        make_map(&st.map_b8, st.P8b.p, c.n_pad, 2 * c.ldh, true);
+    } else {
+        make_map(&st.map_lo, c.Xh_lo.p, c.n_pad, c.ldh);
+    }
 
     st.T_r = (int) (c.n_pad / tc::BM);
     st.T_c = (int) (c.n_pad / tc::BN);
@@ -542,8 +605,10 @@ void tc_prepare_split(ctx &c) {
     B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));  // `tiles` (host vector) must outlive the copy
     static bool attr_set = false;
     if (!attr_set) {
-        B200_CUDA_CHECK(cudaFuncSetAttribute(tc::k_gram_tc<B200SVM_RBF>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
-        B200_CUDA_CHECK(cudaFuncSetAttribute(tc::k_gram_tc<B200SVM_POLYNOMIAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+        B200_CUDA_CHECK(cudaFuncSetAttribute(tc::k_gram_tc<B200SVM_RBF, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+        B200_CUDA_CHECK(cudaFuncSetAttribute(tc::k_gram_tc<B200SVM_POLYNOMIAL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+        B200_CUDA_CHECK(cudaFuncSetAttribute(tc::k_gram_tc<B200SVM_RBF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+        B200_CUDA_CHECK(cudaFuncSetAttribute(tc::k_gram_tc<B200SVM_POLYNOMIAL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
         attr_set = true;
     }
     c.has_split = true;
@@ -578,10 +643,16 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out) {
     }
     tc::k_pack<<<(unsigned) ((c.n_pad + 255) / 256), 256, 0, c.stream>>>(c.norms.as<float>(), c.q.as<float>(), d, m, c.n_pad, cscale, st.pk.as<float4>());
     const int grid = std::min(NUM_SMS, std::max(st.num_tiles, 1));
-    if (c.kernel == B200SVM_RBF) {
-        tc::k_gram_tc<B200SVM_RBF><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_lo, p);
+    if (st.fp8x) {
+        if (c.kernel == B200SVM_RBF) {
+            tc::k_gram_tc<B200SVM_RBF, true><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_a8, st.map_b8, p);
+        } else {
+            tc::k_gram_tc<B200SVM_POLYNOMIAL, true><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_a8, st.map_b8, p);
+        }
+    } else if (c.kernel == B200SVM_RBF) {
+        tc::k_gram_tc<B200SVM_RBF, false><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_lo, st.map_lo, p);
     } else {
-        tc::k_gram_tc<B200SVM_POLYNOMIAL><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_lo, p);
+        tc::k_gram_tc<B200SVM_POLYNOMIAL, false><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_lo, st.map_lo, p);
     }
     tc::k_tc_reduce<<<(unsigned) ((m + 255) / 256), 256, 0, c.stream>>>(st.Pr.as<float>(), st.Pc.as<float>(), st.ldP, m, st.T_r, out);
     count_launch(c, 3);

@@ -104,6 +104,7 @@ struct ctx {
     // options
     int64_t opt_matvec_path{ 0 };
     int64_t opt_sync_every{ 1 };
+    int64_t opt_tc_mode{ 0 };       // tcgen05 cross terms: 0 / 2 = fp8 chain, 1 = three f16 MMAs
     int64_t opt_sparse_block{ 0 };  // 0 = default
     int64_t opt_sparse_group{ 0 };  // 0 = auto
     int64_t opt_sparse_lanes{ 0 };  // 0 = auto

@@ -207,9 +207,10 @@ def test_errors_are_loud():
             h._chk(h.L.b200svm_set_data_dense(h.h, np.zeros(1).ctypes.data, 0, 4, 4))
 
 
+@pytest.mark.parametrize("mode", [capi.TC_F16X3, capi.TC_FP8X])
 @pytest.mark.parametrize("kernel", ["rbf", "polynomial"])
 @pytest.mark.parametrize("shape", [(2, 3), (130, 64), (257, 33), (513, 100), (1000, 200), (2049, 1024)])
-def test_tcgen05_path_vs_simt_and_oracle(kernel, shape):
+def test_tcgen05_path_vs_simt_and_oracle(kernel, shape, mode):
     """The tcgen05/TMA path (fp16x2-split Gram tiles, symmetric) against the SIMT fp32 path and the f64 oracle on ragged sizes
     (rows not a multiple of the 128x256 tile, features not a multiple of the 64-wide K block)."""
     n, F = shape
@@ -220,6 +221,7 @@ def test_tcgen05_path_vs_simt_and_oracle(kernel, shape):
     for path in (capi.PATH_SIMT, capi.PATH_TC):
         with capi.Handle(np.float32, kernel, 3, 1.0 / F, coef0, 1.0) as h:
             h.set_option(capi.OPT_MATVEC_PATH, path)
+            h.set_option(capi.OPT_TC_MODE, mode)
             h.set_data(X)
             q = h.generate_q()
             h.set_q(q, h.kxx_last() + 1.0)
