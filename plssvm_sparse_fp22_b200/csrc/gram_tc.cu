@@ -17,10 +17,10 @@
 //                operands make an error of ~2^-15 of a product: the same size as the fp32 accumulation noise of a 1024-term
 //                dot product (DESIGN.md §3.1 has the measured error of both modes).
 //
-// Structure (one persistent CTA per SM, 192 threads):
-//   warp 0 / lane 0 : TMA producer  — cp.async.bulk.tensor 2-D boxes (64 fp16 x 128 rows, SWIZZLE_128B) into a 2-stage ring
+// Structure (one persistent CTA per SM, 320 threads):
+//   warp 0 / lane 0 : TMA producer  — cp.async.bulk.tensor 2-D boxes (128 bytes x 128 rows, SWIZZLE_128B) into a ring of four 48 KB slots
 //   warp 1 / lane 0 : MMA issuer    — tcgen05.mma.cta_group::1.kind::f16, M=128 N=256 K=16, accumulator double-buffered in TMEM
-//   warps 2..5      : epilogue      — tcgen05.ld 32x32b, exp2 / pow, centring, row sums in registers, column sums by a
+//   warps 2..9      : epilogue      — (lane quadrant, column half) each; tcgen05.ld 32x32b, exp2 / pow, centring, row sums in registers, column sums by a
 //                                     warp-shuffle butterfly + shared memory
 #include "internal.cuh"
 
@@ -39,13 +39,13 @@ namespace tc {
 constexpr int BM = 128;       // tile rows   (A operand, "i")
 constexpr int BN = 256;       // tile cols   (B operand, "j")
 constexpr int BK = 64;        // fp16 elements per K block = 128 bytes = one SWIZZLE_128B row
-constexpr int STAGES = 2;
+constexpr int STAGES = 4;                                 // ring of 48 KB slots; a K block uses two: (A_hi, B_hi) then the cross-term operands
 constexpr int UMMA_K = 16;
 constexpr int A_BYTES = BM * BK * 2;                      // 16 KB per plane
 constexpr int B_BYTES = BN * BK * 2;                      // 32 KB per plane
-constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;    // hi + lo planes: 96 KB
-constexpr int NUM_THREADS = 192;
-constexpr int EPI_THREADS = 128;
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;            // one A box + two B boxes: 48 KB
+constexpr int EPI_WARPS = 8;                              // two per SM sub-partition: one per (TMEM lane quadrant, column half)
+constexpr int NUM_THREADS = 64 + EPI_WARPS * 32;          // TMA warp + MMA warp + epilogue warps = 320
 constexpr int TMEM_COLS = 512;                            // two 256-column fp32 accumulators
 
 struct smem_layout {
@@ -53,7 +53,8 @@ struct smem_layout {
     static constexpr int OPERANDS = 0;
     static constexpr int COLBUF = STAGES * STAGE_BYTES;              // float4[2][BN]   per-column {c_j, q_j, d_j, -}
     static constexpr int COLRED = COLBUF + 2 * BN * 16;              // float[2][4][BN] per-warp column partial sums
-    static constexpr int BARRIERS = COLRED + 2 * 4 * BN * 4;         // uint64: full[S], empty[S], tmem_full[2], tmem_empty[2]
+    static constexpr int ROWRED = COLRED + 2 * 4 * BN * 4;           // float[2][BM] row sums of the upper column half
+    static constexpr int BARRIERS = ROWRED + 2 * BM * 4;             // uint64: full[S], empty[S], tmem_full[2], tmem_empty[2]
     static constexpr int TMEM_PTR = BARRIERS + (2 * STAGES + 4) * 8;
     static constexpr int TOTAL = TMEM_PTR + 16;
 };
@@ -205,8 +206,8 @@ __device__ __forceinline__ float warp_column_sums(float (&v)[32], int lane) {
 }
 
 // FP8X: map_lo / map_b are the e4m3 planes [hi8 | lo8] (A role) and [lo8 | hi8] (B role), 128 bytes per 64-element K block;
-// otherwise map_lo is the fp16 lo plane and map_b is unused.  Stage layout (96 KB either way):
-//   F16X3: [A_hi 16K | A_lo 16K | B_hi 32K | B_lo 32K]        FP8X: [A_hi 16K | A_8 16K | B_hi 32K | B_8 32K]
+// otherwise map_lo is the fp16 lo plane and map_b is unused.  Every K block fills two ring slots of [A 16K | B 32K]:
+//   slot 0 = (A_hi, B_hi), slot 1 = (A_lo, B_lo) for F16X3 or (A_8, B_8) for FP8X.
 template <int KERNEL, bool FP8X>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
     k_gram_tc(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo, const __grid_constant__ CUtensorMap map_b,
@@ -229,7 +230,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(bar_tfull + b * 8, 1);
-            mbar_init(bar_tempty + b * 8, 4);  // one arrival per epilogue warp
+            mbar_init(bar_tempty + b * 8, EPI_WARPS);  // one arrival per epilogue warp
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -257,27 +258,31 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
                 const int2 tile = p.tiles[t];
                 const int row_a = tile.x * BM, row_b = tile.y * BN;
                 for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-                    mbar_wait(bar_empty + stage * 8, phase ^ 1);
-                    const uint32_t full = bar_full + stage * 8;
-                    mbar_arrive_expect_tx(full, STAGE_BYTES);
-                    const uint32_t s0 = sbase + smem_layout::OPERANDS + stage * STAGE_BYTES;
                     const int kc = kb * BK;
-                    tma_load_2d(s0, &map_hi, full, kc, row_a);                                  // A_hi  128 rows
-                    tma_load_2d(s0 + 2 * A_BYTES, &map_hi, full, kc, row_b);                    // B_hi  rows 0..127
-                    tma_load_2d(s0 + 2 * A_BYTES + A_BYTES, &map_hi, full, kc, row_b + 128);    // B_hi  rows 128..255
-                    if constexpr (FP8X) {
-                        const int kc8 = kb * 128;  // bytes: [hi8 | lo8] of this K block
-                        tma_load_2d(s0 + A_BYTES, &map_lo, full, kc8, row_a);                               // A_8
-                        tma_load_2d(s0 + 2 * A_BYTES + B_BYTES, &map_b, full, kc8, row_b);                  // B_8
-                        tma_load_2d(s0 + 2 * A_BYTES + B_BYTES + A_BYTES, &map_b, full, kc8, row_b + 128);
-                    } else {
-                        tma_load_2d(s0 + A_BYTES, &map_lo, full, kc, row_a);                                // A_lo
-                        tma_load_2d(s0 + 2 * A_BYTES + B_BYTES, &map_lo, full, kc, row_b);                  // B_lo
-                        tma_load_2d(s0 + 2 * A_BYTES + B_BYTES + A_BYTES, &map_lo, full, kc, row_b + 128);
-                    }
-                    if (++stage == STAGES) {
-                        stage = 0;
-                        phase ^= 1;
+#pragma unroll
+                    for (int half = 0; half < 2; ++half) {
+                        mbar_wait(bar_empty + stage * 8, phase ^ 1);
+                        const uint32_t full = bar_full + stage * 8;
+                        mbar_arrive_expect_tx(full, STAGE_BYTES);
+                        const uint32_t s0 = sbase + smem_layout::OPERANDS + stage * STAGE_BYTES;
+                        if (half == 0) {
+                            tma_load_2d(s0, &map_hi, full, kc, row_a);                          // A_hi  128 rows
+                            tma_load_2d(s0 + A_BYTES, &map_hi, full, kc, row_b);                // B_hi  rows 0..127
+                            tma_load_2d(s0 + 2 * A_BYTES, &map_hi, full, kc, row_b + 128);      // B_hi  rows 128..255
+                        } else if constexpr (FP8X) {
+                            const int kc8 = kb * 128;  // bytes: [hi8 | lo8] of this K block
+                            tma_load_2d(s0, &map_lo, full, kc8, row_a);                         // A_8
+                            tma_load_2d(s0 + A_BYTES, &map_b, full, kc8, row_b);                // B_8
+                            tma_load_2d(s0 + 2 * A_BYTES, &map_b, full, kc8, row_b + 128);
+                        } else {
+                            tma_load_2d(s0, &map_lo, full, kc, row_a);                          // A_lo
+                            tma_load_2d(s0 + A_BYTES, &map_lo, full, kc, row_b);                // B_lo
+                            tma_load_2d(s0 + 2 * A_BYTES, &map_lo, full, kc, row_b + 128);
+                        }
+                        if (++stage == STAGES) {
+                            stage = 0;
+                            phase ^= 1;
+                        }
                     }
                 }
             }
@@ -296,15 +301,31 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + buf * BN;
                 for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-                    mbar_wait(bar_full + stage * 8, phase);
+                    // slot 0: (A_hi, B_hi)
+                    const int st0 = stage;
+                    mbar_wait(bar_full + st0 * 8, phase);
                     tc_fence_after();
-                    const uint32_t s0 = sbase + smem_layout::OPERANDS + stage * STAGE_BYTES;
-                    const uint64_t a_hi = make_desc_sw128(s0), a_lo = make_desc_sw128(s0 + A_BYTES);
-                    const uint64_t b_hi = make_desc_sw128(s0 + 2 * A_BYTES), b_lo = make_desc_sw128(s0 + 2 * A_BYTES + B_BYTES);
+                    const uint32_t s0 = sbase + smem_layout::OPERANDS + st0 * STAGE_BYTES;
+                    const uint64_t a_hi = make_desc_sw128(s0), b_hi = make_desc_sw128(s0 + A_BYTES);
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k) {
                         const uint64_t adv = static_cast<uint64_t>((k * UMMA_K * 2) >> 4);  // +32 bytes per K step inside the swizzle row
                         tc_mma_f16(tmem_d, a_hi + adv, b_hi + adv, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    if constexpr (FP8X) { tc_commit(bar_empty + st0 * 8); }  // frees the slot when these MMAs retire
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                    // slot 1: cross-term operands
+                    const int st1 = stage;
+                    mbar_wait(bar_full + st1 * 8, phase);
+                    tc_fence_after();
+                    const uint32_t s1 = sbase + smem_layout::OPERANDS + st1 * STAGE_BYTES;
+                    const uint64_t a_lo = make_desc_sw128(s1), b_lo = make_desc_sw128(s1 + A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) {
+                        const uint64_t adv = static_cast<uint64_t>((k * UMMA_K * 2) >> 4);
                         if constexpr (FP8X) {
                             // same 32-byte step: 32 e4m3 elements of [hi8 | lo8] x [lo8 | hi8]^T (idesc formats 0 = E4M3, same bit layout)
                             tc_mma_f8(tmem_d, a_lo + adv, b_lo + adv, idesc, 1u);
@@ -313,7 +334,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
                             tc_mma_f16(tmem_d, a_lo + adv, b_hi + adv, idesc, 1u);
                         }
                     }
-                    tc_commit(bar_empty + stage * 8);  // frees the smem stage when these MMAs retire
+                    if constexpr (!FP8X) { tc_commit(bar_empty + st0 * 8); }
+                    tc_commit(bar_empty + st1 * 8);
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1;
@@ -325,7 +347,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     } else {
         // ============================== epilogue warps (2..5) ==============================
         const int q = warp & 3;                 // TMEM lane quadrant this warp may access
-        const int et = threadIdx.x - 64;        // 0..127
+        const int half = (warp - 2) >> 2;       // column half of the 256-wide tile this warp evaluates
+        const int et = threadIdx.x - 64;        // 0..255
+        float *rowred = reinterpret_cast<float *>(smem + smem_layout::ROWRED);
         float4 *colbuf = reinterpret_cast<float4 *>(smem + smem_layout::COLBUF);
         float *colred = reinterpret_cast<float *>(smem + smem_layout::COLRED);
         int it = 0;
@@ -336,7 +360,6 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
             const int64_t row0 = static_cast<int64_t>(tile.x) * BM, col0 = static_cast<int64_t>(tile.y) * BN;
             // stage the per-column data of this tile
             colbuf[buf * BN + et] = __ldg(&p.pk[col0 + et]);
-            colbuf[buf * BN + 128 + et] = __ldg(&p.pk[col0 + 128 + et]);
             const int r = q * 32 + lane;
             const int64_t gi = row0 + r;
             const float4 mine = __ldg(&p.pk[gi]);  // {c_i, q_i, d_i, -}
@@ -346,12 +369,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 
             mbar_wait(bar_tfull + buf * 8, use & 1);
             tc_fence_after();
-            asm volatile("bar.sync 1, 128;" ::: "memory");  // colbuf visible to the 4 epilogue warps
+            asm volatile("bar.sync 1, 256;" ::: "memory");  // colbuf visible to the epilogue warps
 
             float rowsum = 0.f;
             float *cr = colred + (buf * 4 + q) * BN;
 #pragma unroll 1
-            for (int g = 0; g < BN / 32; ++g) {
+            for (int g = half * (BN / 64); g < (half + 1) * (BN / 64); ++g) {
                 uint32_t u[32];
                 tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * BN + g * 32), u);
                 tmem_ld_wait();
@@ -383,15 +406,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
             tc_fence_before();
             __syncwarp();
             if (lane == 0) { mbar_arrive(bar_tempty + buf * 8); }
-            p.Pr[static_cast<int64_t>(tile.y) * p.ldP + gi] = rowsum;
-            asm volatile("bar.sync 1, 128;" ::: "memory");  // colred complete
+            if (half == 1) { rowred[buf * BM + r] = rowsum; }
+            asm volatile("bar.sync 1, 256;" ::: "memory");  // colred / rowred complete
+            if (half == 0) { p.Pr[static_cast<int64_t>(tile.y) * p.ldP + gi] = rowsum + rowred[buf * BM + r]; }
             {
                 const float *c0 = colred + buf * 4 * BN;
-                const float s_lo = (c0[et] + c0[BN + et]) + (c0[2 * BN + et] + c0[3 * BN + et]);
-                const float s_hi = (c0[128 + et] + c0[BN + 128 + et]) + (c0[2 * BN + 128 + et] + c0[3 * BN + 128 + et]);
-                float *pc = p.Pc + static_cast<int64_t>(tile.x) * p.ldP + col0;
-                pc[et] = s_lo;
-                pc[128 + et] = s_hi;
+                p.Pc[static_cast<int64_t>(tile.x) * p.ldP + col0 + et] = (c0[et] + c0[BN + et]) + (c0[2 * BN + et] + c0[3 * BN + et]);
             }
         }
     }
