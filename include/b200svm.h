@@ -114,9 +114,12 @@ int b200svm_partition_tiles(int64_t n, int rank, int world, int64_t *first, int6
 #define B200SVM_OPT_MATVEC_PATH 1 /* 0 = auto, 1 = SIMT full-square, 2 = tcgen05 symmetric tiles (f32 dense only) */
 #define B200SVM_OPT_SYNC_EVERY 2  /* CG: host polls the convergence flag every k iterations (default 1)            */
 #define B200SVM_OPT_SPARSE_GROUP 4 /* CSR paths: blocks per launch group (0 = sized so that a group's slice of the transpose fits L2) */
-#define B200SVM_OPT_SPARSE_LANES 5 /* CSR paths: lanes sharing one (feature, block) segment: 0 auto, 1 or 8 */
+#define B200SVM_OPT_SPARSE_LANES 5 /* CSR paths: lanes sharing one (feature, block) segment: 0 auto, or a power of two up to 32 */
+#define B200SVM_OPT_SPARSE_THREADS 7 /* CSR paths: threads of the CTA that owns one row (0 auto: 256 float / 512 double; power of two 64..1024) */
 #define B200SVM_OPT_TC_MODE 6 /* tcgen05 path, cross terms of the fp16x2 split: 0 = default (fp8 chain), 1 = three f16 MMAs, 2 = fp8 chain; set before set_data */
-#define B200SVM_OPT_SPARSE_BLOCK 3 /* CSR paths: columns of the implicit matrix per block (power of two, 128..4096; set before set_data_csr) */
+#define B200SVM_OPT_SPARSE_CACHE 8 /* CSR paths, polynomial / rbf: 0 = cache S = f(X X^T) on first use if it fits (then the matvec is an HBM-bound SpMV), 1 = never (recompute on the fly), 2 = required (error if it does not fit) */
+#define B200SVM_OPT_SPARSE_CACHE_MB 9 /* CSR paths: memory budget of the S cache in MiB (0 = 85 % of the free device memory) */
+#define B200SVM_OPT_SPARSE_BLOCK 3 /* CSR paths: columns of the implicit matrix per block (power of two, 128..32768, default 8192; set before set_data_csr) */
 int b200svm_set_option(b200svm_handle h, int option, int64_t value);
 
 typedef struct b200svm_stats {
@@ -128,6 +131,7 @@ typedef struct b200svm_stats {
     int64_t d2h_bytes;        /* device->host bytes copied                                        */
     int64_t collectives;      /* NCCL collectives enqueued                                        */
     int64_t collective_bytes; /* payload bytes of those collectives (per rank)                    */
+    int64_t sparse_cache_entries; /* CSR paths: stored entries of the cached S matrix on this rank (0 = recomputed on the fly) */
 } b200svm_stats;
 int b200svm_get_stats(b200svm_handle h, b200svm_stats *out);
 int b200svm_reset_stats(b200svm_handle h);

@@ -189,7 +189,7 @@ int b200svm_set_option(b200svm_handle h, int option, int64_t value) {
                 c->opt_sync_every = value;
                 break;
             case B200SVM_OPT_SPARSE_BLOCK:
-                B200_REQUIRE(value == 0 || (value >= 128 && value <= 4096 && (value & (value - 1)) == 0), "sparse block width must be 0 or a power of two in [128, 4096]");
+                B200_REQUIRE(value == 0 || (value >= 128 && value <= 32768 && (value & (value - 1)) == 0), "sparse block width must be 0 or a power of two in [128, 32768]");
                 c->opt_sparse_block = value;
                 break;
             case B200SVM_OPT_TC_MODE:
@@ -198,8 +198,22 @@ int b200svm_set_option(b200svm_handle h, int option, int64_t value) {
                 if (c->has_data && c->has_split) { tc_prepare_split(*c); }
                 break;
             case B200SVM_OPT_SPARSE_LANES:
-                B200_REQUIRE(value == 0 || value == 1 || value == 8, "lanes per segment must be 0, 1 or 8");
+                B200_REQUIRE(value >= 0 && value <= 32 && (value & (value - 1)) == 0, "lanes per segment must be 0 (auto) or a power of two up to 32");
                 c->opt_sparse_lanes = value;
+                break;
+            case B200SVM_OPT_SPARSE_THREADS:
+                B200_REQUIRE(value == 0 || (value >= 64 && value <= 1024 && (value & (value - 1)) == 0), "threads per row must be 0 (auto) or a power of two in [64, 1024]");
+                c->opt_sparse_threads = value;
+                break;
+            case B200SVM_OPT_SPARSE_CACHE:
+                B200_REQUIRE(value >= 0 && value <= 2, "sparse cache mode must be 0 (auto), 1 (off) or 2 (required)");
+                c->opt_sparse_cache = value;
+                sp_invalidate_cache(*c);
+                break;
+            case B200SVM_OPT_SPARSE_CACHE_MB:
+                B200_REQUIRE(value >= 0, "sparse cache budget must be >= 0 MiB");
+                c->opt_sparse_cache_mb = value;
+                sp_invalidate_cache(*c);
                 break;
             case B200SVM_OPT_SPARSE_GROUP:
                 B200_REQUIRE(value >= 0, "blocks per group must be >= 0");

@@ -108,6 +108,9 @@ struct ctx {
     int64_t opt_sparse_block{ 0 };  // 0 = default
     int64_t opt_sparse_group{ 0 };  // 0 = auto
     int64_t opt_sparse_lanes{ 0 };  // 0 = auto
+    int64_t opt_sparse_threads{ 0 };  // 0 = auto
+    int64_t opt_sparse_cache{ 0 };    // 0 = auto, 1 = off, 2 = required
+    int64_t opt_sparse_cache_mb{ 0 }; // 0 = 85 % of the free memory
 
     // data
     bool has_data{ false };
@@ -184,6 +187,7 @@ bool tc_available(const ctx &c);
 void tc_kernel_matvec(ctx &c, const float *d, float *out_Kd);    // out = K d via symmetric tcgen05 tiles
 
 // sparse path (sparse.cu)
+void sp_invalidate_cache(ctx &c);  // drop the cached S (options changed); rebuilt on the next matvec
 void sp_set_data(ctx &c, const int64_t *rowptr, const int32_t *colidx, const void *values, int64_t n, int64_t F, int64_t nnz, int fmt);
 template <typename T> void sp_generate_q(ctx &c);
 template <typename T> void sp_kernel_matvec(ctx &c, const T *d, T *out);  // out[0..m) = K d (un-centred), this rank's rows

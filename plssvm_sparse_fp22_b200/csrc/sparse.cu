@@ -8,11 +8,11 @@
 //   rbf         K_ij = u_i u_j (1 + expm1(2 gamma G_ij)),  u_i = exp(-gamma |x_i|^2)
 //   polynomial  K_ij = c0^deg + [(gamma G_ij + c0)^deg - c0^deg]
 // The bracket S_ij vanishes unless rows i and j share a feature, so K v = rank-1 part + S v and only sum_f c_f^2 products are formed
-// instead of m^2 F.  G is never stored: for every (row i, block b of W columns) a warp accumulates x_if * x_jf over the features of
-// row i into a warp-private shared-memory accumulator, driven by a column-blocked transpose of X (per block, per feature: the list
-// of (j_local, x_jf)), compacts the touched slots from a bitmap and evaluates the kernel function only on those.
+// instead of m^2 F.  G is never stored: for every (row i, block b of W columns) a CTA accumulates x_if * x_jf over the features of
+// row i into a shared-memory accumulator, driven by a column-blocked transpose of X (per block, per feature: the list of
+// (j_local, x_jf)), compacts the touched slots from a bitmap and evaluates the kernel function only on those.
 //   linear      K v = X (X^T v): two O(nnz) passes over the same structures.
-// FP22 values (1|8|13 = top 22 bits of binary32, packed with a 10-bit column delta / local column) are decoded in registers.
+// FP22 rows (1|8|13 = top 22 bits of binary32, packed with a 10-bit column delta) are decoded in registers.
 #include "device_utils.cuh"
 
 #include <algorithm>
@@ -34,16 +34,15 @@ struct csr_view {
 };
 
 // Transpose of X (CSC, rows ascending inside a column) cut into column blocks of the implicit matrix:
-//   block b  = rows [b W, (b+1) W) of X  -> one pass of the warp-private accumulator
+//   block b  = rows [b W, (b+1) W) of X  -> one pass of a CTA's shared-memory accumulator
 //   group g  = G consecutive blocks      -> one kernel launch (its slice of the transpose stays L2-resident)
-// A lane that owns feature f walks column f sequentially across the blocks of a group, so its loads are contiguous; the
-// per-(feature, block) end pointers give every segment a known trip count (loads issue back to back, no pointer chasing).
+// The per-(feature, block) pointers give every segment a known extent: a group of lanes reads it as one contiguous run.
 struct csc_view {
     const uint32_t *ptrT;    // [F][nb + 1] index of the first entry of column f inside block b; ptrT[f][nb] = end of the column
-    const uint16_t *j;       // [entries] row of X relative to its block (plain formats)
-    const void *val;         // T[entries], or uint32 packed (fp22 << 10 | row_in_block), W <= 1024
+    const uint16_t *j;       // [entries] row of X relative to its block
+    const void *val;         // T[entries] (FP22 storage: the FP22-exact binary32 value; the row index needs more than 10 bits)
     int64_t F;
-    int W;                   // rows of X per block (power of two, 128..4096; <= 1024 for FP22)
+    int W;                   // rows of X per block (power of two, 128..32768)
     int nb;                  // blocks
     int G;                   // blocks per group
     int ng;                  // groups
@@ -148,7 +147,7 @@ __global__ void __launch_bounds__(256) k_sp_row_dot(csr_view A, const T *__restr
 }
 
 // w[f] = sum_j x_jf v_j  via the transpose (thread per feature, fixed order => deterministic); v has nb * W entries
-template <typename T, bool FP22>
+template <typename T>
 __global__ void __launch_bounds__(256) k_sp_xt_v(csc_view B, const T *__restrict__ v, T *__restrict__ w) {
     const int64_t f = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (f >= B.F) { return; }
@@ -157,12 +156,7 @@ __global__ void __launch_bounds__(256) k_sp_xt_v(csc_view B, const T *__restrict
     for (int b = 0; b < B.nb; ++b) {
         const T *vb = v + (int64_t) b * B.W;
         for (uint32_t e = pt[b], e1 = pt[b + 1]; e < e1; ++e) {
-            if constexpr (FP22) {
-                const uint32_t wd = __ldg(static_cast<const uint32_t *>(B.val) + e);
-                s = fma((T) fp22_value(wd), vb[wd & 1023u], s);
-            } else {
-                s = fma(__ldg(static_cast<const T *>(B.val) + e), vb[__ldg(B.j + e)], s);
-            }
+            s = fma(__ldg(static_cast<const T *>(B.val) + e), vb[__ldg(B.j + e)], s);
         }
     }
     w[f] = s;
@@ -200,6 +194,7 @@ struct kfun {
     double coef0;
     double c0pow;   // coef0^degree
     double fx_scale, fx_inv;  // 2^s and 2^-s of the fixed-point Gram accumulation
+    int lb;                   // double: bit at which q is split into limbs
 };
 
 template <typename T, int KERNEL>
@@ -221,183 +216,436 @@ __device__ __forceinline__ T s_value(T g, const kfun &k) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// out[row] += sum_{j in group g} S(G_row,j) v_j      rows [row_lo, row_hi) of A, grid-strided over warps
-//   per-warp shared memory: acc T[W] | touched bitmap uint32[W/32] | touched list uint16[W]
-//   A lane keeps up to K features of the row in registers (value, feature, cursor into the feature's column) and, block after
-//   block, consumes the entries whose row falls into the block (segment end from ptrT: known trip count, loads batched by 4).
-//   COMPACT: touched slots are recorded in a bitmap and compacted, the kernel function runs on those only (sparse fill);
-//   otherwise all W slots are evaluated (S(0) = 0), which is cheaper when most slots are hit.
+// out[row] += sum_{j in group g} S(G_row,j) v_j      rows [row_lo, row_hi) of A, one CTA per row (grid-strided)
+//
+// Shared memory of a CTA: the accumulator of one block of W columns (fixed-point limbs), a touched bitmap, the compacted list of
+// touched slots, and the current row: (feature, value) of its stored entries plus the [start, end) of each feature's segment of
+// the transpose inside the current block.  Per block:
+//   1. owner threads prefetch the end pointer of the NEXT block's segments (latency hidden behind the products);
+//   2. groups of GS lanes walk one segment each (contiguous (row_in_block, value) pairs => coalesced), one integer atomic per limb
+//      into the shared accumulator and one atomicOr into the bitmap; segments longer than `thr` are taken by the whole CTA;
+//   3. COMPACT: the bitmap is compacted (block scan, fixed order) and the kernel function runs on the touched slots only;
+//      otherwise all W slots are evaluated (S(0) = 0), cheaper when most slots are hit.
+// Every reduction has a fixed order and the accumulation is integer => bit-reproducible.
 // ---------------------------------------------------------------------------------------------------------------------
-// Fixed-point accumulation of the Gram entries in 32-bit limbs: shared-memory floating-point atomics are CAS loops on sm_100,
-// 32-bit integer atomics are single fire-and-forget instructions.  A product p is scaled by 2^s (s chosen from the largest
-// squared row norm, which bounds every partial sum by Cauchy-Schwarz), rounded to an integer q and split into limbs with 10 bits
-// of head-room each, so up to 1024 products can be added per slot without a carry; limbs are recombined in the epilogue.
-// The sum is exact in the fixed-point grid (2^-42 / 2^-61 of the bound for float / double) and independent of the order of the
-// additions => bit-reproducible.
+// Fixed-point accumulation of the Gram entries: shared-memory floating-point (and 64-bit integer) atomics are CAS loops on
+// sm_100, 32-bit integer atomics are single fire-and-forget instructions.  A product p is scaled by 2^s, s chosen from the largest
+// squared row norm (which bounds every Gram entry and every partial sum by Cauchy-Schwarz), and rounded to an integer q.
+//   float : one signed 32-bit limb, |sum q| < 2^30 (resolution 2^-30 of the bound; binary32 carries 2^-24 of the value)
+//   double: q is split at bit `lb` into an unsigned low limb (32 - lb bits of head-room: up to 2^(32-lb) additions per slot
+//           without a carry) and a signed high limb; lb + 30 significant bits (52 for rows of up to 1024 stored entries)
+// The sum is exact on the fixed-point grid and independent of the order of the additions.
 template <typename T>
 struct fixp;
 template <>
 struct fixp<float> {
-    static constexpr int LIMBS = 2;
-    static constexpr int BITS = 42;  // |q| <= 2^42
-    static __device__ __forceinline__ void add(uint32_t *acc, int W, int jl, float p, float scale) {
-        const long long q = __float2ll_rn(p * scale);
-        atomicAdd(&acc[jl], (uint32_t) (q & 0x3FFFFFll));
-        atomicAdd(reinterpret_cast<int *>(&acc[W + jl]), (int) (q >> 22));
+    static constexpr int LIMBS = 1;
+    static __device__ __forceinline__ void add(uint32_t *acc, int, int jl, float p, float scale, int) {
+        atomicAdd(reinterpret_cast<int *>(&acc[jl]), __float2int_rn(p * scale));
     }
-    static __device__ __forceinline__ float take(uint32_t *acc, int W, int jl, double inv_scale) {
-        const uint32_t lo = acc[jl];
-        const int hi = (int) acc[W + jl];
+    static __device__ __forceinline__ float take(uint32_t *acc, int, int jl, double inv_scale, int) {
+        const int q = (int) acc[jl];
         acc[jl] = 0u;
-        acc[W + jl] = 0u;
-        const long long q = ((long long) hi << 22) + (long long) lo;
         return (float) q * (float) inv_scale;  // 2^-s: exact scaling, one rounding of q to 24 bits
     }
 };
 template <>
 struct fixp<double> {
-    static constexpr int LIMBS = 3;
-    static constexpr int BITS = 61;  // |q| <= 2^61
-    static __device__ __forceinline__ void add(uint32_t *acc, int W, int jl, double p, double scale) {
+    static constexpr int LIMBS = 2;
+    static __device__ __forceinline__ void add(uint32_t *acc, int W, int jl, double p, double scale, int lb) {
         const long long q = __double2ll_rn(p * scale);
-        atomicAdd(&acc[jl], (uint32_t) (q & 0x1FFFFFll));
-        atomicAdd(&acc[W + jl], (uint32_t) ((q >> 21) & 0x1FFFFFll));
-        atomicAdd(reinterpret_cast<int *>(&acc[2 * W + jl]), (int) (q >> 42));
+        atomicAdd(&acc[jl], (uint32_t) (q & ((1ll << lb) - 1ll)));
+        atomicAdd(reinterpret_cast<int *>(&acc[W + jl]), (int) (q >> lb));
     }
-    static __device__ __forceinline__ double take(uint32_t *acc, int W, int jl, double inv_scale) {
-        const uint32_t lo = acc[jl], mid = acc[W + jl];
-        const int hi = (int) acc[2 * W + jl];
+    static __device__ __forceinline__ double take(uint32_t *acc, int W, int jl, double inv_scale, int lb) {
+        const uint32_t lo = acc[jl];
+        const int hi = (int) acc[W + jl];
         acc[jl] = 0u;
         acc[W + jl] = 0u;
-        acc[2 * W + jl] = 0u;
-        const long long q = ((long long) hi << 42) + ((long long) mid << 21) + (long long) lo;
+        const long long q = ((long long) hi << lb) + (long long) lo;
         return (double) q * inv_scale;
     }
 };
 
-template <typename T, bool FP22>
-__device__ __forceinline__ void load_b_entry(const csc_view &B, uint32_t e, int &jl, T &xv) {
-    if constexpr (FP22) {
-        const uint32_t wd = __ldg(static_cast<const uint32_t *>(B.val) + e);
-        jl = (int) (wd & 1023u);
-        xv = (T) fp22_value(wd);
-    } else {
-        jl = (int) __ldg(B.j + e);
-        xv = __ldg(static_cast<const T *>(B.val) + e);
+constexpr int SP_MAX_OWN = 4;  // stored entries of a row per thread: rows of up to 4 * blockDim.x entries
+
+// MODE 0: out[row] += sum_j S_ij v_j (S never stored)
+// MODE 1: count the touched slots of every (block, row) visit            -> cache.ptr[b * rows + (row - row_lo)]
+// MODE 2: store (row_in_block, S value) of every touched slot, ascending -> cache.j / cache.val at cache.ptr[...]   
+struct cache_view {
+    int64_t *ptr;   // [nb * rows + 1]
+    uint16_t *j;    // [entries]
+    void *val;      // T[entries]
+    int64_t rows;   // rows of the implicit matrix held by this rank
+};
+
+template <typename T, int KERNEL, bool FP22, bool COMPACT, int MODE>
+__global__ void __launch_bounds__(1024)
+    k_sp_kmv(csr_view A, int64_t row_lo, int64_t row_hi, csc_view B, int g, int rmax, int gs_log2, int thr, const T *__restrict__ v, kfun kf,
+             T *__restrict__ out, cache_view cache) {
+    static_assert(MODE == 0 || COMPACT, "the cache passes work from the compacted slot list");
+    extern __shared__ __align__(16) unsigned char sp_smem[];
+    __shared__ int wtot[32];
+    __shared__ T red[32];
+    __shared__ int nlong_s;
+    using FX = fixp<T>;
+    const int t = threadIdx.x, TT = blockDim.x, lane = t & 31, warp = t >> 5, nwarps = TT >> 5;
+    const int W = B.W, words = W >> 5;
+    uint32_t *acc = reinterpret_cast<uint32_t *>(sp_smem);
+    uint32_t *bits = acc + (size_t) W * FX::LIMBS;
+    T *xs = reinterpret_cast<T *>(bits + words);
+    int32_t *feat = reinterpret_cast<int32_t *>(xs + rmax);
+    uint32_t *s0 = reinterpret_cast<uint32_t *>(feat + rmax);
+    uint32_t *s1 = s0 + rmax;
+    uint16_t *longk = reinterpret_cast<uint16_t *>(s1 + rmax);
+    uint16_t *list = longk + rmax;
+    for (int k = t; k < W * FX::LIMBS + words; k += TT) { acc[k] = 0u; }
+    if (t == 0) { nlong_s = 0; }
+    const T fx_scale = (T) kf.fx_scale;
+    const double fx_inv = kf.fx_inv;
+    const int lb = kf.lb;
+    const int GS = 1 << gs_log2, NG = TT >> gs_log2, gid = t >> gs_log2, gl = t & (GS - 1);
+    const int b0 = g * B.G, b1 = min(B.nb, b0 + B.G);
+    const int64_t ldp = (int64_t) B.nb + 1;
+    const uint16_t *__restrict__ Bj = B.j;
+    const T *__restrict__ Bv = static_cast<const T *>(B.val);
+    __syncthreads();
+
+    for (int64_t row = row_lo + blockIdx.x; row < row_hi; row += gridDim.x) {
+        const int64_t p0 = A.rowptr[row];
+        const int R = (int) (A.rowptr[row + 1] - p0);
+        if (R == 0) { continue; }  // block-uniform
+        // ---- the row: (feature, value) of every stored entry; entry k is owned by thread k % TT
+        if constexpr (FP22) {
+            int carry = 0;
+            for (int base = 0; base < R; base += TT) {
+                const int k = base + t;
+                const uint32_t w = k < R ? __ldg(static_cast<const uint32_t *>(A.val) + p0 + k) : 0u;
+                const int incl = warp_incl_scan((int) (w & 1023u), lane);
+                if (lane == 31) { wtot[warp] = incl; }
+                __syncthreads();
+                int off = 0, tot = 0;
+                for (int w2 = 0; w2 < nwarps; ++w2) {
+                    const int c = wtot[w2];
+                    off += w2 < warp ? c : 0;
+                    tot += c;
+                }
+                if (k < R) {
+                    const T x = (T) fp22_value(w);
+                    xs[k] = x;
+                    feat[k] = x != T(0) ? carry + off + incl : -1;
+                }
+                carry += tot;
+                __syncthreads();
+            }
+        } else {
+            for (int k = t; k < R; k += TT) {
+                const T x = __ldg(static_cast<const T *>(A.val) + p0 + k);
+                xs[k] = x;
+                feat[k] = x != T(0) ? __ldg(A.col + p0 + k) : -1;
+            }
+        }
+        // ---- segments of the first block of the group
+#pragma unroll
+        for (int q = 0; q < SP_MAX_OWN; ++q) {
+            const int k = t + q * TT;
+            if (k < R) {
+                const int f = feat[k];
+                uint32_t a = 0u, e = 0u;
+                if (f >= 0) {
+                    const uint32_t *pt = B.ptrT + (int64_t) f * ldp + b0;
+                    a = __ldg(pt);
+                    e = __ldg(pt + 1);
+                }
+                s0[k] = a;
+                s1[k] = e;
+            }
+        }
+        __syncthreads();
+
+        T rowsum = T(0);
+        for (int b = b0; b < b1; ++b) {
+            // ---- 1. prefetch the next block's segment ends; note the long segments of this block
+            uint32_t nxt[SP_MAX_OWN];
+#pragma unroll
+            for (int q = 0; q < SP_MAX_OWN; ++q) {
+                const int k = t + q * TT;
+                nxt[q] = 0u;
+                if (k < R) {
+                    const int f = feat[k];
+                    const uint32_t e1 = s1[k];
+                    if ((int) (e1 - s0[k]) > thr) { longk[atomicAdd(&nlong_s, 1)] = (uint16_t) k; }
+                    nxt[q] = e1;
+                    if (f >= 0 && b + 1 < b1) { nxt[q] = __ldg(B.ptrT + (int64_t) f * ldp + b + 2); }
+                }
+            }
+            // ---- 2. products: GS lanes per segment, four segments (two entries each) in flight per lane
+            for (int k0 = gid; k0 < R; k0 += 4 * NG) {
+                uint32_t e[4], e1[4];
+                int ja[4], jb[4];
+                T x[4], va[4], vb2[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int k = k0 + u * NG;
+                    e[u] = 0u;
+                    e1[u] = 0u;
+                    if (k < R) {
+                        const uint32_t a0 = s0[k], a1 = s1[k];
+                        if ((int) (a1 - a0) <= thr) {
+                            e[u] = a0 + (uint32_t) gl;
+                            e1[u] = a1;
+                            x[u] = xs[k];
+                        }
+                    }
+                    if (e[u] < e1[u]) {
+                        ja[u] = (int) __ldg(Bj + e[u]);
+                        va[u] = __ldg(Bv + e[u]);
+                    }
+                    if (e[u] + (uint32_t) GS < e1[u]) {
+                        jb[u] = (int) __ldg(Bj + e[u] + GS);
+                        vb2[u] = __ldg(Bv + e[u] + GS);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (e[u] < e1[u]) {
+                        FX::add(acc, W, ja[u], x[u] * va[u], fx_scale, lb);
+                        if constexpr (COMPACT) { atomicOr(&bits[ja[u] >> 5], 1u << (ja[u] & 31)); }
+                    }
+                    if (e[u] + (uint32_t) GS < e1[u]) {
+                        FX::add(acc, W, jb[u], x[u] * vb2[u], fx_scale, lb);
+                        if constexpr (COMPACT) { atomicOr(&bits[jb[u] >> 5], 1u << (jb[u] & 31)); }
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {  // what is left of longer segments
+                    for (uint32_t ee = e[u] + 2u * (uint32_t) GS; ee < e1[u]; ee += (uint32_t) GS) {
+                        const int jc = (int) __ldg(Bj + ee);
+                        FX::add(acc, W, jc, x[u] * __ldg(Bv + ee), fx_scale, lb);
+                        if constexpr (COMPACT) { atomicOr(&bits[jc >> 5], 1u << (jc & 31)); }
+                    }
+                }
+            }
+            __syncthreads();
+            const int nl = nlong_s;
+            if (nl > 0) {  // block-uniform
+                for (int i = 0; i < nl; ++i) {
+                    const int k = longk[i];
+                    const T x = xs[k];
+                    for (uint32_t e = s0[k] + (uint32_t) t, e1 = s1[k]; e < e1; e += (uint32_t) TT) {
+                        const int ja = (int) __ldg(Bj + e);
+                        FX::add(acc, W, ja, x * __ldg(Bv + e), fx_scale, lb);
+                        if constexpr (COMPACT) { atomicOr(&bits[ja >> 5], 1u << (ja & 31)); }
+                    }
+                }
+                __syncthreads();
+                if (t == 0) { nlong_s = 0; }
+            }
+            // ---- rotate the segment pointers (owner threads; everybody is done reading them)
+#pragma unroll
+            for (int q = 0; q < SP_MAX_OWN; ++q) {
+                const int k = t + q * TT;
+                if (k < R) {
+                    s0[k] = s1[k];
+                    s1[k] = nxt[q];
+                }
+            }
+            // ---- 3. kernel function on the touched slots, times v_j
+            const T *vb = v + (int64_t) b * W;
+            if constexpr (COMPACT) {
+                int cnt = 0;
+                for (int w0 = 0; w0 < words; w0 += TT) {
+                    const int idx = w0 + t;
+                    uint32_t word = idx < words ? bits[idx] : 0u;
+                    if (word != 0u) { bits[idx] = 0u; }
+                    const int c = __popc(word);
+                    const int incl = warp_incl_scan(c, lane);
+                    if (lane == 31) { wtot[warp] = incl; }
+                    __syncthreads();
+                    int off = 0, tot = 0;
+                    for (int w2 = 0; w2 < nwarps; ++w2) {
+                        const int cw = wtot[w2];
+                        off += w2 < warp ? cw : 0;
+                        tot += cw;
+                    }
+                    int pos = cnt + off + incl - c;
+                    while (word != 0u) {
+                        const int bit = __ffs((int) word) - 1;
+                        list[pos++] = (uint16_t) ((idx << 5) + bit);
+                        word &= word - 1u;
+                    }
+                    cnt += tot;
+                    __syncthreads();
+                }
+                if constexpr (MODE == 0) {
+                    for (int i = t; i < cnt; i += TT) {
+                        const int jl = list[i];
+                        const T gv = FX::take(acc, W, jl, fx_inv, lb);
+                        rowsum = fma(s_value<T, KERNEL>(gv, kf), __ldg(vb + jl), rowsum);
+                    }
+                } else {
+                    const int64_t visit = (int64_t) b * cache.rows + (row - row_lo);
+                    if constexpr (MODE == 1) {
+                        if (t == 0) { cache.ptr[visit] = (cnt + 3) & ~3; }  // visits are padded to whole quads (vector loads)
+                        for (int i = t; i < cnt; i += TT) { (void) FX::take(acc, W, list[i], fx_inv, lb); }
+                    } else {
+                        const int64_t base = cache.ptr[visit];
+                        T *sval = static_cast<T *>(cache.val);
+                        for (int i = t; i < cnt; i += TT) {
+                            const int jl = list[i];
+                            const T gv = FX::take(acc, W, jl, fx_inv, lb);
+                            cache.j[base + i] = (uint16_t) jl;
+                            sval[base + i] = s_value<T, KERNEL>(gv, kf);
+                        }
+                        for (int i = cnt + t; i < ((cnt + 3) & ~3); i += TT) {
+                            cache.j[base + i] = (uint16_t) 0;
+                            sval[base + i] = T(0);
+                        }
+                    }
+                }
+            } else {
+                for (int jl = t; jl < W; jl += TT) {
+                    const T gv = FX::take(acc, W, jl, fx_inv, lb);
+                    rowsum = fma(s_value<T, KERNEL>(gv, kf), __ldg(vb + jl), rowsum);
+                }
+            }
+            __syncthreads();
+        }
+        // ---- row sum in a fixed order
+        if constexpr (MODE == 0) {
+            rowsum = warp_sum(rowsum);
+            if (lane == 0) { red[warp] = rowsum; }
+            __syncthreads();
+            if (t == 0) {
+                T s = red[0];
+                for (int w2 = 1; w2 < nwarps; ++w2) { s += red[w2]; }
+                out[row] += s;
+            }
+        }
     }
 }
 
-template <typename T, int KERNEL, bool FP22, int K, int MAXT, bool COMPACT, int GS>
-__global__ void __launch_bounds__(MAXT, 1)
-    k_sp_kmv(csr_view A, int64_t row_lo, int64_t row_hi, csc_view B, int g, const T *__restrict__ v, kfun kf, T *__restrict__ out) {
+// ---------------------------------------------------------------------------------------------------------------------
+// Cached S: P[b][r] = sum over the stored entries of visit (b, r) of S * v[b W + j]
+// One CTA per (block b, chunk of rows): the W weights of the block are staged in shared memory once, then every warp streams the
+// entries of its rows (coalesced 2-byte index + value loads; the gather hits shared memory).  HBM-bound: sizeof(T) + 2 bytes per entry.
+// ---------------------------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) k_sp_cached_mv(cache_view S, int W, int rows_per_cta, const T *__restrict__ v, T *__restrict__ P) {
     extern __shared__ __align__(16) unsigned char sp_smem[];
-    using FX = fixp<T>;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    const int W = B.W, words = W >> 5;
-    const size_t per_warp = (size_t) W * 4 * FX::LIMBS + (size_t) words * 4 + (size_t) W * 2;
-    unsigned char *mine = sp_smem + (size_t) warp * per_warp;
-    uint32_t *acc = reinterpret_cast<uint32_t *>(mine);
-    uint32_t *bits = acc + (size_t) W * FX::LIMBS;
-    uint16_t *list = reinterpret_cast<uint16_t *>(bits + words);
-    for (int k = lane; k < W * FX::LIMBS + words; k += 32) { acc[k] = 0u; }
-    const T fx_scale = (T) kf.fx_scale;
-    const double fx_inv = kf.fx_inv;
-    __syncwarp();
+    T *vs = reinterpret_cast<T *>(sp_smem);
+    const int b = blockIdx.y;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5, nwarps = blockDim.x >> 5;
+    const T *vb = v + (int64_t) b * W;
+    for (int k = t; k < W; k += blockDim.x) { vs[k] = vb[k]; }
+    __syncthreads();
+    const int64_t r0 = (int64_t) blockIdx.x * rows_per_cta, r1 = min(S.rows, r0 + rows_per_cta);
+    const T *__restrict__ sval = static_cast<const T *>(S.val);
+    const uint16_t *__restrict__ sj = S.j;
+    for (int64_t r = r0 + warp; r < r1; r += nwarps) {
+        const int64_t visit = (int64_t) b * S.rows + r;
+        const int64_t q0 = S.ptr[visit] >> 2, q1 = S.ptr[visit + 1] >> 2;  // quads of entries (visits are padded to multiples of 4)
+        T s0 = T(0), s1 = T(0), s2 = T(0), s3 = T(0);
+        const uint2 *__restrict__ jq = reinterpret_cast<const uint2 *>(sj);
+        auto quad = [&](const uint2 jj, const T a0, const T a1, const T a2, const T a3) {
+            s0 = fma(a0, vs[jj.x & 0xFFFFu], s0);
+            s1 = fma(a1, vs[jj.x >> 16], s1);
+            s2 = fma(a2, vs[jj.y & 0xFFFFu], s2);
+            s3 = fma(a3, vs[jj.y >> 16], s3);
+        };
+        int64_t q = q0 + lane;
+        if constexpr (sizeof(T) == 4) {
+            const float4 *__restrict__ vq = reinterpret_cast<const float4 *>(sval);
+            for (; q + 32 < q1; q += 64) {  // two quads in flight per lane
+                const uint2 ja = __ldcs(jq + q), jb = __ldcs(jq + q + 32);
+                const float4 a = __ldcs(vq + q), c2 = __ldcs(vq + q + 32);
+                quad(ja, a.x, a.y, a.z, a.w);
+                quad(jb, c2.x, c2.y, c2.z, c2.w);
+            }
+            if (q < q1) {
+                const uint2 ja = __ldcs(jq + q);
+                const float4 a = __ldcs(vq + q);
+                quad(ja, a.x, a.y, a.z, a.w);
+            }
+        } else {
+            const double2 *__restrict__ vq = reinterpret_cast<const double2 *>(sval);
+            for (; q + 32 < q1; q += 64) {
+                const uint2 ja = __ldcs(jq + q), jb = __ldcs(jq + q + 32);
+                const double2 a = __ldcs(vq + 2 * q), a2 = __ldcs(vq + 2 * q + 1);
+                const double2 c2 = __ldcs(vq + 2 * (q + 32)), c3 = __ldcs(vq + 2 * (q + 32) + 1);
+                quad(ja, a.x, a.y, a2.x, a2.y);
+                quad(jb, c2.x, c2.y, c3.x, c3.y);
+            }
+            if (q < q1) {
+                const uint2 ja = __ldcs(jq + q);
+                const double2 a = __ldcs(vq + 2 * q), a2 = __ldcs(vq + 2 * q + 1);
+                quad(ja, a.x, a.y, a2.x, a2.y);
+            }
+        }
+        const T sum = warp_sum((s0 + s1) + (s2 + s3));
+        if (lane == 0) { P[visit] = sum; }
+    }
+}
 
-    constexpr int UNR = K <= 8 ? K : 1;  // the 32-features-per-lane fallback keeps its state in local memory
-    const int b0 = g * B.G, b1 = min(B.nb, b0 + B.G);
-    const int64_t gwarp = (int64_t) blockIdx.x * nwarps + warp, twarps = (int64_t) gridDim.x * nwarps;
-    for (int64_t row = row_lo + gwarp; row < row_hi; row += twarps) {
-        const int64_t p0 = A.rowptr[row], p1 = A.rowptr[row + 1];
-        // ---- this lane's features: value, end-pointer row of ptrT, cursor
-        T x[K];
-        const uint32_t *pt[K];
-        uint32_t cur[K];
-        int colrun = 0;
-#pragma unroll UNR
-        for (int k = 0; k < K; ++k) {
-            int f = 0;
-            x[k] = T(0);
-            pt[k] = nullptr;
-            cur[k] = 0u;
-            if (p0 + (int64_t) k * 32 < p1) {  // warp-uniform
-                const bool valid = load_entry<T, FP22>(A, p0 + (int64_t) k * 32, p1, lane, colrun, f, x[k]);
-                if (valid && x[k] != T(0)) {
-                    pt[k] = B.ptrT + (int64_t) f * (B.nb + 1) + b0;
-                    cur[k] = __ldg(pt[k]);
-                }
-            }
+// out[r] = sum_b P[b][r] in block order (fixed => deterministic), rows [0, rows) -> out[lo + r]
+template <typename T>
+__global__ void __launch_bounds__(256) k_sp_fold_blocks(const T *__restrict__ P, int nb, int64_t rows, T *__restrict__ out) {
+    for (int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += (int64_t) gridDim.x * blockDim.x) {
+        T s = T(0);
+        for (int b = 0; b < nb; ++b) { s += P[(int64_t) b * rows + r]; }
+        out[r] = s;
+    }
+}
+
+// exclusive prefix sum of int64 counts, in place, three passes (4096 elements per CTA)
+constexpr int SCAN_CHUNK = 4096;
+__global__ void __launch_bounds__(1024) k_scan_chunks(int64_t *x, int64_t n, int64_t *chunk_sum) {
+    __shared__ int64_t wsum[32];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int64_t base = (int64_t) blockIdx.x * SCAN_CHUNK + (int64_t) t * 4;
+    int64_t a[4], tot = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        a[k] = base + k < n ? x[base + k] : 0;
+        tot += a[k];
+    }
+    int64_t incl = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int64_t u = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) { incl += u; }
+    }
+    if (lane == 31) { wsum[warp] = incl; }
+    __syncthreads();
+    int64_t off = 0, all = 0;
+    for (int w = 0; w < 32; ++w) {
+        off += w < warp ? wsum[w] : 0;
+        all += wsum[w];
+    }
+    int64_t run = off + incl - tot;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        if (base + k < n) { x[base + k] = run; }
+        run += a[k];
+    }
+    if (t == 0) { chunk_sum[blockIdx.x] = all; }
+}
+__global__ void __launch_bounds__(32) k_scan_top(int64_t *chunk_sum, int64_t chunks) {
+    if (threadIdx.x == 0) {
+        int64_t run = 0;
+        for (int64_t k = 0; k < chunks; ++k) {
+            const int64_t c = chunk_sum[k];
+            chunk_sum[k] = run;
+            run += c;
         }
-        T rowsum = T(0);
-        for (int b = b0; b < b1; ++b) {
-            // ---- segment ends of this block (independent loads), then the products
-            uint32_t e1[K];
-#pragma unroll UNR
-            for (int k = 0; k < K; ++k) { e1[k] = pt[k] != nullptr ? __ldg(pt[k] + (b - b0) + 1) : cur[k]; }
-            // GS lanes share one feature's segment (GS = 1: a lane walks its own features; larger GS for longer segments)
-            constexpr int NG = 32 / GS;
-#pragma unroll UNR
-            for (int k = 0; k < K; ++k) {
-                if (p0 + (int64_t) k * 32 >= p1) { break; }  // warp-uniform: no more stored entries in this row
-                for (int l0 = 0; l0 < 32; l0 += NG) {
-                    if (p0 + (int64_t) k * 32 + l0 >= p1) { break; }
-                    uint32_t e, ee;
-                    T xs;
-                    if constexpr (GS == 1) {
-                        e = cur[k];
-                        ee = e1[k];
-                        xs = x[k];
-                    } else {
-                        const int src = l0 + lane / GS;
-                        e = __shfl_sync(0xffffffffu, cur[k], src) + (uint32_t) (lane % GS);
-                        ee = __shfl_sync(0xffffffffu, e1[k], src);
-                        xs = __shfl_sync(0xffffffffu, x[k], src);
-                    }
-                    for (; e < ee; e += GS) {
-                        int jl;
-                        T xv;
-                        load_b_entry<T, FP22>(B, e, jl, xv);
-                        FX::add(acc, W, jl, xs * xv, fx_scale);  // lanes of one warp may meet on a slot
-                        if constexpr (COMPACT) { atomicOr(&bits[jl >> 5], 1u << (jl & 31)); }
-                    }
-                }
-                cur[k] = e1[k];
-            }
-            __syncwarp();
-            const T *vb = v + (int64_t) b * W;
-            if constexpr (COMPACT) {
-                // ---- compact the touched slots (bitmap -> list), fixed order
-                int cnt = 0;
-                for (int w0 = 0; w0 < words; w0 += 32) {
-                    uint32_t word = (w0 + lane < words) ? bits[w0 + lane] : 0u;
-                    const int c = __popc(word);
-                    const int incl = warp_incl_scan(c, lane);
-                    int pos = cnt + incl - c;
-                    if (word != 0u) { bits[w0 + lane] = 0u; }
-                    while (word != 0u) {
-                        const int bit = __ffs((int) word) - 1;
-                        list[pos++] = (uint16_t) (((w0 + lane) << 5) + bit);
-                        word &= word - 1u;
-                    }
-                    cnt += __shfl_sync(0xffffffffu, incl, 31);
-                }
-                __syncwarp();
-                // ---- kernel function on the touched slots only, times v_j
-                for (int t = lane; t < cnt; t += 32) {
-                    const int jl = list[t];
-                    const T gv = FX::take(acc, W, jl, fx_inv);
-                    rowsum = fma(s_value<T, KERNEL>(gv, kf), __ldg(vb + jl), rowsum);
-                }
-            } else {
-                for (int jl = lane; jl < W; jl += 32) {
-                    const T gv = FX::take(acc, W, jl, fx_inv);
-                    rowsum = fma(s_value<T, KERNEL>(gv, kf), __ldg(vb + jl), rowsum);
-                }
-            }
-            __syncwarp();
-        }
-        rowsum = warp_sum(rowsum);
-        if (lane == 0) { out[row] += rowsum; }
+    }
+}
+__global__ void __launch_bounds__(1024) k_scan_add(int64_t *x, int64_t n, const int64_t *chunk_sum) {
+    const int64_t base = (int64_t) blockIdx.x * SCAN_CHUNK + (int64_t) threadIdx.x * 4;
+    const int64_t off = chunk_sum[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        if (base + k < n) { x[base + k] += off; }
     }
 }
 
@@ -456,8 +704,11 @@ struct sparse_state {
     // per-row data and work vectors
     dbuf norms, u, v, xl, wvec;
     // launch geometry of k_sp_kmv
-    int warps{ 0 };
-    size_t smem{ 0 };
+    int threads{ 256 };
+    // cached S of the rows [c_lo, c_hi) owned by this rank: visit-major (block, row) CSR with 16-bit row-in-block indices
+    dbuf c_ptr, c_j, c_val, c_P, c_chunks;
+    bool c_valid{ false }, c_refused{ false };
+    int64_t c_lo{ 0 }, c_hi{ 0 }, c_entries{ 0 };
     // predict staging
     dbuf p_rowptr, p_col, p_val, p_norms, p_u, p_out;
 };
@@ -533,7 +784,7 @@ host_csr<T> decode_input(const int64_t *rowptr, const int32_t *colidx, const voi
     return h;
 }
 
-// Transpose (CSC, rows ascending) + per-(feature, block) pointers.  FP22: entries are re-packed as (fp22 << 10 | row_in_block).
+// Transpose (CSC, rows ascending) + per-(feature, block) pointers.  FP22 storage: the values are the decoded (FP22-exact) floats.
 template <typename T>
 void build_transpose(ctx &c, sparse_state &st, const host_csr<T> &h) {
     const int64_t n = st.n, F = st.F;
@@ -548,16 +799,9 @@ void build_transpose(ctx &c, sparse_state &st, const host_csr<T> &h) {
         colptr[(size_t) f + 1] += colptr[(size_t) f];
     }
     st.fill = n > 0 ? std::min(1.0, sumsq / ((double) n * (double) n)) : 0.0;  // products per visit / W (upper bound of the hit fraction)
-    std::vector<uint16_t> tj;
-    std::vector<T> tval;
-    std::vector<uint32_t> pack;
+    std::vector<uint16_t> tj((size_t) nnz);
+    std::vector<T> tval((size_t) nnz);
     std::vector<int32_t> trow((size_t) nnz);  // global row of every transposed entry (for the block pointers)
-    if (st.fp22) {
-        pack.resize((size_t) nnz);
-    } else {
-        tj.resize((size_t) nnz);
-        tval.resize((size_t) nnz);
-    }
     {
         std::vector<int64_t> cursor(colptr.begin(), colptr.end() - 1);
         for (int64_t j = 0; j < n; ++j) {
@@ -565,12 +809,8 @@ void build_transpose(ctx &c, sparse_state &st, const host_csr<T> &h) {
             for (int64_t p = h.rowptr[(size_t) j]; p < h.rowptr[(size_t) j + 1]; ++p) {
                 const size_t e = (size_t) cursor[(size_t) h.col[(size_t) p]]++;
                 trow[e] = (int32_t) j;
-                if (st.fp22) {
-                    pack[e] = h.bits[(size_t) p] | jl;
-                } else {
-                    tj[e] = (uint16_t) jl;
-                    tval[e] = h.val[(size_t) p];
-                }
+                tj[e] = (uint16_t) jl;
+                tval[e] = h.val[(size_t) p];
             }
         }
     }
@@ -589,33 +829,24 @@ void build_transpose(ctx &c, sparse_state &st, const host_csr<T> &h) {
     }
     st.b_entries = nnz;
     st.avg_seg = (double) nnz / std::max(1.0, (double) F * (double) nb);
-    if (st.fp22) {
-        st.b_j.reserve(16);
-        upload(c, st.b_val, pack.data(), pack.size() * sizeof(uint32_t));
-    } else {
-        upload(c, st.b_j, tj.data(), tj.size() * sizeof(uint16_t));
-        upload(c, st.b_val, tval.data(), tval.size() * sizeof(T));
-    }
+    upload(c, st.b_j, tj.data(), tj.size() * sizeof(uint16_t));
+    upload(c, st.b_val, tval.data(), tval.size() * sizeof(T));
     upload(c, st.b_ptrT, ptrT.data(), ptrT.size() * sizeof(uint32_t));
     B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));  // host vectors go out of scope
 }
 
-// k_sp_kmv variants: K features per lane in registers -> rows of up to 32 K stored entries
+// shared memory of one k_sp_kmv CTA: accumulator limbs | bitmap | row (value, feature, segment start / end, long list) | slot list
+template <typename T>
+size_t kmv_smem_bytes(int W, int rmax) {
+    return (size_t) W * 4 * sp::fixp<T>::LIMBS + (size_t) W / 8 + (size_t) rmax * (sizeof(T) + 4 + 4 + 4 + 2) + (size_t) W * 2;
+}
+
 template <typename T, int KERNEL, bool FP22>
 void kmv_set_smem(int smem) {
-#define B200_SP_ATTR(KK, MT, CP, GG) \
-    B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, KERNEL, FP22, KK, MT, CP, GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))
-#define B200_SP_ATTR_G(KK, MT, CP) \
-    B200_SP_ATTR(KK, MT, CP, 1);   \
-    B200_SP_ATTR(KK, MT, CP, 8)
-    B200_SP_ATTR_G(4, 1024, true);
-    B200_SP_ATTR_G(8, 512, true);
-    B200_SP_ATTR_G(32, 256, true);
-    B200_SP_ATTR_G(4, 1024, false);
-    B200_SP_ATTR_G(8, 512, false);
-    B200_SP_ATTR_G(32, 256, false);
-#undef B200_SP_ATTR_G
-#undef B200_SP_ATTR
+    B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, KERNEL, FP22, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, KERNEL, FP22, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, KERNEL, FP22, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, KERNEL, FP22, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
 }
 
 template <typename T>
@@ -651,6 +882,8 @@ void set_data_typed(ctx &c, const int64_t *rowptr, const int32_t *colidx, const 
     st.fp22 = fmt == B200SVM_VAL_FP22;
     st.n = n;
     st.F = F;
+    st.c_valid = false;
+    st.c_refused = false;
     const host_csr<T> h = decode_input<T>(rowptr, colidx, values, n, F, fmt);
     // rows: FP22 keeps the caller's packed stream (decoded in registers by the kernels); otherwise (col, val) in the handle's type
     if (st.fp22) {
@@ -675,22 +908,19 @@ void set_data_typed(ctx &c, const int64_t *rowptr, const int32_t *colidx, const 
         const int64_t *rpx = st.fp22 ? rowptr : h.rowptr.data();
         for (int64_t i = 0; i < n; ++i) { st.a_max_row = std::max(st.a_max_row, rpx[i + 1] - rpx[i]); }
     }
-    // block width (rows of X per accumulator pass): option or default; shared memory per warp = W (sizeof(T) + 2) + W / 8
-    const int W = c.opt_sparse_block > 0 ? (int) c.opt_sparse_block : 1024;
-    B200_REQUIRE(W >= 128 && W <= 4096 && (W & (W - 1)) == 0, "sparse block width must be a power of two in [128, 4096]");
-    B200_REQUIRE(!st.fp22 || W <= 1024, "FP22 storage packs a 10-bit row-in-block index: sparse block width must be <= 1024");
+    // block width (rows of X per accumulator pass): option or default (8192: 50 KB float / 84 KB double per CTA => 4 / 2 CTAs per SM)
+    const int W = c.opt_sparse_block > 0 ? (int) c.opt_sparse_block : 8192;
+    B200_REQUIRE(W >= 128 && W <= 32768 && (W & (W - 1)) == 0, "sparse block width must be a power of two in [128, 32768]");
+    B200_REQUIRE(kmv_smem_bytes<T>(W, 1024) <= (size_t) 200 * 1024, "sparse block width too large for the shared memory of one SM");
     st.W = W;
     st.nb = (int) ((n + W - 1) / W);
     // blocks per launch group: keep the group's slice of the transpose L2-resident (~48 MB)
-    const double bytes_per_block = (double) h.col.size() / std::max(1, st.nb) * (st.fp22 ? 4.0 : 2.0 + sizeof(T)) + 4.0 * (double) F;
+    const double bytes_per_block = (double) h.col.size() / std::max(1, st.nb) * (2.0 + sizeof(T)) + 4.0 * (double) F;
     st.G = (int) std::max(1.0, std::min((double) st.nb, 48.0e6 / std::max(1.0, bytes_per_block)));
     if (c.opt_sparse_group > 0) { st.G = (int) std::min<int64_t>(c.opt_sparse_group, st.nb); }
     st.ng = (st.nb + st.G - 1) / st.G;
     build_transpose<T>(c, st, h);
-    const size_t per_warp = (size_t) W * 4 * (sizeof(T) == 4 ? 2 : 3) + (size_t) W / 8 + (size_t) W * 2;
-    st.warps = (int) std::min<size_t>(32, (size_t) (220 * 1024) / per_warp);
-    st.smem = per_warp * (size_t) st.warps;
-    set_kmv_attributes<T>(st.smem);
+    st.threads = sizeof(T) == 4 ? 256 : 512;
     // per-row norms, u = exp(-gamma |x|^2), work vectors
     st.norms.reserve((size_t) n * sizeof(T));
     st.u.reserve((size_t) n * sizeof(T));
@@ -706,6 +936,14 @@ void set_data_typed(ctx &c, const int64_t *rowptr, const int32_t *colidx, const 
 }
 
 }  // namespace
+
+void sp_invalidate_cache(ctx &c) {
+    if (c.sp_opaque != nullptr) {
+        sparse_state &st = state_of(c);
+        st.c_valid = false;
+        st.c_refused = false;
+    }
+}
 
 void sp_set_data(ctx &c, const int64_t *rowptr, const int32_t *colidx, const void *values, int64_t n, int64_t F, int64_t nnz, int fmt) {
     B200_REQUIRE(rowptr != nullptr && rowptr[0] == 0 && rowptr[n] == nnz, "CSR row pointers inconsistent with nnz");
@@ -731,11 +969,15 @@ namespace {
         }                                                   \
     } while (0)
 
-// max_norm2 bounds |G_ij| and every partial sum of its products (Cauchy-Schwarz): scale = 2^(BITS - ceil(log2 bound))
-sp::kfun make_kfun(const ctx &c, double max_norm2 = 1.0) {
+// max_norm2 bounds |G_ij| and every partial sum of its products (Cauchy-Schwarz): scale = 2^(bits - ceil(log2 bound));
+// max_row bounds the number of additions per slot (head-room of the low limb of the double accumulator)
+sp::kfun make_kfun(const ctx &c, double max_norm2 = 1.0, int64_t max_row = 1024) {
     sp::kfun k{};
     {
-        const int bits = c.dtype == B200SVM_F32 ? 42 : 61;
+        int headroom = 1;
+        while ((int64_t(1) << headroom) < max_row) { ++headroom; }
+        k.lb = 32 - headroom;
+        const int bits = c.dtype == B200SVM_F32 ? 30 : k.lb + 30;
         int e = 0;
         if (max_norm2 > 0 && std::isfinite(max_norm2)) { std::frexp(max_norm2, &e); }  // max_norm2 < 2^e
         k.fx_scale = std::ldexp(1.0, bits - e);
@@ -754,62 +996,125 @@ sp::kfun make_kfun(const ctx &c, double max_norm2 = 1.0) {
 }
 
 // out[row] (rows [lo, hi) of A, zero on entry) += sum_j S(G_row,j) v_j over all column groups; max_row = longest row of A
+// mode 0: on-the-fly matvec; 1 / 2: count / fill pass of the S cache (`cache` describes the destination)
 template <typename T, int KERNEL, bool FP22>
 void launch_kmv_variant(ctx &c, const sparse_state &st, const sp::csr_view &A, int64_t lo, int64_t hi, int64_t max_row, double max_norm2,
-                        const T *v, T *out) {
+                        const T *v, T *out, int mode, const sp::cache_view &cache) {
     const sp::csc_view B = view_blocks(st);
-    const sp::kfun kf = make_kfun(c, max_norm2);
+    const sp::kfun kf = make_kfun(c, max_norm2, max_row);
     const int64_t rows = hi - lo;
-    B200_REQUIRE(max_row <= 1024, "rows with more than 1024 stored entries are not supported by the sparse path: pass the data dense");
-    const int K = max_row <= 128 ? 4 : (max_row <= 256 ? 8 : 32);
-    const int warps = std::min(st.warps, K == 4 ? 32 : (K == 8 ? 16 : 8));
-    const int grid = (int) std::min<int64_t>(NUM_SMS, (rows + warps - 1) / warps);
-    const size_t smem = st.smem / (size_t) st.warps * (size_t) warps;
-    const bool compact = st.fill < 0.5;
-    // lanes per (feature, block) segment: one lane walks its own features unless the segments are long (measured on B200:
-    // 8 lanes per segment only pays beyond ~64 entries per segment)
-    const int gs = c.opt_sparse_lanes > 0 ? (int) c.opt_sparse_lanes : (st.avg_seg < 64.0 ? 1 : 8);
+    B200_REQUIRE(max_row <= 4096, "rows with more than 4096 stored entries are not supported by the sparse path: pass the data dense");
+    int threads = c.opt_sparse_threads > 0 ? (int) c.opt_sparse_threads : st.threads;
+    while ((int64_t) threads * sp::SP_MAX_OWN < max_row) { threads *= 2; }
+    const int rmax = (int) std::max<int64_t>(32, (max_row + 31) / 32 * 32);
+    const size_t smem = kmv_smem_bytes<T>(st.W, rmax);
+    B200_REQUIRE(smem <= (size_t) 227 * 1024, "sparse block width and row length exceed the shared memory of one SM");
+    set_kmv_attributes<T>(smem);
+    const int per_sm = (int) std::max<size_t>(1, std::min<size_t>((size_t) 2048 / (size_t) threads, (size_t) (227 * 1024) / (smem + 1024)));
+    const int grid = (int) std::min<int64_t>((int64_t) NUM_SMS * per_sm, rows);
+    const bool compact = mode != 0 || st.fill < 0.5;
+    // lanes per (feature, block) segment: the power of two next to the mean segment length (option: fixed)
+    int gs_log2 = 0;
+    if (c.opt_sparse_lanes > 0) {
+        while ((2 << gs_log2) <= (int) c.opt_sparse_lanes && gs_log2 < 5) { ++gs_log2; }
+    } else {
+        while ((double) (1 << gs_log2) < st.avg_seg && gs_log2 < 5) { ++gs_log2; }
+    }
+    const int thr = std::max(64, 16 << gs_log2);
     for (int g = 0; g < st.ng; ++g) {
-#define B200_SP_LAUNCH_G(KK, MT, CP)                                                                                               \
-    do {                                                                                                                           \
-        if (gs == 1) {                                                                                                             \
-            sp::k_sp_kmv<T, KERNEL, FP22, KK, MT, CP, 1><<<grid, warps * 32, smem, c.stream>>>(A, lo, hi, B, g, v, kf, out);       \
-        } else {                                                                                                                   \
-            sp::k_sp_kmv<T, KERNEL, FP22, KK, MT, CP, 8><<<grid, warps * 32, smem, c.stream>>>(A, lo, hi, B, g, v, kf, out);       \
-        }                                                                                                                          \
-    } while (0)
-#define B200_SP_LAUNCH(KK, MT)                \
-    do {                                      \
-        if (compact) {                        \
-            B200_SP_LAUNCH_G(KK, MT, true);   \
-        } else {                              \
-            B200_SP_LAUNCH_G(KK, MT, false);  \
-        }                                     \
-    } while (0)
-        if (K == 4) {
-            B200_SP_LAUNCH(4, 1024);
-        } else if (K == 8) {
-            B200_SP_LAUNCH(8, 512);
+        if (mode == 1) {
+            sp::k_sp_kmv<T, KERNEL, FP22, true, 1><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache);
+        } else if (mode == 2) {
+            sp::k_sp_kmv<T, KERNEL, FP22, true, 2><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache);
+        } else if (compact) {
+            sp::k_sp_kmv<T, KERNEL, FP22, true, 0><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache);
         } else {
-            B200_SP_LAUNCH(32, 256);
+            sp::k_sp_kmv<T, KERNEL, FP22, false, 0><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache);
         }
-#undef B200_SP_LAUNCH_G
-#undef B200_SP_LAUNCH
         count_launch(c);
         B200_CUDA_CHECK(cudaGetLastError());
     }
 }
 
 template <typename T>
-void launch_kmv(ctx &c, const sparse_state &st, const sp::csr_view &A, int64_t lo, int64_t hi, int64_t max_row, double max_norm2, const T *v, T *out) {
+void launch_kmv(ctx &c, const sparse_state &st, const sp::csr_view &A, int64_t lo, int64_t hi, int64_t max_row, double max_norm2, const T *v, T *out,
+                int mode = 0, const sp::cache_view &cache = sp::cache_view{}) {
     if (hi <= lo) { return; }
     if (c.kernel == B200SVM_RBF) {
-        B200_SP_DISPATCH_FP22(st, T, (launch_kmv_variant<T, B200SVM_RBF, true>(c, st, A, lo, hi, max_row, max_norm2, v, out)),
-                              (launch_kmv_variant<T, B200SVM_RBF, false>(c, st, A, lo, hi, max_row, max_norm2, v, out)));
+        B200_SP_DISPATCH_FP22(st, T, (launch_kmv_variant<T, B200SVM_RBF, true>(c, st, A, lo, hi, max_row, max_norm2, v, out, mode, cache)),
+                              (launch_kmv_variant<T, B200SVM_RBF, false>(c, st, A, lo, hi, max_row, max_norm2, v, out, mode, cache)));
     } else {
-        B200_SP_DISPATCH_FP22(st, T, (launch_kmv_variant<T, B200SVM_POLYNOMIAL, true>(c, st, A, lo, hi, max_row, max_norm2, v, out)),
-                              (launch_kmv_variant<T, B200SVM_POLYNOMIAL, false>(c, st, A, lo, hi, max_row, max_norm2, v, out)));
+        B200_SP_DISPATCH_FP22(st, T, (launch_kmv_variant<T, B200SVM_POLYNOMIAL, true>(c, st, A, lo, hi, max_row, max_norm2, v, out, mode, cache)),
+                              (launch_kmv_variant<T, B200SVM_POLYNOMIAL, false>(c, st, A, lo, hi, max_row, max_norm2, v, out, mode, cache)));
     }
+}
+
+// Assemble the S cache of rows [lo, hi) (two passes of the on-the-fly kernel: count, prefix sum, fill).  Returns false (and
+// remembers the refusal) when the entries do not fit the memory budget; the caller then keeps the on-the-fly path.
+template <typename T>
+bool build_cache(ctx &c, sparse_state &st, int64_t lo, int64_t hi) {
+    const int64_t rows = hi - lo;
+    const int64_t visits = (int64_t) st.nb * rows;
+    st.c_valid = false;
+    if (rows <= 0) { return false; }
+    st.c_ptr.reserve((size_t) (visits + 1) * sizeof(int64_t));
+    B200_CUDA_CHECK(cudaMemsetAsync(st.c_ptr.p, 0, (size_t) (visits + 1) * sizeof(int64_t), c.stream));
+    sp::cache_view cv{ st.c_ptr.as<int64_t>(), nullptr, nullptr, rows };
+    const sp::csr_view A = view_rows(st, 0, st.n);
+    launch_kmv<T>(c, st, A, lo, hi, st.a_max_row, st.max_norm2, static_cast<const T *>(nullptr), static_cast<T *>(nullptr), 1, cv);
+    // exclusive prefix sum over the visits (+ the total in the last slot)
+    const int64_t n = visits + 1, chunks = (n + sp::SCAN_CHUNK - 1) / sp::SCAN_CHUNK;
+    st.c_chunks.reserve((size_t) chunks * sizeof(int64_t));
+    sp::k_scan_chunks<<<(unsigned) chunks, 1024, 0, c.stream>>>(st.c_ptr.as<int64_t>(), n, st.c_chunks.as<int64_t>());
+    sp::k_scan_top<<<1, 32, 0, c.stream>>>(st.c_chunks.as<int64_t>(), chunks);
+    sp::k_scan_add<<<(unsigned) chunks, 1024, 0, c.stream>>>(st.c_ptr.as<int64_t>(), n, st.c_chunks.as<int64_t>());
+    count_launch(c, 3);
+    B200_CUDA_CHECK(cudaGetLastError());
+    int64_t entries = 0;
+    B200_CUDA_CHECK(cudaMemcpyAsync(&entries, st.c_ptr.as<int64_t>() + visits, sizeof(int64_t), cudaMemcpyDeviceToHost, c.stream));
+    B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));
+    const size_t need = (size_t) entries * (sizeof(T) + 2) + (size_t) visits * sizeof(T) + (size_t) (64 << 20);
+    size_t free_b = 0, total_b = 0;
+    B200_CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
+    free_b += st.c_j.bytes + st.c_val.bytes + st.c_P.bytes;  // buffers of a previous cache are reused
+    const double budget = c.opt_sparse_cache_mb > 0 ? (double) c.opt_sparse_cache_mb * 1048576.0 : 0.85 * (double) free_b;
+    if ((double) need > budget) {
+        B200_REQUIRE(c.opt_sparse_cache != 2, "the cached kernel-matrix entries do not fit the device memory budget");
+        st.c_refused = true;
+        return false;
+    }
+    st.c_j.reserve(std::max<size_t>((size_t) entries * 2, 16));
+    st.c_val.reserve(std::max<size_t>((size_t) entries * sizeof(T), 16));
+    st.c_P.reserve((size_t) visits * sizeof(T));
+    cv.j = st.c_j.as<uint16_t>();
+    cv.val = st.c_val.p;
+    launch_kmv<T>(c, st, A, lo, hi, st.a_max_row, st.max_norm2, static_cast<const T *>(nullptr), static_cast<T *>(nullptr), 2, cv);
+    st.c_lo = lo;
+    st.c_hi = hi;
+    st.c_entries = entries;
+    st.c_valid = true;
+    c.stats.sparse_cache_entries = entries;
+    return true;
+}
+
+// out[lo..hi) = S v from the cache
+template <typename T>
+void cached_matvec(ctx &c, sparse_state &st, const T *v, T *out) {
+    const int64_t rows = st.c_hi - st.c_lo;
+    const sp::cache_view cv{ st.c_ptr.as<int64_t>(), st.c_j.as<uint16_t>(), st.c_val.p, rows };
+    const int rows_per_cta = 256;
+    static size_t attr_smem[2] = { 0, 0 };
+    const size_t smem = (size_t) st.W * sizeof(T);
+    if (smem > attr_smem[sizeof(T) == 8]) {
+        B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_cached_mv<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        attr_smem[sizeof(T) == 8] = smem;
+    }
+    const dim3 grid((unsigned) ((rows + rows_per_cta - 1) / rows_per_cta), (unsigned) st.nb);
+    sp::k_sp_cached_mv<T><<<grid, 256, smem, c.stream>>>(cv, st.W, rows_per_cta, v, st.c_P.as<T>());
+    const int64_t g = std::max<int64_t>(1, std::min<int64_t>((rows + 255) / 256, 8 * NUM_SMS));
+    sp::k_sp_fold_blocks<T><<<(unsigned) g, 256, 0, c.stream>>>(st.c_P.as<T>(), st.nb, rows, out + st.c_lo);
+    count_launch(c, 2);
+    B200_CUDA_CHECK(cudaGetLastError());
 }
 
 template <typename T>
@@ -836,7 +1141,7 @@ template <typename T>
 void xt_v_blocks(ctx &c, const sparse_state &st, const T *v, T *w) {
     const sp::csc_view B = view_blocks(st);
     const unsigned grid = (unsigned) ((st.F + 255) / 256);
-    B200_SP_DISPATCH_FP22(st, T, (sp::k_sp_xt_v<T, true><<<grid, 256, 0, c.stream>>>(B, v, w)), (sp::k_sp_xt_v<T, false><<<grid, 256, 0, c.stream>>>(B, v, w)));
+    sp::k_sp_xt_v<T><<<grid, 256, 0, c.stream>>>(B, v, w);
     count_launch(c);
     B200_CUDA_CHECK(cudaGetLastError());
 }
@@ -892,7 +1197,18 @@ void sp_kernel_matvec(ctx &c, const T *d, T *out) {
     const bool rbf = c.kernel == B200SVM_RBF;
     weights<T>(c, d, rbf ? st.u.as<T>() : static_cast<const T *>(nullptr), m, nbW, v);
     B200_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t) m * sizeof(T), c.stream));
-    launch_kmv<T>(c, st, view_rows(st, 0, st.n), lo, hi, st.a_max_row, st.max_norm2, v, out);
+    // S is cached on first use when it fits the memory budget (then the matvec is an HBM-bound SpMV), else recomputed on the fly
+    if (c.opt_sparse_cache != 1 && hi > lo) {
+        if (st.c_valid && (st.c_lo != lo || st.c_hi != hi)) { st.c_valid = false; }
+        if (!st.c_valid && !st.c_refused) { build_cache<T>(c, st, lo, hi); }
+    } else {
+        st.c_valid = false;
+    }
+    if (st.c_valid) {
+        cached_matvec<T>(c, st, v, out);
+    } else {
+        launch_kmv<T>(c, st, view_rows(st, 0, st.n), lo, hi, st.a_max_row, st.max_norm2, v, out);
+    }
     const sp::kfun kf = make_kfun(c);
     int64_t g = std::max<int64_t>(1, std::min<int64_t>((m + 1023) / 1024, 8 * NUM_SMS));
     sp::k_sp_finish<T><<<(unsigned) g, 256, 0, c.stream>>>(out, st.u.as<T>(), m, lo, hi, rbf ? 1 : 0, (T) kf.c0pow, c.scal.as<T>(), S_TMP0, T(0),

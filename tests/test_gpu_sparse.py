@@ -23,10 +23,12 @@ def make(n, F, density, seed, dt, min_nnz=1):
     return rp, ci, v, y
 
 
+@pytest.mark.parametrize("cache", [capi.CACHE_OFF, capi.CACHE_REQUIRED])
 @pytest.mark.parametrize("dt", [np.float64, np.float32])
 @pytest.mark.parametrize("kernel", KERNELS)
 @pytest.mark.parametrize("shape", [(2, 7, 0.5, 0), (67, 40, 0.2, 128), (300, 1000, 0.01, 128), (1100, 300, 0.05, 256), (700, 5000, 0.004, 0)])
-def test_csr_q_and_matvec_vs_oracle(kernel, dt, shape):
+def test_csr_q_and_matvec_vs_oracle(kernel, dt, shape, cache):
+    """cache OFF: S recomputed on the fly in every matvec; REQUIRED: S assembled once, matvec = SpMV over the stored entries."""
     n, F, density, W = shape
     rp, ci, v, _ = make(n, F, density, seed=n + F, dt=dt, min_nnz=0 if n > 2 else 1)
     coef0 = 0.5 if kernel == "polynomial" else 0.0
@@ -34,6 +36,7 @@ def test_csr_q_and_matvec_vs_oracle(kernel, dt, shape):
     with capi.Handle(dt, kernel, 3, 1.0 / F, coef0, 1.5) as h:
         if W:
             h.set_option(capi.OPT_SPARSE_BLOCK, W)
+        h.set_option(capi.OPT_SPARSE_CACHE, cache)
         h.set_data_csr(rp, ci, v, F)
         q = h.generate_q()
         q_o = port.csr_generate_q(rp, ci, v, F, kernel, 3, 1.0 / F, coef0)
@@ -51,6 +54,8 @@ def test_csr_q_and_matvec_vs_oracle(kernel, dt, shape):
         base = np.linspace(-1, 1, n - 1).astype(dt)
         got2 = h.matvec(d, -1.0, ret=base)
         assert nrm_rel(base - want, got2) < (1e-12 if dt == np.float64 else 2e-5)
+        if kernel != "linear":
+            assert (h.stats().sparse_cache_entries > 0) == (cache == capi.CACHE_REQUIRED)
 
 
 @pytest.mark.parametrize("kernel", KERNELS)
@@ -155,20 +160,26 @@ def test_csr_predict_and_update_w(kernel, dt):
 @pytest.mark.parametrize("kernel", ["polynomial", "rbf"])
 @pytest.mark.parametrize("shape", [(300, 2000, 0.1, 128, 1), (200, 1500, 0.4, 128, 1), (900, 500, 0.05, 128, 2), (1000, 3000, 0.01, 256, 1)])
 def test_csr_long_rows_and_launch_groups(kernel, dt, shape):
-    """Rows of > 128 / > 256 stored entries (8 / 32 features per lane) and several launch groups (cursor restart per group)."""
+    """Rows of hundreds of stored entries, dense fill of the accumulator and several launch groups (segment pointers restart per group)."""
     n, F, density, W, G = shape
     rp, ci, v, _ = make(n, F, density, seed=n, dt=dt)
     d = np.random.default_rng(n).uniform(-1, 2, n - 1).astype(dt)
-    with capi.Handle(dt, kernel, 2, 1.0 / F, 0.0, 1.0) as h:
-        h.set_option(capi.OPT_SPARSE_BLOCK, W)
-        h.set_option(capi.OPT_SPARSE_GROUP, G)
-        h.set_data_csr(rp, ci, v, F)
-        q = h.generate_q()
-        qa = h.kxx_last() + 1.0
-        h.set_q(q, qa)
-        got = h.matvec(d, 1.0)
-    want = port.csr_matvec(rp, ci, v.astype(np.float64), F, q.astype(np.float64), d.astype(np.float64), qa, 1.0, kernel, 2, 1.0 / F, 0.0, 1.0)
-    assert nrm_rel(want, got) < (1e-12 if dt == np.float64 else 2e-5), nrm_rel(want, got)
+    want = None
+    for cache in (capi.CACHE_OFF, capi.CACHE_AUTO):
+        with capi.Handle(dt, kernel, 2, 1.0 / F, 0.0, 1.0) as h:
+            h.set_option(capi.OPT_SPARSE_BLOCK, W)
+            h.set_option(capi.OPT_SPARSE_GROUP, G)
+            h.set_option(capi.OPT_SPARSE_CACHE, cache)
+            h.set_data_csr(rp, ci, v, F)
+            q = h.generate_q()
+            qa = h.kxx_last() + 1.0
+            h.set_q(q, qa)
+            got = h.matvec(d, 1.0)
+            again = h.matvec(d, 1.0)
+            assert np.array_equal(got, again)  # bit-reproducible
+        if want is None:
+            want = port.csr_matvec(rp, ci, v.astype(np.float64), F, q.astype(np.float64), d.astype(np.float64), qa, 1.0, kernel, 2, 1.0 / F, 0.0, 1.0)
+        assert nrm_rel(want, got) < (1e-12 if dt == np.float64 else 2e-5), nrm_rel(want, got)
 
 
 def test_fp22_launch_groups():
@@ -193,14 +204,81 @@ def test_fp22_launch_groups():
 
 
 def test_csr_row_too_long_is_rejected():
-    n, F = 40, 3000
+    n, F = 24, 12000
     rp, ci, v, _ = make(n, F, 0.5, seed=1, dt=np.float64)
     with capi.Handle(np.float64, "rbf", gamma=1.0 / F) as h:
         h.set_data_csr(rp, ci, v, F)
         q = h.generate_q()
         h.set_q(q, 2.0)
-        with pytest.raises(capi.B200Error, match="1024 stored entries"):
+        with pytest.raises(capi.B200Error, match="4096 stored entries"):
             h.matvec(np.ones(n - 1))
+
+
+@pytest.mark.parametrize("dt", [np.float64, np.float32])
+def test_csr_rows_of_thousands_of_entries(dt):
+    """Rows beyond 4 x the default CTA size (the CTA is widened) and more than 1024 additions per accumulator slot."""
+    n, F = 60, 5000
+    rp, ci, v, _ = make(n, F, 0.5, seed=2, dt=dt)
+    d = np.random.default_rng(2).uniform(-1, 2, n - 1).astype(dt)
+    with capi.Handle(dt, "rbf", 3, 1.0 / F, 0.0, 1.0) as h:
+        h.set_data_csr(rp, ci, v, F)
+        q = h.generate_q()
+        qa = h.kxx_last() + 1.0
+        h.set_q(q, qa)
+        got = h.matvec(d, 1.0)
+    want = port.csr_matvec(rp, ci, v.astype(np.float64), F, q.astype(np.float64), d.astype(np.float64), qa, 1.0, "rbf", 3, 1.0 / F, 0.0, 1.0)
+    assert nrm_rel(want, got) < (1e-12 if dt == np.float64 else 2e-5), nrm_rel(want, got)
+
+
+@pytest.mark.parametrize("dt", [np.float64, np.float32])
+@pytest.mark.parametrize("kernel", ["polynomial", "rbf"])
+def test_csr_dense_columns_take_the_long_segment_path(kernel, dt):
+    """Two features present in (almost) every row: their segments exceed the group threshold and are walked by the whole CTA."""
+    n, F = 1500, 4000
+    rng = np.random.default_rng(11)
+    X = np.zeros((n, F), dt)
+    mask = rng.random((n, F)) < 0.004
+    X[mask] = rng.uniform(-1, 1, int(mask.sum())).astype(dt)
+    X[:, 7] = rng.uniform(-1, 1, n).astype(dt)
+    X[::2, 1234] = rng.uniform(-1, 1, (n + 1) // 2).astype(dt)
+    rp, ci, v = datagen.dense_to_csr(X)
+    d = rng.uniform(-1, 2, n - 1).astype(dt)
+    outs = []
+    for lanes, threads in ((0, 0), (1, 128), (32, 1024), (4, 256)):
+        with capi.Handle(dt, kernel, 2, 1.0 / 16, 0.5, 1.0) as h:
+            h.set_option(capi.OPT_SPARSE_BLOCK, 512)
+            h.set_option(capi.OPT_SPARSE_CACHE, capi.CACHE_OFF if lanes else capi.CACHE_AUTO)
+            h.set_option(capi.OPT_SPARSE_LANES, lanes)
+            h.set_option(capi.OPT_SPARSE_THREADS, threads)
+            h.set_data_csr(rp, ci, v, F)
+            q = h.generate_q()
+            qa = h.kxx_last() + 1.0
+            h.set_q(q, qa)
+            outs.append(h.matvec(d, 1.0))
+    want = port.csr_matvec(rp, ci, v.astype(np.float64), F, q.astype(np.float64), d.astype(np.float64), qa, 1.0, kernel, 2, 1.0 / 16, 0.5, 1.0)
+    for o in outs:
+        assert nrm_rel(want, o) < (1e-12 if dt == np.float64 else 2e-5), nrm_rel(want, o)
+
+
+def test_csr_cache_budget_falls_back_or_fails_loudly():
+    n, F = 900, 600
+    rp, ci, v, _ = make(n, F, 0.05, seed=9, dt=np.float32)
+    d = np.random.default_rng(9).uniform(-1, 2, n - 1).astype(np.float32)
+    outs = []
+    for mode, mb in ((capi.CACHE_AUTO, 0), (capi.CACHE_AUTO, 1), (capi.CACHE_REQUIRED, 1)):
+        with capi.Handle(np.float32, "rbf", gamma=1.0 / F) as h:
+            h.set_option(capi.OPT_SPARSE_CACHE, mode)
+            h.set_option(capi.OPT_SPARSE_CACHE_MB, mb)
+            h.set_data_csr(rp, ci, v, F)
+            q = h.generate_q()
+            h.set_q(q, 2.0)
+            if mode == capi.CACHE_REQUIRED:
+                with pytest.raises(capi.B200Error, match="do not fit"):
+                    h.matvec(d)
+                continue
+            outs.append(h.matvec(d))
+            assert (h.stats().sparse_cache_entries > 0) == (mb == 0)  # a 1 MiB budget cannot hold the fixed 64 MiB reserve
+    assert nrm_rel(outs[0], outs[1]) < 2e-6
 
 
 def test_csr_errors_are_loud():

@@ -22,6 +22,9 @@ def main():
     ap.add_argument("--block", type=int, default=0)
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--lanes", type=int, default=0)
+    ap.add_argument("--threads", type=int, default=0)
+    ap.add_argument("--group", type=int, default=0)
+    ap.add_argument("--cache", type=int, default=0, help="0 auto, 1 off (on the fly), 2 required")
     a = ap.parse_args()
     dt = np.float64 if a.dtype == "f64" else np.float32
     t0 = time.time()
@@ -34,6 +37,11 @@ def main():
             h.set_option(capi.OPT_SPARSE_BLOCK, a.block)
         if a.lanes:
             h.set_option(capi.OPT_SPARSE_LANES, a.lanes)
+        if a.threads:
+            h.set_option(capi.OPT_SPARSE_THREADS, a.threads)
+        if a.group:
+            h.set_option(capi.OPT_SPARSE_GROUP, a.group)
+        h.set_option(capi.OPT_SPARSE_CACHE, a.cache)
         t0 = time.time()
         if a.dtype == "fp22":
             prp, packed = datagen.pack_fp22_csr(rp, ci, v)
@@ -44,15 +52,18 @@ def main():
         q = h.generate_q()
         h.set_q(q, h.kxx_last() + 1.0)
         d = np.random.default_rng(1).standard_normal(a.points - 1).astype(dt)
-        h.matvec(d)  # warm-up
+        t0 = time.time()
+        h.matvec(d)  # warm-up (assembles the S cache when enabled)
+        t_first = time.time() - t0
+        cache_entries = h.stats().sparse_cache_entries
         h.reset_stats()
         for _ in range(a.reps):
             out = h.matvec(d)
         st = h.stats()
         ms = st.matvec_ms / st.matvecs
-    print(json.dumps({"points": a.points, "features": a.features, "density": a.density, "kernel": a.kernel, "dtype": a.dtype, "block": a.block, "lanes": a.lanes,
+    print(json.dumps({"points": a.points, "features": a.features, "density": a.density, "kernel": a.kernel, "dtype": a.dtype, "block": a.block, "lanes": a.lanes, "threads": a.threads, "group": a.group,
                       "nnz": int(rp[-1]), "gram_products": products, "ms_per_matvec": ms, "gproducts_per_s": products / ms / 1e6,
-                      "pairs_per_s": (a.points - 1.0) ** 2 / ms / 1e6 * 1e-3, "gen_s": t_gen, "set_data_s": t_set, "checksum": float(np.abs(out).sum())}))
+                      "pairs_per_s": (a.points - 1.0) ** 2 / ms / 1e6 * 1e-3, "cache": a.cache, "cache_entries": int(cache_entries), "first_matvec_s": t_first, "gen_s": t_gen, "set_data_s": t_set, "checksum": float(np.abs(out).sum())}))
 
 
 if __name__ == "__main__":
