@@ -50,10 +50,23 @@ def parse_args():
     ap.add_argument("--cpu-sample-points", type=int, default=0, help="row subset for the CPU baseline (0 = calibrate to ~10 s)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--seed", type=int, default=43)
+    ap.add_argument("--density", type=float, default=0.0,
+                    help="> 0: SPARSE workload (not the driver's default line): CSR rows of this density, e.g. configs[2] "
+                         "--points 1000000 --features 100000 --density 1e-3 --dtype f64, configs[3] --points 262144 --features 20000 "
+                         "--density 1e-2 --kernel polynomial --storage fp22")
+    ap.add_argument("--storage", default="native", choices=["native", "fp22"], help="sparse value storage")
+    ap.add_argument("--cache", type=int, default=0, help="sparse: 0 cache S if it fits, 1 recompute on the fly, 2 require the cache")
     return ap.parse_args()
 
 
 def workload_config(a):
+    if a.density > 0:
+        return {
+            "workload": f"sparse: {a.kernel} kernel, {a.points} points x {a.features} features at density {a.density:g} (CSR, "
+                        f"{'FP22-packed' if a.storage == 'fp22' else a.dtype} values), gamma=1/F, C=1, fixed-iteration CG (eps=0)",
+            "points": a.points, "features": a.features, "kernel": a.kernel, "density": a.density, "storage": a.storage,
+            "l2": "inputs larger than L2 (the cached S matrix / the transpose are streamed from HBM every step)",
+        }
     return {
         "workload": f"configs[1]: {a.kernel} kernel, {a.points} points x {a.features} dense features, {a.dtype}, gamma=1/F, C=1, "
                     "fixed-iteration CG (eps=0)",
@@ -188,18 +201,36 @@ def run_b200_arm(a):
     dt = np.float32 if a.dtype == "f32" else np.float64
     n, F, K, W = a.points, a.features, a.steps, a.warmup
 
-    X, y = datagen.make_dense(n, F, seed=a.seed, problem="blobs", dtype=dt)
-    # pinned host staging for the e2e leg
-    Xp = torch.empty((n, F), dtype=torch.float32 if dt == np.float32 else torch.float64, pin_memory=True)
-    Xp.numpy()[:] = X
-    Xh = Xp.numpy()
+    sparse = a.density > 0
+    if sparse:
+        rp, ci, vals, y = datagen.make_sparse_csr(n, F, a.density, seed=a.seed, dtype=dt)
+        if a.storage == "fp22":
+            assert a.dtype == "f32", "FP22 storage needs --dtype f32"
+            prp, packed = datagen.pack_fp22_csr(rp, ci, vals)
+        X = None
+    else:
+        X, y = datagen.make_dense(n, F, seed=a.seed, problem="blobs", dtype=dt)
+        # pinned host staging for the e2e leg
+        Xp = torch.empty((n, F), dtype=torch.float32 if dt == np.float32 else torch.float64, pin_memory=True)
+        Xp.numpy()[:] = X
+        Xh = Xp.numpy()
     b = (y[:-1] - y[-1]).astype(dt)
+
+    def set_data():
+        if not sparse:
+            h.set_data(Xh)
+        elif a.storage == "fp22":
+            h.set_data_csr(prp, None, packed, F, value_format=capi.VAL_FP22)
+        else:
+            h.set_data_csr(rp, ci, vals, F)
 
     h = capi.Handle(dt, a.kernel, 3, 1.0 / F, 0.0, 1.0, device=local_rank)
     stream = torch.cuda.current_stream()
     h.set_stream(stream.cuda_stream)
     if a.path:
         h.set_option(capi.OPT_MATVEC_PATH, a.path)
+    if sparse:
+        h.set_option(capi.OPT_SPARSE_CACHE, a.cache)
     if world > 1:
         idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
@@ -213,7 +244,7 @@ def run_b200_arm(a):
         torch.cuda.synchronize()
 
     # ---- resident leg (value) ----
-    h.set_data(Xh)
+    set_data()
     q = h.generate_q()
     QA = h.kxx_last() + 1.0
     h.solver_cg(b, None, QA, max(W, 3), 0.0)  # warm-up steps (untimed)
@@ -233,10 +264,15 @@ def run_b200_arm(a):
     matvec_ms = st.matvec_ms / max(st.matvecs, 1)
     n_matvecs = int(st.matvecs)
     path = int(st.matvec_path)
+    cache_entries = int(st.sparse_cache_entries) if sparse else 0
+    if sparse and world > 1:
+        ce = torch.tensor([cache_entries], device="cuda", dtype=torch.int64)
+        dist.all_reduce(ce, op=dist.ReduceOp.MAX)
+        cache_entries = int(ce[0])  # the largest rank bounds the step
 
     # ---- e2e leg: host buffers through the C ABI ----
     def e2e_once():
-        h.set_data(Xh)
+        set_data()
         h.generate_q()
         return h.solver_cg(b, None, QA, K, 0.0)
 
@@ -267,6 +303,19 @@ def run_b200_arm(a):
         roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
                 "peak_source": f"{peak_kind} bf16 dense (sustained)", "kernel": {1: "k_kmv_tile (SIMT fp32)", 2: "k_gram_tc (tcgen05 fp16x2-split)", 3: "gemv pair"}.get(path, "?"),
                 "alg_flops_per_launch": flops, "ms_per_launch": matvec_ms, "launches_timed": n_matvecs}
+        if sparse and cache_entries > 0:
+            # cached S: the matvec streams (value + 16-bit index) per stored entry, once (SURVEY.md §8d "cached S" row)
+            nbytes = float(cache_entries) * (np.dtype(dt).itemsize + 2)
+            ach = nbytes / (matvec_ms * 1e-3) / 1e9
+            hb = float(peaks.get("hbm_gbs", 6650.0))
+            roof = {"bound": "hbm", "achieved": ach, "peak": hb, "unit": "GB/s", "frac": ach / hb, "traffic": None, "peak_source": f"{peak_kind} HBM copy",
+                    "kernel": "k_sp_cached_mv (SpMV over the cached S entries; weights / fold / finish kernels inside the timed span)",
+                    "alg_bytes_per_launch": nbytes, "entries_per_gpu": cache_entries, "ms_per_launch": matvec_ms, "launches_timed": n_matvecs}
+            flops = 2.0 * cache_entries
+        elif sparse:
+            roof = {"bound": "fp", "achieved": None, "peak": None, "unit": "TFLOP/s", "frac": None, "traffic": None,
+                    "kernel": "k_sp_kmv (S recomputed on the fly: the cache did not fit or was disabled)", "ms_per_launch": matvec_ms, "launches_timed": n_matvecs}
+            flops = 0.0
         line = {
             "metric": METRIC, "value": K / (t_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(W, 3),
             "ms_per_step": t_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -278,7 +327,7 @@ def run_b200_arm(a):
             "gpu_launches": launches,
             "roofline": roof,
         }
-        if world == 1 and not a.no_cpu_baseline:
+        if world == 1 and not a.no_cpu_baseline and not sparse:
             res = cpu_reference_iteration_rate(a, 1, 0, X, a.cpu_sample_points, budget_s=12.0)
             line["cpu_baseline"] = {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")}
         print(json.dumps(line), flush=True)

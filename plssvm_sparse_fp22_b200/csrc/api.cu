@@ -234,7 +234,11 @@ int b200svm_get_stats(b200svm_handle h, b200svm_stats *out) {
 
 int b200svm_reset_stats(b200svm_handle h) {
     ctx *c = reinterpret_cast<ctx *>(h);
-    return guarded(c, [&]() { c->stats = b200svm_stats{}; });
+    return guarded(c, [&]() {
+        const int64_t cached = c->stats.sparse_cache_entries;  // a property of the resident data, not a counter
+        c->stats = b200svm_stats{};
+        c->stats.sparse_cache_entries = cached;
+    });
 }
 
 int b200svm_set_data_dense(b200svm_handle h, const void *X, int64_t n, int64_t F, int64_t ld) {

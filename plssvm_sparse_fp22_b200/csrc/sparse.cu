@@ -884,6 +884,7 @@ void set_data_typed(ctx &c, const int64_t *rowptr, const int32_t *colidx, const 
     st.F = F;
     st.c_valid = false;
     st.c_refused = false;
+    c.stats.sparse_cache_entries = 0;
     const host_csr<T> h = decode_input<T>(rowptr, colidx, values, n, F, fmt);
     // rows: FP22 keeps the caller's packed stream (decoded in registers by the kernels); otherwise (col, val) in the handle's type
     if (st.fp22) {
@@ -942,6 +943,7 @@ void sp_invalidate_cache(ctx &c) {
         sparse_state &st = state_of(c);
         st.c_valid = false;
         st.c_refused = false;
+        c.stats.sparse_cache_entries = 0;
     }
 }
 
