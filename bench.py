@@ -55,6 +55,7 @@ def parse_args():
                          "--points 1000000 --features 100000 --density 1e-3 --dtype f64, configs[3] --points 262144 --features 20000 "
                          "--density 1e-2 --kernel polynomial --storage fp22")
     ap.add_argument("--storage", default="native", choices=["native", "fp22"], help="sparse value storage")
+    ap.add_argument("--skip-e2e", action="store_true", help="large sparse runs only: skip the host-buffer leg (e2e = null)")
     ap.add_argument("--cache", type=int, default=0, help="sparse: 0 cache S if it fits, 1 recompute on the fly, 2 require the cache")
     return ap.parse_args()
 
@@ -261,8 +262,8 @@ def run_b200_arm(a):
     st = h.stats()
     assert iters == K, (iters, K)
     launches = int(st.kernel_launches)
-    matvec_ms = st.matvec_ms / max(st.matvecs, 1)
-    n_matvecs = int(st.matvecs)
+    matvec_ms = st.matvec_ms / max(st.matvecs_timed, 1)
+    n_matvecs = int(st.matvecs_timed)
     path = int(st.matvec_path)
     cache_entries = int(st.sparse_cache_entries) if sparse else 0
     if sparse and world > 1:
@@ -276,16 +277,19 @@ def run_b200_arm(a):
         h.generate_q()
         return h.solver_cg(b, None, QA, K, 0.0)
 
-    e2e_once()  # warm-up (allocations)
-    barrier()
-    h.reset_stats()
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    f0.record(stream)
-    e2e_once()
-    f1.record(stream)
-    barrier()
-    t_e2e_ms = f0.elapsed_time(f1)
-    st2 = h.stats()
+    if a.skip_e2e:
+        t_e2e_ms, st2 = float("nan"), h.stats()
+    else:
+        e2e_once()  # warm-up (allocations)
+        barrier()
+        h.reset_stats()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record(stream)
+        e2e_once()
+        f1.record(stream)
+        barrier()
+        t_e2e_ms = f0.elapsed_time(f1)
+        st2 = h.stats()
     sampler.stop_flag.set()
     sampler.join(timeout=2)
 
@@ -330,6 +334,8 @@ def run_b200_arm(a):
         if world == 1 and not a.no_cpu_baseline and not sparse:
             res = cpu_reference_iteration_rate(a, 1, 0, X, a.cpu_sample_points, budget_s=12.0)
             line["cpu_baseline"] = {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        if a.skip_e2e:
+            line["e2e"] = None
         print(json.dumps(line), flush=True)
     h.close()
     if world > 1:

@@ -112,7 +112,8 @@ int b200svm_partition_tiles(int64_t n, int rank, int world, int64_t *first, int6
 
 /* Tuning / introspection. */
 #define B200SVM_OPT_MATVEC_PATH 1 /* 0 = auto, 1 = SIMT full-square, 2 = tcgen05 symmetric tiles (f32 dense only) */
-#define B200SVM_OPT_SYNC_EVERY 2  /* CG: host polls the convergence flag every k iterations (default 1)            */
+#define B200SVM_OPT_SYNC_EVERY 2  /* CG look-ahead: the host queues up to k iterations beyond the one whose delta it has read (default 1; 0 = synchronous).
+                                     A device-side flag freezes alpha / delta at the converged iteration, so results do not depend on k. */
 #define B200SVM_OPT_SPARSE_GROUP 4 /* CSR paths: blocks per launch group (0 = sized so that a group's slice of the transpose fits L2) */
 #define B200SVM_OPT_SPARSE_LANES 5 /* CSR paths: lanes sharing one (feature, block) segment: 0 auto, or a power of two up to 32 */
 #define B200SVM_OPT_SPARSE_THREADS 7 /* CSR paths: threads of the CTA that owns one row (0 auto: 256 float / 512 double; power of two 64..1024) */
@@ -131,6 +132,7 @@ typedef struct b200svm_stats {
     int64_t d2h_bytes;        /* device->host bytes copied                                        */
     int64_t collectives;      /* NCCL collectives enqueued                                        */
     int64_t collective_bytes; /* payload bytes of those collectives (per rank)                    */
+    int64_t matvecs_timed;    /* matvecs whose duration is included in matvec_ms (all of them unless the event ring overflowed) */
     int64_t sparse_cache_entries; /* CSR paths: stored entries of the cached S matrix on this rank (0 = recomputed on the fly) */
 } b200svm_stats;
 int b200svm_get_stats(b200svm_handle h, b200svm_stats *out);

@@ -42,6 +42,7 @@ class Stats(C.Structure):
         ("d2h_bytes", C.c_int64),
         ("collectives", C.c_int64),
         ("collective_bytes", C.c_int64),
+        ("matvecs_timed", C.c_int64),
         ("sparse_cache_entries", C.c_int64),
     ]
 

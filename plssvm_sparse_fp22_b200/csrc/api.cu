@@ -134,7 +134,8 @@ int b200svm_create(b200svm_handle *h, int dtype, int kernel, int degree, double 
         B200_CUDA_CHECK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
         c->stream = c->own_stream;
         for (auto &ev : c->ev) { B200_CUDA_CHECK(cudaEventCreate(&ev)); }
-        B200_CUDA_CHECK(cudaMallocHost(&c->pinned, 256));
+        for (auto &ev : c->cg_ev) { B200_CUDA_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)); }
+        B200_CUDA_CHECK(cudaMallocHost(&c->pinned, 512));
         c->scal.reserve(S_COUNT * sizeof(double));
         c->partials.reserve(4 * MAX_PARTIAL_BLOCKS * sizeof(double));
         c->counters.reserve(8 * sizeof(unsigned int));
@@ -162,6 +163,9 @@ int b200svm_destroy(b200svm_handle h) {
     for (auto &ev : c->ev) {
         if (ev != nullptr) { cudaEventDestroy(ev); }
     }
+    for (auto &ev : c->cg_ev) {
+        if (ev != nullptr) { cudaEventDestroy(ev); }
+    }
     if (c->pinned != nullptr) { cudaFreeHost(c->pinned); }
     if (c->own_stream != nullptr) { cudaStreamDestroy(c->own_stream); }
     delete c;
@@ -185,7 +189,7 @@ int b200svm_set_option(b200svm_handle h, int option, int64_t value) {
                 c->opt_matvec_path = value;
                 break;
             case B200SVM_OPT_SYNC_EVERY:
-                B200_REQUIRE(value >= 1, "sync interval must be >= 1");
+                B200_REQUIRE(value >= 0 && value <= 8, "CG look-ahead must be in [0, 8] iterations");
                 c->opt_sync_every = value;
                 break;
             case B200SVM_OPT_SPARSE_BLOCK:
@@ -236,6 +240,7 @@ int b200svm_reset_stats(b200svm_handle h) {
     ctx *c = reinterpret_cast<ctx *>(h);
     return guarded(c, [&]() {
         const int64_t cached = c->stats.sparse_cache_entries;  // a property of the resident data, not a counter
+        sync_stream(*c);                                       // account the events still in flight before zeroing
         c->stats = b200svm_stats{};
         c->stats.sparse_cache_entries = cached;
     });

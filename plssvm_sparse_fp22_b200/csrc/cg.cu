@@ -48,8 +48,12 @@ __global__ void __launch_bounds__(VEC_THREADS) k_sums2(const T *__restrict__ v, 
 template <typename T, int MODE>
 __global__ void __launch_bounds__(VEC_THREADS) k_abar_finish(const T *__restrict__ P, int64_t ldP, int splits, const T *__restrict__ d,
                                                              int64_t m, T inv_cost, int center, const T *__restrict__ q, T qa, T add,
-                                                             T *__restrict__ out, T *__restrict__ scal, T *partials, unsigned int *ticket) {
+                                                             T *__restrict__ out, T *__restrict__ scal, T *partials, unsigned int *ticket,
+                                                             T target) {
     __shared__ T red[32];
+    if constexpr (MODE == 0 || MODE == 1) {
+        if (scal[S_DONE] != T(0)) { return; }  // CG has converged: this queued iteration must not touch r / delta
+    }
     const T sum_d = center != 0 ? scal[S_SUM_D] : T(0);
     const T q_d = center == 2 ? scal[S_Q_D] : T(0);
     const T rank1 = center == 1 ? sum_d * inv_cost : T(0);
@@ -79,6 +83,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_abar_finish(const T *__restrict
                 scal[S_DELTA_OLD] = old;
                 scal[S_DELTA] = res[0];
                 scal[S_BETA] = res[0] / old;
+                if (res[0] <= target) { scal[S_DONE] = T(1); }  // csvm.cpp:145
             } else {
                 scal[S_DELTA] = res[0];
                 scal[S_DELTA0] = res[0];
@@ -91,8 +96,9 @@ __global__ void __launch_bounds__(VEC_THREADS) k_abar_finish(const T *__restrict
 template <typename T, int REFRESH>
 __global__ void __launch_bounds__(VEC_THREADS) k_cg_update(T *__restrict__ x, T *__restrict__ r, const T *__restrict__ d,
                                                            const T *__restrict__ Ad, int64_t m, T *__restrict__ scal, T *partials,
-                                                           unsigned int *ticket) {
+                                                           unsigned int *ticket, T target) {
     __shared__ T red[32];
+    if (scal[S_DONE] != T(0)) { return; }  // converged at an earlier iteration: alpha stays frozen
     const T delta = scal[S_DELTA];
     const T alpha_cd = delta / scal[S_DAD];  // csvm.cpp:125
     T acc[1] = { T(0) };
@@ -111,6 +117,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_cg_update(T *__restrict__ x, T 
             scal[S_DELTA_OLD] = delta;         // csvm.cpp:142
             scal[S_DELTA] = res[0];            // csvm.cpp:143
             scal[S_BETA] = res[0] / delta;     // csvm.cpp:153
+            if (res[0] <= target) { scal[S_DONE] = T(1); }  // csvm.cpp:145 (set by the last block: no block of this grid reads it afterwards)
         }
     }
 }
@@ -156,17 +163,21 @@ __global__ void __launch_bounds__(VEC_THREADS) k_fill(T *__restrict__ v, int64_t
 // ---------------------------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------------------------
-void drain_matvec_events(ctx &c) {
-    for (int k = 0; k < c.ev_pending; ++k) {
+// account the (start, stop) pairs [ev_tail, upto): the caller knows that these matvecs have completed
+void drain_matvec_events(ctx &c, int64_t upto) {
+    for (; c.ev_tail < upto; ++c.ev_tail) {
+        const int k = (int) (c.ev_tail % ctx::EV_RING);
         float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, c.ev[2 * k], c.ev[2 * k + 1]) == cudaSuccess) { c.stats.matvec_ms += ms; }
+        if (cudaEventElapsedTime(&ms, c.ev[2 * k], c.ev[2 * k + 1]) == cudaSuccess) {
+            c.stats.matvec_ms += ms;
+            ++c.stats.matvecs_timed;
+        }
     }
-    c.ev_pending = 0;
 }
 
 void sync_stream(ctx &c) {
     B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));
-    drain_matvec_events(c);
+    drain_matvec_events(c, c.ev_head);
 }
 
 template <typename T>
@@ -195,8 +206,9 @@ kd_result kernel_times_vector(ctx &c, const T *d) {
     const int64_t ldP = (m + 255) / 256 * 256;
     constexpr int MAXS = 64;
     kd_result res{ ldP, 1, 0 };
-    const bool timed = c.ev_pending < 4;
-    if (timed) { B200_CUDA_CHECK(cudaEventRecord(c.ev[2 * c.ev_pending], c.stream)); }
+    const bool timed = c.ev_head - c.ev_tail < ctx::EV_RING;
+    const int ev_slot = (int) (c.ev_head % ctx::EV_RING);
+    if (timed) { B200_CUDA_CHECK(cudaEventRecord(c.ev[2 * ev_slot], c.stream)); }
     if (c.is_csr) {
         // sparse rows: un-centred K d of this rank's rows, rank-1 centring in the O(m) epilogue
         c.P.reserve((size_t) ldP * sizeof(T));
@@ -250,19 +262,19 @@ kd_result kernel_times_vector(ctx &c, const T *d) {
         }
     }
     if (timed) {
-        B200_CUDA_CHECK(cudaEventRecord(c.ev[2 * c.ev_pending + 1], c.stream));
-        ++c.ev_pending;
+        B200_CUDA_CHECK(cudaEventRecord(c.ev[2 * ev_slot + 1], c.stream));
+        ++c.ev_head;
     }
     ++c.stats.matvecs;
     return res;
 }
 
 template <typename T, int MODE>
-void abar_finish(ctx &c, const kd_result &kd, const T *d, T add, T *out) {
+void abar_finish(ctx &c, const kd_result &kd, const T *d, T add, T *out, T target = T(-1)) {
     const int64_t m = c.m();
     k_abar_finish<T, MODE><<<vec_grid(m), VEC_THREADS, 0, c.stream>>>(c.P.as<T>(), kd.ldP, kd.splits, d, m, T(1) / (T) c.cost, kd.center,
                                                                        c.q.as<T>(), (T) c.QA_cost, add, out, c.scal.as<T>(),
-                                                                       c.partials.as<T>(), c.counters.as<unsigned int>());
+                                                                       c.partials.as<T>(), c.counters.as<unsigned int>(), target);
     count_launch(c);
     B200_CUDA_CHECK(cudaGetLastError());
 }
@@ -293,6 +305,7 @@ int64_t cg_solve(ctx &c, const T *b, int64_t imax, T eps, T *x, double *delta_ou
     T *partials = c.partials.as<T>();
 
     // alpha = 1 (csvm.cpp:85), r = b (:91), r -= Abar alpha (:94), delta0 = delta = r.r (:97-98), d = r (:101)
+    B200_CUDA_CHECK(cudaMemsetAsync(scal + S_DONE, 0, sizeof(T), c.stream));
     k_fill<T><<<g, VEC_THREADS, 0, c.stream>>>(x, m, T(1));
     count_launch(c);
     B200_CUDA_CHECK(cudaMemcpyAsync(r, b, vb, cudaMemcpyDeviceToDevice, c.stream));
@@ -307,6 +320,20 @@ int64_t cg_solve(ctx &c, const T *b, int64_t imax, T eps, T *x, double *delta_ou
     T delta = delta0;
     const T target = eps * eps * delta0;
 
+    // The host runs `ahead` iterations in front of the one whose delta it has read, so the stream never drains between
+    // iterations (and ranks never wait for each other's launch latency inside the allreduce).  The stop test of csvm.cpp:145 is
+    // taken on the device: the kernel that produces delta raises scal[S_DONE], which turns the already queued iterations into
+    // no-ops — alpha and delta are exactly those of the converged iteration whatever `ahead` is.
+    const int64_t ahead = std::min<int64_t>(c.opt_sync_every, ctx::CG_RING - 2);
+    int64_t marks[ctx::CG_RING] = {};
+    int64_t converged = -1, polled = 0;
+    const auto poll = [&](int64_t it) {
+        const int slot = (int) (it % ctx::CG_RING);
+        B200_CUDA_CHECK(cudaEventSynchronize(c.cg_ev[slot]));
+        drain_matvec_events(c, marks[slot]);
+        delta = mailbox[1 + slot];
+        return delta <= target;
+    };
     int64_t run = 0;
     for (; run < imax; ++run) {
         // Ad = Abar d (:121-122) and d.Ad
@@ -314,28 +341,40 @@ int64_t cg_solve(ctx &c, const T *b, int64_t imax, T eps, T *x, double *delta_ou
         abar_finish<T, 0>(c, kd, d, T(1), Ad);
         if (run % 50 == 49) {
             // x += alpha_cd d ; r = b - Abar x (:130-135)
-            k_cg_update<T, 1><<<g, VEC_THREADS, 0, c.stream>>>(x, r, d, Ad, m, scal, partials, ticket);
+            k_cg_update<T, 1><<<g, VEC_THREADS, 0, c.stream>>>(x, r, d, Ad, m, scal, partials, ticket, target);
             count_launch(c);
             B200_CUDA_CHECK(cudaMemcpyAsync(r, b, vb, cudaMemcpyDeviceToDevice, c.stream));
             const kd_result kx = kernel_times_vector<T>(c, x);
-            abar_finish<T, 1>(c, kx, x, T(-1), r);
+            abar_finish<T, 1>(c, kx, x, T(-1), r, target);
         } else {
-            k_cg_update<T, 0><<<g, VEC_THREADS, 0, c.stream>>>(x, r, d, Ad, m, scal, partials, ticket);
+            k_cg_update<T, 0><<<g, VEC_THREADS, 0, c.stream>>>(x, r, d, Ad, m, scal, partials, ticket, target);
             count_launch(c);
         }
         B200_CUDA_CHECK(cudaGetLastError());
-        // stop test on the host (:145) — one scalar per iteration
-        B200_CUDA_CHECK(cudaMemcpyAsync(mailbox, scal + S_DELTA, sizeof(T), cudaMemcpyDeviceToHost, c.stream));
-        // speculatively queue the direction update; it is only *used* if the loop continues
+        // delta of this iteration -> pinned mailbox; the direction update is queued right behind it
+        const int slot = (int) (run % ctx::CG_RING);
+        B200_CUDA_CHECK(cudaMemcpyAsync(mailbox + 1 + slot, scal + S_DELTA, sizeof(T), cudaMemcpyDeviceToHost, c.stream));
+        B200_CUDA_CHECK(cudaEventRecord(c.cg_ev[slot], c.stream));
+        marks[slot] = c.ev_head;
         k_cg_direction<T><<<g, VEC_THREADS, 0, c.stream>>>(d, r, c.q.as<T>(), m, scal, partials, ticket);
         count_launch(c);
         B200_CUDA_CHECK(cudaGetLastError());
-        sync_stream(c);
-        delta = mailbox[0];
-        if (delta <= target) { break; }
+        while (converged < 0 && polled + ahead <= run) {
+            if (poll(polled)) { converged = polled; }
+            ++polled;
+        }
+        if (converged >= 0) { break; }
     }
+    const int64_t queued = std::min(run + 1, imax);
+    while (converged < 0 && polled < queued) {
+        if (poll(polled)) { converged = polled; }
+        ++polled;
+    }
+    B200_CUDA_CHECK(cudaMemsetAsync(scal + S_DONE, 0, sizeof(T), c.stream));
+    sync_stream(c);
     if (delta_out != nullptr) { *delta_out = (double) delta; }
-    return run + 1 < imax ? run + 1 : imax;  // std::min(run + 1, imax), csvm.cpp:162-167
+    const int64_t last = converged >= 0 ? converged : imax - 1;
+    return last + 1 < imax ? last + 1 : imax;  // std::min(run + 1, imax), csvm.cpp:162-167
 }
 template int64_t cg_solve<float>(ctx &, const float *, int64_t, float, float *, double *);
 template int64_t cg_solve<double>(ctx &, const double *, int64_t, double, double *, double *);

@@ -73,6 +73,7 @@ struct params {
     float qa;          // QA_cost
     int degree;
     int kernel;
+    const float *done;  // CG convergence flag (scal[S_DONE]): a launch queued behind the converged iteration returns at once
 };
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -213,6 +214,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     k_gram_tc(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo, const __grid_constant__ CUtensorMap map_b,
               const params p) {
     extern __shared__ uint8_t smem_raw[];
+    if (p.done != nullptr && *p.done != 0.f) { return; }  // uniform over the grid (the flag is only written between launches)
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     const uint32_t sbase = smem_u32(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -654,6 +656,7 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out) {
     p.qa = (float) c.QA_cost;
     p.degree = c.degree;
     p.kernel = c.kernel;
+    p.done = c.scal.as<float>() + S_DONE;
     float cscale = 0.f;
     if (c.kernel == B200SVM_RBF) {
         p.w = (float) (2.0 * c.gamma * (double) LOG2E / (double) s2);

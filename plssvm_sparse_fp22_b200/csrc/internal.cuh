@@ -85,6 +85,7 @@ enum scal_index : int {
     S_KXX,    // k(x_n, x_n)
     S_TMP0,
     S_TMP1,
+    S_DONE,   // CG: non-zero once delta <= eps^2 delta0; later iterations already queued by the host become no-ops
     S_COUNT
 };
 
@@ -157,8 +158,11 @@ struct ctx {
 
     // stats
     b200svm_stats stats{};
-    cudaEvent_t ev[8]{};   // 4 (start, stop) pairs around the O(m^2) kernel, drained at the next stream sync
-    int ev_pending{ 0 };
+    static constexpr int EV_RING = 16;
+    cudaEvent_t ev[2 * EV_RING]{};  // ring of (start, stop) pairs around the O(m^2) kernel, drained when known to be complete
+    int64_t ev_head{ 0 }, ev_tail{ 0 };
+    static constexpr int CG_RING = 16;
+    cudaEvent_t cg_ev[CG_RING]{};   // one per queued CG iteration (its delta has reached the pinned mailbox)
 
     size_t esize() const { return dtype == B200SVM_F32 ? 4 : 8; }
     int64_t m() const { return n - 1; }
@@ -201,7 +205,7 @@ void comm_allreduce_sum(ctx &c, void *buf, int64_t count);  // in place, real ty
 void partition_rows(int64_t m, int rank, int world, int64_t *lo, int64_t *hi);
 
 inline void count_launch(ctx &c, int k = 1) { c.stats.kernel_launches += k; }
-void drain_matvec_events(ctx &c);   // call after a stream synchronisation
+void drain_matvec_events(ctx &c, int64_t upto);   // account the matvec event pairs [ev_tail, upto) known to be complete
 void sync_stream(ctx &c);           // cudaStreamSynchronize + drain
 template <typename T> void sums2(ctx &c, const T *v, int idx_sum, int idx_qv);
 

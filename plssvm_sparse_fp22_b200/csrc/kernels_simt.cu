@@ -103,8 +103,10 @@ template <typename T, int KERNEL, int TM, int TN, bool CENTER>
 __global__ void __launch_bounds__(256)
     k_kmv_tile(const T *__restrict__ A, const T *__restrict__ normA, int64_t rowsA, int64_t ldA, const T *__restrict__ B,
                const T *__restrict__ normB, int64_t rowsB, int64_t ldB, int64_t K, const T *__restrict__ v, int degree, T gamma, T coef0,
-               const T *__restrict__ qrow, const T *__restrict__ qcol, T qa, T *__restrict__ P, int64_t ldP, int col_tiles) {
+               const T *__restrict__ qrow, const T *__restrict__ qcol, T qa, T *__restrict__ P, int64_t ldP, int col_tiles,
+               const T *__restrict__ done) {
     constexpr int BM = 16 * TM, BN = 16 * TN;
+    if (*done != T(0)) { return; }  // CG convergence flag (scal[S_DONE]); uniform over the grid
     using V = typename vec16<T>::type;
     constexpr int VN = vec16<T>::N;
     constexpr int EA = BM * BK / 256, TPRA = BK / EA;  // elements per thread / threads per row when loading the A slice
@@ -258,10 +260,12 @@ int kmv_simt_launch(ctx &c, const T *A, const T *normA, int64_t rowsA, int64_t l
     do {                                                                                                                                 \
         if (qrow != nullptr) {                                                                                                           \
             k_kmv_tile<T, KN, TM, TN, true><<<grid, 256, 0, c.stream>>>(A, normA, rowsA, ldA, B, normB, rowsB, ldB, K, v, c.degree,      \
-                                                                         (T) c.gamma, (T) c.coef0, qrow, qcol, qa, P, ldP, col_tiles);   \
+                                                                         (T) c.gamma, (T) c.coef0, qrow, qcol, qa, P, ldP, col_tiles,    \
+                                                                         c.scal.as<T>() + S_DONE);                                       \
         } else {                                                                                                                         \
             k_kmv_tile<T, KN, TM, TN, false><<<grid, 256, 0, c.stream>>>(A, normA, rowsA, ldA, B, normB, rowsB, ldB, K, v, c.degree,     \
-                                                                          (T) c.gamma, (T) c.coef0, qrow, qcol, qa, P, ldP, col_tiles);  \
+                                                                          (T) c.gamma, (T) c.coef0, qrow, qcol, qa, P, ldP, col_tiles,   \
+                                                                          c.scal.as<T>() + S_DONE);                                      \
         }                                                                                                                                \
     } while (0)
     switch (c.kernel) {

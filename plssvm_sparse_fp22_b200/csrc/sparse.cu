@@ -282,8 +282,9 @@ struct cache_view {
 template <typename T, int KERNEL, bool FP22, bool COMPACT, int MODE>
 __global__ void __launch_bounds__(1024)
     k_sp_kmv(csr_view A, int64_t row_lo, int64_t row_hi, csc_view B, int g, int rmax, int gs_log2, int thr, const T *__restrict__ v, kfun kf,
-             T *__restrict__ out, cache_view cache) {
+             T *__restrict__ out, cache_view cache, const T *__restrict__ done) {
     static_assert(MODE == 0 || COMPACT, "the cache passes work from the compacted slot list");
+    if (*done != T(0)) { return; }  // CG convergence flag (scal[S_DONE]); uniform over the grid
     extern __shared__ __align__(16) unsigned char sp_smem[];
     __shared__ int wtot[32];
     __shared__ T red[32];
@@ -531,8 +532,10 @@ __global__ void __launch_bounds__(1024)
 // entries of its rows (coalesced 2-byte index + value loads; the gather hits shared memory).  HBM-bound: sizeof(T) + 2 bytes per entry.
 // ---------------------------------------------------------------------------------------------------------------------
 template <typename T>
-__global__ void __launch_bounds__(256) k_sp_cached_mv(cache_view S, int W, int rows_per_cta, const T *__restrict__ v, T *__restrict__ P) {
+__global__ void __launch_bounds__(256) k_sp_cached_mv(cache_view S, int W, int rows_per_cta, const T *__restrict__ v, T *__restrict__ P,
+                                                      const T *__restrict__ done) {
     extern __shared__ __align__(16) unsigned char sp_smem[];
+    if (*done != T(0)) { return; }  // CG convergence flag (scal[S_DONE]); uniform over the grid
     T *vs = reinterpret_cast<T *>(sp_smem);
     const int b = blockIdx.y;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5, nwarps = blockDim.x >> 5;
@@ -1023,15 +1026,16 @@ void launch_kmv_variant(ctx &c, const sparse_state &st, const sp::csr_view &A, i
         while ((double) (1 << gs_log2) < st.avg_seg && gs_log2 < 5) { ++gs_log2; }
     }
     const int thr = std::max(64, 16 << gs_log2);
+    const T *done = c.scal.as<T>() + S_DONE;
     for (int g = 0; g < st.ng; ++g) {
         if (mode == 1) {
-            sp::k_sp_kmv<T, KERNEL, FP22, true, 1><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache);
+            sp::k_sp_kmv<T, KERNEL, FP22, true, 1><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache, done);
         } else if (mode == 2) {
-            sp::k_sp_kmv<T, KERNEL, FP22, true, 2><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache);
+            sp::k_sp_kmv<T, KERNEL, FP22, true, 2><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache, done);
         } else if (compact) {
-            sp::k_sp_kmv<T, KERNEL, FP22, true, 0><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache);
+            sp::k_sp_kmv<T, KERNEL, FP22, true, 0><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache, done);
         } else {
-            sp::k_sp_kmv<T, KERNEL, FP22, false, 0><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache);
+            sp::k_sp_kmv<T, KERNEL, FP22, false, 0><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache, done);
         }
         count_launch(c);
         B200_CUDA_CHECK(cudaGetLastError());
@@ -1112,7 +1116,7 @@ void cached_matvec(ctx &c, sparse_state &st, const T *v, T *out) {
         attr_smem[sizeof(T) == 8] = smem;
     }
     const dim3 grid((unsigned) ((rows + rows_per_cta - 1) / rows_per_cta), (unsigned) st.nb);
-    sp::k_sp_cached_mv<T><<<grid, 256, smem, c.stream>>>(cv, st.W, rows_per_cta, v, st.c_P.as<T>());
+    sp::k_sp_cached_mv<T><<<grid, 256, smem, c.stream>>>(cv, st.W, rows_per_cta, v, st.c_P.as<T>(), c.scal.as<T>() + S_DONE);
     const int64_t g = std::max<int64_t>(1, std::min<int64_t>((rows + 255) / 256, 8 * NUM_SMS));
     sp::k_sp_fold_blocks<T><<<(unsigned) g, 256, 0, c.stream>>>(st.c_P.as<T>(), st.nb, rows, out + st.c_lo);
     count_launch(c, 2);

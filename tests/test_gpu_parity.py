@@ -158,6 +158,41 @@ def test_solver_cg_direct_and_refresh(kernel, dt):
         assert nrm_rel(a_t, a) < max(2 * nrm_rel(a_t, a_o), 1e-3), (nrm_rel(a_t, a), nrm_rel(a_t, a_o))
 
 
+@pytest.mark.parametrize("dt", DTYPES)
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("eps,imax", [(1e-3, 64), (1e-8, 120), (0.0, 7)])
+def test_cg_lookahead_depth_does_not_change_the_result(kernel, dt, eps, imax):
+    """The host queues up to k iterations beyond the one whose delta it has read (B200SVM_OPT_SYNC_EVERY); the device-side stop
+    flag must freeze alpha / delta at the converged iteration: bit-identical alpha, same iteration count and delta for every k,
+    including the every-50th-iteration residual refresh (csvm.cpp:130-135) and convergence on the last allowed iteration."""
+    n, F = 400, 24
+    X, y = datagen.make_dense(n, F, seed=5, problem="planes", dtype=dt)
+    b = (y[:-1] - y[-1]).astype(dt)
+    results = []
+    for ahead in (0, 1, 3, 8):
+        with capi.Handle(dt, kernel, gamma=1.0 / F) as h:
+            h.set_option(capi.OPT_SYNC_EVERY, ahead)
+            h.set_data(X)
+            q = h.generate_q()
+            qa = h.kxx_last() + 1.0
+            results.append(h.solver_cg(b, q, qa, imax, eps))
+            # the handle is reusable afterwards (flag cleared): one more solve gives the same answer
+            again = h.solver_cg(b, q, qa, imax, eps)
+            assert again[1] == results[-1][1] and np.array_equal(again[0], results[-1][0])
+            st = h.stats()
+            assert st.matvecs_timed == st.matvecs
+    a0, it0, d0 = results[0]
+    for a, it, d in results[1:]:
+        assert it == it0 and d == d0
+        assert np.array_equal(a, a0)
+    if dt == np.float64 and eps > 0:
+        a_o, it_o, _ = port.solver_cg(X, b, port.generate_q(X, kernel), port.kernel_function(X[-1], X[-1], kernel, gamma=1.0 / F) + 1.0, imax, eps, kernel, use_rows=True)
+        if eps == 1e-3:
+            assert it0 == it_o
+        else:
+            assert abs(it0 - it_o) <= 2  # at eps = 1e-8 the recursion's rounding decides the last step or two
+
+
 @pytest.mark.parametrize("kernel", KERNELS)
 def test_predict_golden_labels(golden, kernel):
     """Reference golden fixture (tests/backends/generic_tests.hpp:229-258): bit-identical labels, label * decision > 0."""

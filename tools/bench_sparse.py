@@ -60,7 +60,7 @@ def main():
         for _ in range(a.reps):
             out = h.matvec(d)
         st = h.stats()
-        ms = st.matvec_ms / st.matvecs
+        ms = st.matvec_ms / max(st.matvecs_timed, 1)
     print(json.dumps({"points": a.points, "features": a.features, "density": a.density, "kernel": a.kernel, "dtype": a.dtype, "block": a.block, "lanes": a.lanes, "threads": a.threads, "group": a.group,
                       "nnz": int(rp[-1]), "gram_products": products, "ms_per_matvec": ms, "gproducts_per_s": products / ms / 1e6,
                       "pairs_per_s": (a.points - 1.0) ** 2 / ms / 1e6 * 1e-3, "cache": a.cache, "cache_entries": int(cache_entries), "first_matvec_s": t_first, "gen_s": t_gen, "set_data_s": t_set, "checksum": float(np.abs(out).sum())}))

@@ -34,6 +34,6 @@ for kernel in ("rbf", "polynomial"):
                 a, rho, it = h.learn(y, eps=1e-3)
             a_o, rho_o, it_o = port.learn(X64, y.astype(np.float64), kernel, eps=1e-3, use_rows=True)
             res[f"{kernel}/{problem}/{name}"] = {
-                "matvec_relerr": float(np.linalg.norm(got - want) / np.linalg.norm(want)), "ms": st.matvec_ms / st.matvecs,
+                "matvec_relerr": float(np.linalg.norm(got - want) / np.linalg.norm(want)), "ms": st.matvec_ms / max(st.matvecs_timed, 1),
                 "iters": it, "iters_oracle": it_o, "alpha_relerr": float(np.linalg.norm(a - a_o) / np.linalg.norm(a_o))}
 print(json.dumps(res, indent=1))
