@@ -477,14 +477,25 @@ __global__ void __launch_bounds__(256) k_pack(const float *__restrict__ norms, c
 }
 
 // out[i] = sum_{J <= I_i / 2} Pr[J][i] + sum_{I' >= 2 J_i} Pc[I'][i]   (fixed order; slots of tiles owned by other ranks are zero)
+// own (multi-GPU): byte map [T_r][T_c] of the tiles this rank computes — the partials of the others are skipped, not read
 __global__ void __launch_bounds__(256) k_tc_reduce(const float *__restrict__ Pr, const float *__restrict__ Pc, int64_t ldP, int64_t m, int T_r,
-                                                   float *__restrict__ out) {
+                                                   int T_c, const uint8_t *__restrict__ own, float *__restrict__ out, const float *__restrict__ done) {
+    if (*done != 0.f) { return; }
     const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= m) { return; }
     const int Ii = (int) (i / BM), Ji = (int) (i / BN);
     float s0 = 0.f, s1 = 0.f;
-    for (int J = 0; J <= Ii / 2; ++J) { s0 += Pr[(int64_t) J * ldP + i]; }
-    for (int I = 2 * Ji; I < T_r; ++I) { s1 += Pc[(int64_t) I * ldP + i]; }
+    if (own == nullptr) {
+        for (int J = 0; J <= Ii / 2; ++J) { s0 += Pr[(int64_t) J * ldP + i]; }
+        for (int I = 2 * Ji; I < T_r; ++I) { s1 += Pc[(int64_t) I * ldP + i]; }
+    } else {  // the map entries are warp-uniform (32 consecutive i share Ii and Ji)
+        for (int J = 0; J <= Ii / 2; ++J) {
+            if (own[Ii * T_c + J] != 0) { s0 += Pr[(int64_t) J * ldP + i]; }
+        }
+        for (int I = 2 * Ji; I < T_r; ++I) {
+            if (own[I * T_c + Ji] != 0) { s1 += Pc[(int64_t) I * ldP + i]; }
+        }
+    }
     out[i] = s0 + s1;
 }
 
@@ -497,7 +508,8 @@ namespace {
 
 struct tc_state {
     CUtensorMap map_hi{}, map_lo{}, map_a8{}, map_b8{};
-    dbuf tiles, pk, Pr, Pc, amax, P8a, P8b;
+    dbuf tiles, pk, Pr, Pc, amax, P8a, P8b, own;
+    bool has_own{ false };
     bool fp8x{ false };
     int num_tiles{ 0 };
     int T_r{ 0 }, T_c{ 0 };
@@ -619,6 +631,14 @@ void tc_prepare_split(ctx &c) {
     st.num_tiles = (int) tiles.size();
     st.tiles.reserve(std::max<size_t>(tiles.size(), 1) * sizeof(int2));
     B200_CUDA_CHECK(cudaMemcpyAsync(st.tiles.p, tiles.data(), tiles.size() * sizeof(int2), cudaMemcpyHostToDevice, c.stream));
+    std::vector<uint8_t> own_map;
+    st.has_own = c.world > 1;
+    if (st.has_own) {
+        own_map.assign((size_t) st.T_r * (size_t) st.T_c, 0);
+        for (const int2 &t : tiles) { own_map[(size_t) t.x * (size_t) st.T_c + (size_t) t.y] = 1; }
+        st.own.reserve(own_map.size());
+        B200_CUDA_CHECK(cudaMemcpyAsync(st.own.p, own_map.data(), own_map.size(), cudaMemcpyHostToDevice, c.stream));
+    }
     st.pk.reserve((size_t) c.n_pad * sizeof(float4));
     st.Pr.reserve((size_t) st.T_c * st.ldP * sizeof(float));
     st.Pc.reserve((size_t) st.T_r * st.ldP * sizeof(float));
@@ -677,7 +697,8 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out) {
     } else {
         tc::k_gram_tc<B200SVM_POLYNOMIAL, false><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_lo, st.map_lo, p);
     }
-    tc::k_tc_reduce<<<(unsigned) ((m + 255) / 256), 256, 0, c.stream>>>(st.Pr.as<float>(), st.Pc.as<float>(), st.ldP, m, st.T_r, out);
+    tc::k_tc_reduce<<<(unsigned) ((m + 255) / 256), 256, 0, c.stream>>>(st.Pr.as<float>(), st.Pc.as<float>(), st.ldP, m, st.T_r, st.T_c,
+                                                                        st.has_own ? st.own.as<uint8_t>() : nullptr, out, p.done);
     count_launch(c, 3);
     B200_CUDA_CHECK(cudaGetLastError());
 }

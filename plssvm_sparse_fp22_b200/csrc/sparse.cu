@@ -81,21 +81,40 @@ __device__ __forceinline__ bool load_entry(const csr_view &A, int64_t p, int64_t
 // O(nnz) kernels: one warp per row
 // ---------------------------------------------------------------------------------------------------------------------
 // norms[i] = |x_i|^2 ; u[i] = exp(-gamma |x_i|^2) (rbf only, else 1)
+// stats (optional, predict points): [0] = bits of the largest squared norm as a double (non-negative => ordered like the integer),
+//                                   [1] = non-zero if a column index lies outside [0, F) or is not ascending within its row
 template <typename T, bool FP22>
-__global__ void __launch_bounds__(256) k_sp_norms(csr_view A, T gamma, int rbf, T *__restrict__ norms, T *__restrict__ u) {
+__global__ void __launch_bounds__(256) k_sp_norms(csr_view A, T gamma, int rbf, T *__restrict__ norms, T *__restrict__ u, int64_t F,
+                                                  unsigned long long *__restrict__ stats) {
     const int64_t row = (int64_t) blockIdx.x * 8 + (threadIdx.x >> 5);
     if (row >= A.rows) { return; }
     const int lane = threadIdx.x & 31;
     const int64_t p0 = A.rowptr[row], p1 = A.rowptr[row + 1];
     T s = 0;
     int colrun = 0;
+    bool bad = false;
+    int prev_last = -1;
     for (int64_t p = p0; p < p1; p += 32) {
         int f;
         T x;
-        load_entry<T, FP22>(A, p, p1, lane, colrun, f, x);
+        const bool valid = load_entry<T, FP22>(A, p, p1, lane, colrun, f, x);
         s = fma(x, x, s);
+        if (stats != nullptr) {
+            // ascending and in range (FP22: the running sum of the deltas is ascending by construction; only the range can fail)
+            const int before = __shfl_up_sync(0xffffffffu, f, 1);
+            const int prev = lane == 0 ? prev_last : before;
+            if (valid && (f < 0 || f >= F || (!FP22 && f <= prev))) { bad = true; }
+            prev_last = __shfl_sync(0xffffffffu, f, 31);
+        }
     }
     s = warp_sum(s);
+    if (stats != nullptr) {
+        bad = __any_sync(0xffffffffu, bad);
+        if (lane == 0) {
+            atomicMax(&stats[0], (unsigned long long) __double_as_longlong((double) s));
+            if (bad) { atomicOr(&stats[1], 1ull); }
+        }
+    }
     if (lane == 0) {
         norms[row] = s;
         if (u != nullptr) { u[row] = rbf ? (T) exp(-(double) gamma * (double) s) : T(1); }
@@ -713,7 +732,7 @@ struct sparse_state {
     bool c_valid{ false }, c_refused{ false };
     int64_t c_lo{ 0 }, c_hi{ 0 }, c_entries{ 0 };
     // predict staging
-    dbuf p_rowptr, p_col, p_val, p_norms, p_u, p_out;
+    dbuf p_rowptr, p_col, p_val, p_norms, p_u, p_out, p_stats;
 };
 
 sparse_state &state_of(ctx &c) {
@@ -866,14 +885,14 @@ void set_kmv_attributes(size_t smem) {
 }
 
 template <typename T>
-void norms_and_u(ctx &c, const sparse_state &st, const sp::csr_view &A, T *norms, T *u) {
+void norms_and_u(ctx &c, const sparse_state &st, const sp::csr_view &A, T *norms, T *u, unsigned long long *stats = nullptr) {
     if (A.rows == 0) { return; }
     const unsigned grid = (unsigned) ((A.rows + 7) / 8);
     const int rbf = c.kernel == B200SVM_RBF ? 1 : 0;
     if (st.fp22) {
-        if constexpr (sizeof(T) == 4) { sp::k_sp_norms<T, true><<<grid, 256, 0, c.stream>>>(A, (T) c.gamma, rbf, norms, u); }
+        if constexpr (sizeof(T) == 4) { sp::k_sp_norms<T, true><<<grid, 256, 0, c.stream>>>(A, (T) c.gamma, rbf, norms, u, st.F, stats); }
     } else {
-        sp::k_sp_norms<T, false><<<grid, 256, 0, c.stream>>>(A, (T) c.gamma, rbf, norms, u);
+        sp::k_sp_norms<T, false><<<grid, 256, 0, c.stream>>>(A, (T) c.gamma, rbf, norms, u, st.F, stats);
     }
     count_launch(c);
     B200_CUDA_CHECK(cudaGetLastError());
@@ -1249,61 +1268,61 @@ void sp_predict(ctx &c, const T *alpha_dev, T bias, const int64_t *rowptr, const
     } else {
         weights<T>(c, alpha_dev, rbf ? st.u.as<T>() : static_cast<const T *>(nullptr), st.n, nbW, st.v.as<T>());  // sum v -> scal[S_TMP0]
     }
-    // stage the points in chunks of at most ~2^27 stored entries
+    // stage the points in chunks of at most ~2^27 stored entries; values already in the handle's type (and FP22 words) are
+    // uploaded straight from the caller's arrays, validated on the device together with the row norms
     const int64_t max_entries = int64_t(1) << 27;
+    const bool same_type = st.fp22 || (fmt == B200SVM_VAL_F32 ? sizeof(T) == 4 : sizeof(T) == 8);
     std::vector<int64_t> rp;
-    std::vector<int32_t> ci;
     std::vector<T> vals;
+    st.p_stats.reserve(2 * sizeof(unsigned long long));
+    unsigned long long *mailbox = static_cast<unsigned long long *>(c.pinned);
     for (int64_t r0 = 0; r0 < P;) {
         int64_t r1 = r0 + 1;
         while (r1 < P && rowptr[r1 + 1] - rowptr[r0] <= max_entries) { ++r1; }
         const int64_t rows = r1 - r0, e0 = rowptr[r0], entries = rowptr[r1] - e0;
         rp.resize((size_t) rows + 1);
-        for (int64_t i = 0; i <= rows; ++i) { rp[(size_t) i] = rowptr[r0 + i] - e0; }
+        int64_t max_row = 0;
+        for (int64_t i = 0; i <= rows; ++i) {
+            rp[(size_t) i] = rowptr[r0 + i] - e0;
+            if (i > 0) {
+                B200_REQUIRE(rp[(size_t) i] >= rp[(size_t) i - 1], "CSR row pointers must be non-decreasing");
+                max_row = std::max(max_row, rp[(size_t) i] - rp[(size_t) i - 1]);
+            }
+        }
         upload(c, st.p_rowptr, rp.data(), rp.size() * sizeof(int64_t));
         if (st.fp22) {
             upload(c, st.p_val, static_cast<const uint32_t *>(values) + e0, (size_t) entries * sizeof(uint32_t));
             st.p_col.reserve(16);
         } else {
             B200_REQUIRE(colidx != nullptr || entries == 0, "null column index array");
-            ci.assign(colidx + e0, colidx + e0 + entries);
-            for (int32_t f : ci) { B200_REQUIRE(f >= 0 && f < st.F, "Number of features per data point must match the number of features per predict point!"); }
-            vals.resize((size_t) entries);
-            for (int64_t p = 0; p < entries; ++p) {
-                vals[(size_t) p] = fmt == B200SVM_VAL_F32 ? (T) static_cast<const float *>(values)[e0 + p] : (T) static_cast<const double *>(values)[e0 + p];
+            upload(c, st.p_col, colidx + e0, (size_t) entries * sizeof(int32_t));
+            if (same_type) {
+                upload(c, st.p_val, static_cast<const T *>(values) + e0, (size_t) entries * sizeof(T));
+            } else {
+                vals.resize((size_t) entries);
+                for (int64_t p = 0; p < entries; ++p) {
+                    vals[(size_t) p] = fmt == B200SVM_VAL_F32 ? (T) static_cast<const float *>(values)[e0 + p] : (T) static_cast<const double *>(values)[e0 + p];
+                }
+                upload(c, st.p_val, vals.data(), vals.size() * sizeof(T));
             }
-            upload(c, st.p_col, ci.data(), ci.size() * sizeof(int32_t));
-            upload(c, st.p_val, vals.data(), vals.size() * sizeof(T));
         }
         st.p_out.reserve((size_t) rows * sizeof(T));
+        st.p_norms.reserve((size_t) rows * sizeof(T));
+        st.p_u.reserve((size_t) rows * sizeof(T));
         const sp::csr_view A{ st.p_rowptr.as<int64_t>(), st.p_col.as<int32_t>(), st.p_val.p, rows };
+        // norms, u and the validation of the column indices in one pass; two scalars come back
+        B200_CUDA_CHECK(cudaMemsetAsync(st.p_stats.p, 0, 2 * sizeof(unsigned long long), c.stream));
+        norms_and_u<T>(c, st, A, st.p_norms.as<T>(), st.p_u.as<T>(), st.p_stats.as<unsigned long long>());
+        B200_CUDA_CHECK(cudaMemcpyAsync(mailbox, st.p_stats.p, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
+        sync_stream(c);
+        B200_REQUIRE(mailbox[1] == 0ull, "Number of features per data point must match the number of features per predict point!");
+        double pts_norm2 = 0;
+        std::memcpy(&pts_norm2, &mailbox[0], sizeof(double));
         if (linear) {
             row_dot<T>(c, st, A, st.wvec.as<T>(), bias, st.p_out.as<T>());
         } else {
-            st.p_norms.reserve((size_t) rows * sizeof(T));
-            st.p_u.reserve((size_t) rows * sizeof(T));
-            norms_and_u<T>(c, st, A, st.p_norms.as<T>(), st.p_u.as<T>());
             B200_CUDA_CHECK(cudaMemsetAsync(st.p_out.p, 0, (size_t) rows * sizeof(T), c.stream));
-            int64_t max_row = 0;
-            double max_norm2 = st.max_norm2;
-            for (int64_t i = 0; i < rows; ++i) {
-                max_row = std::max(max_row, rp[(size_t) i + 1] - rp[(size_t) i]);
-                double nrm = 0;
-                for (int64_t p = rowptr[r0 + i]; p < rowptr[r0 + i + 1]; ++p) {
-                    double x;
-                    if (st.fp22) {
-                        const uint32_t vb = static_cast<const uint32_t *>(values)[p] & 0xFFFFFC00u;
-                        float xf;
-                        std::memcpy(&xf, &vb, 4);
-                        x = xf;
-                    } else {
-                        x = fmt == B200SVM_VAL_F32 ? (double) static_cast<const float *>(values)[p] : static_cast<const double *>(values)[p];
-                    }
-                    nrm += x * x;
-                }
-                max_norm2 = std::max(max_norm2, nrm);
-            }
-            launch_kmv<T>(c, st, A, 0, rows, max_row, max_norm2, st.v.as<T>(), st.p_out.as<T>());
+            launch_kmv<T>(c, st, A, 0, rows, max_row, std::max(st.max_norm2, pts_norm2), st.v.as<T>(), st.p_out.as<T>());
             const sp::kfun kf = make_kfun(c);
             int64_t g = std::max<int64_t>(1, std::min<int64_t>((rows + 1023) / 1024, 8 * NUM_SMS));
             sp::k_sp_finish<T><<<(unsigned) g, 256, 0, c.stream>>>(st.p_out.as<T>(), st.p_u.as<T>(), rows, 0, rows, rbf ? 1 : 0, (T) kf.c0pow,

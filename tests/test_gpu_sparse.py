@@ -281,6 +281,24 @@ def test_csr_cache_budget_falls_back_or_fails_loudly():
     assert nrm_rel(outs[0], outs[1]) < 2e-6
 
 
+def test_csr_predict_rejects_bad_points():
+    """Column indices of predict points are validated on the device together with the norms (no host pass over the entries)."""
+    n, F = 200, 300
+    rp, ci, v, _ = make(n, F, 0.05, seed=4, dt=np.float64)
+    alpha = np.ones(n)
+    with capi.Handle(np.float64, "rbf", gamma=1.0 / F) as h:
+        h.set_data_csr(rp, ci, v, F)
+        prp = np.array([0, 2, 3], np.int64)
+        ok = h.predict_csr(alpha, 0.0, prp, np.array([1, 5, 0], np.int32), np.ones(3))
+        assert ok.shape == (2,)
+        for bad_cols in ([1, F, 0], [5, 1, 0], [-1, 2, 0]):  # out of range, not ascending, negative
+            with pytest.raises(capi.B200Error, match="Number of features per data point must match"):
+                h.predict_csr(alpha, 0.0, prp, np.array(bad_cols, np.int32), np.ones(3))
+        # float points into a double handle are converted on the host
+        dec32 = h.predict_csr(alpha, 0.0, prp, np.array([1, 5, 0], np.int32), np.ones(3, np.float32))
+        assert np.array_equal(dec32, ok)
+
+
 def test_csr_errors_are_loud():
     with capi.Handle(np.float64, "rbf", gamma=0.5) as h:
         rp = np.array([0, 2, 3], np.int64)
