@@ -575,33 +575,34 @@ __global__ void __launch_bounds__(256) k_sp_cached_mv(cache_view S, int W, int r
             s2 = fma(a2, vs[jj.y & 0xFFFFu], s2);
             s3 = fma(a3, vs[jj.y >> 16], s3);
         };
-        int64_t q = q0 + lane;
-        if constexpr (sizeof(T) == 4) {
-            const float4 *__restrict__ vq = reinterpret_cast<const float4 *>(sval);
-            for (; q + 32 < q1; q += 64) {  // two quads in flight per lane
-                const uint2 ja = __ldcs(jq + q), jb = __ldcs(jq + q + 32);
-                const float4 a = __ldcs(vq + q), c2 = __ldcs(vq + q + 32);
-                quad(ja, a.x, a.y, a.z, a.w);
-                quad(jb, c2.x, c2.y, c2.z, c2.w);
+        // four quads in flight per lane (predicated: no tail loop), streamed past L1/L2 residency with ld.global.cs
+        for (int64_t q = q0 + lane; q < q1; q += 128) {
+            uint2 jj[4];
+            T a[4][4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int64_t qq = q + 32 * u;
+                if (qq < q1) {
+                    jj[u] = __ldcs(jq + qq);
+                    if constexpr (sizeof(T) == 4) {
+                        const float4 f = __ldcs(reinterpret_cast<const float4 *>(sval) + qq);
+                        a[u][0] = f.x;
+                        a[u][1] = f.y;
+                        a[u][2] = f.z;
+                        a[u][3] = f.w;
+                    } else {
+                        const double2 d0 = __ldcs(reinterpret_cast<const double2 *>(sval) + 2 * qq);
+                        const double2 d1 = __ldcs(reinterpret_cast<const double2 *>(sval) + 2 * qq + 1);
+                        a[u][0] = d0.x;
+                        a[u][1] = d0.y;
+                        a[u][2] = d1.x;
+                        a[u][3] = d1.y;
+                    }
+                }
             }
-            if (q < q1) {
-                const uint2 ja = __ldcs(jq + q);
-                const float4 a = __ldcs(vq + q);
-                quad(ja, a.x, a.y, a.z, a.w);
-            }
-        } else {
-            const double2 *__restrict__ vq = reinterpret_cast<const double2 *>(sval);
-            for (; q + 32 < q1; q += 64) {
-                const uint2 ja = __ldcs(jq + q), jb = __ldcs(jq + q + 32);
-                const double2 a = __ldcs(vq + 2 * q), a2 = __ldcs(vq + 2 * q + 1);
-                const double2 c2 = __ldcs(vq + 2 * (q + 32)), c3 = __ldcs(vq + 2 * (q + 32) + 1);
-                quad(ja, a.x, a.y, a2.x, a2.y);
-                quad(jb, c2.x, c2.y, c3.x, c3.y);
-            }
-            if (q < q1) {
-                const uint2 ja = __ldcs(jq + q);
-                const double2 a = __ldcs(vq + 2 * q), a2 = __ldcs(vq + 2 * q + 1);
-                quad(ja, a.x, a.y, a2.x, a2.y);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (q + 32 * u < q1) { quad(jj[u], a[u][0], a[u][1], a[u][2], a[u][3]); }
             }
         }
         const T sum = warp_sum((s0 + s1) + (s2 + s3));
@@ -1127,7 +1128,7 @@ template <typename T>
 void cached_matvec(ctx &c, sparse_state &st, const T *v, T *out) {
     const int64_t rows = st.c_hi - st.c_lo;
     const sp::cache_view cv{ st.c_ptr.as<int64_t>(), st.c_j.as<uint16_t>(), st.c_val.p, rows };
-    const int rows_per_cta = 256;
+    const int rows_per_cta = 512;
     static size_t attr_smem[2] = { 0, 0 };
     const size_t smem = (size_t) st.W * sizeof(T);
     if (smem > attr_smem[sizeof(T) == 8]) {
