@@ -136,7 +136,7 @@ def run_reference_arm(a):
     res = cpu_reference_iteration_rate(a, a.steps, a.warmup, X, a.cpu_sample_points, budget_s=60.0)
     line = {
         "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
-        "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": a.dtype, "data": "synthetic", "config": workload_config(a), "impl": "reference",
         "cpu_baseline": {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": res["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -307,6 +307,10 @@ def run_b200_arm(a):
         roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
                 "peak_source": f"{peak_kind} bf16 dense (sustained)", "kernel": {1: "k_kmv_tile (SIMT fp32)", 2: "k_gram_tc (tcgen05 fp16x2-split)", 3: "gemv pair"}.get(path, "?"),
                 "alg_flops_per_launch": flops, "ms_per_launch": matvec_ms, "launches_timed": n_matvecs}
+        if not sparse and world == 1 and path == 2 and (n, F, a.kernel, a.dtype) == (65536, 1024, "rbf", "f32"):
+            # dram__bytes_read.sum + dram__bytes_write.sum of one k_gram_tc launch of this exact workload (ncu --set full capture)
+            roof["traffic"] = 2.807074e9 + 0.102859e9
+            roof["traffic_source"] = "profiles/r1_gram_tc_final_ncu_full_raw.csv"
         if sparse and cache_entries > 0:
             # cached S: the matvec streams (value + 16-bit index) per stored entry, once (SURVEY.md §8d "cached S" row)
             nbytes = float(cache_entries) * (np.dtype(dt).itemsize + 2)

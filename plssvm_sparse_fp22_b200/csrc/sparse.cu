@@ -399,16 +399,16 @@ __global__ void __launch_bounds__(1024)
                     if (f >= 0 && b + 1 < b1) { nxt[q] = __ldg(B.ptrT + (int64_t) f * ldp + b + 2); }
                 }
             }
-            // ---- 2. products: GS lanes per segment, four segments (two entries each) in flight per lane
+            // ---- 2. products: GS lanes per segment; four segments x two entries in flight per lane and round
             for (int k0 = gid; k0 < R; k0 += 4 * NG) {
                 uint32_t e[4], e1[4];
-                int ja[4], jb[4];
-                T x[4], va[4], vb2[4];
+                T x[4];
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     const int k = k0 + u * NG;
                     e[u] = 0u;
                     e1[u] = 0u;
+                    x[u] = T(0);
                     if (k < R) {
                         const uint32_t a0 = s0[k], a1 = s1[k];
                         if ((int) (a1 - a0) <= thr) {
@@ -417,32 +417,35 @@ __global__ void __launch_bounds__(1024)
                             x[u] = xs[k];
                         }
                     }
-                    if (e[u] < e1[u]) {
-                        ja[u] = (int) __ldg(Bj + e[u]);
-                        va[u] = __ldg(Bv + e[u]);
-                    }
-                    if (e[u] + (uint32_t) GS < e1[u]) {
-                        jb[u] = (int) __ldg(Bj + e[u] + GS);
-                        vb2[u] = __ldg(Bv + e[u] + GS);
-                    }
                 }
+                bool more = (e[0] < e1[0]) | (e[1] < e1[1]) | (e[2] < e1[2]) | (e[3] < e1[3]);
+                while (more) {
+                    int ja[4], jb[4];
+                    T va[4], vb2[4];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    if (e[u] < e1[u]) {
-                        FX::add(acc, W, ja[u], x[u] * va[u], fx_scale, lb);
-                        if constexpr (COMPACT) { atomicOr(&bits[ja[u] >> 5], 1u << (ja[u] & 31)); }
+                    for (int u = 0; u < 4; ++u) {
+                        if (e[u] < e1[u]) {
+                            ja[u] = (int) __ldg(Bj + e[u]);
+                            va[u] = __ldg(Bv + e[u]);
+                        }
+                        if (e[u] + (uint32_t) GS < e1[u]) {
+                            jb[u] = (int) __ldg(Bj + e[u] + GS);
+                            vb2[u] = __ldg(Bv + e[u] + GS);
+                        }
                     }
-                    if (e[u] + (uint32_t) GS < e1[u]) {
-                        FX::add(acc, W, jb[u], x[u] * vb2[u], fx_scale, lb);
-                        if constexpr (COMPACT) { atomicOr(&bits[jb[u] >> 5], 1u << (jb[u] & 31)); }
-                    }
-                }
+                    more = false;
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {  // what is left of longer segments
-                    for (uint32_t ee = e[u] + 2u * (uint32_t) GS; ee < e1[u]; ee += (uint32_t) GS) {
-                        const int jc = (int) __ldg(Bj + ee);
-                        FX::add(acc, W, jc, x[u] * __ldg(Bv + ee), fx_scale, lb);
-                        if constexpr (COMPACT) { atomicOr(&bits[jc >> 5], 1u << (jc & 31)); }
+                    for (int u = 0; u < 4; ++u) {
+                        if (e[u] < e1[u]) {
+                            FX::add(acc, W, ja[u], x[u] * va[u], fx_scale, lb);
+                            if constexpr (COMPACT) { atomicOr(&bits[ja[u] >> 5], 1u << (ja[u] & 31)); }
+                        }
+                        if (e[u] + (uint32_t) GS < e1[u]) {
+                            FX::add(acc, W, jb[u], x[u] * vb2[u], fx_scale, lb);
+                            if constexpr (COMPACT) { atomicOr(&bits[jb[u] >> 5], 1u << (jb[u] & 31)); }
+                        }
+                        e[u] = min(e[u] + 2u * (uint32_t) GS, e1[u]);
+                        more |= e[u] < e1[u];
                     }
                 }
             }
@@ -524,9 +527,20 @@ __global__ void __launch_bounds__(1024)
                     }
                 }
             } else {
-                for (int jl = t; jl < W; jl += TT) {
-                    const T gv = FX::take(acc, W, jl, fx_inv, lb);
-                    rowsum = fma(s_value<T, KERNEL>(gv, kf), __ldg(vb + jl), rowsum);
+                for (int jl0 = t; jl0 < W; jl0 += 4 * TT) {  // four slots per thread in flight (the weights come from L2)
+                    T gv[4], vv[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int jl = jl0 + u * TT;
+                        gv[u] = T(0);
+                        vv[u] = T(0);
+                        if (jl < W) {
+                            gv[u] = FX::take(acc, W, jl, fx_inv, lb);
+                            vv[u] = __ldg(vb + jl);
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) { rowsum = fma(s_value<T, KERNEL>(gv[u], kf), vv[u], rowsum); }
                 }
             }
             __syncthreads();
@@ -813,7 +827,7 @@ void build_transpose(ctx &c, sparse_state &st, const host_csr<T> &h) {
     const int64_t n = st.n, F = st.F;
     const int64_t nnz = (int64_t) h.col.size();
     const int nb = st.nb, W = st.W;
-    B200_REQUIRE(nnz < (int64_t) 0xFFFFFFFFll, "more than 2^32 - 1 stored entries are not supported by the sparse path");
+    B200_REQUIRE(nnz < (int64_t) 0xFFFF0000ll, "more than 2^32 - 2^16 stored entries are not supported by the sparse path");
     std::vector<int64_t> colptr((size_t) F + 1, 0);
     for (int64_t p = 0; p < nnz; ++p) { ++colptr[(size_t) h.col[(size_t) p] + 1]; }
     double sumsq = 0;
@@ -994,6 +1008,26 @@ namespace {
         }                                                   \
     } while (0)
 
+template <typename T>
+T pow_like_device(T b, int degree) {
+    switch (degree) {
+        case 1: return b;
+        case 2: return b * b;
+        case 3: return b * b * b;
+        case 4: return (b * b) * (b * b);
+        default: break;
+    }
+    const bool neg = degree < 0;
+    unsigned int u = neg ? (unsigned int) (-degree) : (unsigned int) degree;
+    T r = T(1), x = b;
+    while (u != 0u) {  // ipow() of device_utils.cuh
+        if (u & 1u) { r *= x; }
+        x *= x;
+        u >>= 1;
+    }
+    return neg ? T(1) / r : r;
+}
+
 // max_norm2 bounds |G_ij| and every partial sum of its products (Cauchy-Schwarz): scale = 2^(bits - ceil(log2 bound));
 // max_row bounds the number of additions per slot (head-room of the low limb of the double accumulator)
 sp::kfun make_kfun(const ctx &c, double max_norm2 = 1.0, int64_t max_row = 1024) {
@@ -1015,7 +1049,9 @@ sp::kfun make_kfun(const ctx &c, double max_norm2 = 1.0, int64_t max_row = 1024)
         k.c0pow = 0.0;
     } else {
         k.a = c.gamma;
-        k.c0pow = std::pow(c.coef0, (double) c.degree);
+        // coef0^degree in the handle's type with the multiplication order of s_value(): S(0) is then exactly zero, so evaluating
+        // untouched accumulator slots (dense epilogue) adds nothing
+        k.c0pow = c.dtype == B200SVM_F32 ? (double) pow_like_device<float>((float) c.coef0, c.degree) : pow_like_device<double>(c.coef0, c.degree);
     }
     return k;
 }
