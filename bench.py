@@ -307,6 +307,11 @@ def run_b200_arm(a):
         roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
                 "peak_source": f"{peak_kind} bf16 dense (sustained)", "kernel": {1: "k_kmv_tile (SIMT fp32)", 2: "k_gram_tc (tcgen05 fp16x2-split)", 3: "gemv pair"}.get(path, "?"),
                 "alg_flops_per_launch": flops, "ms_per_launch": matvec_ms, "launches_timed": n_matvecs}
+        if not sparse and path == 2:
+            # the fp16x2 split issues two pass-equivalents of fp16-rate MMA per algorithmic flop (hi.hi in fp16, both cross terms as one
+            # fp8 chain of twice the K extent at twice the rate): `frac` stays on ALGORITHMIC flops, this is the tensor pipe's own view
+            roof["issued_fp16_equiv_tflops"] = 2.0 * achieved
+            roof["frac_issued"] = 2.0 * achieved / peak
         if not sparse and world == 1 and path == 2 and (n, F, a.kernel, a.dtype) == (65536, 1024, "rbf", "f32"):
             # dram__bytes_read.sum + dram__bytes_write.sum of one k_gram_tc launch of this exact workload (ncu --set full capture)
             roof["traffic"] = 2.807074e9 + 0.102859e9
