@@ -55,6 +55,9 @@ def parse_args():
                          "--points 1000000 --features 100000 --density 1e-3 --dtype f64, configs[3] --points 262144 --features 20000 "
                          "--density 1e-2 --kernel polynomial --storage fp22")
     ap.add_argument("--storage", default="native", choices=["native", "fp22"], help="sparse value storage")
+    ap.add_argument("--dense-cache", type=int, default=0,
+                    help="dense tcgen05 path: 0 store the kernel-matrix tiles on first use if they fit (matvec = HBM-bound sweep), "
+                         "1 recompute the Gram tiles on the tensor cores in every matvec")
     ap.add_argument("--skip-e2e", action="store_true", help="large sparse runs only: skip the host-buffer leg (e2e = null)")
     ap.add_argument("--cache", type=int, default=0, help="sparse: 0 cache S if it fits, 1 recompute on the fly, 2 require the cache")
     return ap.parse_args()
@@ -232,6 +235,15 @@ def run_b200_arm(a):
         h.set_option(capi.OPT_MATVEC_PATH, a.path)
     if sparse:
         h.set_option(capi.OPT_SPARSE_CACHE, a.cache)
+    else:
+        h.set_option(capi.OPT_DENSE_CACHE, a.dense_cache)
+
+    def drop_caches():
+        # derived data (cached kernel-matrix tiles / sparse S) is NOT carried into a timed region: its assembly is part of the job
+        if sparse:
+            h.set_option(capi.OPT_SPARSE_CACHE, a.cache)
+        else:
+            h.set_option(capi.OPT_DENSE_CACHE, a.dense_cache)
     if world > 1:
         idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
@@ -249,6 +261,7 @@ def run_b200_arm(a):
     q = h.generate_q()
     QA = h.kxx_last() + 1.0
     h.solver_cg(b, None, QA, max(W, 3), 0.0)  # warm-up steps (untimed)
+    drop_caches()
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -262,7 +275,10 @@ def run_b200_arm(a):
     st = h.stats()
     assert iters == K, (iters, K)
     launches = int(st.kernel_launches)
-    matvec_ms = st.matvec_ms / max(st.matvecs_timed, 1)
+    build_ms = float(st.cache_build_ms)
+    dense_cache_bytes = int(st.dense_cache_bytes)
+    # the matvec that assembles a cache is timed as a whole: take the assembly out to get the steady-state launch duration
+    matvec_ms = (st.matvec_ms - build_ms) / max(st.matvecs_timed, 1)
     n_matvecs = int(st.matvecs_timed)
     path = int(st.matvec_path)
     cache_entries = int(st.sparse_cache_entries) if sparse else 0
@@ -307,12 +323,23 @@ def run_b200_arm(a):
         roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
                 "peak_source": f"{peak_kind} bf16 dense (sustained)", "kernel": {1: "k_kmv_tile (SIMT fp32)", 2: "k_gram_tc (tcgen05 fp16x2-split)", 3: "gemv pair"}.get(path, "?"),
                 "alg_flops_per_launch": flops, "ms_per_launch": matvec_ms, "launches_timed": n_matvecs}
-        if not sparse and path == 2:
+        if not sparse and path == 2 and dense_cache_bytes > 0:
+            # cached kernel matrix: the per-iteration kernel streams the stored lower-triangle tiles once (SURVEY.md §8d "cached dense K")
+            hb = float(peaks.get("hbm_gbs", 6650.0))
+            ach = dense_cache_bytes / (matvec_ms * 1e-3) / 1e9
+            asm_tf = flops / (build_ms * 1e-3) / 1e12 if build_ms > 0 else None
+            roof = {"bound": "hbm", "achieved": ach, "peak": hb, "unit": "GB/s", "frac": ach / hb, "traffic": None, "peak_source": f"{peak_kind} HBM copy",
+                    "kernel": "k_cached_gemv (sweep over the stored kernel-matrix tiles; k_pack / k_tc_reduce inside the timed span)",
+                    "alg_bytes_per_launch": float(dense_cache_bytes), "ms_per_launch": matvec_ms, "launches_timed": n_matvecs,
+                    "assembly": {"kernel": "k_gram_tc<STORE> (tcgen05 fp16x2-split, once per data set, inside the timed region)", "ms": build_ms,
+                                 "alg_flops": flops, "achieved_tflops": asm_tf, "frac_of_bf16_sustained": asm_tf / peak if asm_tf else None,
+                                 "frac_issued": 2.0 * asm_tf / peak if asm_tf else None}}
+        elif not sparse and path == 2:
             # the fp16x2 split issues two pass-equivalents of fp16-rate MMA per algorithmic flop (hi.hi in fp16, both cross terms as one
             # fp8 chain of twice the K extent at twice the rate): `frac` stays on ALGORITHMIC flops, this is the tensor pipe's own view
             roof["issued_fp16_equiv_tflops"] = 2.0 * achieved
             roof["frac_issued"] = 2.0 * achieved / peak
-        if not sparse and world == 1 and path == 2 and (n, F, a.kernel, a.dtype) == (65536, 1024, "rbf", "f32"):
+        if not sparse and world == 1 and path == 2 and dense_cache_bytes == 0 and (n, F, a.kernel, a.dtype) == (65536, 1024, "rbf", "f32"):
             # dram__bytes_read.sum + dram__bytes_write.sum of one k_gram_tc launch of this exact workload (ncu --set full capture)
             roof["traffic"] = 2.807074e9 + 0.102859e9
             roof["traffic_source"] = "profiles/r1_gram_tc_final_ncu_full_raw.csv"
@@ -338,6 +365,7 @@ def run_b200_arm(a):
             "e2e": {"value": K / (t_e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": st2.h2d_bytes / K, "d2h_bytes_per_step": st2.d2h_bytes / K,
                     "ms_total": t_e2e_ms},
             "gpu_launches": launches,
+            "cache_build_ms": build_ms,
             "roofline": roof,
         }
         if world == 1 and not a.no_cpu_baseline and not sparse:

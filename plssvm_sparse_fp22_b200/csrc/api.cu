@@ -135,6 +135,7 @@ int b200svm_create(b200svm_handle *h, int dtype, int kernel, int degree, double 
         c->stream = c->own_stream;
         for (auto &ev : c->ev) { B200_CUDA_CHECK(cudaEventCreate(&ev)); }
         for (auto &ev : c->cg_ev) { B200_CUDA_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)); }
+        for (auto &ev : c->cb_ev) { B200_CUDA_CHECK(cudaEventCreate(&ev)); }
         B200_CUDA_CHECK(cudaMallocHost(&c->pinned, 512));
         c->scal.reserve(S_COUNT * sizeof(double));
         c->partials.reserve(4 * MAX_PARTIAL_BLOCKS * sizeof(double));
@@ -164,6 +165,9 @@ int b200svm_destroy(b200svm_handle h) {
         if (ev != nullptr) { cudaEventDestroy(ev); }
     }
     for (auto &ev : c->cg_ev) {
+        if (ev != nullptr) { cudaEventDestroy(ev); }
+    }
+    for (auto &ev : c->cb_ev) {
         if (ev != nullptr) { cudaEventDestroy(ev); }
     }
     if (c->pinned != nullptr) { cudaFreeHost(c->pinned); }
@@ -215,9 +219,15 @@ int b200svm_set_option(b200svm_handle h, int option, int64_t value) {
                 sp_invalidate_cache(*c);
                 break;
             case B200SVM_OPT_SPARSE_CACHE_MB:
-                B200_REQUIRE(value >= 0, "sparse cache budget must be >= 0 MiB");
+                B200_REQUIRE(value >= 0, "cache budget must be >= 0 MiB");
                 c->opt_sparse_cache_mb = value;
                 sp_invalidate_cache(*c);
+                tc_invalidate_cache(*c);
+                break;
+            case B200SVM_OPT_DENSE_CACHE:
+                B200_REQUIRE(value >= 0 && value <= 2, "dense cache mode must be 0 (auto), 1 (off) or 2 (required)");
+                c->opt_dense_cache = value;
+                tc_invalidate_cache(*c);
                 break;
             case B200SVM_OPT_SPARSE_GROUP:
                 B200_REQUIRE(value >= 0, "blocks per group must be >= 0");
@@ -239,10 +249,11 @@ int b200svm_get_stats(b200svm_handle h, b200svm_stats *out) {
 int b200svm_reset_stats(b200svm_handle h) {
     ctx *c = reinterpret_cast<ctx *>(h);
     return guarded(c, [&]() {
-        const int64_t cached = c->stats.sparse_cache_entries;  // a property of the resident data, not a counter
+        const int64_t cached = c->stats.sparse_cache_entries, dense = c->stats.dense_cache_bytes;  // properties of the resident data
         sync_stream(*c);                                       // account the events still in flight before zeroing
         c->stats = b200svm_stats{};
         c->stats.sparse_cache_entries = cached;
+        c->stats.dense_cache_bytes = dense;
     });
 }
 

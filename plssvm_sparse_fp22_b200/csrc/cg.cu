@@ -178,6 +178,11 @@ void drain_matvec_events(ctx &c, int64_t upto) {
 void sync_stream(ctx &c) {
     B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));
     drain_matvec_events(c, c.ev_head);
+    if (c.cb_pending) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, c.cb_ev[0], c.cb_ev[1]) == cudaSuccess) { c.stats.cache_build_ms += ms; }
+        c.cb_pending = false;
+    }
 }
 
 template <typename T>

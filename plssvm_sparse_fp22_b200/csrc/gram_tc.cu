@@ -73,6 +73,7 @@ struct params {
     float qa;          // QA_cost
     int degree;
     int kernel;
+    float *Kc;          // STORE mode: kernel values of every tile, [num_tiles][BM][BN]
     const float *done;  // CG convergence flag (scal[S_DONE]): a launch queued behind the converged iteration returns at once
 };
 
@@ -209,7 +210,8 @@ __device__ __forceinline__ float warp_column_sums(float (&v)[32], int lane) {
 // FP8X: map_lo / map_b are the e4m3 planes [hi8 | lo8] (A role) and [lo8 | hi8] (B role), 128 bytes per 64-element K block;
 // otherwise map_lo is the fp16 lo plane and map_b is unused.  Every K block fills two ring slots of [A 16K | B 32K]:
 //   slot 0 = (A_hi, B_hi), slot 1 = (A_lo, B_lo) for F16X3 or (A_8, B_8) for FP8X.
-template <int KERNEL, bool FP8X>
+// STORE: the epilogue writes the kernel values k(x_i, x_j) of the tile to p.Kc instead of reducing them against d
+template <int KERNEL, bool FP8X, bool STORE>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
     k_gram_tc(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo, const __grid_constant__ CUtensorMap map_b,
               const params p) {
@@ -380,6 +382,21 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
                 uint32_t u[32];
                 tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * BN + g * 32), u);
                 tmem_ld_wait();
+                if constexpr (STORE) {
+                    // 32 consecutive columns of row r: one 128-byte line per thread
+                    float4 *dst = reinterpret_cast<float4 *>(p.Kc + (static_cast<int64_t>(t) * BM + r) * BN + g * 32);
+#pragma unroll
+                    for (int c4 = 0; c4 < 8; ++c4) {
+                        float kv[4];
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            const float4 cj = colbuf[buf * BN + g * 32 + c4 * 4 + c];
+                            kv[c] = kernel_from_gram<KERNEL>(__uint_as_float(u[c4 * 4 + c]), mine.x, cj.x, p.w, p.coef0, p.degree);
+                        }
+                        __stcs(dst + c4, make_float4(kv[0], kv[1], kv[2], kv[3]));
+                    }
+                    continue;
+                }
                 float v[32];
                 if (!diag_tile) {
 #pragma unroll
@@ -408,12 +425,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
             tc_fence_before();
             __syncwarp();
             if (lane == 0) { mbar_arrive(bar_tempty + buf * 8); }
-            if (half == 1) { rowred[buf * BM + r] = rowsum; }
-            asm volatile("bar.sync 1, 256;" ::: "memory");  // colred / rowred complete
-            if (half == 0) { p.Pr[static_cast<int64_t>(tile.y) * p.ldP + gi] = rowsum + rowred[buf * BM + r]; }
-            {
-                const float *c0 = colred + buf * 4 * BN;
-                p.Pc[static_cast<int64_t>(tile.x) * p.ldP + col0 + et] = (c0[et] + c0[BN + et]) + (c0[2 * BN + et] + c0[3 * BN + et]);
+            if constexpr (!STORE) {
+                if (half == 1) { rowred[buf * BM + r] = rowsum; }
+                asm volatile("bar.sync 1, 256;" ::: "memory");  // colred / rowred complete
+                if (half == 0) { p.Pr[static_cast<int64_t>(tile.y) * p.ldP + gi] = rowsum + rowred[buf * BM + r]; }
+                {
+                    const float *c0 = colred + buf * 4 * BN;
+                    p.Pc[static_cast<int64_t>(tile.x) * p.ldP + col0 + et] = (c0[et] + c0[BN + et]) + (c0[2 * BN + et] + c0[3 * BN + et]);
+                }
             }
         }
     }
@@ -423,6 +442,82 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Cached kernel matrix: the same partial vectors as k_gram_tc, from the stored tiles — an HBM-bound symmetric GEMV.
+//   t_ij = K_ij + QA_cost - q_i - q_j ;  Pr[J][i] = sum_j t_ij d_j (i >= j) ;  Pc[I][j] = sum_i t_ij d_i (i > j)
+// One CTA per tile (grid-strided).  Thread (ty = warp / 2, tx = thread % 64) reads float4 (row ty + 4k, columns 4 tx..4 tx + 3): a warp
+// streams 512 contiguous bytes per row.  Column sums stay in registers; the 32 row partials of a thread are reduced over the warp
+// by the fixed butterfly of warp_column_sums.  All reductions have a fixed order => bit-reproducible.
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_cached_gemv(const float *__restrict__ Kc, const params p) {
+    if (p.done != nullptr && *p.done != 0.f) { return; }
+    __shared__ float2 rowqd[BM];       // (QA_cost - q_i, d_i)
+    __shared__ float rowpart[8][32];   // per warp: totals of its 32 rows over its 128 columns
+    __shared__ float colpart[4][BN];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5, ty = w >> 1, tx = t & 63;
+    for (int tt = blockIdx.x; tt < p.num_tiles; tt += gridDim.x) {
+        const int2 tile = p.tiles[tt];
+        const int64_t row0 = static_cast<int64_t>(tile.x) * BM, col0 = static_cast<int64_t>(tile.y) * BN;
+        const bool diag_tile = row0 < col0 + BN;
+        __syncthreads();  // the previous tile's shared-memory readers are done
+        if (t < BM) {
+            const float4 v = __ldg(&p.pk[row0 + t]);
+            rowqd[t] = make_float2(p.qa - v.y, v.z);
+        }
+        float qj[4], dj[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float4 v = __ldg(&p.pk[col0 + 4 * tx + c]);
+            qj[c] = v.y;
+            dj[c] = v.z;
+        }
+        __syncthreads();
+        const float4 *base = reinterpret_cast<const float4 *>(Kc + static_cast<int64_t>(tt) * (BM * BN)) + tx;
+        float rs[32];
+        float cs[4] = { 0.f, 0.f, 0.f, 0.f };
+#pragma unroll
+        for (int k0 = 0; k0 < 32; k0 += 8) {
+            float4 kv[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { kv[k] = __ldcs(base + (ty + 4 * (k0 + k)) * (BN / 4)); }  // eight 16-byte loads in flight
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int row = ty + 4 * (k0 + k);
+                const float2 qd = rowqd[row];
+                const float e[4] = { kv[k].x, kv[k].y, kv[k].z, kv[k].w };
+                float r = 0.f;
+                if (!diag_tile) {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        const float tv = e[c] + (qd.x - qj[c]);
+                        r = fmaf(tv, dj[c], r);
+                        cs[c] = fmaf(tv, qd.y, cs[c]);
+                    }
+                } else {
+                    const int64_t gi = row0 + row;
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        const int64_t gj = col0 + 4 * tx + c;
+                        const float tv = e[c] + (qd.x - qj[c]);
+                        r = gi >= gj ? fmaf(tv, dj[c], r) : r;
+                        cs[c] = gi > gj ? fmaf(tv, qd.y, cs[c]) : cs[c];
+                    }
+                }
+                rs[k0 + k] = r;
+            }
+        }
+        rowpart[w][lane] = warp_column_sums(rs, lane);  // lane l: row ty + 4 l over this warp's 128 columns
+#pragma unroll
+        for (int c = 0; c < 4; ++c) { colpart[ty][4 * tx + c] = cs[c]; }
+        __syncthreads();
+        if (t < BM) {
+            const int g = t & 3, k = t >> 2;
+            p.Pr[static_cast<int64_t>(tile.y) * p.ldP + row0 + t] = rowpart[2 * g][k] + rowpart[2 * g + 1][k];
+        }
+        p.Pc[static_cast<int64_t>(tile.x) * p.ldP + col0 + t] = (colpart[0][t] + colpart[1][t]) + (colpart[2][t] + colpart[3][t]);
     }
 }
 
@@ -508,8 +603,9 @@ namespace {
 
 struct tc_state {
     CUtensorMap map_hi{}, map_lo{}, map_a8{}, map_b8{};
-    dbuf tiles, pk, Pr, Pc, amax, P8a, P8b, own;
+    dbuf tiles, pk, Pr, Pc, amax, P8a, P8b, own, Kc;
     bool has_own{ false };
+    bool kc_valid{ false }, kc_refused{ false };  // cached kernel-matrix tiles of this rank
     bool fp8x{ false };
     int num_tiles{ 0 };
     int T_r{ 0 }, T_c{ 0 };
@@ -647,15 +743,56 @@ void tc_prepare_split(ctx &c) {
     B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));  // `tiles` (host vector) must outlive the copy
     static bool attr_set = false;
     if (!attr_set) {
-        B200_CUDA_CHECK(cudaFuncSetAttribute(tc::k_gram_tc<B200SVM_RBF, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
-        B200_CUDA_CHECK(cudaFuncSetAttribute(tc::k_gram_tc<B200SVM_POLYNOMIAL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
-        B200_CUDA_CHECK(cudaFuncSetAttribute(tc::k_gram_tc<B200SVM_RBF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
-        B200_CUDA_CHECK(cudaFuncSetAttribute(tc::k_gram_tc<B200SVM_POLYNOMIAL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+#define B200_TC_ATTR(KN, F8, ST) \
+    B200_CUDA_CHECK(cudaFuncSetAttribute(tc::k_gram_tc<KN, F8, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES))
+        B200_TC_ATTR(B200SVM_RBF, false, false);
+        B200_TC_ATTR(B200SVM_POLYNOMIAL, false, false);
+        B200_TC_ATTR(B200SVM_RBF, true, false);
+        B200_TC_ATTR(B200SVM_POLYNOMIAL, true, false);
+        B200_TC_ATTR(B200SVM_RBF, false, true);
+        B200_TC_ATTR(B200SVM_POLYNOMIAL, false, true);
+        B200_TC_ATTR(B200SVM_RBF, true, true);
+        B200_TC_ATTR(B200SVM_POLYNOMIAL, true, true);
+#undef B200_TC_ATTR
         attr_set = true;
     }
     c.has_split = true;
     st.ready = true;
+    st.kc_valid = false;
+    st.kc_refused = false;
+    c.stats.dense_cache_bytes = 0;
 }
+
+void tc_invalidate_cache(ctx &c) {
+    if (c.tc_opaque != nullptr) {
+        tc_state &st = state_of(c);
+        st.kc_valid = false;
+        st.kc_refused = false;
+        c.stats.dense_cache_bytes = 0;
+    }
+}
+
+namespace {
+
+template <bool STORE>
+void launch_gram(ctx &c, tc_state &st, const tc::params &p) {
+    const int grid = std::min(NUM_SMS, std::max(st.num_tiles, 1));
+    if (st.fp8x) {
+        if (c.kernel == B200SVM_RBF) {
+            tc::k_gram_tc<B200SVM_RBF, true, STORE><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_a8, st.map_b8, p);
+        } else {
+            tc::k_gram_tc<B200SVM_POLYNOMIAL, true, STORE><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_a8, st.map_b8, p);
+        }
+    } else if (c.kernel == B200SVM_RBF) {
+        tc::k_gram_tc<B200SVM_RBF, false, STORE><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_lo, st.map_lo, p);
+    } else {
+        tc::k_gram_tc<B200SVM_POLYNOMIAL, false, STORE><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_lo, st.map_lo, p);
+    }
+    count_launch(c);
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace
 
 // out[i] = sum_j (k(x_i, x_j) + QA_cost - q_i - q_j) d_j  over the tiles owned by this rank (all tiles when world == 1)
 void tc_kernel_matvec(ctx &c, const float *d, float *out) {
@@ -676,6 +813,7 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out) {
     p.qa = (float) c.QA_cost;
     p.degree = c.degree;
     p.kernel = c.kernel;
+    p.Kc = nullptr;
     p.done = c.scal.as<float>() + S_DONE;
     float cscale = 0.f;
     if (c.kernel == B200SVM_RBF) {
@@ -685,21 +823,43 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out) {
         p.w = (float) (c.gamma / (double) s2);
     }
     tc::k_pack<<<(unsigned) ((c.n_pad + 255) / 256), 256, 0, c.stream>>>(c.norms.as<float>(), c.q.as<float>(), d, m, c.n_pad, cscale, st.pk.as<float4>());
-    const int grid = std::min(NUM_SMS, std::max(st.num_tiles, 1));
-    if (st.fp8x) {
-        if (c.kernel == B200SVM_RBF) {
-            tc::k_gram_tc<B200SVM_RBF, true><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_a8, st.map_b8, p);
+    // The kernel values depend only on the data: when the tiles of this rank fit in HBM they are stored once (one pass of the
+    // tcgen05 kernel in STORE mode) and every later matvec is an HBM-bound sweep over them.
+    if (c.opt_dense_cache != 1 && !st.kc_valid && !st.kc_refused && st.num_tiles > 0) {
+        const size_t need = (size_t) st.num_tiles * tc::BM * tc::BN * sizeof(float);
+        size_t free_b = 0, total_b = 0;
+        B200_CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
+        free_b += st.Kc.bytes;
+        const double budget = c.opt_sparse_cache_mb > 0 ? (double) c.opt_sparse_cache_mb * 1048576.0 : 0.85 * (double) free_b;
+        if ((double) need > budget) {
+            B200_REQUIRE(c.opt_dense_cache != 2, "the cached kernel-matrix tiles do not fit the device memory budget");
+            st.kc_refused = true;
         } else {
-            tc::k_gram_tc<B200SVM_POLYNOMIAL, true><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_a8, st.map_b8, p);
+            st.Kc.reserve(need);
+            tc::params ps = p;
+            ps.Kc = st.Kc.as<float>();
+            ps.done = nullptr;  // never skipped: the stored tiles outlive the solve
+            if (c.cb_pending) { sync_stream(c); }
+            B200_CUDA_CHECK(cudaEventRecord(c.cb_ev[0], c.stream));
+            launch_gram<true>(c, st, ps);
+            B200_CUDA_CHECK(cudaEventRecord(c.cb_ev[1], c.stream));
+            c.cb_pending = true;
+            st.kc_valid = true;
+            c.stats.dense_cache_bytes = (int64_t) need;
         }
-    } else if (c.kernel == B200SVM_RBF) {
-        tc::k_gram_tc<B200SVM_RBF, false><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_lo, st.map_lo, p);
+    }
+    if (c.opt_dense_cache == 1) { st.kc_valid = false; }
+    if (st.kc_valid) {
+        const int grid = std::min(st.num_tiles, 4 * NUM_SMS);
+        tc::k_cached_gemv<<<grid, 256, 0, c.stream>>>(st.Kc.as<float>(), p);
+        count_launch(c);
+        B200_CUDA_CHECK(cudaGetLastError());
     } else {
-        tc::k_gram_tc<B200SVM_POLYNOMIAL, false><<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(st.map_hi, st.map_lo, st.map_lo, p);
+        launch_gram<false>(c, st, p);
     }
     tc::k_tc_reduce<<<(unsigned) ((m + 255) / 256), 256, 0, c.stream>>>(st.Pr.as<float>(), st.Pc.as<float>(), st.ldP, m, st.T_r, st.T_c,
                                                                         st.has_own ? st.own.as<uint8_t>() : nullptr, out, p.done);
-    count_launch(c, 3);
+    count_launch(c, 2);
     B200_CUDA_CHECK(cudaGetLastError());
 }
 

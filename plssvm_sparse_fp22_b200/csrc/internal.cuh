@@ -111,7 +111,8 @@ struct ctx {
     int64_t opt_sparse_lanes{ 0 };  // 0 = auto
     int64_t opt_sparse_threads{ 0 };  // 0 = auto
     int64_t opt_sparse_cache{ 0 };    // 0 = auto, 1 = off, 2 = required
-    int64_t opt_sparse_cache_mb{ 0 }; // 0 = 85 % of the free memory
+    int64_t opt_sparse_cache_mb{ 0 }; // 0 = 85 % of the free memory (both caches)
+    int64_t opt_dense_cache{ 0 };     // tcgen05 path: 0 = auto, 1 = off, 2 = required
 
     // data
     bool has_data{ false };
@@ -161,6 +162,8 @@ struct ctx {
     static constexpr int EV_RING = 16;
     cudaEvent_t ev[2 * EV_RING]{};  // ring of (start, stop) pairs around the O(m^2) kernel, drained when known to be complete
     int64_t ev_head{ 0 }, ev_tail{ 0 };
+    cudaEvent_t cb_ev[2]{};         // around the assembly of a kernel-matrix cache (dense tiles / sparse S)
+    bool cb_pending{ false };
     static constexpr int CG_RING = 16;
     cudaEvent_t cg_ev[CG_RING]{};   // one per queued CG iteration (its delta has reached the pinned mailbox)
 
@@ -188,6 +191,7 @@ template <typename T> void predict_dense(ctx &c, const T *alpha_dev, T bias, con
 // tcgen05 path (gram_tc.cu), f32 dense only
 void tc_prepare_split(ctx &c);                                   // build fp16 hi/lo operands + TMA descriptors
 bool tc_available(const ctx &c);
+void tc_invalidate_cache(ctx &c);  // drop the cached kernel-matrix tiles (option changed); rebuilt on the next matvec
 void tc_kernel_matvec(ctx &c, const float *d, float *out_Kd);    // out = K d via symmetric tcgen05 tiles
 
 // sparse path (sparse.cu)

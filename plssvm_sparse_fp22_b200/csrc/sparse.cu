@@ -1120,6 +1120,8 @@ bool build_cache(ctx &c, sparse_state &st, int64_t lo, int64_t hi) {
     st.c_valid = false;
     if (rows <= 0) { return false; }
     st.c_ptr.reserve((size_t) (visits + 1) * sizeof(int64_t));
+    if (c.cb_pending) { sync_stream(c); }
+    B200_CUDA_CHECK(cudaEventRecord(c.cb_ev[0], c.stream));
     B200_CUDA_CHECK(cudaMemsetAsync(st.c_ptr.p, 0, (size_t) (visits + 1) * sizeof(int64_t), c.stream));
     sp::cache_view cv{ st.c_ptr.as<int64_t>(), nullptr, nullptr, rows };
     const sp::csr_view A = view_rows(st, 0, st.n);
@@ -1151,6 +1153,8 @@ bool build_cache(ctx &c, sparse_state &st, int64_t lo, int64_t hi) {
     cv.j = st.c_j.as<uint16_t>();
     cv.val = st.c_val.p;
     launch_kmv<T>(c, st, A, lo, hi, st.a_max_row, st.max_norm2, static_cast<const T *>(nullptr), static_cast<T *>(nullptr), 2, cv);
+    B200_CUDA_CHECK(cudaEventRecord(c.cb_ev[1], c.stream));
+    c.cb_pending = true;
     st.c_lo = lo;
     st.c_hi = hi;
     st.c_entries = entries;

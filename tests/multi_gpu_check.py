@@ -35,13 +35,15 @@ def main():
         return bytes(idbuf.cpu().numpy().tobytes())
 
     ok = True
-    cases = [("rbf", np.float32, capi.PATH_TC, 1500, 96), ("polynomial", np.float32, capi.PATH_TC, 1100, 70),
+    cases = [("rbf", np.float32, capi.PATH_TC, 1500, 96), ("polynomial", np.float32, capi.PATH_TC, 1100, 70), ("rbf", np.float32, "tc_nocache", 1500, 96),
              ("rbf", np.float32, capi.PATH_SIMT, 900, 64), ("rbf", np.float64, capi.PATH_AUTO, 1200, 80),
              ("polynomial", np.float64, capi.PATH_AUTO, 700, 33), ("linear", np.float64, capi.PATH_AUTO, 1000, 50)]
     cases += [("rbf", np.float64, "csr", 1300, 900), ("polynomial", np.float64, "csr", 800, 500), ("linear", np.float64, "csr", 600, 700)]
     cases += [("rbf", np.float64, "csr_otf", 1300, 900), ("polynomial", np.float32, "csr_fp22", 900, 600)]  # S on the fly; FP22-packed rows
     for kernel, dt, path, n, F in cases:
         variant = path if isinstance(path, str) else ""
+        if variant == "tc_nocache":
+            path = capi.PATH_TC
         if variant.startswith("csr"):
             path = "csr"
             rp, ci, v, y = datagen.make_sparse_csr(n, F, 0.02, seed=n, dtype=dt)
@@ -54,6 +56,7 @@ def main():
         with capi.Handle(dt, kernel, gamma=1.0 / F, device=local) as h:
             if path and path != "csr":
                 h.set_option(capi.OPT_MATVEC_PATH, path)
+                h.set_option(capi.OPT_DENSE_CACHE, capi.CACHE_OFF if variant == "tc_nocache" else capi.CACHE_AUTO)
             h.comm_init(fresh_uid(), rank, world)
             if path == "csr":
                 h.set_option(capi.OPT_SPARSE_BLOCK, 256)

@@ -46,12 +46,13 @@ def test_dense_configs1_full_size_properties():
     d2 = rng.uniform(-1, 2, n - 1).astype(np.float32)
     gamma = 1.0 / F
     with capi.Handle(np.float32, "rbf", 3, gamma, 0.0, 1.0) as h:
+        h.set_option(capi.OPT_DENSE_CACHE, capi.CACHE_OFF)  # Gram tiles recomputed on the tensor cores in every matvec
         h.set_data(X)
         q = h.generate_q()
         qa = h.kxx_last() + 1.0
         h.set_q(q, qa)
         y1 = h.matvec(d1)
-        assert h.stats().matvec_path == capi.PATH_TC
+        assert h.stats().matvec_path == capi.PATH_TC and h.stats().dense_cache_bytes == 0
         y2 = h.matvec(d2)
         y3 = h.matvec((2.0 * d1 - 3.0 * d2).astype(np.float32))
         assert np.array_equal(y1, h.matvec(d1))  # deterministic reductions: bit-reproducible
@@ -61,6 +62,11 @@ def test_dense_configs1_full_size_properties():
         h.set_option(capi.OPT_MATVEC_PATH, capi.PATH_TC)
         h.set_option(capi.OPT_TC_MODE, capi.TC_F16X3)
         y1_f16 = h.matvec(d1)
+        h.set_option(capi.OPT_TC_MODE, capi.TC_FP8X)
+        h.set_option(capi.OPT_DENSE_CACHE, capi.CACHE_REQUIRED)  # kernel values stored once (8.6 GB), matvec = sweep over them
+        y1_cached = h.matvec(d1)
+        assert h.stats().dense_cache_bytes > 8e9
+        assert np.array_equal(y1_cached, h.matvec(d1))
     # q against the formula
     X64 = X.astype(np.float64)
     nrm = np.einsum("ij,ij->i", X64, X64)
@@ -69,6 +75,7 @@ def test_dense_configs1_full_size_properties():
     # independent device paths
     assert nrm_rel(y1_simt, y1) < 2e-5, nrm_rel(y1_simt, y1)
     assert nrm_rel(y1_f16, y1) < 2e-5, nrm_rel(y1_f16, y1)
+    assert nrm_rel(y1_cached, y1) < 2e-6, nrm_rel(y1_cached, y1)  # same kernel values, different summation order
     # rows of the reference formula in double
     rows = np.array([0, 1, 127, 128, 255, 256, 4097, 32767, 32768, 50001, 65407, 65408, 65533, 65534])
     want = abar_rows_dense(X, rows, d1, q, qa, 1.0, "rbf", 3, gamma, 0.0)

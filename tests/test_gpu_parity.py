@@ -242,12 +242,14 @@ def test_errors_are_loud():
             h._chk(h.L.b200svm_set_data_dense(h.h, np.zeros(1).ctypes.data, 0, 4, 4))
 
 
+@pytest.mark.parametrize("cache", [capi.CACHE_OFF, capi.CACHE_REQUIRED])
 @pytest.mark.parametrize("mode", [capi.TC_F16X3, capi.TC_FP8X])
 @pytest.mark.parametrize("kernel", ["rbf", "polynomial"])
 @pytest.mark.parametrize("shape", [(2, 3), (130, 64), (257, 33), (513, 100), (1000, 200), (2049, 1024)])
-def test_tcgen05_path_vs_simt_and_oracle(kernel, shape, mode):
+def test_tcgen05_path_vs_simt_and_oracle(kernel, shape, mode, cache):
     """The tcgen05/TMA path (fp16x2-split Gram tiles, symmetric) against the SIMT fp32 path and the f64 oracle on ragged sizes
-    (rows not a multiple of the 128x256 tile, features not a multiple of the 64-wide K block)."""
+    (rows not a multiple of the 128x256 tile, features not a multiple of the 64-wide K block).  cache OFF: the Gram tiles are
+    recomputed in every matvec; REQUIRED: the kernel values are stored by one pass of the same kernel and swept by k_cached_gemv."""
     n, F = shape
     X, _ = datagen.make_dense(n, F, seed=n + F, problem="blobs", dtype=np.float32)
     d = np.random.default_rng(1).uniform(-1, 2, n - 1).astype(np.float32)
@@ -257,11 +259,13 @@ def test_tcgen05_path_vs_simt_and_oracle(kernel, shape, mode):
         with capi.Handle(np.float32, kernel, 3, 1.0 / F, coef0, 1.0) as h:
             h.set_option(capi.OPT_MATVEC_PATH, path)
             h.set_option(capi.OPT_TC_MODE, mode)
+            h.set_option(capi.OPT_DENSE_CACHE, cache)
             h.set_data(X)
             q = h.generate_q()
             h.set_q(q, h.kxx_last() + 1.0)
             outs[path] = h.matvec(d, 1.0)
             assert h.stats().matvec_path == path
+            assert (h.stats().dense_cache_bytes > 0) == (path == capi.PATH_TC and cache == capi.CACHE_REQUIRED)
             outs[(path, "neg")] = h.matvec(d, -1.0, ret=np.ones(n - 1, np.float32))
     X64 = X.astype(np.float64)
     q64 = port.generate_q(X64, kernel, 3, 1.0 / F, coef0)
@@ -276,14 +280,16 @@ def test_tcgen05_path_is_deterministic():
     n, F = 1500, 96
     X, _ = datagen.make_dense(n, F, seed=3, dtype=np.float32)
     d = np.random.default_rng(2).standard_normal(n - 1).astype(np.float32)
-    with capi.Handle(np.float32, "rbf", gamma=1.0 / F) as h:
-        h.set_option(capi.OPT_MATVEC_PATH, capi.PATH_TC)
-        h.set_data(X)
-        q = h.generate_q()
-        h.set_q(q, h.kxx_last() + 1.0)
-        a = h.matvec(d)
-        for _ in range(3):
-            assert np.array_equal(a, h.matvec(d))
+    for cache in (capi.CACHE_OFF, capi.CACHE_REQUIRED):
+        with capi.Handle(np.float32, "rbf", gamma=1.0 / F) as h:
+            h.set_option(capi.OPT_MATVEC_PATH, capi.PATH_TC)
+            h.set_option(capi.OPT_DENSE_CACHE, cache)
+            h.set_data(X)
+            q = h.generate_q()
+            h.set_q(q, h.kxx_last() + 1.0)
+            a = h.matvec(d)
+            for _ in range(3):
+                assert np.array_equal(a, h.matvec(d))
 
 
 def test_multi_gpu_row_and_tile_partition():
