@@ -31,6 +31,9 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# NCCL prints "NCCL version ..." on stdout at NCCL_DEBUG=VERSION: keep stdout to the one JSON line (INFO / TRACE are left alone)
+if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+    os.environ["NCCL_DEBUG"] = "WARN"
 
 METRIC = "cg_iterations_per_sec"
 UNIT = "iterations/s"
