@@ -368,6 +368,7 @@ def run_b200_arm(a):
             "e2e": {"value": K / (t_e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": st2.h2d_bytes / K, "d2h_bytes_per_step": st2.d2h_bytes / K,
                     "ms_total": t_e2e_ms},
             "gpu_launches": launches,
+            "collectives_per_step": (st.collectives / K) if world > 1 else 0, "peer_exchanges_per_step": (st.peer_exchanges / K) if world > 1 else 0,
             "cache_build_ms": build_ms,
             "roofline": roof,
         }

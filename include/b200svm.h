@@ -120,6 +120,7 @@ int b200svm_partition_tiles(int64_t n, int rank, int world, int64_t *first, int6
 #define B200SVM_OPT_TC_MODE 6 /* tcgen05 path, cross terms of the fp16x2 split: 0 = default (fp8 chain), 1 = three f16 MMAs, 2 = fp8 chain; set before set_data */
 #define B200SVM_OPT_SPARSE_CACHE 8 /* CSR paths, polynomial / rbf: 0 = cache S = f(X X^T) on first use if it fits (then the matvec is an HBM-bound SpMV), 1 = never (recompute on the fly), 2 = required (error if it does not fit) */
 #define B200SVM_OPT_SPARSE_CACHE_MB 9 /* memory budget of the S cache / the dense kernel-matrix cache in MiB (0 = 85 % of the free device memory) */
+#define B200SVM_OPT_PEER_EXCHANGE 11 /* multi-GPU sum of the matvec partials: 0 = stores into CUDA-IPC mapped peer buffers over NVLink, summed in rank order by the O(m) epilogue (falls back to NCCL if the peers cannot be mapped), 1 = ncclAllReduce, 2 = peer exchange required; set before comm_init */
 #define B200SVM_OPT_DENSE_CACHE 10 /* dense float polynomial / rbf (tcgen05 path): 0 = store the kernel-matrix tiles on first use if they fit (later matvecs are HBM-bound sweeps), 1 = never (recompute every matvec on the tensor cores), 2 = required */
 #define B200SVM_OPT_SPARSE_BLOCK 3 /* CSR paths: columns of the implicit matrix per block (power of two, 128..32768, default 8192; set before set_data_csr) */
 int b200svm_set_option(b200svm_handle h, int option, int64_t value);
@@ -133,6 +134,7 @@ typedef struct b200svm_stats {
     int64_t d2h_bytes;        /* device->host bytes copied                                        */
     int64_t collectives;      /* NCCL collectives enqueued                                        */
     int64_t collective_bytes; /* payload bytes of those collectives (per rank)                    */
+    int64_t peer_exchanges;   /* of those collectives: done by peer-memory stores instead of NCCL  */
     int64_t matvecs_timed;    /* matvecs whose duration is included in matvec_ms (all of them unless the event ring overflowed) */
     double cache_build_ms;        /* device time spent assembling a kernel-matrix cache (dense tiles or sparse S); also inside matvec_ms */
     int64_t dense_cache_bytes;    /* dense tcgen05 path: bytes of kernel-matrix tiles cached on this rank (0 = recomputed every matvec) */

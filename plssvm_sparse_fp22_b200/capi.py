@@ -17,7 +17,7 @@ F32, F64 = 0, 1
 KERNELS = {"linear": 0, "polynomial": 1, "rbf": 2}
 VAL_F32, VAL_F64, VAL_FP22 = 0, 1, 2
 OPT_MATVEC_PATH, OPT_SYNC_EVERY, OPT_SPARSE_BLOCK, OPT_SPARSE_GROUP, OPT_SPARSE_LANES, OPT_TC_MODE, OPT_SPARSE_THREADS = 1, 2, 3, 4, 5, 6, 7
-OPT_SPARSE_CACHE, OPT_SPARSE_CACHE_MB, OPT_DENSE_CACHE = 8, 9, 10
+OPT_SPARSE_CACHE, OPT_SPARSE_CACHE_MB, OPT_DENSE_CACHE, OPT_PEER_EXCHANGE = 8, 9, 10, 11
 CACHE_AUTO, CACHE_OFF, CACHE_REQUIRED = 0, 1, 2
 TC_F16X3, TC_FP8X = 1, 2
 PATH_AUTO, PATH_SIMT, PATH_TC = 0, 1, 2
@@ -42,6 +42,7 @@ class Stats(C.Structure):
         ("d2h_bytes", C.c_int64),
         ("collectives", C.c_int64),
         ("collective_bytes", C.c_int64),
+        ("peer_exchanges", C.c_int64),
         ("matvecs_timed", C.c_int64),
         ("cache_build_ms", C.c_double),
         ("dense_cache_bytes", C.c_int64),

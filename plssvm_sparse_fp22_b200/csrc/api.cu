@@ -224,6 +224,11 @@ int b200svm_set_option(b200svm_handle h, int option, int64_t value) {
                 sp_invalidate_cache(*c);
                 tc_invalidate_cache(*c);
                 break;
+            case B200SVM_OPT_PEER_EXCHANGE:
+                B200_REQUIRE(value >= 0 && value <= 2, "peer exchange mode must be 0 (auto), 1 (NCCL allreduce) or 2 (required)");
+                B200_REQUIRE(c->comm == nullptr, "set the peer exchange mode before b200svm_comm_init");
+                c->opt_peer_exchange = value;
+                break;
             case B200SVM_OPT_DENSE_CACHE:
                 B200_REQUIRE(value >= 0 && value <= 2, "dense cache mode must be 0 (auto), 1 (off) or 2 (required)");
                 c->opt_dense_cache = value;

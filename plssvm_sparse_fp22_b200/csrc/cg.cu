@@ -49,10 +49,21 @@ template <typename T, int MODE>
 __global__ void __launch_bounds__(VEC_THREADS) k_abar_finish(const T *__restrict__ P, int64_t ldP, int splits, const T *__restrict__ d,
                                                              int64_t m, T inv_cost, int center, const T *__restrict__ q, T qa, T add,
                                                              T *__restrict__ out, T *__restrict__ scal, T *partials, unsigned int *ticket,
-                                                             T target) {
+                                                             T target, const unsigned long long *wait_flags, unsigned long long wait_seq) {
     __shared__ T red[32];
     if constexpr (MODE == 0 || MODE == 1) {
         if (scal[S_DONE] != T(0)) { return; }  // CG has converged: this queued iteration must not touch r / delta
+    }
+    // multi-GPU peer exchange: the `splits` partial vectors are the slots the ranks pushed into this rank's buffer; wait until
+    // every source has published this exchange's sequence number (one spinning thread per source), then read past L1
+    const bool remote = wait_flags != nullptr;
+    if (remote) {
+        if (threadIdx.x < splits) {
+            const volatile unsigned long long *f = wait_flags + threadIdx.x;
+            while (*f < wait_seq) {}
+            __threadfence_system();
+        }
+        __syncthreads();
     }
     const T sum_d = center != 0 ? scal[S_SUM_D] : T(0);
     const T q_d = center == 2 ? scal[S_Q_D] : T(0);
@@ -60,7 +71,11 @@ __global__ void __launch_bounds__(VEC_THREADS) k_abar_finish(const T *__restrict
     T acc[1] = { T(0) };
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (int64_t) gridDim.x * blockDim.x) {
         T kd = T(0);
-        for (int s = 0; s < splits; ++s) { kd += P[(int64_t) s * ldP + i]; }
+        if (remote) {
+            for (int s = 0; s < splits; ++s) { kd += __ldcg(&P[(int64_t) s * ldP + i]); }  // rank order: identical on every rank
+        } else {
+            for (int s = 0; s < splits; ++s) { kd += P[(int64_t) s * ldP + i]; }
+        }
         const T di = d[i];
         if (center == 2) { kd += fma(qa - q[i], sum_d, -q_d); }
         const T val = kd + rank1 + di * inv_cost;
@@ -202,7 +217,19 @@ struct kd_result {
     int64_t ldP;
     int splits;
     int center;  // see k_abar_finish
+    xchg_view x; // multi-GPU peer exchange: where the partial vectors of all ranks arrive (base == nullptr: c.P holds the sum)
 };
+
+// sum the rank's partial vector (c.P, m reals) over the ranks: peer-memory exchange (the sum happens in k_abar_finish) or NCCL
+template <typename T>
+void reduce_over_ranks(ctx &c, int64_t m, kd_result &res) {
+    if (c.world <= 1) { return; }
+    comm_exchange(c, c.P.p, m, &res.x);
+    if (res.x.base != nullptr) {
+        res.ldP = res.x.ld;
+        res.splits = res.x.slots;
+    }
+}
 
 // K d for the reduced system (rows/cols 0..m-1) into c.P as `splits` partial vectors.
 template <typename T>
@@ -210,7 +237,7 @@ kd_result kernel_times_vector(ctx &c, const T *d) {
     const int64_t m = c.m();
     const int64_t ldP = (m + 255) / 256 * 256;
     constexpr int MAXS = 64;
-    kd_result res{ ldP, 1, 0 };
+    kd_result res{ ldP, 1, 0, xchg_view{} };
     const bool timed = c.ev_head - c.ev_tail < ctx::EV_RING;
     const int ev_slot = (int) (c.ev_head % ctx::EV_RING);
     if (timed) { B200_CUDA_CHECK(cudaEventRecord(c.ev[2 * ev_slot], c.stream)); }
@@ -219,7 +246,7 @@ kd_result kernel_times_vector(ctx &c, const T *d) {
         c.P.reserve((size_t) ldP * sizeof(T));
         sums2<T>(c, d, S_SUM_D, S_Q_D);
         sp_kernel_matvec<T>(c, d, c.P.as<T>());
-        comm_allreduce_sum(c, c.P.p, m);
+        reduce_over_ranks<T>(c, m, res);
         res.center = 2;
         c.stats.matvec_path = 4;
     } else if (c.kernel == B200SVM_LINEAR) {
@@ -244,7 +271,7 @@ kd_result kernel_times_vector(ctx &c, const T *d) {
                 c.P.reserve((size_t) ldP * sizeof(T));
                 tc_kernel_matvec(c, reinterpret_cast<const float *>(d), c.P.as<float>());  // partial over this rank's tiles
             }
-            comm_allreduce_sum(c, c.P.p, m);
+            reduce_over_ranks<T>(c, m, res);
             c.stats.matvec_path = 2;
         } else {
             // full rows [lo, hi) of the implicit matrix on this rank (all rows when world == 1)
@@ -260,8 +287,8 @@ kd_result kernel_times_vector(ctx &c, const T *d) {
                 k_fold_splits<T><<<vec_grid(m), VEC_THREADS, 0, c.stream>>>(c.P.as<T>(), ldP, res.splits, m, lo, hi);
                 count_launch(c);
                 B200_CUDA_CHECK(cudaGetLastError());
-                comm_allreduce_sum(c, c.P.p, m);
                 res.splits = 1;
+                reduce_over_ranks<T>(c, m, res);
             }
             c.stats.matvec_path = 1;
         }
@@ -277,9 +304,10 @@ kd_result kernel_times_vector(ctx &c, const T *d) {
 template <typename T, int MODE>
 void abar_finish(ctx &c, const kd_result &kd, const T *d, T add, T *out, T target = T(-1)) {
     const int64_t m = c.m();
-    k_abar_finish<T, MODE><<<vec_grid(m), VEC_THREADS, 0, c.stream>>>(c.P.as<T>(), kd.ldP, kd.splits, d, m, T(1) / (T) c.cost, kd.center,
-                                                                       c.q.as<T>(), (T) c.QA_cost, add, out, c.scal.as<T>(),
-                                                                       c.partials.as<T>(), c.counters.as<unsigned int>(), target);
+    const T *P = kd.x.base != nullptr ? static_cast<const T *>(kd.x.base) : c.P.as<T>();
+    k_abar_finish<T, MODE><<<vec_grid(m), VEC_THREADS, 0, c.stream>>>(P, kd.ldP, kd.splits, d, m, T(1) / (T) c.cost, kd.center, c.q.as<T>(),
+                                                                       (T) c.QA_cost, add, out, c.scal.as<T>(), c.partials.as<T>(),
+                                                                       c.counters.as<unsigned int>(), target, kd.x.flags, kd.x.seq);
     count_launch(c);
     B200_CUDA_CHECK(cudaGetLastError());
 }

@@ -112,6 +112,7 @@ struct ctx {
     int64_t opt_sparse_threads{ 0 };  // 0 = auto
     int64_t opt_sparse_cache{ 0 };    // 0 = auto, 1 = off, 2 = required
     int64_t opt_sparse_cache_mb{ 0 }; // 0 = 85 % of the free memory (both caches)
+    int64_t opt_peer_exchange{ 0 };   // multi-GPU: 0 = peer-memory exchange if the peers can be mapped, 1 = NCCL allreduce, 2 = required
     int64_t opt_dense_cache{ 0 };     // tcgen05 path: 0 = auto, 1 = off, 2 = required
 
     // data
@@ -206,6 +207,16 @@ template <typename T> void sp_predict(ctx &c, const T *alpha_dev, T bias, const 
 // multi-GPU (comm.cu)
 void comm_destroy(ctx &c);
 void comm_allreduce_sum(ctx &c, void *buf, int64_t count);  // in place, real type of the handle
+// result of comm_exchange: base == nullptr -> the vector was all-reduced in place (NCCL); else `slots` partial vectors of stride
+// `ld` reals start at `base` in this rank's exchange buffer and become valid once flags[0..slots) >= seq (k_abar_finish waits)
+struct xchg_view {
+    void *base{ nullptr };
+    int64_t ld{ 0 };
+    int slots{ 0 };
+    const unsigned long long *flags{ nullptr };
+    unsigned long long seq{ 0 };
+};
+void comm_exchange(ctx &c, void *P, int64_t count, xchg_view *x);
 void partition_rows(int64_t m, int rank, int world, int64_t *lo, int64_t *hi);
 
 inline void count_launch(ctx &c, int k = 1) { c.stats.kernel_launches += k; }

@@ -35,14 +35,14 @@ def main():
         return bytes(idbuf.cpu().numpy().tobytes())
 
     ok = True
-    cases = [("rbf", np.float32, capi.PATH_TC, 1500, 96), ("polynomial", np.float32, capi.PATH_TC, 1100, 70), ("rbf", np.float32, "tc_nocache", 1500, 96),
+    cases = [("rbf", np.float32, capi.PATH_TC, 1500, 96), ("polynomial", np.float32, capi.PATH_TC, 1100, 70), ("rbf", np.float32, "tc_nocache", 1500, 96), ("rbf", np.float32, "tc_nccl", 1500, 96),
              ("rbf", np.float32, capi.PATH_SIMT, 900, 64), ("rbf", np.float64, capi.PATH_AUTO, 1200, 80),
              ("polynomial", np.float64, capi.PATH_AUTO, 700, 33), ("linear", np.float64, capi.PATH_AUTO, 1000, 50)]
     cases += [("rbf", np.float64, "csr", 1300, 900), ("polynomial", np.float64, "csr", 800, 500), ("linear", np.float64, "csr", 600, 700)]
     cases += [("rbf", np.float64, "csr_otf", 1300, 900), ("polynomial", np.float32, "csr_fp22", 900, 600)]  # S on the fly; FP22-packed rows
     for kernel, dt, path, n, F in cases:
         variant = path if isinstance(path, str) else ""
-        if variant == "tc_nocache":
+        if variant in ("tc_nocache", "tc_nccl"):
             path = capi.PATH_TC
         if variant.startswith("csr"):
             path = "csr"
@@ -57,6 +57,8 @@ def main():
             if path and path != "csr":
                 h.set_option(capi.OPT_MATVEC_PATH, path)
                 h.set_option(capi.OPT_DENSE_CACHE, capi.CACHE_OFF if variant == "tc_nocache" else capi.CACHE_AUTO)
+            if variant == "tc_nccl":
+                h.set_option(capi.OPT_PEER_EXCHANGE, 1)  # ncclAllReduce instead of the peer-memory exchange
             h.comm_init(fresh_uid(), rank, world)
             if path == "csr":
                 h.set_option(capi.OPT_SPARSE_BLOCK, 256)
@@ -82,7 +84,7 @@ def main():
         ok &= good
         if rank == 0:
             print(f"[{world} ranks] {kernel:10s} {np.dtype(dt).name} {variant:8s} path={st.matvec_path} cached={st.sparse_cache_entries} iters={it}/{it_o} alpha_relerr={err:.2e} "
-                  f"identical_across_ranks={same} collectives={st.collectives} -> {'OK' if good else 'FAIL'}", flush=True)
+                  f"identical_across_ranks={same} collectives={st.collectives} peer={st.peer_exchanges} -> {'OK' if good else 'FAIL'}", flush=True)
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()
