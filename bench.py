@@ -61,6 +61,7 @@ def parse_args():
     ap.add_argument("--dense-cache", type=int, default=0,
                     help="dense tcgen05 path: 0 store the kernel-matrix tiles on first use if they fit (matvec = HBM-bound sweep), "
                          "1 recompute the Gram tiles on the tensor cores in every matvec")
+    ap.add_argument("--peer-exchange", type=int, default=0, help="multi-GPU: 0 peer-memory exchange (default), 1 ncclAllReduce")
     ap.add_argument("--skip-e2e", action="store_true", help="large sparse runs only: skip the host-buffer leg (e2e = null)")
     ap.add_argument("--cache", type=int, default=0, help="sparse: 0 cache S if it fits, 1 recompute on the fly, 2 require the cache")
     return ap.parse_args()
@@ -248,6 +249,7 @@ def run_b200_arm(a):
         else:
             h.set_option(capi.OPT_DENSE_CACHE, a.dense_cache)
     if world > 1:
+        h.set_option(capi.OPT_PEER_EXCHANGE, a.peer_exchange)
         idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
             idbuf.copy_(torch.frombuffer(bytearray(capi.comm_unique_id()), dtype=torch.uint8))
