@@ -156,32 +156,68 @@ def run_reference_arm(a):
 # GPU arm
 # ----------------------------------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
+    """SM clock and throttle reasons DURING the timed regions.  NVML in-process (a sample every ~5 ms: the default timed region is
+    only tens of milliseconds long); `nvidia-smi` (one sample per ~100 ms) if NVML cannot be initialised."""
     Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index = index
-        self.samples = []
+        self.samples = []   # (sm_mhz, sm_max_mhz, [active reason names])
         self.stop_flag = threading.Event()
+        self.source = "nvidia-smi"
+        self.nv = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            phys = index
+            if vis:
+                tok = vis.split(",")[index].strip()
+                phys = int(tok) if tok.isdigit() else None
+            self.dev = pynvml.nvmlDeviceGetHandleByIndex(phys) if phys is not None else pynvml.nvmlDeviceGetHandleByUUID(tok.encode())
+            self.masks = [(nm, getattr(pynvml, c)) for nm, c in zip(self.NAMES, ("nvmlClocksEventReasonHwSlowdown", "nvmlClocksEventReasonHwThermalSlowdown",
+                                                                                "nvmlClocksEventReasonSwThermalSlowdown", "nvmlClocksEventReasonSwPowerCap"))
+                          if hasattr(pynvml, c)]
+            if len(self.masks) != 4:
+                self.masks = [(nm, getattr(pynvml, c)) for nm, c in zip(self.NAMES, ("nvmlClocksThrottleReasonHwSlowdown", "nvmlClocksThrottleReasonHwThermalSlowdown",
+                                                                                    "nvmlClocksThrottleReasonSwThermalSlowdown", "nvmlClocksThrottleReasonSwPowerCap"))]
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self.dev, pynvml.NVML_CLOCK_SM))
+            pynvml.nvmlDeviceGetClockInfo(self.dev, pynvml.NVML_CLOCK_SM)  # probe
+            self.nv = pynvml
+            self.source = "nvml"
+        except Exception:
+            self.nv = None
 
     def run(self):
         while not self.stop_flag.is_set():
             try:
+                if self.nv is not None:
+                    sm = float(self.nv.nvmlDeviceGetClockInfo(self.dev, self.nv.NVML_CLOCK_SM))
+                    try:
+                        bits = int(self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.dev))
+                    except Exception:
+                        bits = int(self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.dev))
+                    self.samples.append((sm, self.sm_max, [nm for nm, m in self.masks if bits & m]))
+                    self.stop_flag.wait(0.005)
+                    continue
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
                                      capture_output=True, text=True, timeout=5).stdout.strip()
                 if out:
-                    self.samples.append([s.strip() for s in out.split(",")])
+                    f = [t.strip() for t in out.split(",")]
+                    if len(f) >= 7 and f[0].replace(".", "").isdigit() and f[1].replace(".", "").isdigit():
+                        self.samples.append((float(f[0]), float(f[1]), [nm for k, nm in enumerate(self.NAMES) if f[3 + k].lower().startswith("active")]))
             except Exception:
                 pass
             self.stop_flag.wait(0.1)
 
     def summary(self):
-        sm = [float(s[0]) for s in self.samples if s and s[0].replace(".", "").isdigit()]
-        mx = [float(s[1]) for s in self.samples if len(s) > 1 and s[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [nm for k, nm in enumerate(names) if any(len(s) > 3 + k and s[3 + k].lower().startswith("active") for s in self.samples)]
+        sm = [s[0] for s in self.samples]
+        mx = [s[1] for s in self.samples]
+        reasons = [nm for nm in self.NAMES if any(nm in s[2] for s in self.samples)]
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(self.samples)}
+                "samples": len(self.samples), "source": self.source}
 
 
 def measured_peaks():
