@@ -15,6 +15,8 @@
 // FP22 rows (1|8|13 = top 22 bits of binary32, packed with a 10-bit column delta) are decoded in registers.
 #include "device_utils.cuh"
 
+#include <cub/device/device_radix_sort.cuh>
+
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -92,7 +94,7 @@ __global__ void __launch_bounds__(256) k_sp_norms(csr_view A, T gamma, int rbf, 
     const int64_t p0 = A.rowptr[row], p1 = A.rowptr[row + 1];
     T s = 0;
     int colrun = 0;
-    bool bad = false;
+    unsigned int bad = 0u;
     int prev_last = -1;
     for (int64_t p = p0; p < p1; p += 32) {
         int f;
@@ -103,16 +105,17 @@ __global__ void __launch_bounds__(256) k_sp_norms(csr_view A, T gamma, int rbf, 
             // ascending and in range (FP22: the running sum of the deltas is ascending by construction; only the range can fail)
             const int before = __shfl_up_sync(0xffffffffu, f, 1);
             const int prev = lane == 0 ? prev_last : before;
-            if (valid && (f < 0 || f >= F || (!FP22 && f <= prev))) { bad = true; }
+            if (valid && (f < 0 || f >= F)) { bad |= 1u; }
+            if (valid && !FP22 && f <= prev) { bad |= 2u; }
             prev_last = __shfl_sync(0xffffffffu, f, 31);
         }
     }
     s = warp_sum(s);
     if (stats != nullptr) {
-        bad = __any_sync(0xffffffffu, bad);
+        bad = __reduce_or_sync(0xffffffffu, bad);
         if (lane == 0) {
             atomicMax(&stats[0], (unsigned long long) __double_as_longlong((double) s));
-            if (bad) { atomicOr(&stats[1], 1ull); }
+            if (bad != 0u) { atomicOr(&stats[1], (unsigned long long) bad); }  // bit 0: out of range, bit 1: not ascending
         }
     }
     if (lane == 0) {
@@ -686,6 +689,77 @@ __global__ void __launch_bounds__(1024) k_scan_add(int64_t *x, int64_t n, const 
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Transpose of the rows on the device (set_data_csr): emit (column key, row) per stored entry, stable radix sort by key (CSR
+// order is row-major, so a stable sort by column leaves the rows ascending inside a column), gather, and binary searches for
+// the column and (column, block) pointers.  Stored zeros / FP22 padding get the key F and fall off the end.
+// ---------------------------------------------------------------------------------------------------------------------
+template <typename T, bool FP22>
+__global__ void __launch_bounds__(256) k_sp_emit(csr_view A, int64_t F, uint32_t *__restrict__ key, uint32_t *__restrict__ idx,
+                                                 int32_t *__restrict__ erow, T *__restrict__ eval) {
+    const int64_t row = (int64_t) blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= A.rows) { return; }
+    const int lane = threadIdx.x & 31;
+    const int64_t p0 = A.rowptr[row], p1 = A.rowptr[row + 1];
+    int colrun = 0;
+    for (int64_t p = p0; p < p1; p += 32) {
+        int f;
+        T x;
+        if (load_entry<T, FP22>(A, p, p1, lane, colrun, f, x)) {
+            const int64_t e = p + lane;
+            key[e] = (x != T(0) && f >= 0 && f < F) ? (uint32_t) f : (uint32_t) F;
+            idx[e] = (uint32_t) e;
+            erow[e] = (int32_t) row;
+            if (eval != nullptr) { eval[e] = x; }
+        }
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_sp_gather(const uint32_t *__restrict__ sidx, const int32_t *__restrict__ erow, const T *__restrict__ eval,
+                                                   int64_t count, int W, uint16_t *__restrict__ bj, int32_t *__restrict__ srow, T *__restrict__ bval) {
+    for (int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; e < count; e += (int64_t) gridDim.x * blockDim.x) {
+        const uint32_t p = sidx[e];
+        const int32_t r = erow[p];
+        srow[e] = r;
+        bj[e] = (uint16_t) (r & (W - 1));
+        bval[e] = eval[p];
+    }
+}
+
+// colptr[f] = first sorted entry whose key is >= f, f = 0..F  (colptr[F] = number of entries kept)
+__global__ void __launch_bounds__(256) k_sp_colptr(const uint32_t *__restrict__ skey, int64_t count, int64_t F, uint32_t *__restrict__ colptr) {
+    const int64_t f = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (f > F) { return; }
+    int64_t lo = 0, hi = count;
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        if ((int64_t) skey[mid] < f) { lo = mid + 1; } else { hi = mid; }
+    }
+    colptr[f] = (uint32_t) lo;
+}
+
+// ptrT[f][b] = first entry of column f whose row is >= b W, b = 0..nb
+__global__ void __launch_bounds__(256) k_sp_block_ptr(const uint32_t *__restrict__ colptr, const int32_t *__restrict__ srow, int64_t F, int nb, int W,
+                                                      uint32_t *__restrict__ ptrT) {
+    const int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= F * (nb + 1)) { return; }
+    const int64_t f = t / (nb + 1);
+    const int b = (int) (t - f * (nb + 1));
+    int64_t lo = colptr[f], hi = colptr[f + 1];
+    const int64_t limit = (int64_t) b * W;
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        if ((int64_t) srow[mid] < limit) { lo = mid + 1; } else { hi = mid; }
+    }
+    ptrT[t] = (uint32_t) lo;
+}
+
+template <typename S, typename T>
+__global__ void __launch_bounds__(256) k_sp_convert(const S *__restrict__ src, int64_t count, T *__restrict__ dst) {
+    for (int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; e < count; e += (int64_t) gridDim.x * blockDim.x) { dst[e] = (T) src[e]; }
+}
+
 // weights of the columns: v_j = d_j u_j (rbf) or d_j, zero-extended to nbW ; also sums[0] = sum v (two-stage deterministic)
 template <typename T>
 __global__ void __launch_bounds__(256) k_sp_weights(const T *__restrict__ d, const T *__restrict__ u, int64_t m, int64_t nbW, T *__restrict__ v,
@@ -765,111 +839,21 @@ sp::csc_view view_blocks(const sparse_state &st) {
     return sp::csc_view{ st.b_ptrT.as<uint32_t>(), st.b_j.as<uint16_t>(), st.b_val.p, st.F, st.W, st.nb, st.G, st.ng };
 }
 
+#define B200_SP_DISPATCH_FP22(st, T, CALL_TRUE, CALL_FALSE) \
+    do {                                                    \
+        if ((st).fp22) {                                    \
+            if constexpr (sizeof(T) == 4) { CALL_TRUE; }    \
+        } else {                                            \
+            CALL_FALSE;                                     \
+        }                                                   \
+    } while (0)
+
 void upload(ctx &c, dbuf &dst, const void *src, size_t bytes) {
     dst.reserve(std::max<size_t>(bytes, 16));
     if (bytes != 0) {
         B200_CUDA_CHECK(cudaMemcpyAsync(dst.p, src, bytes, cudaMemcpyHostToDevice, c.stream));
         c.stats.h2d_bytes += (int64_t) bytes;
     }
-}
-
-// Host copy of the CSR input in the handle's real type (FP22: decoded values, absolute columns, padding entries dropped).
-template <typename T>
-struct host_csr {
-    std::vector<int64_t> rowptr;
-    std::vector<int32_t> col;
-    std::vector<T> val;
-    std::vector<uint32_t> bits;  // FP22: the 22-bit value pattern (already shifted: word & ~1023)
-};
-
-template <typename T>
-host_csr<T> decode_input(const int64_t *rowptr, const int32_t *colidx, const void *values, int64_t n, int64_t F, int fmt) {
-    host_csr<T> h;
-    h.rowptr.resize((size_t) n + 1);
-    const int64_t entries = rowptr[n];
-    h.col.reserve((size_t) entries);
-    h.val.reserve((size_t) entries);
-    h.rowptr[0] = 0;
-    for (int64_t i = 0; i < n; ++i) {
-        B200_REQUIRE(rowptr[i + 1] >= rowptr[i], "CSR row pointers must be non-decreasing");
-        int64_t colrun = 0;
-        int32_t prev = -1;
-        for (int64_t p = rowptr[i]; p < rowptr[i + 1]; ++p) {
-            if (fmt == B200SVM_VAL_FP22) {
-                const uint32_t w = static_cast<const uint32_t *>(values)[p];
-                colrun += (int64_t) (w & 1023u);
-                const uint32_t vb = w & 0xFFFFFC00u;
-                if ((vb & 0x7FFFFFFFu) == 0u) { continue; }  // padding entry / stored zero
-                B200_REQUIRE(colrun < F, "FP22 column delta runs past the number of features");
-                float x;
-                std::memcpy(&x, &vb, 4);
-                h.col.push_back((int32_t) colrun);
-                h.val.push_back((T) x);
-                h.bits.push_back(vb);
-            } else {
-                const int32_t cidx = colidx[p];
-                B200_REQUIRE(cidx >= 0 && cidx < F, "CSR column index out of range");
-                B200_REQUIRE(cidx > prev, "CSR column indices must be sorted and unique within a row");
-                prev = cidx;
-                const T x = fmt == B200SVM_VAL_F32 ? (T) static_cast<const float *>(values)[p] : (T) static_cast<const double *>(values)[p];
-                h.col.push_back(cidx);
-                h.val.push_back(x);
-            }
-        }
-        h.rowptr[(size_t) i + 1] = (int64_t) h.col.size();
-    }
-    return h;
-}
-
-// Transpose (CSC, rows ascending) + per-(feature, block) pointers.  FP22 storage: the values are the decoded (FP22-exact) floats.
-template <typename T>
-void build_transpose(ctx &c, sparse_state &st, const host_csr<T> &h) {
-    const int64_t n = st.n, F = st.F;
-    const int64_t nnz = (int64_t) h.col.size();
-    const int nb = st.nb, W = st.W;
-    B200_REQUIRE(nnz < (int64_t) 0xFFFF0000ll, "more than 2^32 - 2^16 stored entries are not supported by the sparse path");
-    std::vector<int64_t> colptr((size_t) F + 1, 0);
-    for (int64_t p = 0; p < nnz; ++p) { ++colptr[(size_t) h.col[(size_t) p] + 1]; }
-    double sumsq = 0;
-    for (int64_t f = 0; f < F; ++f) {
-        sumsq += (double) colptr[(size_t) f + 1] * (double) colptr[(size_t) f + 1];
-        colptr[(size_t) f + 1] += colptr[(size_t) f];
-    }
-    st.fill = n > 0 ? std::min(1.0, sumsq / ((double) n * (double) n)) : 0.0;  // products per visit / W (upper bound of the hit fraction)
-    std::vector<uint16_t> tj((size_t) nnz);
-    std::vector<T> tval((size_t) nnz);
-    std::vector<int32_t> trow((size_t) nnz);  // global row of every transposed entry (for the block pointers)
-    {
-        std::vector<int64_t> cursor(colptr.begin(), colptr.end() - 1);
-        for (int64_t j = 0; j < n; ++j) {
-            const uint32_t jl = (uint32_t) (j % W);
-            for (int64_t p = h.rowptr[(size_t) j]; p < h.rowptr[(size_t) j + 1]; ++p) {
-                const size_t e = (size_t) cursor[(size_t) h.col[(size_t) p]]++;
-                trow[e] = (int32_t) j;
-                tj[e] = (uint16_t) jl;
-                tval[e] = h.val[(size_t) p];
-            }
-        }
-    }
-    std::vector<uint32_t> ptrT((size_t) F * (size_t) (nb + 1));
-#pragma omp parallel for schedule(static)
-    for (int64_t f = 0; f < F; ++f) {
-        uint32_t *pt = ptrT.data() + (size_t) f * (size_t) (nb + 1);
-        int64_t e = colptr[(size_t) f];
-        const int64_t e1 = colptr[(size_t) f + 1];
-        for (int b = 0; b < nb; ++b) {
-            pt[b] = (uint32_t) e;
-            const int64_t limit = (int64_t) (b + 1) * W;
-            while (e < e1 && trow[(size_t) e] < limit) { ++e; }
-        }
-        pt[nb] = (uint32_t) e1;
-    }
-    st.b_entries = nnz;
-    st.avg_seg = (double) nnz / std::max(1.0, (double) F * (double) nb);
-    upload(c, st.b_j, tj.data(), tj.size() * sizeof(uint16_t));
-    upload(c, st.b_val, tval.data(), tval.size() * sizeof(T));
-    upload(c, st.b_ptrT, ptrT.data(), ptrT.size() * sizeof(uint32_t));
-    B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));  // host vectors go out of scope
 }
 
 // shared memory of one k_sp_kmv CTA: accumulator limbs | bitmap | row (value, feature, segment start / end, long list) | slot list
@@ -922,29 +906,38 @@ void set_data_typed(ctx &c, const int64_t *rowptr, const int32_t *colidx, const 
     st.c_valid = false;
     st.c_refused = false;
     c.stats.sparse_cache_entries = 0;
-    const host_csr<T> h = decode_input<T>(rowptr, colidx, values, n, F, fmt);
-    // rows: FP22 keeps the caller's packed stream (decoded in registers by the kernels); otherwise (col, val) in the handle's type
+    const int64_t entries = rowptr[n];
+    B200_REQUIRE(entries < (int64_t) 0xFFFF0000ll, "more than 2^32 - 2^16 stored entries are not supported by the sparse path");
+    st.a_max_row = 0;
+    for (int64_t i = 0; i < n; ++i) {
+        B200_REQUIRE(rowptr[i + 1] >= rowptr[i], "CSR row pointers must be non-decreasing");
+        st.a_max_row = std::max(st.a_max_row, rowptr[i + 1] - rowptr[i]);
+    }
+    // rows (A side): the caller's arrays go to the device as they are — FP22 keeps the packed stream (decoded in registers by the
+    // kernels); values of the other real type are converted on the device
+    st.a_entries = entries;
+    upload(c, st.a_rowptr, rowptr, ((size_t) n + 1) * sizeof(int64_t));
+    const int64_t cgrid = std::max<int64_t>(1, std::min<int64_t>((entries + 255) / 256, 16 * NUM_SMS));
+    dbuf raw;
     if (st.fp22) {
-        st.a_entries = rowptr[n];
-        upload(c, st.a_rowptr, rowptr, ((size_t) n + 1) * sizeof(int64_t));
-        upload(c, st.a_val, values, (size_t) st.a_entries * sizeof(uint32_t));
+        upload(c, st.a_val, values, (size_t) entries * sizeof(uint32_t));
         st.a_col.reserve(16);
     } else {
-        st.a_entries = (int64_t) h.col.size();
-        upload(c, st.a_rowptr, h.rowptr.data(), h.rowptr.size() * sizeof(int64_t));
-        upload(c, st.a_col, h.col.data(), h.col.size() * sizeof(int32_t));
-        upload(c, st.a_val, h.val.data(), h.val.size() * sizeof(T));
-    }
-    st.max_norm2 = 0;
-    for (int64_t i = 0; i < n; ++i) {
-        double nrm = 0;
-        for (int64_t p = h.rowptr[(size_t) i]; p < h.rowptr[(size_t) i + 1]; ++p) { nrm += (double) h.val[(size_t) p] * (double) h.val[(size_t) p]; }
-        st.max_norm2 = std::max(st.max_norm2, nrm);
-    }
-    st.a_max_row = 0;
-    {
-        const int64_t *rpx = st.fp22 ? rowptr : h.rowptr.data();
-        for (int64_t i = 0; i < n; ++i) { st.a_max_row = std::max(st.a_max_row, rpx[i + 1] - rpx[i]); }
+        upload(c, st.a_col, colidx, (size_t) entries * sizeof(int32_t));
+        const bool same_type = fmt == B200SVM_VAL_F32 ? sizeof(T) == 4 : sizeof(T) == 8;
+        if (same_type) {
+            upload(c, st.a_val, values, (size_t) entries * sizeof(T));
+        } else {
+            st.a_val.reserve(std::max<size_t>((size_t) entries * sizeof(T), 16));
+            if (fmt == B200SVM_VAL_F32) {
+                upload(c, raw, values, (size_t) entries * sizeof(float));
+                if (entries > 0) { sp::k_sp_convert<float, T><<<(unsigned) cgrid, 256, 0, c.stream>>>(raw.as<float>(), entries, st.a_val.as<T>()); }
+            } else {
+                upload(c, raw, values, (size_t) entries * sizeof(double));
+                if (entries > 0) { sp::k_sp_convert<double, T><<<(unsigned) cgrid, 256, 0, c.stream>>>(raw.as<double>(), entries, st.a_val.as<T>()); }
+            }
+            count_launch(c);
+        }
     }
     // block width (rows of X per accumulator pass): option or default (8192: 50 KB float / 84 KB double per CTA => 4 / 2 CTAs per SM)
     const int W = c.opt_sparse_block > 0 ? (int) c.opt_sparse_block : 8192;
@@ -952,20 +945,83 @@ void set_data_typed(ctx &c, const int64_t *rowptr, const int32_t *colidx, const 
     B200_REQUIRE(kmv_smem_bytes<T>(W, 1024) <= (size_t) 200 * 1024, "sparse block width too large for the shared memory of one SM");
     st.W = W;
     st.nb = (int) ((n + W - 1) / W);
+    // per-row norms, u = exp(-gamma |x|^2); the same pass validates the columns and finds the largest norm
+    st.norms.reserve((size_t) n * sizeof(T));
+    st.u.reserve((size_t) n * sizeof(T));
+    st.p_stats.reserve(2 * sizeof(unsigned long long));
+    B200_CUDA_CHECK(cudaMemsetAsync(st.p_stats.p, 0, 2 * sizeof(unsigned long long), c.stream));
+    const sp::csr_view A = view_rows(st, 0, n);
+    norms_and_u<T>(c, st, A, st.norms.as<T>(), st.u.as<T>(), st.p_stats.as<unsigned long long>());
+    // ---- transpose on the device
+    const size_t cap = std::max<size_t>((size_t) entries, 1);
+    dbuf key_in, key_out, idx_in, idx_out, erow, srow, eval, temp, colptr;
+    key_in.reserve(cap * 4);
+    key_out.reserve(cap * 4);
+    idx_in.reserve(cap * 4);
+    idx_out.reserve(cap * 4);
+    erow.reserve(cap * 4);
+    srow.reserve(cap * 4);
+    const T *values_T = st.a_val.as<T>();
+    if (st.fp22) {
+        eval.reserve(cap * sizeof(T));
+        values_T = eval.as<T>();
+    }
+    if (n > 0) {
+        const unsigned grid = (unsigned) ((n + 7) / 8);
+        B200_SP_DISPATCH_FP22(st, T,
+                              (sp::k_sp_emit<T, true><<<grid, 256, 0, c.stream>>>(A, F, key_in.as<uint32_t>(), idx_in.as<uint32_t>(), erow.as<int32_t>(), eval.as<T>())),
+                              (sp::k_sp_emit<T, false><<<grid, 256, 0, c.stream>>>(A, F, key_in.as<uint32_t>(), idx_in.as<uint32_t>(), erow.as<int32_t>(), nullptr)));
+        count_launch(c);
+    }
+    int key_bits = 1;
+    while ((int64_t(1) << key_bits) <= F) { ++key_bits; }
+    size_t temp_bytes = 0;
+    B200_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, key_in.as<uint32_t>(), key_out.as<uint32_t>(), idx_in.as<uint32_t>(),
+                                                    idx_out.as<uint32_t>(), (int64_t) entries, 0, key_bits, c.stream));
+    temp.reserve(std::max<size_t>(temp_bytes, 16));
+    if (entries > 0) {
+        B200_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(temp.p, temp_bytes, key_in.as<uint32_t>(), key_out.as<uint32_t>(), idx_in.as<uint32_t>(),
+                                                        idx_out.as<uint32_t>(), (int64_t) entries, 0, key_bits, c.stream));
+    }
+    colptr.reserve(((size_t) F + 1) * 4);
+    sp::k_sp_colptr<<<(unsigned) ((F + 1 + 255) / 256), 256, 0, c.stream>>>(key_out.as<uint32_t>(), entries, F, colptr.as<uint32_t>());
+    st.b_j.reserve(cap * sizeof(uint16_t));
+    st.b_val.reserve(cap * sizeof(T));
+    if (entries > 0) {
+        sp::k_sp_gather<T><<<(unsigned) cgrid, 256, 0, c.stream>>>(idx_out.as<uint32_t>(), erow.as<int32_t>(), values_T, entries, W, st.b_j.as<uint16_t>(),
+                                                                   srow.as<int32_t>(), st.b_val.as<T>());
+    }
+    const int64_t np = F * (int64_t) (st.nb + 1);
+    st.b_ptrT.reserve(std::max<size_t>((size_t) np * 4, 16));
+    sp::k_sp_block_ptr<<<(unsigned) ((np + 255) / 256), 256, 0, c.stream>>>(colptr.as<uint32_t>(), srow.as<int32_t>(), F, st.nb, W, st.b_ptrT.as<uint32_t>());
+    count_launch(c, 4);
+    B200_CUDA_CHECK(cudaGetLastError());
+    // ---- back to the host: validation flags, largest norm, column counts (for the fill estimate and the launch geometry)
+    std::vector<uint32_t> cp((size_t) F + 1);
+    unsigned long long stats_h[2] = { 0ull, 0ull };
+    B200_CUDA_CHECK(cudaMemcpyAsync(cp.data(), colptr.p, cp.size() * 4, cudaMemcpyDeviceToHost, c.stream));
+    B200_CUDA_CHECK(cudaMemcpyAsync(stats_h, st.p_stats.p, sizeof(stats_h), cudaMemcpyDeviceToHost, c.stream));
+    B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));
+    B200_REQUIRE((stats_h[1] & 1ull) == 0ull, st.fp22 ? "FP22 column delta runs past the number of features" : "CSR column index out of range");
+    B200_REQUIRE((stats_h[1] & 2ull) == 0ull, "CSR column indices must be sorted and unique within a row");
+    std::memcpy(&st.max_norm2, &stats_h[0], sizeof(double));
+    double sumsq = 0;
+    for (int64_t f = 0; f < F; ++f) {
+        const double cf = (double) (cp[(size_t) f + 1] - cp[(size_t) f]);
+        sumsq += cf * cf;
+    }
+    st.b_entries = (int64_t) cp[(size_t) F];
+    st.fill = n > 0 ? std::min(1.0, sumsq / ((double) n * (double) n)) : 0.0;  // products per visit / W (upper bound of the hit fraction)
+    st.avg_seg = (double) st.b_entries / std::max(1.0, (double) F * (double) st.nb);
     // blocks per launch group: keep the group's slice of the transpose L2-resident (~48 MB)
-    const double bytes_per_block = (double) h.col.size() / std::max(1, st.nb) * (2.0 + sizeof(T)) + 4.0 * (double) F;
+    const double bytes_per_block = (double) st.b_entries / std::max(1, st.nb) * (2.0 + sizeof(T)) + 4.0 * (double) F;
     st.G = (int) std::max(1.0, std::min((double) st.nb, 48.0e6 / std::max(1.0, bytes_per_block)));
     if (c.opt_sparse_group > 0) { st.G = (int) std::min<int64_t>(c.opt_sparse_group, st.nb); }
     st.ng = (st.nb + st.G - 1) / st.G;
-    build_transpose<T>(c, st, h);
     st.threads = sizeof(T) == 4 ? 256 : 512;
-    // per-row norms, u = exp(-gamma |x|^2), work vectors
-    st.norms.reserve((size_t) n * sizeof(T));
-    st.u.reserve((size_t) n * sizeof(T));
     st.v.reserve((size_t) st.nb * W * sizeof(T));
     st.xl.reserve((size_t) F * sizeof(T));
     st.wvec.reserve((size_t) F * sizeof(T));
-    norms_and_u<T>(c, st, view_rows(st, 0, n), st.norms.as<T>(), st.u.as<T>());
     c.n = n;
     c.F = F;
     c.ldx = F;
@@ -999,14 +1055,6 @@ void sp_set_data(ctx &c, const int64_t *rowptr, const int32_t *colidx, const voi
 
 namespace {
 
-#define B200_SP_DISPATCH_FP22(st, T, CALL_TRUE, CALL_FALSE) \
-    do {                                                    \
-        if ((st).fp22) {                                    \
-            if constexpr (sizeof(T) == 4) { CALL_TRUE; }    \
-        } else {                                            \
-            CALL_FALSE;                                     \
-        }                                                   \
-    } while (0)
 
 template <typename T>
 T pow_like_device(T b, int degree) {
