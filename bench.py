@@ -79,7 +79,9 @@ def workload_config(a):
         "workload": f"configs[1]: {a.kernel} kernel, {a.points} points x {a.features} dense features, {a.dtype}, gamma=1/F, C=1, "
                     "fixed-iteration CG (eps=0)",
         "points": a.points, "features": a.features, "kernel": a.kernel,
-        "l2": "inputs larger than L2 (X = %.0f MB > 126 MB); vectors are rewritten every step" % (a.points * a.features * (4 if a.dtype == "f32" else 8) / 1e6),
+        "l2": "inputs larger than L2: every step streams the stored kernel-matrix tiles (8.6 GB at 65536 points) or, with --dense-cache 1, "
+              "re-reads the operand planes of X (%.0f MB) for every tile; no flush needed" % (2 * a.points * a.features * (4 if a.dtype == "f32" else 8) / 1e6),
+        "dense_cache": "auto (kernel-matrix tiles stored once inside the timed region)" if a.dense_cache == 0 else "off (Gram tiles recomputed every matvec)",
     }
 
 
