@@ -377,6 +377,10 @@ def run_b200_arm(a):
                     "assembly": {"kernel": "k_gram_tc<STORE> (tcgen05 fp16x2-split, once per data set, inside the timed region)", "ms": build_ms,
                                  "alg_flops": flops, "achieved_tflops": asm_tf, "frac_of_bf16_sustained": asm_tf / peak if asm_tf else None,
                                  "frac_issued": 2.0 * asm_tf / peak if asm_tf else None}}
+            if world == 1 and (n, F, a.kernel, a.dtype) == (65536, 1024, "rbf", "f32"):
+                # dram__bytes_read.sum + dram__bytes_write.sum of one k_cached_gemv launch of this exact workload (ncu --set full capture)
+                roof["traffic"] = 8.626118e9 + 0.053501e9
+                roof["traffic_source"] = "profiles/r1_cached_gemv_ncu_full_raw.csv"
         elif not sparse and path == 2:
             # the fp16x2 split issues two pass-equivalents of fp16-rate MMA per algorithmic flop (hi.hi in fp16, both cross terms as one
             # fp8 chain of twice the K extent at twice the rate): `frac` stays on ALGORITHMIC flops, this is the tensor pipe's own view
