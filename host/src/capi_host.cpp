@@ -2,6 +2,8 @@
 // reference's own parsers compiled into oracle/_ref (oracle/ref_driver.cpp oref_parse_*).  Not needed by the executables.
 #include "plssvm/core.hpp"
 
+#include <omp.h>
+
 #include <cstring>
 #include <string>
 
@@ -80,6 +82,7 @@ int parse_model(const char *path, int *kernel, int *degree, double *gamma, doubl
 
 extern "C" {
 const char *b200host_last_error() { return g_err.c_str(); }
+void b200host_set_threads(int threads) { omp_set_num_threads(threads > 0 ? threads : 1); }  // parser team size (tests)
 int b200host_parse_data_file(int dtype, const char *path, long *n, long *F, long *nnz, int *has_labels, void *X_out, void *y_out, double *gamma_out) {
     return dtype == 0 ? parse_data<float>(path, n, F, nnz, has_labels, X_out, y_out, gamma_out) : parse_data<double>(path, n, F, nnz, has_labels, X_out, y_out, gamma_out);
 }

@@ -5,6 +5,9 @@
 // has no label.  Unlike the reference, rows are parsed straight into CSR.
 #include "plssvm/core.hpp"
 
+#include <omp.h>
+
+#include <exception>
 #include <algorithm>
 #include <cctype>
 #include <charconv>
@@ -64,9 +67,11 @@ struct text_file {
     text_file(const std::string &filename, const char comment) {
         std::ifstream in{ filename, std::ios::binary };
         if (!in) { throw file_not_found_exception{ "Couldn't find file: '" + filename + "'!" }; }
-        std::ostringstream ss;
-        ss << in.rdbuf();
-        content = ss.str();
+        in.seekg(0, std::ios::end);
+        const std::streamoff size = in.tellg();
+        in.seekg(0, std::ios::beg);
+        content.resize(size > 0 ? (std::size_t) size : 0);
+        if (size > 0) { in.read(content.data(), size); }
         std::string_view rest{ content };
         while (!rest.empty()) {
             const auto nl = rest.find('\n');
@@ -78,7 +83,47 @@ struct text_file {
     }
 };
 
+// One LIBSVM line -> (label / alpha, sorted unique non-zero entries appended to col / val).  Returns the row width (largest index + 1).
+template <typename T>
+std::size_t parse_libsvm_line(std::string_view line, T &first, bool &has_first, std::vector<std::pair<std::int32_t, T>> &row,
+                              std::vector<std::int32_t> &col, std::vector<T> &val) {
+    std::string_view::size_type pos = line.find_first_of(" \n");
+    const std::string_view::size_type first_colon = line.find_first_of(":\n");
+    if (first_colon >= pos) {
+        first = convert_to<T, invalid_file_format_exception>(line.substr(0, pos));
+    } else {
+        has_first = false;  // any unlabeled line marks the file as unlabeled (the reference sets values[0], parameter.cpp:62)
+        pos = 0;
+    }
+    row.clear();
+    std::size_t row_size = 0;
+    while (pos != std::string_view::npos) {
+        const auto colon = line.find_first_of(':', pos);
+        if (colon == std::string_view::npos) { break; }
+        const auto index = convert_to<unsigned long, invalid_file_format_exception>(line.substr(pos, colon - pos));
+        pos = colon + 1;
+        const auto next = line.find_first_of(' ', pos);
+        const T value = convert_to<T, invalid_file_format_exception>(line.substr(pos, next == std::string_view::npos ? next : next - pos));
+        if (index > (unsigned long) std::numeric_limits<std::int32_t>::max() - 1) { throw invalid_file_format_exception{ "Feature index too large!" }; }
+        row_size = std::max<std::size_t>(row_size, index + 1);
+        row.emplace_back((std::int32_t) index, value);
+        pos = next;
+    }
+    // later duplicates overwrite earlier ones (dense semantics of the reference: vline[index] = value); zeros are not stored
+    std::stable_sort(row.begin(), row.end(), [](const auto &a, const auto &b) { return a.first < b.first; });
+    for (std::size_t k = 0; k < row.size(); ++k) {
+        if (k + 1 < row.size() && row[k + 1].first == row[k].first) { continue; }
+        if (row[k].second != T{ 0 }) {
+            col.push_back(row[k].first);
+            val.push_back(row[k].second);
+        }
+    }
+    return row_size;
+}
+
 // Parses lines [start, end) of LIBSVM text into CSR; first[i] = label / alpha of line i.  Returns false if the lines carry no label.
+// The lines are parsed by an OpenMP team in contiguous chunks (the reference parses with `omp parallel for`, parameter.cpp:55-99) and
+// stitched in order; of several malformed lines the first one in file order is reported, as a sequential pass would.
 template <typename T>
 bool parse_libsvm_lines(const text_file &f, const std::size_t start, csr_matrix<T> &m, std::vector<T> &first) {
     const std::size_t n = f.lines.size() - start;
@@ -86,46 +131,56 @@ bool parse_libsvm_lines(const text_file &f, const std::size_t start, csr_matrix<
     m.rows = n;
     m.rowptr.assign(n + 1, 0);
     first.assign(n, T{ 0 });
-    bool has_first = true;
-    std::size_t max_size = 0;
-    std::vector<std::pair<std::int32_t, T>> row;
-    for (std::size_t i = 0; i < n; ++i) {
-        std::string_view line = f.lines[i + start];
-        std::string_view::size_type pos = line.find_first_of(" \n");
-        const std::string_view::size_type first_colon = line.find_first_of(":\n");
-        if (first_colon >= pos) {
-            first[i] = convert_to<T, invalid_file_format_exception>(line.substr(0, pos));
-        } else {
-            has_first = false;  // any unlabeled line marks the file as unlabeled (the reference sets values[0], parameter.cpp:62)
-            pos = 0;
-        }
-        row.clear();
-        std::size_t row_size = 0;
-        while (pos != std::string_view::npos) {
-            const auto colon = line.find_first_of(':', pos);
-            if (colon == std::string_view::npos) { break; }
-            const auto index = convert_to<unsigned long, invalid_file_format_exception>(line.substr(pos, colon - pos));
-            pos = colon + 1;
-            const auto next = line.find_first_of(' ', pos);
-            const T value = convert_to<T, invalid_file_format_exception>(line.substr(pos, next == std::string_view::npos ? next : next - pos));
-            if (index > (unsigned long) std::numeric_limits<std::int32_t>::max() - 1) { throw invalid_file_format_exception{ "Feature index too large!" }; }
-            row_size = std::max<std::size_t>(row_size, index + 1);
-            row.emplace_back((std::int32_t) index, value);
-            pos = next;
-        }
-        max_size = std::max(max_size, row_size);
-        // later duplicates overwrite earlier ones (dense semantics of the reference: vline[index] = value); zeros are not stored
-        std::stable_sort(row.begin(), row.end(), [](const auto &a, const auto &b) { return a.first < b.first; });
-        for (std::size_t k = 0; k < row.size(); ++k) {
-            if (k + 1 < row.size() && row[k + 1].first == row[k].first) { continue; }
-            if (row[k].second != T{ 0 }) {
-                m.col.push_back(row[k].first);
-                m.val.push_back(row[k].second);
+    const int teams = (int) std::max<std::size_t>(1, std::min<std::size_t>((std::size_t) omp_get_max_threads(), n / 256 + 1));
+    struct chunk {
+        std::vector<std::int32_t> col;
+        std::vector<T> val;
+        std::size_t max_size{ 0 };
+        bool has_first{ true };
+        std::exception_ptr error{};
+    };
+    std::vector<chunk> chunks((std::size_t) teams);
+#pragma omp parallel num_threads(teams)
+    {
+        const std::size_t t = (std::size_t) omp_get_thread_num();
+        const std::size_t nt = (std::size_t) omp_get_num_threads();
+        if (t < chunks.size()) {
+            // contiguous line ranges; with fewer threads than chunks a thread takes several
+            for (std::size_t ci = t; ci < chunks.size(); ci += nt) {
+                chunk &ck = chunks[ci];
+                const std::size_t lo = n * ci / chunks.size(), hi = n * (ci + 1) / chunks.size();
+                std::vector<std::pair<std::int32_t, T>> row;
+                try {
+                    for (std::size_t i = lo; i < hi; ++i) {
+                        const std::size_t before = ck.col.size();
+                        ck.max_size = std::max(ck.max_size, parse_libsvm_line<T>(f.lines[i + start], first[i], ck.has_first, row, ck.col, ck.val));
+                        m.rowptr[i + 1] = (std::int64_t) (ck.col.size() - before);  // entries of the line; turned into offsets below
+                    }
+                } catch (...) { ck.error = std::current_exception(); }
             }
         }
-        m.rowptr[i + 1] = (std::int64_t) m.col.size();
+    }
+    for (const chunk &ck : chunks) {  // file order: the first malformed line wins
+        if (ck.error) { std::rethrow_exception(ck.error); }
+    }
+    bool has_first = true;
+    std::size_t max_size = 0, total = 0;
+    std::vector<std::size_t> offset(chunks.size());
+    for (std::size_t ci = 0; ci < chunks.size(); ++ci) {
+        has_first = has_first && chunks[ci].has_first;
+        max_size = std::max(max_size, chunks[ci].max_size);
+        offset[ci] = total;
+        total += chunks[ci].col.size();
     }
     if (max_size == 0) { throw invalid_file_format_exception{ "Can't parse file: no data points are given!" }; }
+    for (std::size_t i = 0; i < n; ++i) { m.rowptr[i + 1] += m.rowptr[i]; }
+    m.col.resize(total);
+    m.val.resize(total);
+#pragma omp parallel for num_threads(teams) schedule(static, 1)
+    for (std::size_t ci = 0; ci < chunks.size(); ++ci) {
+        std::copy(chunks[ci].col.begin(), chunks[ci].col.end(), m.col.begin() + (std::ptrdiff_t) offset[ci]);
+        std::copy(chunks[ci].val.begin(), chunks[ci].val.end(), m.val.begin() + (std::ptrdiff_t) offset[ci]);
+    }
     m.cols = max_size;
     return has_first;
 }

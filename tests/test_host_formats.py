@@ -274,3 +274,39 @@ def test_cli_sparse_fp22_round_trip(host, tmp_path):
     dec_o = port.predict(Xq, a_o, rho_o, Xq, "rbf", gamma=0.05)
     safe = np.abs(dec_o) > 1e-3 * np.abs(dec_o).max()
     assert np.array_equal(labels[safe], port.sign(dec_o)[safe])
+
+
+def test_parallel_libsvm_parser_is_order_preserving(host, tmp_path):
+    """The LIBSVM parser splits the lines over an OpenMP team (like the reference, src/plssvm/parameter.cpp:55-99): the result
+    must not depend on the team size, and of several malformed lines the first one in file order is the one reported."""
+    rng = np.random.default_rng(12)
+    n, F = 3000, 60
+    X = np.where(rng.random((n, F)) < 0.2, rng.standard_normal((n, F)), 0.0)
+    X[:, -1] = rng.standard_normal(n)  # the width of the file is F
+    y = np.where(rng.random(n) < 0.5, 1.0, -1.0)
+    path = str(tmp_path / "big.libsvm")
+    datagen.write_libsvm(path, X, y)
+    results = []
+    for threads in (1, 2, 7, 64):
+        host.b200host_set_threads(threads)
+        rc, out = host_parse(host, path)
+        assert rc == 0, out
+        results.append(out)
+    X0, y0, nnz0, g0 = results[0]
+    assert np.array_equal(X0, X) and np.array_equal(y0, y) and nnz0 == int((X != 0).sum())
+    for Xk, yk, nnzk, gk in results[1:]:
+        assert np.array_equal(Xk, X0) and np.array_equal(yk, y0) and nnzk == nnz0 and gk == g0
+    # two malformed lines: line 500 (bad value) comes before line 2500 (bad index)
+    lines = open(path).read().split("\n")
+    lines[500] = "1 0:0.5 3:abc"
+    lines[2500] = "1 x:0.5"
+    bad = str(tmp_path / "bad.libsvm")
+    open(bad, "w").write("\n".join(lines))
+    msgs = set()
+    for threads in (1, 5, 64):
+        host.b200host_set_threads(threads)
+        rc, msg = host_parse(host, bad)
+        assert rc != 0
+        msgs.add(msg)
+    assert msgs == {"Can't convert 'abc' to a value of type double!"}
+    host.b200host_set_threads(os.cpu_count() or 1)
