@@ -150,6 +150,12 @@ bool parse_libsvm_lines(const text_file &f, const std::size_t start, csr_matrix<
                 chunk &ck = chunks[ci];
                 const std::size_t lo = n * ci / chunks.size(), hi = n * (ci + 1) / chunks.size();
                 std::vector<std::pair<std::int32_t, T>> row;
+                if (hi > lo) {  // one allocation per chunk: an "index:value " token is at least 4 characters long
+                    const std::string_view a = f.lines[lo + start], b = f.lines[hi - 1 + start];
+                    const std::size_t bytes = (std::size_t) ((b.data() + b.size()) - a.data());
+                    ck.col.reserve(bytes / 4);
+                    ck.val.reserve(bytes / 4);
+                }
                 try {
                     for (std::size_t i = lo; i < hi; ++i) {
                         const std::size_t before = ck.col.size();
@@ -185,7 +191,7 @@ bool parse_libsvm_lines(const text_file &f, const std::size_t start, csr_matrix<
     return has_first;
 }
 
-constexpr std::size_t dense_view_limit_bytes = std::size_t{ 1 } << 30;
+constexpr std::size_t dense_view_limit_bytes = std::size_t{ 64 } << 20;  // the vector-of-vectors view of the reference API costs more than the parse itself
 
 template <typename T>
 std::shared_ptr<const std::vector<std::vector<T>>> dense_view(const csr_matrix<T> &m) {
