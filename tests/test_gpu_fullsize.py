@@ -143,3 +143,25 @@ def test_sparse_full_size_properties(case):
     a, b = float(np.dot(d1.astype(np.float64), y2)), float(np.dot(d2.astype(np.float64), y1))
     assert abs(a - b) <= 10 * tol * max(abs(a), abs(b)), (a, b)
     assert nrm_rel(2.0 * y1.astype(np.float64) - 3.0 * y2.astype(np.float64), y3) < 10 * tol
+
+
+@pytest.mark.parametrize("problem", ["blobs", "planes"])
+def test_configs0_linear_double_against_the_reference(problem):
+    """BASELINE.json configs[0] at its exact size (5000 points x 256 dense features, double, linear, eps = 1e-3): the reference's
+    own OpenMP learn() on the host cores against b200svm_learn — identical CG iteration count, alpha and rho within 1e-10,
+    bit-identical labels on the training points."""
+    from oracle import port
+
+    n, F = 5000, 256
+    X, y = datagen.make_dense(n, F, seed=42, problem=problem, dtype=np.float64)
+    a_o, rho_o, it_o = port.learn(X, y, "linear", eps=1e-3, use_rows=True)
+    with capi.Handle(np.float64, "linear", gamma=1.0 / F) as h:
+        h.set_data(X)
+        alpha, rho, it = h.learn(y, eps=1e-3)
+        dec = h.predict(alpha, rho, X)
+    assert it == it_o
+    assert nrm_rel(a_o, alpha) < 1e-10, nrm_rel(a_o, alpha)
+    assert abs(rho - rho_o) <= 1e-10 * max(abs(rho_o), 1.0) + 1e-9 * abs(rho_o)
+    dec_o = port.predict(X, a_o, rho_o, X, "linear")
+    safe = np.abs(dec_o) > 1e-9 * np.abs(dec_o).max()
+    assert np.array_equal(np.sign(dec[safe]), np.sign(dec_o[safe]))
