@@ -292,13 +292,19 @@ struct fixp<double> {
 constexpr int SP_MAX_OWN = 4;  // stored entries of a row per thread: rows of up to 4 * blockDim.x entries
 
 // MODE 0: out[row] += sum_j S_ij v_j (S never stored)
-// MODE 1: count the touched slots of every (block, row) visit            -> cache.ptr[b * rows + (row - row_lo)]
+// MODE 1: count the touched slots of every (block, row) visit            -> cache.ptr / cache.cnt [b * rows + (row - row_lo)]
 // MODE 2: store (row_in_block, S value) of every touched slot, ascending -> cache.j / cache.val at cache.ptr[...]   
+// MODE 3: one-pass assembly: the visit reserves its (padded) entries with one atomicAdd on a cursor (capacity = an upper bound
+//         known from the column counts) and stores them at once; ptr / cnt describe where.  Which visit lands where depends on
+//         the schedule, what it stores does not: the SpMV result is unchanged.
 struct cache_view {
-    int64_t *ptr;   // [nb * rows + 1]
+    int64_t *ptr;   // [nb * rows + 1] first entry of a visit
+    int32_t *cnt;   // [nb * rows] entries of a visit (multiple of 4)
     uint16_t *j;    // [entries]
     void *val;      // T[entries]
     int64_t rows;   // rows of the implicit matrix held by this rank
+    unsigned long long *cursor;  // MODE 3: next free entry; cursor[1] != 0: capacity exceeded
+    int64_t capacity;
 };
 
 template <typename T, int KERNEL, bool FP22, bool COMPACT, int MODE>
@@ -311,6 +317,7 @@ __global__ void __launch_bounds__(1024)
     __shared__ int wtot[32];
     __shared__ T red[32];
     __shared__ int nlong_s;
+    __shared__ long long base_s;
     using FX = fixp<T>;
     const int t = threadIdx.x, TT = blockDim.x, lane = t & 31, warp = t >> 5, nwarps = TT >> 5;
     const int W = B.W, words = W >> 5;
@@ -511,11 +518,36 @@ __global__ void __launch_bounds__(1024)
                     }
                 } else {
                     const int64_t visit = (int64_t) b * cache.rows + (row - row_lo);
+                    const int cnt4 = (cnt + 3) & ~3;  // visits are padded to whole quads (vector loads)
                     if constexpr (MODE == 1) {
-                        if (t == 0) { cache.ptr[visit] = (cnt + 3) & ~3; }  // visits are padded to whole quads (vector loads)
+                        if (t == 0) {
+                            cache.ptr[visit] = cnt4;
+                            cache.cnt[visit] = cnt4;
+                        }
                         for (int i = t; i < cnt; i += TT) { (void) FX::take(acc, W, list[i], fx_inv, lb); }
                     } else {
-                        const int64_t base = cache.ptr[visit];
+                        int64_t base;
+                        if constexpr (MODE == 2) {
+                            base = cache.ptr[visit];
+                        } else {
+                            if (t == 0) {
+                                long long b64 = (long long) atomicAdd(cache.cursor, (unsigned long long) cnt4);
+                                if (b64 + cnt4 > cache.capacity) {
+                                    atomicExch(cache.cursor + 1, 1ull);
+                                    b64 = -1;
+                                }
+                                cache.ptr[visit] = b64 < 0 ? 0 : b64;
+                                cache.cnt[visit] = b64 < 0 ? 0 : cnt4;
+                                base_s = b64;
+                            }
+                            __syncthreads();
+                            base = base_s;
+                            if (base < 0) {  // block-uniform: out of capacity, the host falls back to the two-pass assembly
+                                for (int i = t; i < cnt; i += TT) { (void) FX::take(acc, W, list[i], fx_inv, lb); }
+                                __syncthreads();
+                                continue;
+                            }
+                        }
                         T *sval = static_cast<T *>(cache.val);
                         for (int i = t; i < cnt; i += TT) {
                             const int jl = list[i];
@@ -583,7 +615,7 @@ __global__ void __launch_bounds__(256) k_sp_cached_mv(cache_view S, int W, int r
     const uint16_t *__restrict__ sj = S.j;
     for (int64_t r = r0 + warp; r < r1; r += nwarps) {
         const int64_t visit = (int64_t) b * S.rows + r;
-        const int64_t q0 = S.ptr[visit] >> 2, q1 = S.ptr[visit + 1] >> 2;  // quads of entries (visits are padded to multiples of 4)
+        const int64_t q0 = S.ptr[visit] >> 2, q1 = q0 + (S.cnt[visit] >> 2);  // quads of entries (visits are padded to multiples of 4)
         T s0 = T(0), s1 = T(0), s2 = T(0), s3 = T(0);
         const uint2 *__restrict__ jq = reinterpret_cast<const uint2 *>(sj);
         auto quad = [&](const uint2 jj, const T a0, const T a1, const T a2, const T a3) {
@@ -817,7 +849,8 @@ struct sparse_state {
     // launch geometry of k_sp_kmv
     int threads{ 256 };
     // cached S of the rows [c_lo, c_hi) owned by this rank: visit-major (block, row) CSR with 16-bit row-in-block indices
-    dbuf c_ptr, c_j, c_val, c_P, c_chunks;
+    dbuf c_ptr, c_cnt, c_cursor, c_j, c_val, c_P, c_chunks;
+    double sum_cf2{ 0 };  // sum over the features of (rows containing it)^2 = Gram products of a full matvec
     bool c_valid{ false }, c_refused{ false };
     int64_t c_lo{ 0 }, c_hi{ 0 }, c_entries{ 0 };
     // predict staging
@@ -868,6 +901,7 @@ void kmv_set_smem(int smem) {
     B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, KERNEL, FP22, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, KERNEL, FP22, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, KERNEL, FP22, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, KERNEL, FP22, true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
 }
 
 template <typename T>
@@ -1011,6 +1045,7 @@ void set_data_typed(ctx &c, const int64_t *rowptr, const int32_t *colidx, const 
         sumsq += cf * cf;
     }
     st.b_entries = (int64_t) cp[(size_t) F];
+    st.sum_cf2 = sumsq;
     st.fill = n > 0 ? std::min(1.0, sumsq / ((double) n * (double) n)) : 0.0;  // products per visit / W (upper bound of the hit fraction)
     st.avg_seg = (double) st.b_entries / std::max(1.0, (double) F * (double) st.nb);
     // blocks per launch group: keep the group's slice of the transpose L2-resident (~48 MB)
@@ -1105,7 +1140,7 @@ sp::kfun make_kfun(const ctx &c, double max_norm2 = 1.0, int64_t max_row = 1024)
 }
 
 // out[row] (rows [lo, hi) of A, zero on entry) += sum_j S(G_row,j) v_j over all column groups; max_row = longest row of A
-// mode 0: on-the-fly matvec; 1 / 2: count / fill pass of the S cache (`cache` describes the destination)
+// mode 0: on-the-fly matvec; 1 / 2: count / fill pass of the S cache, 3: one-pass assembly (`cache` describes the destination)
 template <typename T, int KERNEL, bool FP22>
 void launch_kmv_variant(ctx &c, const sparse_state &st, const sp::csr_view &A, int64_t lo, int64_t hi, int64_t max_row, double max_norm2,
                         const T *v, T *out, int mode, const sp::cache_view &cache) {
@@ -1136,6 +1171,8 @@ void launch_kmv_variant(ctx &c, const sparse_state &st, const sp::csr_view &A, i
             sp::k_sp_kmv<T, KERNEL, FP22, true, 1><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache, done);
         } else if (mode == 2) {
             sp::k_sp_kmv<T, KERNEL, FP22, true, 2><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache, done);
+        } else if (mode == 3) {
+            sp::k_sp_kmv<T, KERNEL, FP22, true, 3><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache, done);
         } else if (compact) {
             sp::k_sp_kmv<T, KERNEL, FP22, true, 0><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache, done);
         } else {
@@ -1168,39 +1205,67 @@ bool build_cache(ctx &c, sparse_state &st, int64_t lo, int64_t hi) {
     st.c_valid = false;
     if (rows <= 0) { return false; }
     st.c_ptr.reserve((size_t) (visits + 1) * sizeof(int64_t));
+    st.c_cnt.reserve((size_t) visits * sizeof(int32_t));
+    st.c_cursor.reserve(2 * sizeof(unsigned long long));
     if (c.cb_pending) { sync_stream(c); }
     B200_CUDA_CHECK(cudaEventRecord(c.cb_ev[0], c.stream));
-    B200_CUDA_CHECK(cudaMemsetAsync(st.c_ptr.p, 0, (size_t) (visits + 1) * sizeof(int64_t), c.stream));
-    sp::cache_view cv{ st.c_ptr.as<int64_t>(), nullptr, nullptr, rows };
     const sp::csr_view A = view_rows(st, 0, st.n);
-    launch_kmv<T>(c, st, A, lo, hi, st.a_max_row, st.max_norm2, static_cast<const T *>(nullptr), static_cast<T *>(nullptr), 1, cv);
-    // exclusive prefix sum over the visits (+ the total in the last slot)
-    const int64_t n = visits + 1, chunks = (n + sp::SCAN_CHUNK - 1) / sp::SCAN_CHUNK;
-    st.c_chunks.reserve((size_t) chunks * sizeof(int64_t));
-    sp::k_scan_chunks<<<(unsigned) chunks, 1024, 0, c.stream>>>(st.c_ptr.as<int64_t>(), n, st.c_chunks.as<int64_t>());
-    sp::k_scan_top<<<1, 32, 0, c.stream>>>(st.c_chunks.as<int64_t>(), chunks);
-    sp::k_scan_add<<<(unsigned) chunks, 1024, 0, c.stream>>>(st.c_ptr.as<int64_t>(), n, st.c_chunks.as<int64_t>());
-    count_launch(c, 3);
-    B200_CUDA_CHECK(cudaGetLastError());
-    int64_t entries = 0;
-    B200_CUDA_CHECK(cudaMemcpyAsync(&entries, st.c_ptr.as<int64_t>() + visits, sizeof(int64_t), cudaMemcpyDeviceToHost, c.stream));
-    B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));
-    const size_t need = (size_t) entries * (sizeof(T) + 2) + (size_t) visits * sizeof(T) + (size_t) (64 << 20);
     size_t free_b = 0, total_b = 0;
     B200_CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
     free_b += st.c_j.bytes + st.c_val.bytes + st.c_P.bytes;  // buffers of a previous cache are reused
     const double budget = c.opt_sparse_cache_mb > 0 ? (double) c.opt_sparse_cache_mb * 1048576.0 : 0.85 * (double) free_b;
-    if ((double) need > budget) {
-        B200_REQUIRE(c.opt_sparse_cache != 2, "the cached kernel-matrix entries do not fit the device memory budget");
-        st.c_refused = true;
-        return false;
+    const auto bytes_for = [&](double entries) { return entries * (double) (sizeof(T) + 2) + (double) visits * sizeof(T) + (double) (64 << 20); };
+    sp::cache_view cv{ st.c_ptr.as<int64_t>(), st.c_cnt.as<int32_t>(), nullptr, nullptr, rows, st.c_cursor.as<unsigned long long>(), 0 };
+    int64_t entries = -1;
+
+    // ---- one pass: every product touches one slot, so the products of this rank's rows (estimated from the column counts,
+    //      15 % slack for the row split) plus the padding bound the entries; a visit never holds more than W
+    const char *two_pass_env = std::getenv("B200SVM_CACHE_TWO_PASS");
+    const bool allow_one_pass = !(two_pass_env != nullptr && two_pass_env[0] == '1');
+    const double bound = std::min(st.sum_cf2 * ((double) rows / (double) std::max<int64_t>(st.n, 1)) * 1.15, (double) visits * (double) st.W) + 4.0 * (double) visits + 1024.0;
+    if (allow_one_pass && bytes_for(bound) <= budget && bound < 9.0e18) {
+        const int64_t capacity = (int64_t) bound;
+        st.c_j.reserve((size_t) capacity * 2);
+        st.c_val.reserve((size_t) capacity * sizeof(T));
+        cv.j = st.c_j.as<uint16_t>();
+        cv.val = st.c_val.p;
+        cv.capacity = capacity;
+        B200_CUDA_CHECK(cudaMemsetAsync(st.c_ptr.p, 0, (size_t) (visits + 1) * sizeof(int64_t), c.stream));
+        B200_CUDA_CHECK(cudaMemsetAsync(st.c_cnt.p, 0, (size_t) visits * sizeof(int32_t), c.stream));
+        B200_CUDA_CHECK(cudaMemsetAsync(st.c_cursor.p, 0, 2 * sizeof(unsigned long long), c.stream));
+        launch_kmv<T>(c, st, A, lo, hi, st.a_max_row, st.max_norm2, static_cast<const T *>(nullptr), static_cast<T *>(nullptr), 3, cv);
+        unsigned long long cur[2] = { 0ull, 0ull };
+        B200_CUDA_CHECK(cudaMemcpyAsync(cur, st.c_cursor.p, sizeof(cur), cudaMemcpyDeviceToHost, c.stream));
+        B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));
+        if (cur[1] == 0ull) { entries = (int64_t) cur[0]; }  // else: the estimate was too small for this row range -> exact sizing below
     }
-    st.c_j.reserve(std::max<size_t>((size_t) entries * 2, 16));
-    st.c_val.reserve(std::max<size_t>((size_t) entries * sizeof(T), 16));
+
+    // ---- two passes: count, prefix sum, fill (exact allocation)
+    if (entries < 0) {
+        B200_CUDA_CHECK(cudaMemsetAsync(st.c_ptr.p, 0, (size_t) (visits + 1) * sizeof(int64_t), c.stream));
+        B200_CUDA_CHECK(cudaMemsetAsync(st.c_cnt.p, 0, (size_t) visits * sizeof(int32_t), c.stream));
+        launch_kmv<T>(c, st, A, lo, hi, st.a_max_row, st.max_norm2, static_cast<const T *>(nullptr), static_cast<T *>(nullptr), 1, cv);
+        const int64_t n = visits + 1, chunks = (n + sp::SCAN_CHUNK - 1) / sp::SCAN_CHUNK;
+        st.c_chunks.reserve((size_t) chunks * sizeof(int64_t));
+        sp::k_scan_chunks<<<(unsigned) chunks, 1024, 0, c.stream>>>(st.c_ptr.as<int64_t>(), n, st.c_chunks.as<int64_t>());
+        sp::k_scan_top<<<1, 32, 0, c.stream>>>(st.c_chunks.as<int64_t>(), chunks);
+        sp::k_scan_add<<<(unsigned) chunks, 1024, 0, c.stream>>>(st.c_ptr.as<int64_t>(), n, st.c_chunks.as<int64_t>());
+        count_launch(c, 3);
+        B200_CUDA_CHECK(cudaGetLastError());
+        B200_CUDA_CHECK(cudaMemcpyAsync(&entries, st.c_ptr.as<int64_t>() + visits, sizeof(int64_t), cudaMemcpyDeviceToHost, c.stream));
+        B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));
+        if (bytes_for((double) entries) > budget) {
+            B200_REQUIRE(c.opt_sparse_cache != 2, "the cached kernel-matrix entries do not fit the device memory budget");
+            st.c_refused = true;
+            return false;
+        }
+        st.c_j.reserve(std::max<size_t>((size_t) entries * 2, 16));
+        st.c_val.reserve(std::max<size_t>((size_t) entries * sizeof(T), 16));
+        cv.j = st.c_j.as<uint16_t>();
+        cv.val = st.c_val.p;
+        launch_kmv<T>(c, st, A, lo, hi, st.a_max_row, st.max_norm2, static_cast<const T *>(nullptr), static_cast<T *>(nullptr), 2, cv);
+    }
     st.c_P.reserve((size_t) visits * sizeof(T));
-    cv.j = st.c_j.as<uint16_t>();
-    cv.val = st.c_val.p;
-    launch_kmv<T>(c, st, A, lo, hi, st.a_max_row, st.max_norm2, static_cast<const T *>(nullptr), static_cast<T *>(nullptr), 2, cv);
     B200_CUDA_CHECK(cudaEventRecord(c.cb_ev[1], c.stream));
     c.cb_pending = true;
     st.c_lo = lo;
@@ -1215,7 +1280,7 @@ bool build_cache(ctx &c, sparse_state &st, int64_t lo, int64_t hi) {
 template <typename T>
 void cached_matvec(ctx &c, sparse_state &st, const T *v, T *out) {
     const int64_t rows = st.c_hi - st.c_lo;
-    const sp::cache_view cv{ st.c_ptr.as<int64_t>(), st.c_j.as<uint16_t>(), st.c_val.p, rows };
+    const sp::cache_view cv{ st.c_ptr.as<int64_t>(), st.c_cnt.as<int32_t>(), st.c_j.as<uint16_t>(), st.c_val.p, rows, nullptr, 0 };
     const int rows_per_cta = 512;
     static size_t attr_smem[2] = { 0, 0 };
     const size_t smem = (size_t) st.W * sizeof(T);

@@ -260,6 +260,29 @@ def test_csr_dense_columns_take_the_long_segment_path(kernel, dt):
         assert nrm_rel(want, o) < (1e-12 if dt == np.float64 else 2e-5), nrm_rel(want, o)
 
 
+@pytest.mark.parametrize("dt", [np.float64, np.float32])
+def test_csr_cache_one_pass_and_two_pass_assembly_agree(dt, monkeypatch):
+    """The S cache is normally assembled in one pass (entries reserved per visit with an atomic cursor, capacity bounded by the
+    column counts); B200SVM_CACHE_TWO_PASS=1 forces the exact count / prefix-sum / fill assembly.  Where a visit lands in memory
+    differs, what it holds does not: the matvec is bit-identical."""
+    n, F = 2500, 1500
+    rp, ci, v, _ = make(n, F, 0.02, seed=21, dt=dt)
+    d = np.random.default_rng(21).uniform(-1, 2, n - 1).astype(dt)
+    outs, entries = [], []
+    for two_pass in ("0", "1"):
+        monkeypatch.setenv("B200SVM_CACHE_TWO_PASS", two_pass)
+        with capi.Handle(dt, "rbf", gamma=1.0 / F) as h:
+            h.set_option(capi.OPT_SPARSE_BLOCK, 256)
+            h.set_option(capi.OPT_SPARSE_CACHE, capi.CACHE_REQUIRED)
+            h.set_data_csr(rp, ci, v, F)
+            q = h.generate_q()
+            h.set_q(q, h.kxx_last() + 1.0)
+            outs.append(h.matvec(d))
+            entries.append(h.stats().sparse_cache_entries)
+    assert entries[0] == entries[1] > 0
+    assert np.array_equal(outs[0], outs[1])
+
+
 def test_csr_cache_budget_falls_back_or_fails_loudly():
     n, F = 900, 600
     rp, ci, v, _ = make(n, F, 0.05, seed=9, dt=np.float32)
