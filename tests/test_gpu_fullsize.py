@@ -148,7 +148,7 @@ def test_sparse_full_size_properties(case):
 @pytest.mark.parametrize("problem", ["blobs", "planes"])
 def test_configs0_linear_double_against_the_reference(problem):
     """BASELINE.json configs[0] at its exact size (5000 points x 256 dense features, double, linear, eps = 1e-3): the reference's
-    own OpenMP learn() on the host cores against b200svm_learn — identical CG iteration count, alpha and rho within 1e-10,
+    own OpenMP learn() on the host cores against b200svm_learn — identical CG iteration count, alpha within 1e-10 (rho within its cancellation noise),
     bit-identical labels on the training points."""
     from oracle import port
 
@@ -161,7 +161,9 @@ def test_configs0_linear_double_against_the_reference(problem):
         dec = h.predict(alpha, rho, X)
     assert it == it_o
     assert nrm_rel(a_o, alpha) < 1e-10, nrm_rel(a_o, alpha)
-    assert abs(rho - rho_o) <= 1e-10 * max(abs(rho_o), 1.0) + 1e-9 * abs(rho_o)
+    # rho = y_n + QA_cost sum(alpha) - q.alpha cancels sums of ~5000 terms: the reference differs from itself by
+    # 1e-7 relative between thread counts (SURVEY.md §8c noise floor), so rho is held to 1e-6 while alpha is held to 1e-10
+    assert abs(rho - rho_o) <= 1e-6 * max(abs(rho_o), 1.0), (rho, rho_o)
     dec_o = port.predict(X, a_o, rho_o, X, "linear")
     safe = np.abs(dec_o) > 1e-9 * np.abs(dec_o).max()
     assert np.array_equal(np.sign(dec[safe]), np.sign(dec_o[safe]))
