@@ -3,6 +3,8 @@
 //   train:   -t/--kernel_type -d/--degree -g/--gamma -r/--coef0 -c/--cost -e/--epsilon -b/--backend -p/--target_platform -q/--quiet -h/--help
 //            training_set_file [model_file]
 //   predict: -b/--backend -p/--target_platform -q/--quiet -h/--help   test_file model_file [output_file]
+// cxxopts also accepts the positionals by name (--input/--model, --test/--model/--output; parameter_train.cpp:60-61,
+// parameter_predict.cpp:54-56); a named value wins over the positional slot it fills, the remaining positionals fill the free slots in order.
 // Extension of this build: --fp22 (store sparse feature values as FP22 on the device; single precision only).
 #include "plssvm/core.hpp"
 
@@ -89,6 +91,21 @@ parsed_args parse_args(int argc, char **argv, const std::vector<option_spec> &sp
     return res;
 }
 
+// Slots of the positional list: a slot given by name is taken from the option, the others consume the bare arguments in order.
+std::vector<std::string> fill_slots(const parsed_args &args, const std::vector<const char *> &names) {
+    std::vector<std::string> slots(names.size());
+    std::size_t next = 0;
+    for (std::size_t k = 0; k < names.size(); ++k) {
+        const auto it = args.values.find(names[k]);
+        if (it != args.values.end()) {
+            slots[k] = it->second;
+        } else if (next < args.positionals.size()) {
+            slots[k] = args.positionals[next++];
+        }
+    }
+    return slots;
+}
+
 template <typename V>
 V value_as(const parsed_args &args, const char *name, const V fallback, const std::string &help) {
     const auto it = args.values.find(name);
@@ -136,7 +153,7 @@ template <typename T>
 parameter_train<T>::parameter_train(int argc, char **argv) {
     const std::vector<option_spec> specs = { { 't', "kernel_type", true }, { 'd', "degree", true }, { 'g', "gamma", true }, { 'r', "coef0", true },
                                              { 'c', "cost", true }, { 'e', "epsilon", true }, { 'b', "backend", true }, { 'p', "target_platform", true },
-                                             { 0, "fp22", false }, { 'q', "quiet", false }, { 'h', "help", false } };
+                                             { 0, "fp22", false }, { 'q', "quiet", false }, { 'h', "help", false }, { 0, "input", true }, { 0, "model", true } };
     const parsed_args args = parse_args(argc, argv, specs, train_help);
     if (args.values.count("help")) {
         std::cout << train_help;
@@ -159,13 +176,14 @@ parameter_train<T>::parameter_train(int argc, char **argv) {
     this->target = value_as(args, "target_platform", this->target, train_help);
     this->storage = args.values.count("fp22") ? value_storage::fp22 : value_storage::native;
     this->print_info = args.values.count("quiet") == 0;
-    if (args.positionals.empty()) {
+    const std::vector<std::string> slots = fill_slots(args, { "input", "model" });
+    if (slots[0].empty()) {
         std::cerr << "Error missing input file!";  // parameter_train.cpp:127-131
         std::cout << train_help;
         std::exit(EXIT_FAILURE);
     }
-    this->input_filename = args.positionals[0];
-    this->model_filename = args.positionals.size() > 1 ? args.positionals[1] : this->model_name_from_input();
+    this->input_filename = slots[0];
+    this->model_filename = !slots[1].empty() ? slots[1] : this->model_name_from_input();
     this->parse_train_file(this->input_filename);
 }
 
@@ -179,7 +197,7 @@ parameter_predict<T>::parameter_predict(std::string input_filename, std::string 
 template <typename T>
 parameter_predict<T>::parameter_predict(int argc, char **argv) {
     const std::vector<option_spec> specs = { { 'b', "backend", true }, { 'p', "target_platform", true }, { 0, "fp22", false }, { 'q', "quiet", false },
-                                             { 'h', "help", false } };
+                                             { 'h', "help", false }, { 0, "test", true }, { 0, "model", true }, { 0, "output", true } };
     const parsed_args args = parse_args(argc, argv, specs, predict_help);
     if (args.values.count("help")) {
         std::cout << predict_help;
@@ -189,19 +207,20 @@ parameter_predict<T>::parameter_predict(int argc, char **argv) {
     this->target = value_as(args, "target_platform", this->target, predict_help);
     this->storage = args.values.count("fp22") ? value_storage::fp22 : value_storage::native;
     this->print_info = args.values.count("quiet") == 0;
-    if (args.positionals.empty()) {
+    const std::vector<std::string> slots = fill_slots(args, { "test", "model", "output" });
+    if (slots[0].empty()) {
         std::cerr << "Error missing test file!";  // parameter_predict.cpp:88-92
         std::cout << predict_help;
         std::exit(EXIT_FAILURE);
     }
-    if (args.positionals.size() < 2) {
+    if (slots[1].empty()) {
         std::cerr << "Error missing model file!";  // parameter_predict.cpp:96-100
         std::cout << predict_help;
         std::exit(EXIT_FAILURE);
     }
-    this->parse_model_file(args.positionals[1]);
-    this->parse_test_file(args.positionals[0]);
-    this->predict_filename = args.positionals.size() > 2 ? args.positionals[2] : this->predict_name_from_input();
+    this->parse_model_file(slots[1]);
+    this->parse_test_file(slots[0]);
+    this->predict_filename = !slots[2].empty() ? slots[2] : this->predict_name_from_input();
 }
 
 template class parameter_train<float>;

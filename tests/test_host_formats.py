@@ -211,6 +211,15 @@ def test_cli_help_and_loud_failure_without_gpu(host, tmp_path):
         assert r.returncode == 1 and "no CPU fallback" in r.stderr and "backend_exception" in r.stderr
         r = subprocess.run([os.path.join(BIN, "plssvm-train"), "-q", "-b", "openmp", p], capture_output=True, text=True)
         assert r.returncode == 1 and "No openmp backend available!" in r.stderr
+        # cxxopts takes the positionals by name as well (parameter_train.cpp:60-61): the file is parsed before the device is asked for
+        r = subprocess.run([os.path.join(BIN, "plssvm-train"), "--model", str(tmp_path / "n.model"), "--input", p], capture_output=True, text=True)
+        assert r.returncode == 1 and "no CPU fallback" in r.stderr and f"input file (data set): '{p}'" in r.stdout and "n.model'" in r.stdout
+    r = subprocess.run([os.path.join(BIN, "plssvm-predict"), "--model", "m"], capture_output=True, text=True)
+    assert r.returncode == 1 and "Error missing test file!" in r.stderr
+    r = subprocess.run([os.path.join(BIN, "plssvm-predict"), "--test=t"], capture_output=True, text=True)
+    assert r.returncode == 1 and "Error missing model file!" in r.stderr
+    r = subprocess.run([os.path.join(BIN, "plssvm-train"), "--nope"], capture_output=True, text=True)
+    assert r.returncode == 1 and "Option 'nope' does not exist" in r.stdout
 
 
 @pytest.mark.gpu
