@@ -303,7 +303,19 @@ def run_b200_arm(a):
     set_data()
     q = h.generate_q()
     QA = h.kxx_last() + 1.0
-    h.solver_cg(b, None, QA, max(W, 3), 0.0)  # warm-up steps (untimed)
+    # warm-up (untimed): solves of max(W, 3) steps, repeated until the device has been busy for ~0.3 s — the first solves of a fresh
+    # process run the same kernels up to 1.4x slower (tools/probe_sweep.py) and a 3-step solve lasts only ~13 ms.  The repeat count
+    # is taken from the first solve and agreed over the ranks (every solve contains exchanges).
+    t_warm = time.perf_counter()
+    h.solver_cg(b, None, QA, max(W, 3), 0.0)
+    reps = int(min(50, max(1, 0.3 / max(time.perf_counter() - t_warm, 1e-4))))
+    if world > 1:
+        rt = torch.tensor([reps], device="cuda", dtype=torch.int64)
+        dist.all_reduce(rt, op=dist.ReduceOp.MAX)
+        reps = int(rt[0])
+    for _ in range(reps):
+        h.solver_cg(b, None, QA, max(W, 3), 0.0)
+    warm_steps = (1 + reps) * max(W, 3)
     drop_caches()
     barrier()
     sampler = ClockSampler(local_rank)
@@ -321,8 +333,10 @@ def run_b200_arm(a):
     build_ms = float(st.cache_build_ms)
     dense_cache_bytes = int(st.dense_cache_bytes)
     # the matvec that assembles a cache is timed as a whole: take the assembly out to get the steady-state launch duration
-    matvec_ms = (st.matvec_ms - build_ms) / max(st.matvecs_timed, 1)
     n_matvecs = int(st.matvecs_timed)
+    if not sparse and dense_cache_bytes > 0 and build_ms > 0:
+        n_matvecs -= 1  # dense tiles: the STORE pass of the tcgen05 kernel also serves the matvec that triggered it (no sweep in that one)
+    matvec_ms = (st.matvec_ms - build_ms) / max(n_matvecs, 1)
     path = int(st.matvec_path)
     cache_entries = int(st.sparse_cache_entries) if sparse else 0
     if sparse and world > 1:
@@ -374,13 +388,13 @@ def run_b200_arm(a):
             roof = {"bound": "hbm", "achieved": ach, "peak": hb, "unit": "GB/s", "frac": ach / hb, "traffic": None, "peak_source": f"{peak_kind} HBM copy",
                     "kernel": "k_cached_gemv (sweep over the stored kernel-matrix tiles; k_pack / k_tc_reduce inside the timed span)",
                     "alg_bytes_per_launch": float(dense_cache_bytes), "ms_per_launch": matvec_ms, "launches_timed": n_matvecs,
-                    "assembly": {"kernel": "k_gram_tc<STORE> (tcgen05 fp16x2-split, once per data set, inside the timed region)", "ms": build_ms,
+                    "assembly": {"kernel": "k_gram_tc<STORE> (tcgen05 fp16x2-split, once per data set, inside the timed region; it also serves the first matvec)", "ms": build_ms,
                                  "alg_flops": flops, "achieved_tflops": asm_tf, "frac_of_bf16_sustained": asm_tf / peak if asm_tf else None,
                                  "frac_issued": 2.0 * asm_tf / peak if asm_tf else None}}
             if world == 1 and (n, F, a.kernel, a.dtype) == (65536, 1024, "rbf", "f32"):
                 # dram__bytes_read.sum + dram__bytes_write.sum of one k_cached_gemv launch of this exact workload (ncu --set full capture)
-                roof["traffic"] = 8.626118e9 + 0.053501e9
-                roof["traffic_source"] = "profiles/r1_cached_gemv_ncu_full_raw.csv"
+                roof["traffic"] = 8.625233e9 + 0.068885e9
+                roof["traffic_source"] = "profiles/r1_cached_gemv_v2_ncu_full_raw.csv"
         elif not sparse and path == 2:
             # the fp16x2 split issues two pass-equivalents of fp16-rate MMA per algorithmic flop (hi.hi in fp16, both cross terms as one
             # fp8 chain of twice the K extent at twice the rate): `frac` stays on ALGORITHMIC flops, this is the tensor pipe's own view
@@ -411,7 +425,7 @@ def run_b200_arm(a):
             "clocks": sampler.summary(),
             "e2e": {"value": K / (t_e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": st2.h2d_bytes / K, "d2h_bytes_per_step": st2.d2h_bytes / K,
                     "ms_total": t_e2e_ms},
-            "gpu_launches": launches,
+            "gpu_launches": launches, "warmup_steps_run": warm_steps,
             "collectives_per_step": (st.collectives / K) if world > 1 else 0, "peer_exchanges_per_step": (st.peer_exchanges / K) if world > 1 else 0,
             "cache_build_ms": build_ms,
             "roofline": roof,

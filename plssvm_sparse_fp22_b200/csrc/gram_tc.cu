@@ -73,7 +73,7 @@ struct params {
     float qa;          // QA_cost
     int degree;
     int kernel;
-    float *Kc;          // STORE mode: kernel values of every tile, [num_tiles][BM][BN]
+    float *Kc;          // STORE mode: kernel values of every tile, [num_tiles][BN / 4][BM] float4 (kc_quad_index)
     const float *done;  // CG convergence flag (scal[S_DONE]): a launch queued behind the converged iteration returns at once
 };
 
@@ -191,6 +191,10 @@ __device__ __forceinline__ float kernel_from_gram(float g, float ci, float cj, f
     }
 }
 
+// Stored kernel-matrix tile (STORE pass -> k_cached_gemv): quad-column-major, float4 index of (columns 4 cq .. 4 cq + 3, row r).
+// Both kernels put 32 consecutive rows on the 32 lanes of a warp, so every global access is 512 contiguous bytes.
+__host__ __device__ constexpr int kc_quad_index(int cq, int r) { return cq * BM + r; }
+
 // Sum v[c] over the 32 lanes of the warp for each of the 32 columns c; lane l returns the total of column l.
 // Fixed exchange pattern => bit-reproducible.
 __device__ __forceinline__ float warp_column_sums(float (&v)[32], int lane) {
@@ -210,7 +214,7 @@ __device__ __forceinline__ float warp_column_sums(float (&v)[32], int lane) {
 // FP8X: map_lo / map_b are the e4m3 planes [hi8 | lo8] (A role) and [lo8 | hi8] (B role), 128 bytes per 64-element K block;
 // otherwise map_lo is the fp16 lo plane and map_b is unused.  Every K block fills two ring slots of [A 16K | B 32K]:
 //   slot 0 = (A_hi, B_hi), slot 1 = (A_lo, B_lo) for F16X3 or (A_8, B_8) for FP8X.
-// STORE: the epilogue writes the kernel values k(x_i, x_j) of the tile to p.Kc instead of reducing them against d
+// STORE: the epilogue also writes the kernel values k(x_i, x_j) of the tile to p.Kc (the matvec that assembles the cache needs no sweep)
 template <int KERNEL, bool FP8X, bool STORE>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
     k_gram_tc(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo, const __grid_constant__ CUtensorMap map_b,
@@ -382,30 +386,16 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
                 uint32_t u[32];
                 tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * BN + g * 32), u);
                 tmem_ld_wait();
-                if constexpr (STORE) {
-                    // 32 consecutive columns of row r: one 128-byte line per thread
-                    float4 *dst = reinterpret_cast<float4 *>(p.Kc + (static_cast<int64_t>(t) * BM + r) * BN + g * 32);
-#pragma unroll
-                    for (int c4 = 0; c4 < 8; ++c4) {
-                        float kv[4];
-#pragma unroll
-                        for (int c = 0; c < 4; ++c) {
-                            const float4 cj = colbuf[buf * BN + g * 32 + c4 * 4 + c];
-                            kv[c] = kernel_from_gram<KERNEL>(__uint_as_float(u[c4 * 4 + c]), mine.x, cj.x, p.w, p.coef0, p.degree);
-                        }
-                        __stcs(dst + c4, make_float4(kv[0], kv[1], kv[2], kv[3]));
-                    }
-                    continue;
-                }
                 float v[32];
                 if (!diag_tile) {
 #pragma unroll
                     for (int cc = 0; cc < 32; ++cc) {
                         const float4 cj = colbuf[buf * BN + g * 32 + cc];
                         const float kv = kernel_from_gram<KERNEL>(__uint_as_float(u[cc]), mine.x, cj.x, p.w, p.coef0, p.degree);
+                        if constexpr (STORE) { u[cc] = __float_as_uint(kv); }
                         const float tv = kv + (ai - cj.y);
                         rowsum = fmaf(tv, cj.z, rowsum);
-                        v[cc] = tv * di;
+                        v[cc] = __fmul_rn(tv, di);  // a separate multiply in every instantiation: the STORE pass returns the recompute pass's bits
                     }
                 } else {
 #pragma unroll
@@ -413,9 +403,19 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
                         const float4 cj = colbuf[buf * BN + g * 32 + cc];
                         const int64_t gj = col0 + g * 32 + cc;
                         const float kv = kernel_from_gram<KERNEL>(__uint_as_float(u[cc]), mine.x, cj.x, p.w, p.coef0, p.degree);
+                        if constexpr (STORE) { u[cc] = __float_as_uint(kv); }   // the stored tile is complete (no triangle mask)
                         const float tv = kv + (ai - cj.y);
                         rowsum = gi >= gj ? fmaf(tv, cj.z, rowsum) : rowsum;  // lower triangle incl. diagonal -> row i
-                        v[cc] = gi > gj ? tv * di : 0.f;                        // strictly lower -> mirrored into column j
+                        v[cc] = gi > gj ? __fmul_rn(tv, di) : 0.f;                        // strictly lower -> mirrored into column j
+                    }
+                }
+                if constexpr (STORE) {
+                    // the 32 lanes of the warp hold 32 consecutive rows: every store instruction writes 512 contiguous bytes (kc_quad_index)
+                    float4 *dst = reinterpret_cast<float4 *>(p.Kc) + static_cast<int64_t>(t) * (BM * BN / 4) + kc_quad_index(g * 8, r);
+#pragma unroll
+                    for (int c4 = 0; c4 < 8; ++c4) {
+                        __stcs(dst + c4 * BM, make_float4(__uint_as_float(u[c4 * 4]), __uint_as_float(u[c4 * 4 + 1]), __uint_as_float(u[c4 * 4 + 2]),
+                                                          __uint_as_float(u[c4 * 4 + 3])));
                     }
                 }
                 const float cs = warp_column_sums(v, lane);
@@ -425,14 +425,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
             tc_fence_before();
             __syncwarp();
             if (lane == 0) { mbar_arrive(bar_tempty + buf * 8); }
-            if constexpr (!STORE) {
-                if (half == 1) { rowred[buf * BM + r] = rowsum; }
-                asm volatile("bar.sync 1, 256;" ::: "memory");  // colred / rowred complete
-                if (half == 0) { p.Pr[static_cast<int64_t>(tile.y) * p.ldP + gi] = rowsum + rowred[buf * BM + r]; }
-                {
-                    const float *c0 = colred + buf * 4 * BN;
-                    p.Pc[static_cast<int64_t>(tile.x) * p.ldP + col0 + et] = (c0[et] + c0[BN + et]) + (c0[2 * BN + et] + c0[3 * BN + et]);
-                }
+            if (half == 1) { rowred[buf * BM + r] = rowsum; }
+            asm volatile("bar.sync 1, 256;" ::: "memory");  // colred / rowred complete
+            if (half == 0) { p.Pr[static_cast<int64_t>(tile.y) * p.ldP + gi] = rowsum + rowred[buf * BM + r]; }
+            {
+                const float *c0 = colred + buf * 4 * BN;
+                p.Pc[static_cast<int64_t>(tile.x) * p.ldP + col0 + et] = (c0[et] + c0[BN + et]) + (c0[2 * BN + et] + c0[3 * BN + et]);
             }
         }
     }
@@ -448,76 +446,91 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 // ---------------------------------------------------------------------------------------------------------------------
 // Cached kernel matrix: the same partial vectors as k_gram_tc, from the stored tiles — an HBM-bound symmetric GEMV.
 //   t_ij = K_ij + QA_cost - q_i - q_j ;  Pr[J][i] = sum_j t_ij d_j (i >= j) ;  Pc[I][j] = sum_i t_ij d_i (i > j)
-// One CTA per tile (grid-strided).  Thread (ty = warp / 2, tx = thread % 64) reads float4 (row ty + 4k, columns 4 tx..4 tx + 3): a warp
-// streams 512 contiguous bytes per row.  Column sums stay in registers; the 32 row partials of a thread are reduced over the warp
-// by the fixed butterfly of warp_column_sums.  All reductions have a fixed order => bit-reproducible.
+// One CTA per tile (grid-strided), tiles in the quad-column-major layout of kc_quad_index.  Warp w owns the 32 columns
+// [32 w, 32 w + 32) (column quads 8 w .. 8 w + 7) over all 128 rows; lane l holds rows l, 32 + l, 64 + l, 96 + l, so every load
+// instruction of a warp streams 512 contiguous bytes and the warp's 16 KB are one contiguous range.  Row partials stay in four
+// registers per thread and are combined over the eight warps through shared memory; the 32 column partials of a thread are summed
+// over the lanes by the fixed butterfly of warp_column_sums (lane j ends with column 32 w + j) — ONE butterfly per warp and tile.
+// Fixed order => bit-reproducible.  (Variants that replay the exact summation order of the Gram kernel's epilogue — one butterfly
+// per row quadrant and 32-column group, with register or cp.async.bulk ring staging — were bit-identical to the recompute mode but
+// issue-bound at 1.55-1.65 ms per sweep against 1.38 ms for this one: profiles/r1_summary.md.)
 // ---------------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_cached_gemv(const float *__restrict__ Kc, const params p) {
     if (p.done != nullptr && *p.done != 0.f) { return; }
-    __shared__ float2 rowqd[BM];       // (QA_cost - q_i, d_i)
-    __shared__ float rowpart[8][32];   // per warp: totals of its 32 rows over its 128 columns
-    __shared__ float colpart[4][BN];
-    const int t = threadIdx.x, lane = t & 31, w = t >> 5, ty = w >> 1, tx = t & 63;
+    __shared__ float4 colq[BN / 4];    // q_j of the tile's columns, one float4 per column quad
+    __shared__ float4 cold[BN / 4];    // d_j
+    __shared__ float rowpart[8][BM];   // per warp: totals of the 128 rows over its 32 columns
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
     for (int tt = blockIdx.x; tt < p.num_tiles; tt += gridDim.x) {
         const int2 tile = p.tiles[tt];
         const int64_t row0 = static_cast<int64_t>(tile.x) * BM, col0 = static_cast<int64_t>(tile.y) * BN;
         const bool diag_tile = row0 < col0 + BN;
         __syncthreads();  // the previous tile's shared-memory readers are done
-        if (t < BM) {
-            const float4 v = __ldg(&p.pk[row0 + t]);
-            rowqd[t] = make_float2(p.qa - v.y, v.z);
+        {
+            const float4 v = __ldg(&p.pk[col0 + t]);
+            reinterpret_cast<float *>(colq)[t] = v.y;
+            reinterpret_cast<float *>(cold)[t] = v.z;
         }
-        float qj[4], dj[4];
+        float ai[4], di[4];  // (QA_cost - q_i, d_i) of this thread's four rows
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const float4 v = __ldg(&p.pk[col0 + 4 * tx + c]);
-            qj[c] = v.y;
-            dj[c] = v.z;
+        for (int rg = 0; rg < 4; ++rg) {
+            const float4 v = __ldg(&p.pk[row0 + rg * 32 + lane]);
+            ai[rg] = p.qa - v.y;
+            di[rg] = v.z;
         }
         __syncthreads();
-        const float4 *base = reinterpret_cast<const float4 *>(Kc + static_cast<int64_t>(tt) * (BM * BN)) + tx;
-        float rs[32];
-        float cs[4] = { 0.f, 0.f, 0.f, 0.f };
+        const float4 *base = reinterpret_cast<const float4 *>(Kc) + static_cast<int64_t>(tt) * (BM * BN / 4) + kc_quad_index(8 * w, lane);
+        float rs[4] = { 0.f, 0.f, 0.f, 0.f };
+        float cs[32];
 #pragma unroll
-        for (int k0 = 0; k0 < 32; k0 += 8) {
-            float4 kv[8];
+        for (int k0 = 0; k0 < 8; k0 += 2) {
+            float4 kv[2][4];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) { kv[k] = __ldcs(base + (ty + 4 * (k0 + k)) * (BN / 4)); }  // eight 16-byte loads in flight
+            for (int kk = 0; kk < 2; ++kk) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                const int row = ty + 4 * (k0 + k);
-                const float2 qd = rowqd[row];
-                const float e[4] = { kv[k].x, kv[k].y, kv[k].z, kv[k].w };
-                float r = 0.f;
-                if (!diag_tile) {
+                for (int rg = 0; rg < 4; ++rg) { kv[kk][rg] = __ldcs(base + (k0 + kk) * BM + rg * 32); }  // eight 16-byte loads in flight
+            }
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        const float tv = e[c] + (qd.x - qj[c]);
-                        r = fmaf(tv, dj[c], r);
-                        cs[c] = fmaf(tv, qd.y, cs[c]);
-                    }
-                } else {
-                    const int64_t gi = row0 + row;
+            for (int kk = 0; kk < 2; ++kk) {
+                const int cq = 8 * w + k0 + kk;
+                const float4 q4 = colq[cq], d4 = cold[cq];  // same address for the whole warp: broadcast
+                const float qj[4] = { q4.x, q4.y, q4.z, q4.w };
+                const float dj[4] = { d4.x, d4.y, d4.z, d4.w };
+                float ca[4] = { 0.f, 0.f, 0.f, 0.f };
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        const int64_t gj = col0 + 4 * tx + c;
-                        const float tv = e[c] + (qd.x - qj[c]);
-                        r = gi >= gj ? fmaf(tv, dj[c], r) : r;
-                        cs[c] = gi > gj ? fmaf(tv, qd.y, cs[c]) : cs[c];
+                for (int rg = 0; rg < 4; ++rg) {
+                    const float e[4] = { kv[kk][rg].x, kv[kk][rg].y, kv[kk][rg].z, kv[kk][rg].w };
+                    if (!diag_tile) {
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            const float tv = e[c] + (ai[rg] - qj[c]);
+                            rs[rg] = fmaf(tv, dj[c], rs[rg]);
+                            ca[c] = fmaf(tv, di[rg], ca[c]);
+                        }
+                    } else {
+                        const int64_t gi = row0 + rg * 32 + lane;
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            const int64_t gj = col0 + 4 * cq + c;
+                            const float tv = e[c] + (ai[rg] - qj[c]);
+                            rs[rg] = gi >= gj ? fmaf(tv, dj[c], rs[rg]) : rs[rg];  // lower triangle incl. diagonal -> row i
+                            ca[c] = gi > gj ? fmaf(tv, di[rg], ca[c]) : ca[c];     // strictly lower -> mirrored into column j
+                        }
                     }
                 }
-                rs[k0 + k] = r;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) { cs[(k0 + kk) * 4 + c] = ca[c]; }
             }
         }
-        rowpart[w][lane] = warp_column_sums(rs, lane);  // lane l: row ty + 4 l over this warp's 128 columns
+        const float ctot = warp_column_sums(cs, lane);  // lane j: column 32 w + j over the 128 rows
+        p.Pc[static_cast<int64_t>(tile.x) * p.ldP + col0 + 32 * w + lane] = ctot;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) { colpart[ty][4 * tx + c] = cs[c]; }
+        for (int rg = 0; rg < 4; ++rg) { rowpart[w][rg * 32 + lane] = rs[rg]; }
         __syncthreads();
         if (t < BM) {
-            const int g = t & 3, k = t >> 2;
-            p.Pr[static_cast<int64_t>(tile.y) * p.ldP + row0 + t] = rowpart[2 * g][k] + rowpart[2 * g + 1][k];
+            p.Pr[static_cast<int64_t>(tile.y) * p.ldP + row0 + t] =
+                ((rowpart[0][t] + rowpart[1][t]) + (rowpart[2][t] + rowpart[3][t])) + ((rowpart[4][t] + rowpart[5][t]) + (rowpart[6][t] + rowpart[7][t]));
         }
-        p.Pc[static_cast<int64_t>(tile.x) * p.ldP + col0 + t] = (colpart[0][t] + colpart[1][t]) + (colpart[2][t] + colpart[3][t]);
     }
 }
 
@@ -824,7 +837,9 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out) {
     }
     tc::k_pack<<<(unsigned) ((c.n_pad + 255) / 256), 256, 0, c.stream>>>(c.norms.as<float>(), c.q.as<float>(), d, m, c.n_pad, cscale, st.pk.as<float4>());
     // The kernel values depend only on the data: when the tiles of this rank fit in HBM they are stored once (one pass of the
-    // tcgen05 kernel in STORE mode) and every later matvec is an HBM-bound sweep over them.
+    // tcgen05 kernel in STORE mode, which also reduces against d: the assembling matvec needs no sweep) and every later matvec is
+    // an HBM-bound sweep over them.
+    bool assembled_now = false;
     if (c.opt_dense_cache != 1 && !st.kc_valid && !st.kc_refused && st.num_tiles > 0) {
         const size_t need = (size_t) st.num_tiles * tc::BM * tc::BN * sizeof(float);
         size_t free_b = 0, total_b = 0;
@@ -845,16 +860,17 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out) {
             B200_CUDA_CHECK(cudaEventRecord(c.cb_ev[1], c.stream));
             c.cb_pending = true;
             st.kc_valid = true;
+            assembled_now = true;
             c.stats.dense_cache_bytes = (int64_t) need;
         }
     }
     if (c.opt_dense_cache == 1) { st.kc_valid = false; }
-    if (st.kc_valid) {
+    if (st.kc_valid && !assembled_now) {  // (the STORE pass has already filled Pr / Pc for this d)
         const int grid = std::min(st.num_tiles, 4 * NUM_SMS);
         tc::k_cached_gemv<<<grid, 256, 0, c.stream>>>(st.Kc.as<float>(), p);
         count_launch(c);
         B200_CUDA_CHECK(cudaGetLastError());
-    } else {
+    } else if (!st.kc_valid) {
         launch_gram<false>(c, st, p);
     }
     tc::k_tc_reduce<<<(unsigned) ((m + 255) / 256), 256, 0, c.stream>>>(st.Pr.as<float>(), st.Pc.as<float>(), st.ldP, m, st.T_r, st.T_c,

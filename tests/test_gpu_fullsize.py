@@ -64,9 +64,11 @@ def test_dense_configs1_full_size_properties():
         y1_f16 = h.matvec(d1)
         h.set_option(capi.OPT_TC_MODE, capi.TC_FP8X)
         h.set_option(capi.OPT_DENSE_CACHE, capi.CACHE_REQUIRED)  # kernel values stored once (8.6 GB), matvec = sweep over them
-        y1_cached = h.matvec(d1)
+        y1_store = h.matvec(d1)  # the STORE pass of the Gram kernel serves this matvec itself
         assert h.stats().dense_cache_bytes > 8e9
+        y1_cached = h.matvec(d1)  # sweep over the stored tiles
         assert np.array_equal(y1_cached, h.matvec(d1))
+        assert np.array_equal(y1_store, y1)  # the STORE pass keeps the recompute mode's work split and order of sums
     # q against the formula
     X64 = X.astype(np.float64)
     nrm = np.einsum("ij,ij->i", X64, X64)

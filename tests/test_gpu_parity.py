@@ -176,9 +176,15 @@ def test_cg_lookahead_depth_does_not_change_the_result(kernel, dt, eps, imax):
             q = h.generate_q()
             qa = h.kxx_last() + 1.0
             results.append(h.solver_cg(b, q, qa, imax, eps))
-            # the handle is reusable afterwards (flag cleared): one more solve gives the same answer
+            # the handle is reusable afterwards (flag cleared): further solves repeat each other bit for bit.  (The very first solve on
+            # a data set may differ from them in the last bits when its first matvec assembled the dense kernel-matrix cache.)
             again = h.solver_cg(b, q, qa, imax, eps)
-            assert again[1] == results[-1][1] and np.array_equal(again[0], results[-1][0])
+            third = h.solver_cg(b, q, qa, imax, eps)
+            assert again[1] == third[1] and np.array_equal(again[0], third[0])
+            if h.stats().dense_cache_bytes == 0:
+                assert again[1] == results[-1][1] and np.array_equal(again[0], results[-1][0])
+            elif eps >= 1e-3 and again[1] == results[-1][1]:  # (runs pushed past convergence drift apart by rounding order)
+                assert nrm_rel(results[-1][0], again[0]) < 1e-2
             st = h.stats()
             assert st.matvecs_timed == st.matvecs
     a0, it0, d0 = results[0]
@@ -277,19 +283,29 @@ def test_tcgen05_path_vs_simt_and_oracle(kernel, shape, mode, cache):
 
 
 def test_tcgen05_path_is_deterministic():
+    """Bit-reproducible for a given call sequence.  With the kernel-matrix cache the first matvec after set_data is served by the
+    assembling (STORE) pass of the Gram kernel — bit for bit the recompute mode's answer — and the later ones by sweeps over the
+    stored tiles: same kernel values, another fixed order of the sums."""
     n, F = 1500, 96
     X, _ = datagen.make_dense(n, F, seed=3, dtype=np.float32)
     d = np.random.default_rng(2).standard_normal(n - 1).astype(np.float32)
-    for cache in (capi.CACHE_OFF, capi.CACHE_REQUIRED):
-        with capi.Handle(np.float32, "rbf", gamma=1.0 / F) as h:
-            h.set_option(capi.OPT_MATVEC_PATH, capi.PATH_TC)
-            h.set_option(capi.OPT_DENSE_CACHE, cache)
-            h.set_data(X)
-            q = h.generate_q()
-            h.set_q(q, h.kxx_last() + 1.0)
-            a = h.matvec(d)
-            for _ in range(3):
-                assert np.array_equal(a, h.matvec(d))
+    for kernel in ("rbf", "polynomial"):
+        first, later = {}, {}
+        for cache in (capi.CACHE_OFF, capi.CACHE_REQUIRED):
+            with capi.Handle(np.float32, kernel, gamma=1.0 / F, coef0=0.25) as h:
+                h.set_option(capi.OPT_MATVEC_PATH, capi.PATH_TC)
+                h.set_option(capi.OPT_DENSE_CACHE, cache)
+                h.set_data(X)
+                q = h.generate_q()
+                h.set_q(q, h.kxx_last() + 1.0)
+                first[cache] = h.matvec(d)
+                later[cache] = h.matvec(d)
+                for _ in range(3):
+                    assert np.array_equal(later[cache], h.matvec(d))
+                assert (h.stats().dense_cache_bytes > 0) == (cache == capi.CACHE_REQUIRED)
+        assert np.array_equal(first[capi.CACHE_OFF], later[capi.CACHE_OFF])
+        assert np.array_equal(first[capi.CACHE_REQUIRED], first[capi.CACHE_OFF])
+        assert nrm_rel(later[capi.CACHE_OFF], later[capi.CACHE_REQUIRED]) < 1e-5
 
 
 def test_multi_gpu_row_and_tile_partition():
