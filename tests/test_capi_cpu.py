@@ -88,3 +88,50 @@ def test_bench_reference_arm_contract(tmp_path):
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     r1 = subprocess.run(cmd, capture_output=True, text=True, env=dict(env, RANK="1", WORLD_SIZE="2"), timeout=60)
     assert r1.returncode == 0 and r1.stdout.strip() == ""
+
+
+def _cuobjdump(*args):
+    import shutil
+    import subprocess
+    exe = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(exe):
+        pytest.skip("cuobjdump not available")
+    from plssvm_sparse_fp22_b200 import build
+    return subprocess.run([exe, *args, build.LIB], capture_output=True, text=True, check=True).stdout
+
+
+def test_hot_kernels_have_no_spills_and_keep_their_register_budgets():
+    """Build-quality gate that needs no GPU: resource usage of the sm_100a code in libb200svm.so.  The hot kernels must not use a
+    local-memory stack (spills), and must stay inside the register budget their occupancy was designed for."""
+    import re
+    out = _cuobjdump("-res-usage")
+    usage = {}
+    for name, reg, stack in re.findall(r"Function (\S+):\s*\n\s*REG:(\d+) STACK:(\d+)", out):
+        usage[name] = (int(reg), int(stack))
+    assert usage, out[:500]
+    budgets = {  # substring of the mangled name -> registers per thread allowed
+        "9k_gram_tc": 204,        # 320 threads, one CTA per SM: 65536 / 320
+        "13k_cached_gemv": 128,   # 256 threads, two CTAs per SM
+        "14k_sp_cached_mv": 128,
+        "10k_kmv_tile": 255,
+        "8k_sp_kmv": 255,
+    }
+    seen = {k: 0 for k in budgets}
+    for name, (reg, stack) in usage.items():
+        for key, cap in budgets.items():
+            if key in name:
+                seen[key] += 1
+                assert reg <= cap, (name, reg, cap)
+                if key != "8k_sp_kmv":
+                    assert stack == 0, (name, stack)
+    assert all(v > 0 for v in seen.values()), seen
+
+
+def test_tensor_core_kernel_is_tcgen05_and_tma():
+    """The dense Gram kernel must be the tcgen05 / TMA / TMEM program DESIGN.md §3.1 describes (SASS mnemonics from B200_PROFILING.md),
+    and the sweep over the cached tiles must use 128-bit streaming loads."""
+    sass = _cuobjdump("-sass", "-fun", "_ZN4b2002tc9k_gram_tcILi2ELb1ELb1EEEv14CUtensorMap_stS2_S2_NS0_6paramsE")
+    for mnemonic in ("UTCHMMA", "UTCQMMA", "UTMALDG", "LDTM", "SYNCS", "STG.E.EF.128"):
+        assert mnemonic in sass, mnemonic
+    sweep = _cuobjdump("-sass", "-fun", "_ZN4b2002tc13k_cached_gemvEPKfNS0_6paramsE")
+    assert sweep.count("LDG.E.EF.128") == 32 and "SHFL.BFLY" in sweep
