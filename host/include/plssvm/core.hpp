@@ -202,6 +202,12 @@ namespace detail {
 /// text of a floating point value as fmt's "{}" prints it (shortest round-trip digits; exponent form below 1e-4 / from 1e16)
 std::string format_shortest(double v);
 std::string format_shortest(float v);
+/// LIBSVM model text (src/plssvm/csvm.cpp:60-204): header, then "{alpha} {index}:{value:e} ..." per support vector, zeros skipped, all rows of
+/// class +1 before those of class -1.  Exactly one of `sparse` / `dense` is used (`sparse` when not null).
+template <typename T>
+void write_model_file(const std::string &model_name, kernel_type kernel, int degree, T gamma, T coef0, T rho, const std::vector<T> &labels,
+                      const std::vector<T> &alphas, const csr_matrix<T> *sparse, const std::vector<std::vector<T>> *dense, std::size_t num_features,
+                      bool print_info);
 /// FP22: binary32 rounded to nearest-even at 13 mantissa bits
 std::uint32_t fp22_encode(float x);
 float fp22_decode(std::uint32_t v22);

@@ -78,6 +78,22 @@ int parse_model(const char *path, int *kernel, int *degree, double *gamma, doubl
         if (y_out != nullptr && p.value_ptr != nullptr) { std::memcpy(y_out, p.value_ptr->data(), p.value_ptr->size() * sizeof(T)); }
     });
 }
+
+// test hook: the model text writer on host data (dense rows, or the same rows as CSR when `as_csr`), no device involved
+template <typename T>
+int write_model(const int kernel, const int degree, const double gamma, const double coef0, const void *X, const void *y, const void *alpha, const long n,
+                const long F, const double rho, const char *path, const int as_csr) {
+    return guarded<T>([&]() {
+        const T *Xp = static_cast<const T *>(X);
+        std::vector<std::vector<T>> rows((std::size_t) n);
+        for (long i = 0; i < n; ++i) { rows[(std::size_t) i].assign(Xp + i * F, Xp + (i + 1) * F); }
+        const std::vector<T> labels(static_cast<const T *>(y), static_cast<const T *>(y) + n);
+        const std::vector<T> alphas(static_cast<const T *>(alpha), static_cast<const T *>(alpha) + n);
+        const plssvm::csr_matrix<T> csr = plssvm::csr_matrix<T>::from_dense(rows);
+        plssvm::detail::write_model_file<T>(path, static_cast<plssvm::kernel_type>(kernel), degree, (T) gamma, (T) coef0, (T) rho, labels, alphas,
+                                            as_csr != 0 ? &csr : nullptr, &rows, (std::size_t) F, false);
+    });
+}
 }  // namespace
 
 extern "C" {
@@ -96,6 +112,11 @@ int b200host_format_shortest(int dtype, double v, char *out, int cap) {
     if ((int) s.size() + 1 > cap) { return 1; }
     std::memcpy(out, s.c_str(), s.size() + 1);
     return 0;
+}
+int b200host_write_model(int dtype, int kernel, int degree, double gamma, double coef0, const void *X, const void *y, const void *alpha, long n, long F,
+                         double rho, const char *path, int as_csr) {
+    return dtype == 0 ? write_model<float>(kernel, degree, gamma, coef0, X, y, alpha, n, F, rho, path, as_csr)
+                      : write_model<double>(kernel, degree, gamma, coef0, X, y, alpha, n, F, rho, path, as_csr);
 }
 unsigned b200host_fp22_encode(float x) { return plssvm::detail::fp22_encode(x); }
 }  // extern "C"

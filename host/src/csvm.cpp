@@ -6,7 +6,10 @@
 
 #include "b200svm.h"
 
+#include <omp.h>
+
 #include <algorithm>
+#include <charconv>
 #include <chrono>
 #include <cstdio>
 #include <fstream>
@@ -285,56 +288,99 @@ void csvm<T>::write_model(const std::string &model_name) {
         throw exception{ "Number of labels (" + std::to_string(value_ptr_->size()) + ") must match the number of data points (" +
                          std::to_string(num_data_points_) + ")!" };  // src/plssvm/csvm.cpp:69-71
     }
+    detail::write_model_file<T>(model_name, kernel_, degree_, gamma_, coef0_, static_cast<T>(-bias_), *value_ptr_, *alpha_ptr_, sparse_ptr_.get(),
+                                data_ptr_.get(), num_features_, print_info_);
+}
+
+namespace detail {
+
+// The text of a LIBSVM model file as src/plssvm/csvm.cpp:60-204 writes it.
+template <typename T>
+void write_model_file(const std::string &model_name, const kernel_type kernel, const int degree, const T gamma, const T coef0, const T rho,
+                      const std::vector<T> &labels, const std::vector<T> &alphas, const csr_matrix<T> *sparse,
+                      const std::vector<std::vector<T>> *dense, const std::size_t num_features, const bool print_info) {
     unsigned long long count_pos = 0, count_neg = 0;
-    for (const T v : *value_ptr_) {
+    for (const T v : labels) {
         count_pos += v > 0;
         count_neg += v < 0;
     }
     std::ostringstream header;
-    header << "svm_type c_svc\nkernel_type " << kernel_ << "\n";
-    switch (kernel_) {
+    header << "svm_type c_svc\nkernel_type " << kernel << "\n";
+    switch (kernel) {
         case kernel_type::linear: break;
         case kernel_type::polynomial:
-            header << "degree " << degree_ << "\ngamma " << detail::format_shortest(gamma_) << "\ncoef0 " << detail::format_shortest(coef0_) << "\n";
+            header << "degree " << degree << "\ngamma " << detail::format_shortest(gamma) << "\ncoef0 " << detail::format_shortest(coef0) << "\n";
             break;
-        case kernel_type::rbf: header << "gamma " << detail::format_shortest(gamma_) << "\n"; break;
+        case kernel_type::rbf: header << "gamma " << detail::format_shortest(gamma) << "\n"; break;
     }
-    header << "nr_class 2\ntotal_sv " << count_pos + count_neg << "\nrho " << detail::format_shortest(static_cast<T>(-bias_)) << "\nlabel 1 -1\nnr_sv " << count_pos
+    header << "nr_class 2\ntotal_sv " << count_pos + count_neg << "\nrho " << detail::format_shortest(rho) << "\nlabel 1 -1\nnr_sv " << count_pos
            << " " << count_neg << "\nSV\n";
-    if (print_info_) { std::cout << "\nOptimization finished\n" << header.str() << "\n"; }
+    if (print_info) { std::cout << "\nOptimization finished\n" << header.str() << "\n"; }
     std::FILE *out = std::fopen(model_name.c_str(), "wb");
     if (out == nullptr) { throw exception{ "Can't open model file '" + model_name + "' for writing!" }; }
     std::fputs(header.str().c_str(), out);
-    std::string line;
-    char buf[64];
-    const auto write_class = [&](const bool positive) {
-        for (std::size_t i = 0; i < num_data_points_; ++i) {
-            const T y = (*value_ptr_)[i];
-            if (positive ? !(y > 0) : !(y < 0)) { continue; }
-            line = detail::format_shortest((*alpha_ptr_)[i]);
-            line.push_back(' ');
-            const auto emit = [&](const std::size_t f, const T v) {
-                if (v != T{ 0 }) {
-                    std::snprintf(buf, sizeof(buf), "%zu:%e ", f, (double) v);
-                    line += buf;
-                }
-            };
-            if (sparse_ptr_ != nullptr) {
-                for (std::int64_t p = sparse_ptr_->rowptr[i]; p < sparse_ptr_->rowptr[i + 1]; ++p) {
-                    emit((std::size_t) sparse_ptr_->col[(std::size_t) p], sparse_ptr_->val[(std::size_t) p]);
-                }
-            } else {
-                for (std::size_t f = 0; f < num_features_; ++f) { emit(f, (*data_ptr_)[i][f]); }
-            }
-            line.push_back('\n');
-            std::fputs(line.c_str(), out);
+    // All support vectors of class 1 first (src/plssvm/csvm.cpp:160-172), then class -1 (:175-195), in file order inside a class.
+    // Batches of rows are formatted by an OpenMP team in contiguous chunks and written in chunk order (the reference formats inside
+    // `omp parallel` as well); "{index}:{value:e} " is produced with std::to_chars(scientific, 6), which prints what "%e" prints.
+    std::vector<std::size_t> order;
+    order.reserve(labels.size());
+    for (const bool positive : { true, false }) {
+        for (std::size_t i = 0; i < labels.size(); ++i) {
+            const T y = labels[i];
+            if (positive ? y > 0 : y < 0) { order.push_back(i); }
         }
+    }
+    const auto format_row = [&](const std::size_t i, std::string &dst) {
+        char buf[64];
+        dst += detail::format_shortest(alphas[i]);
+        dst.push_back(' ');
+        const auto emit = [&](const std::size_t f, const T v) {
+            if (v != T{ 0 }) {
+                char *p = std::to_chars(buf, buf + sizeof(buf), f).ptr;
+                *p++ = ':';
+                p = std::to_chars(p, buf + sizeof(buf) - 1, (double) v, std::chars_format::scientific, 6).ptr;
+                *p++ = ' ';
+                dst.append(buf, p);
+            }
+        };
+        if (sparse != nullptr) {
+            for (std::int64_t p = sparse->rowptr[i]; p < sparse->rowptr[i + 1]; ++p) {
+                emit((std::size_t) sparse->col[(std::size_t) p], sparse->val[(std::size_t) p]);
+            }
+        } else {
+            for (std::size_t f = 0; f < num_features; ++f) { emit(f, (*dense)[i][f]); }
+        }
+        dst.push_back('\n');
     };
-    write_class(true);   // all support vectors of class 1 first (src/plssvm/csvm.cpp:160-172) ...
-    write_class(false);  // ... then class -1 (:175-195)
+    constexpr std::size_t batch = std::size_t{ 1 } << 15;
+    std::vector<std::string> parts;
+    for (std::size_t b0 = 0; b0 < order.size(); b0 += batch) {
+        const std::size_t nb = std::min(batch, order.size() - b0);
+        const int teams = (int) std::max<std::size_t>(1, std::min<std::size_t>((std::size_t) omp_get_max_threads(), nb / 64 + 1));
+        parts.assign((std::size_t) teams, std::string{});
+#pragma omp parallel num_threads(teams)
+        {
+            const std::size_t t = (std::size_t) omp_get_thread_num(), nt = (std::size_t) omp_get_num_threads();
+            std::string &dst = parts[t];
+            for (std::size_t k = b0 + nb * t / nt; k < b0 + nb * (t + 1) / nt; ++k) { format_row(order[k], dst); }
+        }
+        for (const std::string &part : parts) {
+            if (!part.empty() && std::fwrite(part.data(), 1, part.size(), out) != part.size()) {
+                std::fclose(out);
+                throw exception{ "Can't write to model file '" + model_name + "'!" };
+            }
+        }
+    }
     std::fclose(out);
-    if (print_info_) { std::cout << "Wrote model file ('" << model_name << "') with " << count_pos + count_neg << " support vectors.\n"; }
+    if (print_info) { std::cout << "Wrote model file ('" << model_name << "') with " << count_pos + count_neg << " support vectors.\n"; }
 }
+
+template void write_model_file<float>(const std::string &, kernel_type, int, float, float, float, const std::vector<float> &, const std::vector<float> &,
+                                      const csr_matrix<float> *, const std::vector<std::vector<float>> *, std::size_t, bool);
+template void write_model_file<double>(const std::string &, kernel_type, int, double, double, double, const std::vector<double> &,
+                                       const std::vector<double> &, const csr_matrix<double> *, const std::vector<std::vector<double>> *, std::size_t, bool);
+
+}  // namespace detail
 
 template <typename T>
 std::unique_ptr<csvm<T>> make_csvm(const parameter<T> &params) {

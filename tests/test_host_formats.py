@@ -319,3 +319,44 @@ def test_parallel_libsvm_parser_is_order_preserving(host, tmp_path):
         msgs.add(msg)
     assert msgs == {"Can't convert 'abc' to a value of type double!"}
     host.b200host_set_threads(os.cpu_count() or 1)
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("dt", [np.float64, np.float32])
+@pytest.mark.parametrize("kernel", ["linear", "polynomial", "rbf"])
+def test_model_writer_matches_reference_text(host, tmp_path, kernel, dt):
+    """The model text of the host writer (rows formatted by an OpenMP team, std::to_chars) against the reference's own write_model
+    (src/plssvm/csvm.cpp:60-204, run with one thread so that its order inside a class is the file order): byte-identical for dense
+    and CSR storage, any team size, sizes that span several batches of the writer, values that print with 2- and 3-digit exponents."""
+    rng = np.random.default_rng(11)
+    for n, F in ((7, 5), (300, 40), (70001, 3)):
+        X = rng.uniform(-1, 1, (n, F))
+        X[rng.random((n, F)) < 0.4] = 0.0
+        X[0, 0], X[1, F - 1] = 1.5e-30, -7.25e+33  # exponent widths
+        if dt == np.float64:
+            X[2, 1] = 3.0e-200
+        X = X.astype(dt)
+        y = np.where(rng.random(n) < 0.5, 1.0, -1.0).astype(dt)
+        y[:2] = (1.0, -1.0)
+        alpha = rng.standard_normal(n).astype(dt)
+        rho, gamma, coef0, degree = -0.3712, 0.02, 0.5, 2
+        code = 1 if dt == np.float64 else 0
+        L = ref.lib()
+        L.oref_write_model.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_long, C.c_long, C.c_double, C.c_char_p]
+        host.b200host_write_model.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_long, C.c_long, C.c_double,
+                                              C.c_char_p, C.c_int]
+        ref.set_num_threads(1)
+        want_path = str(tmp_path / "ref.model")
+        assert L.oref_write_model(code, port.KERNELS[kernel], degree, gamma, coef0, X.ctypes.data, y.ctypes.data, alpha.ctypes.data, n, F, rho, want_path.encode()) == 0
+        want = open(want_path, "rb").read()
+        try:
+            for threads in (1, 3, os.cpu_count() or 1):
+                host.b200host_set_threads(threads)
+                for as_csr in (0, 1):
+                    got_path = str(tmp_path / f"host_{threads}_{as_csr}.model")
+                    rc = host.b200host_write_model(code, port.KERNELS[kernel], degree, gamma, coef0, X.ctypes.data, y.ctypes.data, alpha.ctypes.data, n, F, rho,
+                                                   got_path.encode(), as_csr)
+                    assert rc == 0, host.b200host_last_error()
+                    assert open(got_path, "rb").read() == want, (n, F, threads, as_csr)
+        finally:
+            host.b200host_set_threads(os.cpu_count() or 1)
