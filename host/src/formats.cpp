@@ -376,15 +376,16 @@ void parameter<T>::parse_arff_file(const std::string &filename, const bool test)
     m->cols = num_features;
     m->rowptr.assign(n + 1, 0);
     std::vector<T> labels(n, T{ 0 });
-    std::vector<T> dense_row(num_features);
-    for (std::size_t i = 0; i < n; ++i) {
+    // One data line -> its non-zero (index, value) entries in ascending index order (what the reference's dense row holds,
+    // parameter.cpp:238-330: a later entry of a sparse line overwrites an earlier one with the same index), appended to col / val.
+    const auto parse_line = [&](const std::size_t i, std::vector<std::pair<std::int32_t, T>> &row, std::vector<std::int32_t> &col, std::vector<T> &val) {
         std::string_view line = f.lines[i + header + 1];
         if (starts_with(line, "@")) { throw invalid_file_format_exception{ "Read @ inside data section!: '" + std::string{ line } + "'" }; }
-        std::fill(dense_row.begin(), dense_row.end(), T{ 0 });
         if (starts_with(line, "{")) {
             if (!ends_with(line, "}")) {
                 throw invalid_file_format_exception{ "Missing closing '}' for sparse data point " + std::to_string(i) + " description!" };
             }
+            row.clear();
             bool is_class_set = false;
             std::string_view::size_type pos = 1;
             while (true) {
@@ -403,14 +404,28 @@ void parameter<T>::parse_arff_file(const std::string &filename, const bool test)
                     if (!rest.empty() && rest.back() == '}') { rest.remove_suffix(1); }
                     labels[i] = sign(convert_to<T, invalid_file_format_exception>(rest));
                 } else {
-                    dense_row[index] = convert_to<T, invalid_file_format_exception>(line.substr(pos, next_pos - pos));
+                    row.emplace_back((std::int32_t) index, convert_to<T, invalid_file_format_exception>(line.substr(pos, next_pos - pos)));
                 }
                 line.remove_prefix(next_pos + 1);
                 line = trim_left(line);
                 pos = 0;
             }
             if (!is_class_set && has_label) { throw invalid_file_format_exception{ "Missing label for data point " + std::to_string(i) + "!" }; }
+            std::stable_sort(row.begin(), row.end(), [](const auto &x, const auto &y) { return x.first < y.first; });
+            for (std::size_t k = 0; k < row.size(); ++k) {
+                if (k + 1 < row.size() && row[k + 1].first == row[k].first) { continue; }  // overwritten by a later entry
+                if (row[k].second != T{ 0 }) {
+                    col.push_back(row[k].first);
+                    val.push_back(row[k].second);
+                }
+            }
         } else {
+            const auto keep = [&](const std::size_t j, const T v) {
+                if (v != T{ 0 }) {
+                    col.push_back((std::int32_t) j);
+                    val.push_back(v);
+                }
+            };
             std::string_view::size_type pos = 0, next_pos = 0;
             for (std::size_t j = 0; j < max_size - 1; ++j) {
                 next_pos = line.find_first_of(',', pos);
@@ -418,7 +433,7 @@ void parameter<T>::parse_arff_file(const std::string &filename, const bool test)
                     throw invalid_file_format_exception{ "Invalid number of features/labels! Found " + std::to_string(j) + " but should be " +
                                                          std::to_string(max_size - 1) + "!" };
                 }
-                dense_row[j] = convert_to<T, invalid_file_format_exception>(line.substr(pos, next_pos - pos));
+                keep(j, convert_to<T, invalid_file_format_exception>(line.substr(pos, next_pos - pos)));
                 pos = next_pos + 1;
             }
             next_pos = line.find_first_of(',', pos);
@@ -429,16 +444,43 @@ void parameter<T>::parse_arff_file(const std::string &filename, const bool test)
             if (has_label) {
                 labels[i] = sign(convert_to<T, invalid_file_format_exception>(line.substr(pos)));
             } else {
-                dense_row[num_features - 1] = convert_to<T, invalid_file_format_exception>(line.substr(pos));
+                keep(num_features - 1, convert_to<T, invalid_file_format_exception>(line.substr(pos)));
             }
         }
-        for (std::size_t j = 0; j < num_features; ++j) {
-            if (dense_row[j] != T{ 0 }) {
-                m->col.push_back((std::int32_t) j);
-                m->val.push_back(dense_row[j]);
-            }
+    };
+    // contiguous chunks of lines per team member, stitched in file order; the first malformed line in file order is reported
+    // (same scheme as parse_libsvm_lines; the reference parses the data section inside `omp parallel for`, parameter.cpp:236)
+    struct chunk {
+        std::vector<std::int32_t> col;
+        std::vector<T> val;
+        std::exception_ptr error{};
+    };
+    const int teams = (int) std::max<std::size_t>(1, std::min<std::size_t>((std::size_t) omp_get_max_threads(), n / 256 + 1));
+    std::vector<chunk> chunks((std::size_t) teams);
+#pragma omp parallel num_threads(teams)
+    {
+        const std::size_t t = (std::size_t) omp_get_thread_num(), nt = (std::size_t) omp_get_num_threads();
+        std::vector<std::pair<std::int32_t, T>> row;
+        for (std::size_t ci = t; ci < chunks.size(); ci += nt) {
+            chunk &ck = chunks[ci];
+            try {
+                for (std::size_t i = n * ci / chunks.size(); i < n * (ci + 1) / chunks.size(); ++i) {
+                    const std::size_t before = ck.col.size();
+                    parse_line(i, row, ck.col, ck.val);
+                    m->rowptr[i + 1] = (std::int64_t) (ck.col.size() - before);  // entries of the line; turned into offsets below
+                }
+            } catch (...) { ck.error = std::current_exception(); }
         }
-        m->rowptr[i + 1] = (std::int64_t) m->col.size();
+    }
+    for (const chunk &ck : chunks) {
+        if (ck.error) { std::rethrow_exception(ck.error); }
+    }
+    for (std::size_t i = 0; i < n; ++i) { m->rowptr[i + 1] += m->rowptr[i]; }
+    m->col.reserve((std::size_t) m->rowptr[n]);
+    m->val.reserve((std::size_t) m->rowptr[n]);
+    for (const chunk &ck : chunks) {
+        m->col.insert(m->col.end(), ck.col.begin(), ck.col.end());
+        m->val.insert(m->val.end(), ck.val.begin(), ck.val.end());
     }
     if (gamma == T{ 0 }) { gamma = T{ 1 } / static_cast<T>(num_features); }
     value_ptr = has_label ? std::make_shared<const std::vector<T>>(std::move(labels)) : nullptr;

@@ -360,3 +360,48 @@ def test_model_writer_matches_reference_text(host, tmp_path, kernel, dt):
                     assert open(got_path, "rb").read() == want, (n, F, threads, as_csr)
         finally:
             host.b200host_set_threads(os.cpu_count() or 1)
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref not built")
+def test_parallel_arff_parser_matches_reference(host, tmp_path):
+    """The ARFF data section is parsed by an OpenMP team straight into CSR (no dense row per line): dense and sparse lines mixed,
+    repeated indices inside a sparse line (the later entry wins, as in the reference's dense row), explicit zeros, comments in
+    between — equal to the reference's parser for every team size; of two malformed lines the first in file order is reported."""
+    rng = np.random.default_rng(21)
+    n, F = 2500, 37
+    lines = ["% generated", "@RELATION big"] + [f"@ATTRIBUTE f{j} NUMERIC" for j in range(F)] + ["@ATTRIBUTE class NUMERIC", "@DATA"]
+    for i in range(n):
+        label = 1 if rng.random() < 0.5 else -1
+        if i % 3 == 0:
+            vals = np.where(rng.random(F) < 0.5, np.round(rng.standard_normal(F), 6), 0.0)
+            lines.append(",".join(repr(float(v)) for v in vals) + f",{label}")
+        else:
+            idx = rng.integers(0, F, rng.integers(1, 9))  # unsorted, may repeat
+            ent = [f"{j} {0.0 if rng.random() < 0.1 else round(float(rng.standard_normal()), 6)!r}" for j in idx]
+            lines.append("{" + ",".join(ent + [f"{F} {label}"]) + "}")  # the class entry comes last (parameter.cpp:270-276 reads it to the end of the line)
+        if i % 400 == 7:
+            lines.append("% a comment inside the data section")
+    path = str(tmp_path / "big.arff")
+    open(path, "w").write("\n".join(lines) + "\n")
+    Xr, yr = ref_parse(path, np.float64)
+    assert Xr.shape == (n, F)
+    for threads in (1, 2, 7, 64):
+        host.b200host_set_threads(threads)
+        rc, out = host_parse(host, path)
+        assert rc == 0, out
+        Xh, yh, nnz, gamma = out
+        assert np.array_equal(Xh, Xr) and np.array_equal(yh, yr) and nnz == int(np.count_nonzero(Xr))
+    data0 = lines.index("@DATA") + 1
+    bad_lines = list(lines)
+    bad_lines[data0 + 300] = "{0 1.5,3 abc," + f"{F} 1" + "}"
+    bad_lines[data0 + 2000] = "@ATTRIBUTE late NUMERIC"
+    bad = str(tmp_path / "bad.arff")
+    open(bad, "w").write("\n".join(bad_lines) + "\n")
+    msgs = set()
+    for threads in (1, 5, 64):
+        host.b200host_set_threads(threads)
+        rc, msg = host_parse(host, bad)
+        assert rc != 0
+        msgs.add(msg)
+    assert msgs == {"Can't convert 'abc' to a value of type double!"}
+    host.b200host_set_threads(os.cpu_count() or 1)
