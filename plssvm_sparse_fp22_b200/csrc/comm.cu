@@ -1,13 +1,17 @@
 // Multi-GPU exchange: one process per GPU, NCCL over NVLink 5 / NVSwitch on the handle's stream.
 //
 // Replaces the reference's host-staged gpu_csvm::device_reduction (src/plssvm/backends/gpu_csvm.cpp:365-386: D2H from every
-// device, add on the host, H2D to every device).  Here each rank computes the partial K d of its tiles / rows and ONE
-// ncclAllReduce(sum) of m reals per matvec makes the full vector resident on every rank; the O(m) CG algebra is then replicated
-// bit-identically on all ranks, so no scalar collectives and no host round trips are needed.
+// device, add on the host, H2D to every device).  Here each rank computes the partial K d of its tiles / rows and stores it
+// straight into every peer's exchange buffer over NVLink (CUDA-IPC mapped peer memory, xchg.cuh); the consumer is fused into the
+// O(m) CG kernel that follows, so the full vector becomes resident on every rank without a collective call and the CG algebra is
+// replicated bit-identically on all ranks: no scalar collectives, no host round trips.  NCCL carries the set-up
+// handshake, the barrier in front of a buffer release, and the fallback (one ncclAllReduce per matvec) when the peers cannot be
+// mapped or B200SVM_OPT_PEER_EXCHANGE = 1.
 //
 // NCCL is bound at run time (dlopen): under Python the copy torch already loaded is reused (RTLD_NOLOAD), a stand-alone C++
 // host picks up the system libnccl.so.2.  Only the six stable entry points below are used.
 #include "internal.cuh"
+#include "xchg.cuh"
 
 #include <dlfcn.h>
 
@@ -81,44 +85,24 @@ void nccl_check(int rc, const char *what) {
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------------------------------
-// Peer-memory exchange: the allreduce of the matvec result without NCCL on the critical path.
-// Every rank owns a buffer  [2 parities][world slots][ld reals] + [2][world] sequence flags, mapped into all peers through
-// CUDA IPC.  Producer (k_xchg_push): stores this rank's partial vector into slot `rank` of EVERY peer's buffer over NVLink,
-// then the last block publishes the sequence number in every peer's flag (system-scope fence before it).  Consumer
-// (k_abar_finish): one thread per source rank spins on the local flags until they reach the sequence number, then the
-// `world` slots are summed in rank order — the same order on every rank, so the replicated CG state stays bit-identical.
-// Two parities suffice: the producer of exchange k + 2 on any rank runs after that rank's consumer of k + 1, which waited
-// for every peer's producer of k + 1, which ran after that peer's consumer of k.
+// Peer-memory exchange (protocol in xchg.cuh): the sum (or gather) of the matvec result over the ranks without
+// NCCL on the critical path.
+//   sum mode    (tile-partitioned paths): rank r stores its full-length partial vector into slot r of EVERY peer's buffer; the
+//               consumer adds the `world` slots in rank order — the same order on every rank, so the replicated CG state stays
+//               bit-identical.  The tcgen05 path does the stores from its own partial-vector reduction kernel (gram_tc.cu).
+//   gather mode (row-partitioned paths): rank r stores only its rows [lo, hi) into slot 0 of every peer — 1 / world of the bytes.
 // ---------------------------------------------------------------------------------------------------------------------
-constexpr int MAX_PEERS = 16;
-
-struct peer_table {
-    void *base[MAX_PEERS];
-};
-
+// generic producer: P[lo, hi) -> slot `slot` of every peer (sum mode: lo = 0, hi = m, slot = rank; gather mode: slot = 0)
 template <typename T>
-__global__ void __launch_bounds__(256) k_xchg_push(const T *__restrict__ P, int64_t m, peer_table peers, int world, int rank, int64_t ld, int parity,
-                                                   unsigned long long seq, size_t flags_offset, unsigned int *ticket) {
+__global__ void __launch_bounds__(256) k_xchg_push(const T *__restrict__ P, int64_t lo, int64_t hi, xchg_push x, int slot, const T *__restrict__ done) {
     __shared__ bool is_last;
-    const size_t slot = ((size_t) parity * (size_t) world + (size_t) rank) * (size_t) ld;
-    for (int r = 0; r < world; ++r) {
-        T *dst = static_cast<T *>(peers.base[r]) + slot;
-        for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (int64_t) gridDim.x * blockDim.x) { dst[i] = P[i]; }
+    if (done != nullptr && *done != T(0)) { return; }  // CG has converged: this queued exchange is skipped on every rank (xchg.cuh)
+    const unsigned long long seq = xchg_next_seq(x);
+    for (int r = 0; r < x.world; ++r) {
+        T *dst = xchg_slot<T>(x, r, seq, slot);
+        for (int64_t i = lo + (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t) gridDim.x * blockDim.x) { dst[i] = P[i]; }
     }
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const unsigned int t = atomicAdd(ticket, 1u);
-        is_last = (t == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (is_last && threadIdx.x < world) {
-        __threadfence_system();  // every block's stores (ordered before its ticket) are visible system-wide before the flag
-        volatile unsigned long long *flag =
-            reinterpret_cast<volatile unsigned long long *>(static_cast<char *>(peers.base[threadIdx.x]) + flags_offset) + (size_t) parity * world + rank;
-        *flag = seq;
-        if (threadIdx.x == 0) { *ticket = 0u; }
-    }
+    xchg_publish(x, seq, &is_last);
 }
 
 struct comm_state {
@@ -128,24 +112,43 @@ struct comm_state {
     int64_t ld{ 0 };            // reals per slot
     size_t flags_offset{ 0 };   // byte offset of the flags inside a buffer
     void *local{ nullptr };
-    peer_table peers{};
-    unsigned long long seq{ 0 };
+    void *peers[MAX_PEERS]{};
+    unsigned long long *dseq{ nullptr };  // device: exchanges performed (advanced by the producers)
     unsigned int *ticket{ nullptr };
+    dbuf bar;                   // one float for the barrier allreduce
     int world{ 1 }, rank{ 0 };
 };
 
 namespace {
 
-void xchg_release(comm_state &cs) {
+// every rank has reached this point and drained its stream: no peer kernel can still be storing into this rank's buffer
+void comm_barrier(ctx &c) {
+    comm_state &cs = *c.comm;
+    if (cs.comm == nullptr || c.world <= 1) { return; }
+    cs.bar.reserve(sizeof(float));
+    if (cudaMemsetAsync(cs.bar.p, 0, sizeof(float), c.stream) != cudaSuccess) { return; }
+    if (api().AllReduce(cs.bar.p, cs.bar.p, 1, NCCL_FLOAT32, NCCL_SUM, cs.comm, c.stream) != NCCL_SUCCESS) { return; }
+    cudaStreamSynchronize(c.stream);
+}
+
+// collective: the exported buffer is unmapped by the peers and freed only after a cross-rank barrier (a peer's queued producer
+// may still be storing into it otherwise)
+void xchg_release(ctx &c) {
+    comm_state &cs = *c.comm;
     if (cs.xchg_ok) {
+        cudaStreamSynchronize(c.stream);
+        comm_barrier(c);
         for (int r = 0; r < cs.world; ++r) {
-            if (r != cs.rank && cs.peers.base[r] != nullptr) { cudaIpcCloseMemHandle(cs.peers.base[r]); }
+            if (r != cs.rank && cs.peers[r] != nullptr) { cudaIpcCloseMemHandle(cs.peers[r]); }
         }
+        comm_barrier(c);  // everybody has unmapped before anybody frees
     }
     if (cs.local != nullptr) { cudaFree(cs.local); }
     if (cs.ticket != nullptr) { cudaFree(cs.ticket); }
+    if (cs.dseq != nullptr) { cudaFree(cs.dseq); }
     cs.local = nullptr;
     cs.ticket = nullptr;
+    cs.dseq = nullptr;
     cs.xchg_ok = false;
 }
 
@@ -164,10 +167,11 @@ void xchg_setup(ctx &c, int64_t count) {
     cudaIpcMemHandle_t mine{};
     int ok = want ? 1 : 0;
     if (ok) {
-        ok = cudaMalloc(&cs.local, bytes) == cudaSuccess && cudaMalloc(&cs.ticket, sizeof(unsigned int)) == cudaSuccess;
+        ok = cudaMalloc(&cs.local, bytes) == cudaSuccess && cudaMalloc(&cs.ticket, sizeof(unsigned int)) == cudaSuccess &&
+             cudaMalloc(reinterpret_cast<void **>(&cs.dseq), sizeof(unsigned long long)) == cudaSuccess;
         if (ok) {
             ok = cudaMemsetAsync(cs.local, 0, bytes, c.stream) == cudaSuccess && cudaMemsetAsync(cs.ticket, 0, sizeof(unsigned int), c.stream) == cudaSuccess &&
-                 cudaIpcGetMemHandle(&mine, cs.local) == cudaSuccess;
+                 cudaMemsetAsync(cs.dseq, 0, sizeof(unsigned long long), c.stream) == cudaSuccess && cudaIpcGetMemHandle(&mine, cs.local) == cudaSuccess;
         }
     }
     // all-gather (handle, ok) through NCCL — setup only
@@ -193,12 +197,12 @@ void xchg_setup(ctx &c, int64_t count) {
     int opened = everyone ? 1 : 0;
     if (everyone) {
         for (int r = 0; r < c.world; ++r) {
-            cs.peers.base[r] = nullptr;
+            cs.peers[r] = nullptr;
             if (r == c.rank) {
-                cs.peers.base[r] = cs.local;
-            } else if (cudaIpcOpenMemHandle(&cs.peers.base[r], all[(size_t) r].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                cs.peers[r] = cs.local;
+            } else if (cudaIpcOpenMemHandle(&cs.peers[r], all[(size_t) r].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
                 (void) cudaGetLastError();
-                cs.peers.base[r] = nullptr;
+                cs.peers[r] = nullptr;
                 opened = 0;
             }
         }
@@ -213,24 +217,35 @@ void xchg_setup(ctx &c, int64_t count) {
     if (!cs.xchg_ok) {
         if (everyone) {
             for (int r = 0; r < c.world; ++r) {
-                if (r != c.rank && cs.peers.base[r] != nullptr) { cudaIpcCloseMemHandle(cs.peers.base[r]); }
+                if (r != c.rank && cs.peers[r] != nullptr) { cudaIpcCloseMemHandle(cs.peers[r]); }
             }
         }
         if (cs.local != nullptr) { cudaFree(cs.local); }
         if (cs.ticket != nullptr) { cudaFree(cs.ticket); }
+        if (cs.dseq != nullptr) { cudaFree(cs.dseq); }
         cs.local = nullptr;
         cs.ticket = nullptr;
+        cs.dseq = nullptr;
         B200_REQUIRE(c.opt_peer_exchange != 2, "peer-memory exchange was required but CUDA IPC mapping of the peers failed");
     }
-    cs.seq = 0;
+}
+
+void ensure_xchg(ctx &c, int64_t count) {
+    if (c.comm == nullptr || c.comm->comm == nullptr) { fail(B200SVM_ERR_NCCL, "NCCL communicator not initialised"); }
+    comm_state &cs = *c.comm;
+    if (!cs.xchg_tried || (cs.xchg_ok && count > cs.ld)) {
+        if (cs.xchg_ok) { xchg_release(c); }
+        xchg_setup(c, count);
+    }
 }
 
 }  // namespace
 
+// collective when the handle owns a communicator (barrier before the exchange buffers are released)
 void comm_destroy(ctx &c) {
     if (c.comm != nullptr) {
         cudaStreamSynchronize(c.stream);
-        xchg_release(*c.comm);
+        xchg_release(c);
         if (c.comm->comm != nullptr) { api().CommDestroy(c.comm->comm); }
         delete c.comm;
         c.comm = nullptr;
@@ -239,44 +254,54 @@ void comm_destroy(ctx &c) {
     c.world = 1;
 }
 
-// Sum over ranks of the partial vector P (count reals of the handle's type).  Peer exchange: P is pushed to every rank and the
-// caller's O(m) epilogue sums `world` slots (returned in *x); NCCL fallback: in-place allreduce, x->base == nullptr.
-void comm_exchange(ctx &c, void *P, int64_t count, xchg_view *x) {
-    x->base = nullptr;
-    if (c.world <= 1 || count == 0) { return; }
-    if (c.comm == nullptr || c.comm->comm == nullptr) { fail(B200SVM_ERR_NCCL, "NCCL communicator not initialised"); }
+// Prepare one exchange of `count` reals per slot.  plan.peer == true: the caller's producer kernel stores through plan.push (or
+// comm_push does) and the O(m) epilogue consumes plan.view; false: no peer mapping — the caller sums with comm_allreduce_sum.
+// Collective on first use (and when `count` outgrows the buffers).
+xchg_plan comm_exchange_begin(ctx &c, int64_t count, int mode) {
+    xchg_plan plan{};
+    if (c.world <= 1 || count == 0) { return plan; }
+    ensure_xchg(c, count);
     comm_state &cs = *c.comm;
-    if (!cs.xchg_tried || (cs.xchg_ok && count > cs.ld)) {
-        if (cs.xchg_ok) {
-            B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));
-            xchg_release(cs);
-        }
-        xchg_setup(c, count);
-    }
-    if (!cs.xchg_ok) {
-        comm_allreduce_sum(c, P, count);
-        return;
-    }
-    ++cs.seq;
-    const int parity = (int) (cs.seq & 1ull);
+    if (!cs.xchg_ok) { return plan; }
+    plan.peer = true;
+    for (int r = 0; r < c.world; ++r) { plan.push.peer[r] = cs.peers[r]; }
+    plan.push.world = c.world;
+    plan.push.rank = c.rank;
+    plan.push.ld = cs.ld;
+    plan.push.flags_offset = cs.flags_offset;
+    plan.push.dseq = cs.dseq;
+    plan.push.ticket = cs.ticket;
+    plan.view.base = cs.local;
+    plan.view.ld = cs.ld;
+    plan.view.slots = mode == XCHG_GATHER ? 1 : c.world;
+    plan.view.world = c.world;
+    plan.view.parity_stride = (int64_t) c.world * cs.ld;
+    plan.view.flags = reinterpret_cast<const unsigned long long *>(static_cast<char *>(cs.local) + cs.flags_offset);
+    plan.view.dseq = cs.dseq;
+    ++c.stats.collectives;
+    ++c.stats.peer_exchanges;
+    return plan;
+}
+
+bool comm_peer_mode(ctx &c, int64_t count) {
+    if (c.world <= 1 || count == 0) { return false; }
+    ensure_xchg(c, count);
+    return c.comm->xchg_ok;
+}
+
+// generic producer of an exchange prepared by comm_exchange_begin: P[lo, hi) of this rank -> every peer
+void comm_push(ctx &c, const xchg_plan &plan, const void *P, int64_t lo, int64_t hi, int mode, const void *done) {
+    const int64_t count = hi - lo;
     const int grid = (int) std::max<int64_t>(1, std::min<int64_t>((count + 2047) / 2048, 2 * NUM_SMS));
+    const int slot = mode == XCHG_GATHER ? 0 : c.rank;
     if (c.dtype == B200SVM_F32) {
-        k_xchg_push<float><<<grid, 256, 0, c.stream>>>(static_cast<const float *>(P), count, cs.peers, c.world, c.rank, cs.ld, parity, cs.seq, cs.flags_offset,
-                                                       cs.ticket);
+        k_xchg_push<float><<<grid, 256, 0, c.stream>>>(static_cast<const float *>(P), lo, hi, plan.push, slot, static_cast<const float *>(done));
     } else {
-        k_xchg_push<double><<<grid, 256, 0, c.stream>>>(static_cast<const double *>(P), count, cs.peers, c.world, c.rank, cs.ld, parity, cs.seq,
-                                                        cs.flags_offset, cs.ticket);
+        k_xchg_push<double><<<grid, 256, 0, c.stream>>>(static_cast<const double *>(P), lo, hi, plan.push, slot, static_cast<const double *>(done));
     }
     count_launch(c);
     B200_CUDA_CHECK(cudaGetLastError());
-    ++c.stats.collectives;
-    ++c.stats.peer_exchanges;
     c.stats.collective_bytes += count * (int64_t) c.esize() * (int64_t) (c.world - 1);
-    x->base = static_cast<char *>(cs.local) + (size_t) parity * (size_t) c.world * (size_t) cs.ld * c.esize();
-    x->ld = cs.ld;
-    x->slots = c.world;
-    x->flags = reinterpret_cast<const unsigned long long *>(static_cast<char *>(cs.local) + cs.flags_offset) + (size_t) parity * c.world;
-    x->seq = cs.seq;
 }
 
 // in-place sum over ranks of `count` reals (type of the handle) on the handle's stream

@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "../../include/b200svm.h"
+#include "xchg.cuh"
 
 namespace b200 {
 
@@ -193,13 +194,18 @@ template <typename T> void predict_dense(ctx &c, const T *alpha_dev, T bias, con
 void tc_prepare_split(ctx &c);                                   // build fp16 hi/lo operands + TMA descriptors
 bool tc_available(const ctx &c);
 void tc_invalidate_cache(ctx &c);  // drop the cached kernel-matrix tiles (option changed); rebuilt on the next matvec
-void tc_kernel_matvec(ctx &c, const float *d, float *out_Kd);    // out = K d via symmetric tcgen05 tiles
+// out = centred K d over this rank's tiles (symmetric tcgen05 tiles or the sweep over the stored tiles).  packed: pk already holds d
+// (written by the CG direction kernel).  push != nullptr: the partial-vector reduction stores into the peers instead of `out`.
+void tc_kernel_matvec(ctx &c, const float *d, float *out_Kd, bool packed, const xchg_push *push, const float *done);
+void *tc_pack_buffer(ctx &c);                                     // float4 pk[n_pad] of the tcgen05 path (nullptr when not prepared)
 
 // sparse path (sparse.cu)
 void sp_invalidate_cache(ctx &c);  // drop the cached S (options changed); rebuilt on the next matvec
 void sp_set_data(ctx &c, const int64_t *rowptr, const int32_t *colidx, const void *values, int64_t n, int64_t F, int64_t nnz, int fmt);
 template <typename T> void sp_generate_q(ctx &c);
-template <typename T> void sp_kernel_matvec(ctx &c, const T *d, T *out);  // out[0..m) = K d (un-centred), this rank's rows
+// out = K d (un-centred).  Returns true: rows [lo, hi) of this rank are in out[lo, hi) (the rest is zeroed when zero_rest);
+// false: out holds a full-length partial vector over this rank's TILES of a densely filled S (to be summed over the ranks)
+template <typename T> bool sp_kernel_matvec(ctx &c, const T *d, T *out, bool zero_rest, const T *done);
 template <typename T> void sp_update_w(ctx &c, const T *alpha_dev, T *w_dev);
 template <typename T> void sp_predict(ctx &c, const T *alpha_dev, T bias, const int64_t *rowptr, const int32_t *colidx, const void *values, int64_t P,
                                       int64_t nnz, int fmt, T *out_host);
@@ -207,16 +213,16 @@ template <typename T> void sp_predict(ctx &c, const T *alpha_dev, T bias, const 
 // multi-GPU (comm.cu)
 void comm_destroy(ctx &c);
 void comm_allreduce_sum(ctx &c, void *buf, int64_t count);  // in place, real type of the handle
-// result of comm_exchange: base == nullptr -> the vector was all-reduced in place (NCCL); else `slots` partial vectors of stride
-// `ld` reals start at `base` in this rank's exchange buffer and become valid once flags[0..slots) >= seq (k_abar_finish waits)
-struct xchg_view {
-    void *base{ nullptr };
-    int64_t ld{ 0 };
-    int slots{ 0 };
-    const unsigned long long *flags{ nullptr };
-    unsigned long long seq{ 0 };
+// peer-memory exchange (protocol and device helpers: xchg.cuh)
+enum xchg_mode : int { XCHG_SUM = 0, XCHG_GATHER = 1 };
+struct xchg_plan {
+    bool peer{ false };  // false: no peer mapping (NCCL fallback) — sum with comm_allreduce_sum
+    xchg_push push;      // producer side
+    xchg_view view;      // consumer side
 };
-void comm_exchange(ctx &c, void *P, int64_t count, xchg_view *x);
+xchg_plan comm_exchange_begin(ctx &c, int64_t count, int mode);  // one exchange of `count` reals per slot; collective on first use
+bool comm_peer_mode(ctx &c, int64_t count);                      // will exchanges of this size use peer memory?  (collective on first use)
+void comm_push(ctx &c, const xchg_plan &plan, const void *P, int64_t lo, int64_t hi, int mode, const void *done);  // generic producer: P[lo, hi) -> every peer
 void partition_rows(int64_t m, int rank, int world, int64_t *lo, int64_t *hi);
 
 inline void count_launch(ctx &c, int k = 1) { c.stats.kernel_launches += k; }
