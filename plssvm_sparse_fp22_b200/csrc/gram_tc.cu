@@ -23,6 +23,7 @@
 //   warps 2..9      : epilogue      — (lane quadrant, column half) each; tcgen05.ld 32x32b, exp2 / pow, centring, row sums in registers, column sums by a
 //                                     warp-shuffle butterfly + shared memory
 #include "internal.cuh"
+#include "xchg.cuh"
 
 #include <cuda.h>
 #include <cuda_fp16.h>
@@ -191,7 +192,7 @@ __device__ __forceinline__ float kernel_from_gram(float g, float ci, float cj, f
     }
 }
 
-// Stored kernel-matrix tile (STORE pass -> k_cached_gemv): quad-column-major, float4 index of (columns 4 cq .. 4 cq + 3, row r).
+// Stored kernel-matrix tile (STORE pass -> k_tile_sweep): quad-column-major, float4 index of (columns 4 cq .. 4 cq + 3, row r).
 // Both kernels put 32 consecutive rows on the 32 lanes of a warp, so every global access is 512 contiguous bytes.
 __host__ __device__ constexpr int kc_quad_index(int cq, int r) { return cq * BM + r; }
 
@@ -444,92 +445,125 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// Cached kernel matrix: the same partial vectors as k_gram_tc, from the stored tiles — an HBM-bound symmetric GEMV.
-//   t_ij = K_ij + QA_cost - q_i - q_j ;  Pr[J][i] = sum_j t_ij d_j (i >= j) ;  Pc[I][j] = sum_i t_ij d_i (i > j)
-// One CTA per tile (grid-strided), tiles in the quad-column-major layout of kc_quad_index.  Warp w owns the 32 columns
-// [32 w, 32 w + 32) (column quads 8 w .. 8 w + 7) over all 128 rows; lane l holds rows l, 32 + l, 64 + l, 96 + l, so every load
-// instruction of a warp streams 512 contiguous bytes and the warp's 16 KB are one contiguous range.  Row partials stay in four
-// registers per thread and are combined over the eight warps through shared memory; the 32 column partials of a thread are summed
-// over the lanes by the fixed butterfly of warp_column_sums (lane j ends with column 32 w + j) — ONE butterfly per warp and tile.
-// Fixed order => bit-reproducible.  (Variants that replay the exact summation order of the Gram kernel's epilogue — one butterfly
-// per row quadrant and 32-column group, with register or cp.async.bulk ring staging — were bit-identical to the recompute mode but
-// issue-bound at 1.55-1.65 ms per sweep against 1.38 ms for this one: profiles/r1_summary.md.)
+// Cached kernel matrix: the matvec from the stored tiles — an HBM-bound symmetric GEMV.
+//   CENTRE:   t_ij = K_ij + QA_cost - q_i - q_j   (dense data: the reference's per-entry centring, svm_kernel.cpp:32)
+//   !CENTRE:  t_ij = S_ij                          (sparse rows with a densely filled S: the rank-1 part is added in the O(m) epilogue)
+//   row part  Pr[J][i]    = sum_j t_ij w_j  (i >= j)   one partial vector per column strip J
+//   col part  Pc[run][j]  = sum_i t_ij w_i  (i > j)    one partial vector per RUN of tiles of a strip
+// The rank's tiles are sorted by (strip J, row block I) and cut into equal chunks, one per CTA: a CTA walks down a strip and keeps
+// the 32 mirrored column sums of every thread in registers across the tiles of the run — ONE shuffle butterfly per run instead of
+// one per tile — so a strip of up to 512 tiles leaves a handful of column partial vectors (runs per strip <= strip length /
+// chunk length + 2) instead of one per tile; the reduction kernel reads ~100x fewer column partials than before.
+// Tile layout = kc_quad_index (quad-column-major): warp w owns the 32 columns [32 w, 32 w + 32) over all 128 rows, lane l the rows
+// l, 32 + l, 64 + l, 96 + l, so every load instruction of a warp streams 512 contiguous bytes and the warp's 16 KB are one
+// contiguous range.  Row partials: four registers per thread, combined over the eight warps through (double-buffered) shared
+// memory in a fixed tree.  Fixed order everywhere => bit-reproducible.
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_cached_gemv(const float *__restrict__ Kc, const params p) {
+struct sweep_params {
+    const float *Kc;         // stored tiles, [storage index][BN / 4][BM] float4
+    const int4 *list;        // tiles of this rank sorted by (J, I): {I, J, storage index, 0}
+    int num_tiles;
+    int nchunks;
+    const int *first_slot;   // [nchunks] run index (within its strip) of the first run of a chunk
+    const float4 *pk;        // [n_pad] {-, q_i, w_i, -}
+    float *Pr;               // [T_c][ldP]
+    float *Pc;               // [max_runs][ldP]
+    int64_t ldP;
+    float qa;
+    const float *done;
+};
+
+template <bool CENTRE>
+__global__ void __launch_bounds__(256, 2) k_tile_sweep(const sweep_params p) {
     if (p.done != nullptr && *p.done != 0.f) { return; }
-    __shared__ float4 colq[BN / 4];    // q_j of the tile's columns, one float4 per column quad
-    __shared__ float4 cold[BN / 4];    // d_j
-    __shared__ float rowpart[8][BM];   // per warp: totals of the 128 rows over its 32 columns
+    __shared__ float4 colq[BN / 4];      // q_j of the strip's columns, one float4 per column quad
+    __shared__ float4 cold[BN / 4];      // w_j
+    __shared__ float rowpart[2][8][BM];  // per warp: totals of the 128 rows over its 32 columns (double-buffered over the tiles)
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
-    for (int tt = blockIdx.x; tt < p.num_tiles; tt += gridDim.x) {
-        const int2 tile = p.tiles[tt];
-        const int64_t row0 = static_cast<int64_t>(tile.x) * BM, col0 = static_cast<int64_t>(tile.y) * BN;
-        const bool diag_tile = row0 < col0 + BN;
-        __syncthreads();  // the previous tile's shared-memory readers are done
-        {
-            const float4 v = __ldg(&p.pk[col0 + t]);
-            reinterpret_cast<float *>(colq)[t] = v.y;
-            reinterpret_cast<float *>(cold)[t] = v.z;
-        }
-        float ai[4], di[4];  // (QA_cost - q_i, d_i) of this thread's four rows
-#pragma unroll
-        for (int rg = 0; rg < 4; ++rg) {
-            const float4 v = __ldg(&p.pk[row0 + rg * 32 + lane]);
-            ai[rg] = p.qa - v.y;
-            di[rg] = v.z;
-        }
-        __syncthreads();
-        const float4 *base = reinterpret_cast<const float4 *>(Kc) + static_cast<int64_t>(tt) * (BM * BN / 4) + kc_quad_index(8 * w, lane);
-        float rs[4] = { 0.f, 0.f, 0.f, 0.f };
+    for (int c = blockIdx.x; c < p.nchunks; c += gridDim.x) {
+        const int k0 = (int) ((int64_t) p.num_tiles * c / p.nchunks), k1 = (int) ((int64_t) p.num_tiles * (c + 1) / p.nchunks);
+        int curJ = -1, slot = 0;
         float cs[32];
+        for (int k = k0; k < k1; ++k) {
+            const int4 tile = __ldg(&p.list[k]);
+            const int64_t row0 = static_cast<int64_t>(tile.x) * BM, col0 = static_cast<int64_t>(tile.y) * BN;
+            if (tile.y != curJ) {  // block-uniform: a new strip (the tile barrier below has retired every reader of colq / cold)
+                if (curJ >= 0) {
+                    const float ctot = warp_column_sums(cs, lane);  // lane j: column 32 w + j over the rows of the run
+                    p.Pc[static_cast<int64_t>(slot) * p.ldP + static_cast<int64_t>(curJ) * BN + 32 * w + lane] = ctot;
+                }
+                slot = k == k0 ? __ldg(&p.first_slot[c]) : 0;
+                curJ = tile.y;
 #pragma unroll
-        for (int k0 = 0; k0 < 8; k0 += 2) {
-            float4 kv[2][4];
-#pragma unroll
-            for (int kk = 0; kk < 2; ++kk) {
-#pragma unroll
-                for (int rg = 0; rg < 4; ++rg) { kv[kk][rg] = __ldcs(base + (k0 + kk) * BM + rg * 32); }  // eight 16-byte loads in flight
+                for (int i = 0; i < 32; ++i) { cs[i] = 0.f; }
+                const float4 v = __ldg(&p.pk[col0 + t]);
+                reinterpret_cast<float *>(colq)[t] = v.y;
+                reinterpret_cast<float *>(cold)[t] = v.z;
+                __syncthreads();
             }
+            const bool diag_tile = row0 < col0 + BN;
+            float ai[4], di[4];  // (QA_cost - q_i, w_i) of this thread's four rows
 #pragma unroll
-            for (int kk = 0; kk < 2; ++kk) {
-                const int cq = 8 * w + k0 + kk;
-                const float4 q4 = colq[cq], d4 = cold[cq];  // same address for the whole warp: broadcast
-                const float qj[4] = { q4.x, q4.y, q4.z, q4.w };
-                const float dj[4] = { d4.x, d4.y, d4.z, d4.w };
-                float ca[4] = { 0.f, 0.f, 0.f, 0.f };
+            for (int rg = 0; rg < 4; ++rg) {
+                const float4 v = __ldg(&p.pk[row0 + rg * 32 + lane]);
+                ai[rg] = p.qa - v.y;
+                di[rg] = v.z;
+            }
+            const float4 *base = reinterpret_cast<const float4 *>(p.Kc) + static_cast<int64_t>(tile.z) * (BM * BN / 4) + kc_quad_index(8 * w, lane);
+            float rs[4] = { 0.f, 0.f, 0.f, 0.f };
 #pragma unroll
-                for (int rg = 0; rg < 4; ++rg) {
-                    const float e[4] = { kv[kk][rg].x, kv[kk][rg].y, kv[kk][rg].z, kv[kk][rg].w };
-                    if (!diag_tile) {
+            for (int q0 = 0; q0 < 8; q0 += 2) {
+                float4 kv[2][4];
 #pragma unroll
-                        for (int c = 0; c < 4; ++c) {
-                            const float tv = e[c] + (ai[rg] - qj[c]);
-                            rs[rg] = fmaf(tv, dj[c], rs[rg]);
-                            ca[c] = fmaf(tv, di[rg], ca[c]);
-                        }
-                    } else {
-                        const int64_t gi = row0 + rg * 32 + lane;
+                for (int kk = 0; kk < 2; ++kk) {
 #pragma unroll
-                        for (int c = 0; c < 4; ++c) {
-                            const int64_t gj = col0 + 4 * cq + c;
-                            const float tv = e[c] + (ai[rg] - qj[c]);
-                            rs[rg] = gi >= gj ? fmaf(tv, dj[c], rs[rg]) : rs[rg];  // lower triangle incl. diagonal -> row i
-                            ca[c] = gi > gj ? fmaf(tv, di[rg], ca[c]) : ca[c];     // strictly lower -> mirrored into column j
-                        }
-                    }
+                    for (int rg = 0; rg < 4; ++rg) { kv[kk][rg] = __ldcs(base + (q0 + kk) * BM + rg * 32); }  // eight 16-byte loads in flight
                 }
 #pragma unroll
-                for (int c = 0; c < 4; ++c) { cs[(k0 + kk) * 4 + c] = ca[c]; }
+                for (int kk = 0; kk < 2; ++kk) {
+                    const int cq = 8 * w + q0 + kk;
+                    const float4 q4 = colq[cq], d4 = cold[cq];  // same address for the whole warp: broadcast
+                    const float qj[4] = { q4.x, q4.y, q4.z, q4.w };
+                    const float dj[4] = { d4.x, d4.y, d4.z, d4.w };
+                    float ca[4] = { 0.f, 0.f, 0.f, 0.f };
+#pragma unroll
+                    for (int rg = 0; rg < 4; ++rg) {
+                        const float e[4] = { kv[kk][rg].x, kv[kk][rg].y, kv[kk][rg].z, kv[kk][rg].w };
+                        if (!diag_tile) {
+#pragma unroll
+                            for (int cc = 0; cc < 4; ++cc) {
+                                const float tv = CENTRE ? e[cc] + (ai[rg] - qj[cc]) : e[cc];
+                                rs[rg] = fmaf(tv, dj[cc], rs[rg]);
+                                ca[cc] = fmaf(tv, di[rg], ca[cc]);
+                            }
+                        } else {
+                            const int64_t gi = row0 + rg * 32 + lane;
+#pragma unroll
+                            for (int cc = 0; cc < 4; ++cc) {
+                                const int64_t gj = col0 + 4 * cq + cc;
+                                const float tv = CENTRE ? e[cc] + (ai[rg] - qj[cc]) : e[cc];
+                                rs[rg] = gi >= gj ? fmaf(tv, dj[cc], rs[rg]) : rs[rg];  // lower triangle incl. diagonal -> row i
+                                ca[cc] = gi > gj ? fmaf(tv, di[rg], ca[cc]) : ca[cc];   // strictly lower -> mirrored into column j
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int cc = 0; cc < 4; ++cc) { cs[(q0 + kk) * 4 + cc] += ca[cc]; }
+                }
+            }
+            const int buf = (k - k0) & 1;
+#pragma unroll
+            for (int rg = 0; rg < 4; ++rg) { rowpart[buf][w][rg * 32 + lane] = rs[rg]; }
+            __syncthreads();  // one barrier per tile: rowpart[buf] complete; nobody still reads this tile's colq / cold
+            if (t < BM) {
+                const float(*rp)[BM] = rowpart[buf];
+                p.Pr[static_cast<int64_t>(tile.y) * p.ldP + row0 + t] =
+                    ((rp[0][t] + rp[1][t]) + (rp[2][t] + rp[3][t])) + ((rp[4][t] + rp[5][t]) + (rp[6][t] + rp[7][t]));
             }
         }
-        const float ctot = warp_column_sums(cs, lane);  // lane j: column 32 w + j over the 128 rows
-        p.Pc[static_cast<int64_t>(tile.x) * p.ldP + col0 + 32 * w + lane] = ctot;
-#pragma unroll
-        for (int rg = 0; rg < 4; ++rg) { rowpart[w][rg * 32 + lane] = rs[rg]; }
-        __syncthreads();
-        if (t < BM) {
-            p.Pr[static_cast<int64_t>(tile.y) * p.ldP + row0 + t] =
-                ((rowpart[0][t] + rowpart[1][t]) + (rowpart[2][t] + rowpart[3][t])) + ((rowpart[4][t] + rowpart[5][t]) + (rowpart[6][t] + rowpart[7][t]));
+        if (curJ >= 0) {
+            const float ctot = warp_column_sums(cs, lane);
+            p.Pc[static_cast<int64_t>(slot) * p.ldP + static_cast<int64_t>(curJ) * BN + 32 * w + lane] = ctot;
         }
     }
 }
@@ -584,27 +618,79 @@ __global__ void __launch_bounds__(256) k_pack(const float *__restrict__ norms, c
     pk[i] = v;
 }
 
-// out[i] = sum_{J <= I_i / 2} Pr[J][i] + sum_{I' >= 2 J_i} Pc[I'][i]   (fixed order; slots of tiles owned by other ranks are zero)
-// own (multi-GPU): byte map [T_r][T_c] of the tiles this rank computes — the partials of the others are skipped, not read
-__global__ void __launch_bounds__(256) k_tc_reduce(const float *__restrict__ Pr, const float *__restrict__ Pc, int64_t ldP, int64_t m, int T_r,
-                                                   int T_c, const uint8_t *__restrict__ own, float *__restrict__ out, const float *__restrict__ done) {
-    if (*done != 0.f) { return; }
-    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= m) { return; }
-    const int Ii = (int) (i / BM), Ji = (int) (i / BN);
-    float s0 = 0.f, s1 = 0.f;
-    if (own == nullptr) {
-        for (int J = 0; J <= Ii / 2; ++J) { s0 += Pr[(int64_t) J * ldP + i]; }
-        for (int I = 2 * Ji; I < T_r; ++I) { s1 += Pc[(int64_t) I * ldP + i]; }
-    } else {  // the map entries are warp-uniform (32 consecutive i share Ii and Ji)
-        for (int J = 0; J <= Ii / 2; ++J) {
-            if (own[Ii * T_c + J] != 0) { s0 += Pr[(int64_t) J * ldP + i]; }
-        }
-        for (int I = 2 * Ji; I < T_r; ++I) {
-            if (own[I * T_c + Ji] != 0) { s1 += Pc[(int64_t) I * ldP + i]; }
-        }
+// Sum of the partial vectors of element i -> out[i], or (several ranks, peer exchange) straight into slot `rank` of every
+// peer's exchange buffer over NVLink: the reduction kernel IS the producer of the exchange (xchg.cuh).
+struct reduce_dst {
+    float *out;
+    xchg_push push;
+    int remote;  // 0: out, 1: peers
+};
+__device__ __forceinline__ void reduce_emit(const reduce_dst &dst, unsigned long long seq, int64_t i, float v) {
+    if (dst.remote) {
+#pragma unroll 1
+        for (int r = 0; r < dst.push.world; ++r) { xchg_slot<float>(dst.push, r, seq, dst.push.rank)[i] = v; }
+    } else {
+        dst.out[i] = v;
     }
-    out[i] = s0 + s1;
+}
+
+// Partial vectors of the Gram kernel (one per tile row / tile column):
+// out[i] = sum_{J <= I_i / 2} Pr[J][i] + sum_{I' >= 2 J_i} Pc[I'][i]   (fixed order; slots of tiles owned by other ranks are skipped)
+// own (multi-GPU): byte map [T_r][T_c] of the tiles this rank computes
+__global__ void __launch_bounds__(256) k_tc_reduce(const float *__restrict__ Pr, const float *__restrict__ Pc, int64_t ldP, int64_t m, int T_r,
+                                                   int T_c, const uint8_t *__restrict__ own, const reduce_dst dst, const float *__restrict__ done) {
+    __shared__ bool is_last;
+    if (done != nullptr && *done != 0.f) { return; }
+    const unsigned long long seq = dst.remote ? xchg_next_seq(dst.push) : 0ull;
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m) {
+        const int Ii = (int) (i / BM), Ji = (int) (i / BN);
+        float s0 = 0.f, s1 = 0.f;
+        if (own == nullptr) {
+            for (int J = 0; J <= Ii / 2; ++J) { s0 += Pr[(int64_t) J * ldP + i]; }
+            for (int I = 2 * Ji; I < T_r; ++I) { s1 += Pc[(int64_t) I * ldP + i]; }
+        } else {  // the map entries are warp-uniform (32 consecutive i share Ii and Ji)
+            for (int J = 0; J <= Ii / 2; ++J) {
+                if (own[Ii * T_c + J] != 0) { s0 += Pr[(int64_t) J * ldP + i]; }
+            }
+            for (int I = 2 * Ji; I < T_r; ++I) {
+                if (own[I * T_c + Ji] != 0) { s1 += Pc[(int64_t) I * ldP + i]; }
+            }
+        }
+        reduce_emit(dst, seq, i, s0 + s1);
+    }
+    if (dst.remote) { xchg_publish(dst.push, seq, &is_last); }
+}
+
+// Partial vectors of the sweep: row partials of the column strips this rank owns in row block I_i (jlist[jptr[I] .. jptr[I + 1])),
+// column partials of the runs of strip J_i.  Four interleaved accumulators, fixed order.
+__global__ void __launch_bounds__(256) k_sweep_reduce(const float *__restrict__ Pr, const float *__restrict__ Pc, int64_t ldP, int64_t m,
+                                                      const int *__restrict__ jptr, const int *__restrict__ jlist, const int *__restrict__ nruns,
+                                                      const reduce_dst dst, const float *__restrict__ done) {
+    __shared__ bool is_last;
+    if (done != nullptr && *done != 0.f) { return; }
+    const unsigned long long seq = dst.remote ? xchg_next_seq(dst.push) : 0ull;
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m) {
+        const int Ii = (int) (i / BM), Ji = (int) (i / BN);
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        const int j0 = __ldg(&jptr[Ii]), j1 = __ldg(&jptr[Ii + 1]);
+        int k = j0;
+        for (; k + 4 <= j1; k += 4) {
+            const int Ja = __ldg(&jlist[k]), Jb = __ldg(&jlist[k + 1]), Jc = __ldg(&jlist[k + 2]), Jd = __ldg(&jlist[k + 3]);
+            const float a0 = Pr[(int64_t) Ja * ldP + i], a1 = Pr[(int64_t) Jb * ldP + i], a2 = Pr[(int64_t) Jc * ldP + i], a3 = Pr[(int64_t) Jd * ldP + i];
+            s0 += a0;
+            s1 += a1;
+            s2 += a2;
+            s3 += a3;
+        }
+        for (; k < j1; ++k) { s0 += Pr[(int64_t) __ldg(&jlist[k]) * ldP + i]; }
+        float c = 0.f;
+        const int nr = __ldg(&nruns[Ji]);
+        for (int r = 0; r < nr; ++r) { c += Pc[(int64_t) r * ldP + i]; }
+        reduce_emit(dst, seq, i, ((s0 + s1) + (s2 + s3)) + c);
+    }
+    if (dst.remote) { xchg_publish(dst.push, seq, &is_last); }
 }
 
 }  // namespace tc
@@ -614,9 +700,61 @@ __global__ void __launch_bounds__(256) k_tc_reduce(const float *__restrict__ Pr,
 // ---------------------------------------------------------------------------------------------------------------------
 namespace {
 
+// sweep over stored tiles: the rank's tiles sorted by (strip, row block), cut into chunks (one per CTA), and what the reduction
+// kernel needs to find the partial vectors (k_tile_sweep / k_sweep_reduce)
+struct sweep_plan {
+    dbuf list, first_slot, nruns, jptr, jlist;
+    int nchunks{ 0 };
+    int max_runs{ 0 };
+};
+
+void build_sweep_plan(ctx &c, sweep_plan &sw, const std::vector<int2> &tiles, int T_r, int T_c) {
+    const int nt = (int) tiles.size();
+    std::vector<int4> list((size_t) nt);
+    for (int t = 0; t < nt; ++t) { list[(size_t) t] = make_int4(tiles[(size_t) t].x, tiles[(size_t) t].y, t, 0); }
+    std::sort(list.begin(), list.end(), [](const int4 &a, const int4 &b) { return a.y != b.y ? a.y < b.y : a.x < b.x; });
+    sw.nchunks = std::max(1, std::min(nt, 4 * NUM_SMS));
+    std::vector<int> first_slot((size_t) sw.nchunks, 0), nruns((size_t) T_c, 0);
+    for (int ch = 0; ch < sw.nchunks; ++ch) {
+        const int k0 = (int) ((int64_t) nt * ch / sw.nchunks), k1 = (int) ((int64_t) nt * (ch + 1) / sw.nchunks);
+        int curJ = -1;
+        for (int k = k0; k < k1; ++k) {
+            const int J = list[(size_t) k].y;
+            if (J != curJ) {
+                if (k == k0) { first_slot[(size_t) ch] = nruns[(size_t) J]; }  // (a run that starts inside a chunk starts its strip: slot 0)
+                ++nruns[(size_t) J];
+                curJ = J;
+            }
+        }
+    }
+    sw.max_runs = 1;
+    for (const int r : nruns) { sw.max_runs = std::max(sw.max_runs, r); }
+    // owned column strips per row block, ascending
+    std::vector<std::vector<int>> per_row((size_t) T_r);
+    for (const int4 &e : list) { per_row[(size_t) e.x].push_back(e.y); }  // list is sorted by J: every per_row list comes out ascending
+    std::vector<int> jptr((size_t) T_r + 1, 0), jlist;
+    jlist.reserve((size_t) nt);
+    for (int I = 0; I < T_r; ++I) {
+        jptr[(size_t) I] = (int) jlist.size();
+        jlist.insert(jlist.end(), per_row[(size_t) I].begin(), per_row[(size_t) I].end());
+    }
+    jptr[(size_t) T_r] = (int) jlist.size();
+    const auto up = [&](dbuf &dst, const void *src, size_t bytes) {
+        dst.reserve(std::max<size_t>(bytes, 16));
+        if (bytes != 0) { B200_CUDA_CHECK(cudaMemcpyAsync(dst.p, src, bytes, cudaMemcpyHostToDevice, c.stream)); }
+    };
+    up(sw.list, list.data(), list.size() * sizeof(int4));
+    up(sw.first_slot, first_slot.data(), first_slot.size() * sizeof(int));
+    up(sw.nruns, nruns.data(), nruns.size() * sizeof(int));
+    up(sw.jptr, jptr.data(), jptr.size() * sizeof(int));
+    up(sw.jlist, jlist.data(), jlist.size() * sizeof(int));
+    B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));  // the host vectors must outlive the copies
+}
+
 struct tc_state {
     CUtensorMap map_hi{}, map_lo{}, map_a8{}, map_b8{};
     dbuf tiles, pk, Pr, Pc, amax, P8a, P8b, own, Kc;
+    sweep_plan sweep;
     bool has_own{ false };
     bool kc_valid{ false }, kc_refused{ false };  // cached kernel-matrix tiles of this rank
     bool fp8x{ false };
@@ -748,6 +886,7 @@ void tc_prepare_split(ctx &c) {
         st.own.reserve(own_map.size());
         B200_CUDA_CHECK(cudaMemcpyAsync(st.own.p, own_map.data(), own_map.size(), cudaMemcpyHostToDevice, c.stream));
     }
+    build_sweep_plan(c, st.sweep, tiles, st.T_r, st.T_c);
     st.pk.reserve((size_t) c.n_pad * sizeof(float4));
     st.Pr.reserve((size_t) st.T_c * st.ldP * sizeof(float));
     st.Pc.reserve((size_t) st.T_r * st.ldP * sizeof(float));
@@ -807,8 +946,11 @@ void launch_gram(ctx &c, tc_state &st, const tc::params &p) {
 
 }  // namespace
 
-// out[i] = sum_j (k(x_i, x_j) + QA_cost - q_i - q_j) d_j  over the tiles owned by this rank (all tiles when world == 1)
-void tc_kernel_matvec(ctx &c, const float *d, float *out) {
+void *tc_pack_buffer(ctx &c) { return tc_available(c) ? state_of(c).pk.p : nullptr; }
+
+// out[i] = sum_j (k(x_i, x_j) + QA_cost - q_i - q_j) d_j  over the tiles owned by this rank (all tiles when world == 1);
+// push != nullptr: the sums go into slot `rank` of every peer's exchange buffer instead (the reduction kernel is the producer)
+void tc_kernel_matvec(ctx &c, const float *d, float *out, bool packed, const xchg_push *push, const float *done) {
     if (!tc_available(c)) { fail(B200SVM_ERR_INVALID, "tcgen05 matvec path requested but the fp16 operand planes are not prepared"); }
     tc_state &st = state_of(c);
     const int64_t m = c.m();
@@ -827,7 +969,7 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out) {
     p.degree = c.degree;
     p.kernel = c.kernel;
     p.Kc = nullptr;
-    p.done = c.scal.as<float>() + S_DONE;
+    p.done = done;
     float cscale = 0.f;
     if (c.kernel == B200SVM_RBF) {
         p.w = (float) (2.0 * c.gamma * (double) LOG2E / (double) s2);
@@ -835,7 +977,10 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out) {
     } else {
         p.w = (float) (c.gamma / (double) s2);
     }
-    tc::k_pack<<<(unsigned) ((c.n_pad + 255) / 256), 256, 0, c.stream>>>(c.norms.as<float>(), c.q.as<float>(), d, m, c.n_pad, cscale, st.pk.as<float4>());
+    if (!packed) {  // (inside the CG loop the direction update keeps the packed operand current: cg.cu)
+        tc::k_pack<<<(unsigned) ((c.n_pad + 255) / 256), 256, 0, c.stream>>>(c.norms.as<float>(), c.q.as<float>(), d, m, c.n_pad, cscale, st.pk.as<float4>());
+        count_launch(c);
+    }
     // The kernel values depend only on the data: when the tiles of this rank fit in HBM they are stored once (one pass of the
     // tcgen05 kernel in STORE mode, which also reduces against d: the assembling matvec needs no sweep) and every later matvec is
     // an HBM-bound sweep over them.
@@ -865,17 +1010,33 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out) {
         }
     }
     if (c.opt_dense_cache == 1) { st.kc_valid = false; }
-    if (st.kc_valid && !assembled_now) {  // (the STORE pass has already filled Pr / Pc for this d)
-        const int grid = std::min(st.num_tiles, 4 * NUM_SMS);
-        tc::k_cached_gemv<<<grid, 256, 0, c.stream>>>(st.Kc.as<float>(), p);
-        count_launch(c);
-        B200_CUDA_CHECK(cudaGetLastError());
-    } else if (!st.kc_valid) {
-        launch_gram<false>(c, st, p);
+    tc::reduce_dst dst{};
+    dst.out = out;
+    dst.remote = push != nullptr ? 1 : 0;
+    if (push != nullptr) { dst.push = *push; }
+    const unsigned rgrid = (unsigned) ((m + 255) / 256);
+    const bool swept = st.kc_valid && !assembled_now;  // (the STORE pass has already filled Pr / Pc for this d)
+    if (swept) {
+        tc::sweep_params sp{};
+        sp.Kc = st.Kc.as<float>();
+        sp.list = st.sweep.list.as<int4>();
+        sp.num_tiles = st.num_tiles;
+        sp.nchunks = st.sweep.nchunks;
+        sp.first_slot = st.sweep.first_slot.as<int>();
+        sp.pk = p.pk;
+        sp.Pr = p.Pr;
+        sp.Pc = p.Pc;
+        sp.ldP = p.ldP;
+        sp.qa = p.qa;
+        sp.done = done;
+        tc::k_tile_sweep<true><<<st.sweep.nchunks, 256, 0, c.stream>>>(sp);
+        tc::k_sweep_reduce<<<rgrid, 256, 0, c.stream>>>(p.Pr, p.Pc, p.ldP, m, st.sweep.jptr.as<int>(), st.sweep.jlist.as<int>(), st.sweep.nruns.as<int>(), dst,
+                                                        done);
+    } else {
+        if (!st.kc_valid) { launch_gram<false>(c, st, p); }
+        tc::k_tc_reduce<<<rgrid, 256, 0, c.stream>>>(p.Pr, p.Pc, p.ldP, m, st.T_r, st.T_c, st.has_own ? st.own.as<uint8_t>() : nullptr, dst, done);
     }
-    tc::k_tc_reduce<<<(unsigned) ((m + 255) / 256), 256, 0, c.stream>>>(st.Pr.as<float>(), st.Pc.as<float>(), st.ldP, m, st.T_r, st.T_c,
-                                                                        st.has_own ? st.own.as<uint8_t>() : nullptr, out, p.done);
-    count_launch(c, 2);
+    count_launch(c, swept ? 2 : 1);
     B200_CUDA_CHECK(cudaGetLastError());
 }
 

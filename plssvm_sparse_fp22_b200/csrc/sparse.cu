@@ -1356,11 +1356,12 @@ void sp_generate_q(ctx &c) {
 template void sp_generate_q<float>(ctx &);
 template void sp_generate_q<double>(ctx &);
 
-// out[0..m) = K d over the reduced system for the rows owned by this rank (zero elsewhere when world > 1); un-centred:
+// out[lo..hi) = K d over the reduced system for the rows owned by this rank (zero elsewhere when zero_rest); un-centred:
 // the caller adds (QA_cost - q_i) sum(d) - q.d + d_i / C (k_abar_finish, centre mode 2).
 template <typename T>
-void sp_kernel_matvec(ctx &c, const T *d, T *out) {
+bool sp_kernel_matvec(ctx &c, const T *d, T *out, bool zero_rest, const T *done) {
     sparse_state &st = state_of(c);
+    (void) done;  // (the sparse kernels read scal[S_DONE] themselves; it is cleared by the caller outside the CG loop)
     const int64_t m = c.m();
     int64_t lo = 0, hi = m;
     partition_rows(m, c.rank, c.world, &lo, &hi);
@@ -1369,9 +1370,9 @@ void sp_kernel_matvec(ctx &c, const T *d, T *out) {
     if (c.kernel == B200SVM_LINEAR) {
         weights<T>(c, d, static_cast<const T *>(nullptr), m, nbW, v);
         xt_v_blocks<T>(c, st, v, st.wvec.as<T>());
-        if (c.world > 1) { B200_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t) m * sizeof(T), c.stream)); }
+        if (zero_rest) { B200_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t) m * sizeof(T), c.stream)); }
         row_dot<T>(c, st, view_rows(st, lo, hi), st.wvec.as<T>(), T(0), out + lo);
-        return;
+        return true;
     }
     const bool rbf = c.kernel == B200SVM_RBF;
     weights<T>(c, d, rbf ? st.u.as<T>() : static_cast<const T *>(nullptr), m, nbW, v);
@@ -1391,12 +1392,13 @@ void sp_kernel_matvec(ctx &c, const T *d, T *out) {
     const sp::kfun kf = make_kfun(c);
     int64_t g = std::max<int64_t>(1, std::min<int64_t>((m + 1023) / 1024, 8 * NUM_SMS));
     sp::k_sp_finish<T><<<(unsigned) g, 256, 0, c.stream>>>(out, st.u.as<T>(), m, lo, hi, rbf ? 1 : 0, (T) kf.c0pow, c.scal.as<T>(), S_TMP0, T(0),
-                                                           c.world > 1 ? 1 : 0);
+                                                           zero_rest ? 1 : 0);
     count_launch(c);
     B200_CUDA_CHECK(cudaGetLastError());
+    return true;
 }
-template void sp_kernel_matvec<float>(ctx &, const float *, float *);
-template void sp_kernel_matvec<double>(ctx &, const double *, double *);
+template bool sp_kernel_matvec<float>(ctx &, const float *, float *, bool, const float *);
+template bool sp_kernel_matvec<double>(ctx &, const double *, double *, bool, const double *);
 
 // w[f] = sum_i alpha_i x_i[f] over all n rows   (src/plssvm/backends/OpenMP/csvm.cpp:173-188)
 template <typename T>
