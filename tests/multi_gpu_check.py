@@ -13,6 +13,63 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
+def stress(torch, dist, capi, datagen, port, rank, world, local, fresh_uid):
+    """Peer-exchange protocol under skew (xchg.cuh): look-ahead 8, convergence at eps = 1e-3 (queued iterations and their exchanges
+    are skipped on the device), 50 back-to-back solves per handle while one rank after the other is delayed on the device
+    (a spinning kernel in front of its solve) and on the host.  Every solve must return the oracle's iteration count and an alpha
+    that is bit-identical on all ranks and bit-identical to the handle's second solve (the first one assembles the caches and has
+    its own summation order)."""
+    import time
+    ok = True
+    stream = torch.cuda.current_stream()
+    for name, dt, kernel, n, F, mode in (("tc", np.float32, "rbf", 1500, 96, "tc"), ("csr", np.float64, "rbf", 1300, 900, "csr"),
+                                         ("simt", np.float64, "polynomial", 700, 33, "dense")):
+        if mode == "csr":
+            rp, ci, v, y = datagen.make_sparse_csr(n, F, 0.02, seed=n, dtype=dt)
+            X = datagen.csr_to_dense(rp, ci, v, F)
+        else:
+            X, y = datagen.make_dense(n, F, seed=n, problem="planes", dtype=dt)
+        a_o, rho_o, it_o = port.learn(X.astype(np.float64), y.astype(np.float64), kernel, eps=1e-3, use_rows=True)
+        with capi.Handle(dt, kernel, gamma=1.0 / F, device=local) as h:
+            h.set_stream(stream.cuda_stream)
+            h.set_option(capi.OPT_SYNC_EVERY, 8)
+            if mode == "tc":
+                h.set_option(capi.OPT_MATVEC_PATH, capi.PATH_TC)
+            h.set_option(capi.OPT_PEER_EXCHANGE, 2)  # required: this is the protocol under test
+            h.comm_init(fresh_uid(), rank, world)
+            if mode == "csr":
+                h.set_option(capi.OPT_SPARSE_BLOCK, 256)
+                h.set_data_csr(rp, ci, v, F)
+            else:
+                h.set_data(X)
+            first = None
+            bad = 0
+            for k in range(50):
+                if rank == k % world:
+                    torch.cuda._sleep(int(3e7))      # ~15 ms of device time in front of this rank's solve
+                if rank == (k + 1) % world:
+                    time.sleep(0.003)                # and a late host on another rank
+                alpha, rho, it = h.learn(y, eps=1e-3)
+                if k == 1:
+                    first = alpha.copy()
+                t = torch.from_numpy(alpha.astype(np.float64)).cuda()
+                ref = t.clone()
+                dist.broadcast(ref, 0)
+                same_ranks = bool(torch.equal(t, ref))
+                same_solves = k < 1 or bool(np.array_equal(alpha, first))
+                err = float(np.linalg.norm(alpha.astype(np.float64) - a_o) / np.linalg.norm(a_o))
+                if not (it == it_o and same_ranks and same_solves and err < (1e-10 if dt == np.float64 else 5e-3)):
+                    bad += 1
+                    if rank == 0 or not same_ranks:
+                        print(f"[stress {name}] rank {rank} solve {k}: iters={it}/{it_o} same_ranks={same_ranks} same_solves={same_solves} err={err:.2e}", flush=True)
+            st = h.stats()
+        good = bad == 0 and st.peer_exchanges > 0
+        ok &= good
+        if rank == 0:
+            print(f"[{world} ranks] stress {name:5s} look-ahead 8, 50 solves, delayed ranks: peer_exchanges={st.peer_exchanges} -> {'OK' if good else 'FAIL'}", flush=True)
+    return ok
+
+
 def main():
     import torch
     import torch.distributed as dist
@@ -85,6 +142,7 @@ def main():
         if rank == 0:
             print(f"[{world} ranks] {kernel:10s} {np.dtype(dt).name} {variant:8s} path={st.matvec_path} cached={st.sparse_cache_entries} iters={it}/{it_o} alpha_relerr={err:.2e} "
                   f"identical_across_ranks={same} collectives={st.collectives} peer={st.peer_exchanges} -> {'OK' if good else 'FAIL'}", flush=True)
+    ok &= stress(torch, dist, capi, datagen, port, rank, world, local, fresh_uid)
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()
