@@ -122,6 +122,7 @@ int b200svm_partition_tiles(int64_t n, int rank, int world, int64_t *first, int6
 #define B200SVM_OPT_SPARSE_CACHE_MB 9 /* memory budget of the S cache / the dense kernel-matrix cache in MiB (0 = 85 % of the free device memory) */
 #define B200SVM_OPT_PEER_EXCHANGE 11 /* multi-GPU sum of the matvec partials: 0 = stores into CUDA-IPC mapped peer buffers over NVLink, summed in rank order by the O(m) epilogue (falls back to NCCL if the peers cannot be mapped), 1 = ncclAllReduce, 2 = peer exchange required; set before comm_init */
 #define B200SVM_OPT_DENSE_CACHE 10 /* dense float polynomial / rbf (tcgen05 path): 0 = store the kernel-matrix tiles on first use if they fit (later matvecs are HBM-bound sweeps), 1 = never (recompute every matvec on the tensor cores), 2 = required */
+#define B200SVM_OPT_SPARSE_TILES 12 /* CSR paths, float handles: keep a densely filled S as dense 128 x 256 lower-triangle tiles (4 bytes per stored entry, half the matrix, no indices) swept like the dense kernel-matrix cache: 0 = when the expected fill is >= 0.4, 1 = never, 2 = always */
 #define B200SVM_OPT_SPARSE_BLOCK 3 /* CSR paths: columns of the implicit matrix per block (power of two, 128..32768, default 8192; set before set_data_csr) */
 int b200svm_set_option(b200svm_handle h, int option, int64_t value);
 

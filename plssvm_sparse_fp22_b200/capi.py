@@ -18,6 +18,7 @@ KERNELS = {"linear": 0, "polynomial": 1, "rbf": 2}
 VAL_F32, VAL_F64, VAL_FP22 = 0, 1, 2
 OPT_MATVEC_PATH, OPT_SYNC_EVERY, OPT_SPARSE_BLOCK, OPT_SPARSE_GROUP, OPT_SPARSE_LANES, OPT_TC_MODE, OPT_SPARSE_THREADS = 1, 2, 3, 4, 5, 6, 7
 OPT_SPARSE_CACHE, OPT_SPARSE_CACHE_MB, OPT_DENSE_CACHE, OPT_PEER_EXCHANGE = 8, 9, 10, 11
+OPT_SPARSE_TILES = 12
 CACHE_AUTO, CACHE_OFF, CACHE_REQUIRED = 0, 1, 2
 TC_F16X3, TC_FP8X = 1, 2
 PATH_AUTO, PATH_SIMT, PATH_TC = 0, 1, 2

@@ -234,6 +234,11 @@ int b200svm_set_option(b200svm_handle h, int option, int64_t value) {
                 c->opt_dense_cache = value;
                 tc_invalidate_cache(*c);
                 break;
+            case B200SVM_OPT_SPARSE_TILES:
+                B200_REQUIRE(value >= 0 && value <= 2, "sparse tile store mode must be 0 (auto), 1 (never) or 2 (always)");
+                c->opt_sparse_tiles = value;
+                sp_invalidate_cache(*c);
+                break;
             case B200SVM_OPT_SPARSE_GROUP:
                 B200_REQUIRE(value >= 0, "blocks per group must be >= 0");
                 c->opt_sparse_group = value;

@@ -698,8 +698,6 @@ __global__ void __launch_bounds__(256) k_sweep_reduce(const float *__restrict__ 
 // ---------------------------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------------------------
-namespace {
-
 // sweep over stored tiles: the rank's tiles sorted by (strip, row block), cut into chunks (one per CTA), and what the reduction
 // kernel needs to find the partial vectors (k_tile_sweep / k_sweep_reduce)
 struct sweep_plan {
@@ -750,6 +748,8 @@ void build_sweep_plan(ctx &c, sweep_plan &sw, const std::vector<int2> &tiles, in
     up(sw.jlist, jlist.data(), jlist.size() * sizeof(int));
     B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));  // the host vectors must outlive the copies
 }
+
+namespace {
 
 struct tc_state {
     CUtensorMap map_hi{}, map_lo{}, map_a8{}, map_b8{};
@@ -1037,6 +1037,116 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out, bool packed, const xch
         tc::k_tc_reduce<<<rgrid, 256, 0, c.stream>>>(p.Pr, p.Pc, p.ldP, m, st.T_r, st.T_c, st.has_own ? st.own.as<uint8_t>() : nullptr, dst, done);
     }
     count_launch(c, swept ? 2 : 1);
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Symmetric tile store for the sparse path: when S = f(X X^T) of a CSR data set is densely filled, it is kept as
+// dense 128 x 256 tiles of the lower block triangle (4 bytes per stored entry, no indices, half the matrix) and the CG matvec is
+// the same HBM-bound sweep as for dense data (k_tile_sweep<false>: un-centred, the rank-1 part is added by the O(m) epilogue).
+// Row blocks are dealt to the ranks in contiguous ranges of equal tile count; storage index = position in the row-block-major
+// list, so sparse.cu can address tile (I, J) of a row without a table: tile_store_cum(I) - tile_store_cum(I_lo) + J.
+// ---------------------------------------------------------------------------------------------------------------------
+struct tile_store {
+    sweep_plan sweep;
+    dbuf pk, Pr, Pc, Kc;
+    int T_r{ 0 }, T_c{ 0 };
+    int I_lo{ 0 }, I_hi{ 0 };
+    int64_t n_pad{ 0 }, ldP{ 0 };
+    int num_tiles{ 0 };
+};
+
+namespace tc {
+// pk[i] = {0, 0, w_i, 0} for i < m, zeros above
+__global__ void __launch_bounds__(256) k_pack_plain(const float *__restrict__ w, int64_t m, int64_t n_pad, float4 *__restrict__ pk) {
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pad) { return; }
+    pk[i] = make_float4(0.f, 0.f, i < m ? w[i] : 0.f, 0.f);
+}
+}  // namespace tc
+
+int64_t tile_store_cum(int64_t I) {  // tiles (I', J), 2 J <= I', of the row blocks I' < I
+    const int64_t k = I >> 1;
+    return (I & 1) ? (k + 1) * (k + 1) : k * (k + 1);
+}
+
+void tile_store_range(int64_t m, int rank, int world, int *I_lo, int *I_hi) {
+    const int64_t n_pad = (m + tc::BN - 1) / tc::BN * tc::BN;
+    const int T_r = (int) (n_pad / tc::BM);
+    const int64_t total = tile_store_cum(T_r);
+    const auto bound = [&](int r) {  // first row block whose cumulative tile count reaches r / world of the total
+        if (r <= 0) { return 0; }
+        if (r >= world) { return T_r; }
+        const int64_t want = total * r / world;
+        int I = 0;
+        while (I < T_r && tile_store_cum(I) < want) { ++I; }
+        return I;
+    };
+    *I_lo = bound(rank);
+    *I_hi = bound(rank + 1);
+}
+
+tile_store *tile_store_create(ctx &c, int64_t m) {
+    tile_store *ts = new tile_store();
+    ts->n_pad = (m + tc::BN - 1) / tc::BN * tc::BN;
+    ts->T_r = (int) (ts->n_pad / tc::BM);
+    ts->T_c = (int) (ts->n_pad / tc::BN);
+    ts->ldP = ts->n_pad;
+    tile_store_range(m, c.rank, c.world, &ts->I_lo, &ts->I_hi);
+    std::vector<int2> tiles;
+    for (int I = ts->I_lo; I < ts->I_hi; ++I) {
+        for (int J = 0; 2 * J <= I; ++J) { tiles.push_back(make_int2(I, J)); }
+    }
+    ts->num_tiles = (int) tiles.size();
+    try {
+        build_sweep_plan(c, ts->sweep, tiles, ts->T_r, ts->T_c);
+        ts->pk.reserve((size_t) ts->n_pad * sizeof(float4));
+        ts->Pr.reserve((size_t) ts->T_c * ts->ldP * sizeof(float));
+        ts->Pc.reserve((size_t) std::max(ts->sweep.max_runs, 1) * ts->ldP * sizeof(float));
+        B200_CUDA_CHECK(cudaMemsetAsync(ts->Pr.p, 0, ts->Pr.bytes, c.stream));
+        B200_CUDA_CHECK(cudaMemsetAsync(ts->Pc.p, 0, ts->Pc.bytes, c.stream));
+    } catch (...) {
+        delete ts;
+        throw;
+    }
+    return ts;
+}
+
+void tile_store_destroy(tile_store *ts) { delete ts; }
+int64_t tile_store_tiles(const tile_store *ts) { return ts->num_tiles; }
+size_t tile_store_bytes(const tile_store *ts) { return (size_t) ts->num_tiles * tc::BM * tc::BN * sizeof(float); }
+void tile_store_rows(const tile_store *ts, int64_t *row_lo, int64_t *row_hi, int64_t *first_tile) {
+    *row_lo = (int64_t) ts->I_lo * tc::BM;
+    *row_hi = (int64_t) ts->I_hi * tc::BM;
+    *first_tile = tile_store_cum(ts->I_lo);
+}
+float *tile_store_alloc(tile_store *ts) {
+    ts->Kc.reserve(std::max<size_t>(tile_store_bytes(ts), 16));
+    return ts->Kc.as<float>();
+}
+
+// out[i] = sum_j S_ij w_j over the tiles of this rank (a full-length partial vector when world > 1)
+void tile_store_matvec(ctx &c, tile_store *ts, const float *w, int64_t m, float *out, const float *done) {
+    tc::k_pack_plain<<<(unsigned) ((ts->n_pad + 255) / 256), 256, 0, c.stream>>>(w, m, ts->n_pad, ts->pk.as<float4>());
+    tc::sweep_params sp{};
+    sp.Kc = ts->Kc.as<float>();
+    sp.list = ts->sweep.list.as<int4>();
+    sp.num_tiles = ts->num_tiles;
+    sp.nchunks = ts->sweep.nchunks;
+    sp.first_slot = ts->sweep.first_slot.as<int>();
+    sp.pk = ts->pk.as<float4>();
+    sp.Pr = ts->Pr.as<float>();
+    sp.Pc = ts->Pc.as<float>();
+    sp.ldP = ts->ldP;
+    sp.qa = 0.f;
+    sp.done = done;
+    if (ts->num_tiles > 0) { tc::k_tile_sweep<false><<<ts->sweep.nchunks, 256, 0, c.stream>>>(sp); }
+    tc::reduce_dst dst{};
+    dst.out = out;
+    dst.remote = 0;
+    tc::k_sweep_reduce<<<(unsigned) ((m + 255) / 256), 256, 0, c.stream>>>(sp.Pr, sp.Pc, sp.ldP, m, ts->sweep.jptr.as<int>(), ts->sweep.jlist.as<int>(),
+                                                                          ts->sweep.nruns.as<int>(), dst, done);
+    count_launch(c, 3);
     B200_CUDA_CHECK(cudaGetLastError());
 }
 

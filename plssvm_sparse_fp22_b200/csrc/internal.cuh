@@ -115,6 +115,7 @@ struct ctx {
     int64_t opt_sparse_cache_mb{ 0 }; // 0 = 85 % of the free memory (both caches)
     int64_t opt_peer_exchange{ 0 };   // multi-GPU: 0 = peer-memory exchange if the peers can be mapped, 1 = NCCL allreduce, 2 = required
     int64_t opt_dense_cache{ 0 };     // tcgen05 path: 0 = auto, 1 = off, 2 = required
+    int64_t opt_sparse_tiles{ 0 };    // CSR paths, float: dense-tile store of a densely filled S: 0 = auto (expected fill >= 0.4), 1 = never, 2 = always
 
     // data
     bool has_data{ false };
@@ -198,6 +199,17 @@ void tc_invalidate_cache(ctx &c);  // drop the cached kernel-matrix tiles (optio
 // (written by the CG direction kernel).  push != nullptr: the partial-vector reduction stores into the peers instead of `out`.
 void tc_kernel_matvec(ctx &c, const float *d, float *out_Kd, bool packed, const xchg_push *push, const float *done);
 void *tc_pack_buffer(ctx &c);                                     // float4 pk[n_pad] of the tcgen05 path (nullptr when not prepared)
+
+// symmetric tile store (gram_tc.cu): a densely filled S of a CSR data set as dense lower-triangle tiles, swept like the dense cache
+struct tile_store;
+tile_store *tile_store_create(ctx &c, int64_t m);          // plan for c.rank / c.world (contiguous row-block ranges of equal tile count)
+void tile_store_destroy(tile_store *ts);
+int64_t tile_store_tiles(const tile_store *ts);
+size_t tile_store_bytes(const tile_store *ts);             // bytes of the stored tiles of this rank
+void tile_store_rows(const tile_store *ts, int64_t *row_lo, int64_t *row_hi, int64_t *first_tile);  // rows of this rank (multiples of 128), storage offset
+int64_t tile_store_cum(int64_t I);                         // tiles of the row blocks < I; tile (I, J) is stored at cum(I) - first_tile + J
+float *tile_store_alloc(tile_store *ts);                   // [tiles][64 column quads][128 rows] float4 (kc_quad_index layout)
+void tile_store_matvec(ctx &c, tile_store *ts, const float *w, int64_t m, float *out, const float *done);
 
 // sparse path (sparse.cu)
 void sp_invalidate_cache(ctx &c);  // drop the cached S (options changed); rebuilt on the next matvec

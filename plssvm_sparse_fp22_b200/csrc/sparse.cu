@@ -297,6 +297,9 @@ constexpr int SP_MAX_OWN = 4;  // stored entries of a row per thread: rows of up
 // MODE 3: one-pass assembly: the visit reserves its (padded) entries with one atomicAdd on a cursor (capacity = an upper bound
 //         known from the column counts) and stores them at once; ptr / cnt describe where.  Which visit lands where depends on
 //         the schedule, what it stores does not: the SpMV result is unchanged.
+// MODE 4: dense-tile assembly (float, S densely filled): row i stores S(G_ij) of ALL columns j below the end of its
+//         diagonal 256-column strip into the 128 x 256 tiles (I = i / 128, J = j / 256) of the lower block triangle, in the
+//         quad-column-major layout the tile sweep reads (kc_quad_index of gram_tc.cu); blocks above the diagonal strip are skipped.
 struct cache_view {
     int64_t *ptr;   // [nb * rows + 1] first entry of a visit
     int32_t *cnt;   // [nb * rows] entries of a visit (multiple of 4)
@@ -305,13 +308,21 @@ struct cache_view {
     int64_t rows;   // rows of the implicit matrix held by this rank
     unsigned long long *cursor;  // MODE 3: next free entry; cursor[1] != 0: capacity exceeded
     int64_t capacity;
+    float *Kc;      // MODE 4: tiles of this rank, storage index of tile (I, J) = cum(I) - tile0 + J
+    int64_t tile0;
 };
+
+__device__ __forceinline__ int64_t tile_cum(int64_t I) {  // = tile_store_cum (gram_tc.cu)
+    const int64_t k = I >> 1;
+    return (I & 1) ? (k + 1) * (k + 1) : k * (k + 1);
+}
 
 template <typename T, int KERNEL, bool FP22, bool COMPACT, int MODE>
 __global__ void __launch_bounds__(1024)
     k_sp_kmv(csr_view A, int64_t row_lo, int64_t row_hi, csc_view B, int g, int rmax, int gs_log2, int thr, const T *__restrict__ v, kfun kf,
              T *__restrict__ out, cache_view cache, const T *__restrict__ done) {
-    static_assert(MODE == 0 || COMPACT, "the cache passes work from the compacted slot list");
+    static_assert(MODE == 0 || MODE == 4 || COMPACT, "the indexed cache passes work from the compacted slot list");
+    static_assert(MODE != 4 || (!COMPACT && sizeof(T) == 4), "dense tiles: float, every slot evaluated");
     if (*done != T(0)) { return; }  // CG convergence flag (scal[S_DONE]); uniform over the grid
     extern __shared__ __align__(16) unsigned char sp_smem[];
     __shared__ int wtot[32];
@@ -344,7 +355,10 @@ __global__ void __launch_bounds__(1024)
     for (int64_t row = row_lo + blockIdx.x; row < row_hi; row += gridDim.x) {
         const int64_t p0 = A.rowptr[row];
         const int R = (int) (A.rowptr[row + 1] - p0);
-        if (R == 0) { continue; }  // block-uniform
+        // MODE 4: columns below the end of the row's diagonal strip only; an empty row still has to store its zeros
+        const int64_t jmax = MODE == 4 ? 256 * ((row >> 8) + 1) : 0;
+        const int b1r = MODE == 4 ? (int) min((int64_t) b1, (jmax + W - 1) / W) : b1;
+        if (MODE == 4 ? b0 >= b1r : R == 0) { continue; }  // block-uniform
         // ---- the row: (feature, value) of every stored entry; entry k is owned by thread k % TT
         if constexpr (FP22) {
             int carry = 0;
@@ -394,7 +408,7 @@ __global__ void __launch_bounds__(1024)
         __syncthreads();
 
         T rowsum = T(0);
-        for (int b = b0; b < b1; ++b) {
+        for (int b = b0; b < b1r; ++b) {
             // ---- 1. prefetch the next block's segment ends; note the long segments of this block
             uint32_t nxt[SP_MAX_OWN];
 #pragma unroll
@@ -406,7 +420,7 @@ __global__ void __launch_bounds__(1024)
                     const uint32_t e1 = s1[k];
                     if ((int) (e1 - s0[k]) > thr) { longk[atomicAdd(&nlong_s, 1)] = (uint16_t) k; }
                     nxt[q] = e1;
-                    if (f >= 0 && b + 1 < b1) { nxt[q] = __ldg(B.ptrT + (int64_t) f * ldp + b + 2); }
+                    if (f >= 0 && b + 1 < b1r) { nxt[q] = __ldg(B.ptrT + (int64_t) f * ldp + b + 2); }
                 }
             }
             // ---- 2. products: GS lanes per segment; four segments x two entries in flight per lane and round
@@ -561,6 +575,21 @@ __global__ void __launch_bounds__(1024)
                         }
                     }
                 }
+            } else if constexpr (MODE == 4) {
+                const int64_t col_base = (int64_t) b * W;
+                const int ncols = (int) min((int64_t) W, jmax - col_base);  // multiple of 256 (W and jmax are)
+                const int rr = (int) (row & 127);
+                float4 *tiles = reinterpret_cast<float4 *>(cache.Kc) + (tile_cum(row >> 7) - cache.tile0) * (int64_t) (128 * 256 / 4);
+                for (int q4 = t; q4 < (ncols >> 2); q4 += TT) {
+                    const int jl = q4 << 2;
+                    float sv[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) { sv[u] = s_value<T, KERNEL>(FX::take(acc, W, jl + u, fx_inv, lb), kf); }
+                    const int64_t col = col_base + jl;
+                    // consecutive rows (other CTAs, same time) fill the neighbouring 16 bytes: the sectors merge in L2
+                    __stcg(tiles + (col >> 8) * (int64_t) (128 * 256 / 4) + (int64_t) (((int) (col & 255)) >> 2) * 128 + rr, make_float4(sv[0], sv[1], sv[2], sv[3]));
+                }
+                for (int jl = ncols + t; jl < W; jl += TT) { (void) FX::take(acc, W, jl, fx_inv, lb); }  // slots above the diagonal strip
             } else {
                 for (int jl0 = t; jl0 < W; jl0 += 4 * TT) {  // four slots per thread in flight (the weights come from L2)
                     T gv[4], vv[4];
@@ -808,12 +837,13 @@ __global__ void __launch_bounds__(256) k_sp_weights(const T *__restrict__ d, con
     if (grid_sum<T, 1>(acc, partials, ticket, red, res)) { scal[idx_sumv] = res[0]; }
 }
 
-// K v from the S-part:  rbf  out_i = u_i (sum_v + S_i) ; polynomial  out_i = c0^deg sum_v + S_i ;  (+ bias)
+// K v from the S-part:  rbf  out_i = u_i (sum_v + S_i) ; polynomial  out_i = c0^deg sum_v + S_i ;  (+ bias)   [linear in S_i]
 // rows [lo, hi) only; the rest of [0, rows) is zeroed when ZERO_REST (multi-GPU partial vectors)
 template <typename T>
 __global__ void __launch_bounds__(256) k_sp_finish(T *__restrict__ S, const T *__restrict__ u, int64_t rows, int64_t lo, int64_t hi, int rbf, T c0pow,
-                                                   const T *__restrict__ scal, int idx_sumv, T bias, int zero_rest) {
-    const T sumv = scal[idx_sumv];
+                                                   const T *__restrict__ scal, int idx_sumv, T bias, int zero_rest, int add_sumv) {
+    // add_sumv == 0: a tile-partitioned partial vector of another rank than 0 — the rank-1 term is added once, by rank 0
+    const T sumv = add_sumv ? scal[idx_sumv] : T(0);
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < rows; i += (int64_t) gridDim.x * blockDim.x) {
         if (i >= lo && i < hi) {
             S[i] = bias + (rbf ? u[i] * (sumv + S[i]) : fma(c0pow, sumv, S[i]));
@@ -853,6 +883,11 @@ struct sparse_state {
     double sum_cf2{ 0 };  // sum over the features of (rows containing it)^2 = Gram products of a full matvec
     bool c_valid{ false }, c_refused{ false };
     int64_t c_lo{ 0 }, c_hi{ 0 }, c_entries{ 0 };
+    // ... or, when S is densely filled (float): dense lower-triangle tiles swept like the dense kernel-matrix cache
+    tile_store *ts{ nullptr };
+    bool t_valid{ false }, t_refused{ false };
+    int t_rank{ -1 }, t_world{ 0 };
+    ~sparse_state() { tile_store_destroy(ts); }
     // predict staging
     dbuf p_rowptr, p_col, p_val, p_norms, p_u, p_out, p_stats;
 };
@@ -902,6 +937,9 @@ void kmv_set_smem(int smem) {
     B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, KERNEL, FP22, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, KERNEL, FP22, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, KERNEL, FP22, true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    if constexpr (sizeof(T) == 4) {
+        B200_CUDA_CHECK(cudaFuncSetAttribute(sp::k_sp_kmv<T, KERNEL, FP22, false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    }
 }
 
 template <typename T>
@@ -939,7 +977,12 @@ void set_data_typed(ctx &c, const int64_t *rowptr, const int32_t *colidx, const 
     st.F = F;
     st.c_valid = false;
     st.c_refused = false;
+    st.t_valid = false;
+    st.t_refused = false;
+    tile_store_destroy(st.ts);
+    st.ts = nullptr;
     c.stats.sparse_cache_entries = 0;
+    c.stats.dense_cache_bytes = 0;
     const int64_t entries = rowptr[n];
     B200_REQUIRE(entries < (int64_t) 0xFFFF0000ll, "more than 2^32 - 2^16 stored entries are not supported by the sparse path");
     st.a_max_row = 0;
@@ -1071,7 +1114,10 @@ void sp_invalidate_cache(ctx &c) {
         sparse_state &st = state_of(c);
         st.c_valid = false;
         st.c_refused = false;
+        st.t_valid = false;
+        st.t_refused = false;
         c.stats.sparse_cache_entries = 0;
+        c.stats.dense_cache_bytes = 0;
     }
 }
 
@@ -1156,7 +1202,7 @@ void launch_kmv_variant(ctx &c, const sparse_state &st, const sp::csr_view &A, i
     set_kmv_attributes<T>(smem);
     const int per_sm = (int) std::max<size_t>(1, std::min<size_t>((size_t) 2048 / (size_t) threads, (size_t) (227 * 1024) / (smem + 1024)));
     const int grid = (int) std::min<int64_t>((int64_t) NUM_SMS * per_sm, rows);
-    const bool compact = mode != 0 || st.fill < 0.5;
+    const bool compact = (mode != 0 && mode != 4) || (mode == 0 && st.fill < 0.5);
     // lanes per (feature, block) segment: the power of two next to the mean segment length (option: fixed)
     int gs_log2 = 0;
     if (c.opt_sparse_lanes > 0) {
@@ -1173,6 +1219,10 @@ void launch_kmv_variant(ctx &c, const sparse_state &st, const sp::csr_view &A, i
             sp::k_sp_kmv<T, KERNEL, FP22, true, 2><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache, done);
         } else if (mode == 3) {
             sp::k_sp_kmv<T, KERNEL, FP22, true, 3><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache, done);
+        } else if (mode == 4) {
+            if constexpr (sizeof(T) == 4) {
+                sp::k_sp_kmv<T, KERNEL, FP22, false, 4><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache, done);
+            }
         } else if (compact) {
             sp::k_sp_kmv<T, KERNEL, FP22, true, 0><<<grid, threads, smem, c.stream>>>(A, lo, hi, B, g, rmax, gs_log2, thr, v, kf, out, cache, done);
         } else {
@@ -1276,6 +1326,60 @@ bool build_cache(ctx &c, sparse_state &st, int64_t lo, int64_t hi) {
     return true;
 }
 
+// Dense-tile store of S (float, densely filled).  Returns false when it does not apply or does not fit.
+template <typename T>
+bool build_tile_store(ctx &c, sparse_state &st) {
+    if constexpr (sizeof(T) != 4) {
+        return false;
+    } else {
+        const int64_t m = c.m();
+        // expected fill of S: sum_f c_f^2 / n^2 products per pair, hit with probability 1 - exp(-that); dense tiles cost 2 bytes per
+        // ordered pair, the indexed layout 6 bytes per hit: dense wins above a fill of 1 / 3
+        const double per_pair = st.n > 0 ? st.sum_cf2 / ((double) st.n * (double) st.n) : 0.0;
+        const double fill_est = 1.0 - std::exp(-per_pair);
+        const bool want = c.opt_sparse_tiles == 2 || (c.opt_sparse_tiles == 0 && fill_est >= 0.4);
+        if (!want || st.W < 256 || m < 1) { return false; }
+        if (st.ts == nullptr || st.t_rank != c.rank || st.t_world != c.world) {
+            tile_store_destroy(st.ts);
+            st.ts = nullptr;
+            st.ts = tile_store_create(c, m);
+            st.t_rank = c.rank;
+            st.t_world = c.world;
+        }
+        const size_t need = tile_store_bytes(st.ts);
+        size_t free_b = 0, total_b = 0;
+        B200_CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
+        const double budget = c.opt_sparse_cache_mb > 0 ? (double) c.opt_sparse_cache_mb * 1048576.0 : 0.85 * (double) free_b;
+        if ((double) need > budget) {
+            st.t_refused = true;
+            return false;
+        }
+        float *Kc = tile_store_alloc(st.ts);
+        int64_t row_lo = 0, row_hi = 0, tile0 = 0;
+        tile_store_rows(st.ts, &row_lo, &row_hi, &tile0);
+        if (c.cb_pending) { sync_stream(c); }
+        B200_CUDA_CHECK(cudaEventRecord(c.cb_ev[0], c.stream));
+        // rows >= m of the padded row blocks are never written: zero the tiles of those row blocks (they end this rank's storage)
+        const int64_t I0 = std::max(row_lo / 128, m / 128);
+        if (I0 * 128 < row_hi) {
+            const int64_t off = (tile_store_cum(I0) - tile0) * (int64_t) (128 * 256);
+            B200_CUDA_CHECK(cudaMemsetAsync(Kc + off, 0, need - (size_t) off * sizeof(float), c.stream));
+        }
+        sp::cache_view cv{};
+        cv.rows = 0;
+        cv.Kc = Kc;
+        cv.tile0 = tile0;
+        const sp::csr_view A = view_rows(st, 0, st.n);
+        launch_kmv<T>(c, st, A, row_lo, std::min(row_hi, m), st.a_max_row, st.max_norm2, static_cast<const T *>(nullptr), static_cast<T *>(nullptr), 4, cv);
+        B200_CUDA_CHECK(cudaEventRecord(c.cb_ev[1], c.stream));
+        c.cb_pending = true;
+        st.t_valid = true;
+        c.stats.dense_cache_bytes = (int64_t) need;
+        c.stats.sparse_cache_entries = tile_store_tiles(st.ts) * (int64_t) (128 * 256);
+        return true;
+    }
+}
+
 // out[lo..hi) = S v from the cache
 template <typename T>
 void cached_matvec(ctx &c, sparse_state &st, const T *v, T *out) {
@@ -1361,7 +1465,10 @@ template void sp_generate_q<double>(ctx &);
 template <typename T>
 bool sp_kernel_matvec(ctx &c, const T *d, T *out, bool zero_rest, const T *done) {
     sparse_state &st = state_of(c);
-    (void) done;  // (the sparse kernels read scal[S_DONE] themselves; it is cleared by the caller outside the CG loop)
+    // (the sparse kernels read scal[S_DONE] themselves; it is cleared by the caller outside the CG loop)
+    const float *done_flag = nullptr;
+    if constexpr (sizeof(T) == 4) { done_flag = done != nullptr ? done : c.scal.as<float>() + S_DONE; }
+    (void) done_flag;
     const int64_t m = c.m();
     int64_t lo = 0, hi = m;
     partition_rows(m, c.rank, c.world, &lo, &hi);
@@ -1377,6 +1484,24 @@ bool sp_kernel_matvec(ctx &c, const T *d, T *out, bool zero_rest, const T *done)
     const bool rbf = c.kernel == B200SVM_RBF;
     weights<T>(c, d, rbf ? st.u.as<T>() : static_cast<const T *>(nullptr), m, nbW, v);
     B200_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t) m * sizeof(T), c.stream));
+    // a densely filled S (float) is kept as dense lower-triangle tiles and swept like the dense kernel-matrix cache: the tiles
+    // (not the rows) are dealt to the ranks, the result is a full-length partial vector
+    if (c.opt_sparse_cache != 1) {
+        if (st.t_valid && (st.t_rank != c.rank || st.t_world != c.world)) { st.t_valid = false; }
+        if (!st.t_valid && !st.t_refused && !st.c_valid) { build_tile_store<T>(c, st); }
+    } else {
+        st.t_valid = false;
+    }
+    if (st.t_valid) {
+        if constexpr (sizeof(T) == 4) { tile_store_matvec(c, st.ts, v, m, out, done_flag); }
+        const sp::kfun kft = make_kfun(c);
+        const int64_t gt = std::max<int64_t>(1, std::min<int64_t>((m + 1023) / 1024, 8 * NUM_SMS));
+        sp::k_sp_finish<T><<<(unsigned) gt, 256, 0, c.stream>>>(out, st.u.as<T>(), m, 0, m, rbf ? 1 : 0, (T) kft.c0pow, c.scal.as<T>(), S_TMP0, T(0), 0,
+                                                                c.rank == 0 ? 1 : 0);
+        count_launch(c);
+        B200_CUDA_CHECK(cudaGetLastError());
+        return false;
+    }
     // S is cached on first use when it fits the memory budget (then the matvec is an HBM-bound SpMV), else recomputed on the fly
     if (c.opt_sparse_cache != 1 && hi > lo) {
         if (st.c_valid && (st.c_lo != lo || st.c_hi != hi)) { st.c_valid = false; }
@@ -1392,7 +1517,7 @@ bool sp_kernel_matvec(ctx &c, const T *d, T *out, bool zero_rest, const T *done)
     const sp::kfun kf = make_kfun(c);
     int64_t g = std::max<int64_t>(1, std::min<int64_t>((m + 1023) / 1024, 8 * NUM_SMS));
     sp::k_sp_finish<T><<<(unsigned) g, 256, 0, c.stream>>>(out, st.u.as<T>(), m, lo, hi, rbf ? 1 : 0, (T) kf.c0pow, c.scal.as<T>(), S_TMP0, T(0),
-                                                           zero_rest ? 1 : 0);
+                                                           zero_rest ? 1 : 0, 1);
     count_launch(c);
     B200_CUDA_CHECK(cudaGetLastError());
     return true;
@@ -1482,7 +1607,7 @@ void sp_predict(ctx &c, const T *alpha_dev, T bias, const int64_t *rowptr, const
             const sp::kfun kf = make_kfun(c);
             int64_t g = std::max<int64_t>(1, std::min<int64_t>((rows + 1023) / 1024, 8 * NUM_SMS));
             sp::k_sp_finish<T><<<(unsigned) g, 256, 0, c.stream>>>(st.p_out.as<T>(), st.p_u.as<T>(), rows, 0, rows, rbf ? 1 : 0, (T) kf.c0pow,
-                                                                   c.scal.as<T>(), S_TMP0, bias, 0);
+                                                                   c.scal.as<T>(), S_TMP0, bias, 0, 1);
             count_launch(c);
             B200_CUDA_CHECK(cudaGetLastError());
         }
