@@ -440,25 +440,35 @@ def run_main_workload(a, env):
     if sparse and world > 1:
         cache_entries = int(env.max_over_ranks([cache_entries])[0])  # the largest rank bounds the step
 
-    # ---- parity (N > 1): bit-identical alpha on every rank; distance to the single-GPU alpha of the same K steps ----
+    # ---- parity (N > 1): the configured solve (eps = 1e-3, imax = F) on N ranks and on one: bit-identical alpha on every rank, same
+    #      iteration count, norm-wise distance.  (The K fixed iterations of the timed solve run far past convergence — delta / delta0
+    #      reaches the float noise floor after 2-3 iterations — so their alpha is rounding noise and is not compared.)
     parity = None
     if world > 1:
-        t_alpha = torch.from_numpy(alpha.astype(np.float64)).cuda()
+        aN, itN, _ = h.solver_cg(b, None, QA, F, 1e-3)
+        t_alpha = torch.from_numpy(aN.astype(np.float64)).cuda()
         ref_alpha = t_alpha.clone()
         env.dist.broadcast(ref_alpha, 0)
         same = torch.tensor([1 if torch.equal(t_alpha, ref_alpha) else 0], device="cuda")
         env.dist.all_reduce(same, op=env.dist.ReduceOp.MIN)
-        dist1 = None
+        t_k = torch.from_numpy(alpha.astype(np.float64)).cuda()
+        ref_k = t_k.clone()
+        env.dist.broadcast(ref_k, 0)
+        same_k = torch.tensor([1 if torch.equal(t_k, ref_k) else 0], device="cuda")
+        env.dist.all_reduce(same_k, op=env.dist.ReduceOp.MIN)
+        dist1, it1 = None, None
         if rank == 0:
             with capi.Handle(dt, a.kernel, 3, 1.0 / F, 0.0, 1.0, device=env.local) as h1:
                 configure(h1)
                 set_data(h1)
                 h1.generate_q()
-                a1, it1, _ = h1.solver_cg(b, None, h1.kxx_last() + 1.0, K, 0.0)
-            dist1 = float(np.linalg.norm(alpha.astype(np.float64) - a1.astype(np.float64)) / np.linalg.norm(a1.astype(np.float64)))
+                a1, it1, _ = h1.solver_cg(b, None, h1.kxx_last() + 1.0, F, 1e-3)
+            dist1 = float(np.linalg.norm(aN.astype(np.float64) - a1.astype(np.float64)) / np.linalg.norm(a1.astype(np.float64)))
         env.barrier()
-        parity = {"alpha_bit_identical_across_ranks": bool(int(same[0]) == 1), "alpha_relerr_vs_single_gpu": dist1, "iterations": int(iters),
-                  "note": "norm-wise ||alpha_N - alpha_1|| / ||alpha_1|| after the same K fixed iterations (float: summation order differs with N)"}
+        parity = {"alpha_bit_identical_across_ranks": bool(int(same[0]) == 1), "alpha_of_the_timed_solve_bit_identical_across_ranks": bool(int(same_k[0]) == 1),
+                  "iterations": int(itN), "iterations_single_gpu": it1, "alpha_relerr_vs_single_gpu": dist1,
+                  "note": "solve at the configured eps = 1e-3 (imax = F) on N ranks vs one rank: norm-wise ||alpha_N - alpha_1|| / ||alpha_1|| "
+                          "(float: the summation order of the partial vectors differs with N)"}
 
     # ---- e2e leg: host buffers through the C ABI ----
     def e2e_once():
@@ -524,9 +534,10 @@ def run_main_workload(a, env):
             "collectives_per_step": (st.collectives / R / K) if world > 1 else 0, "peer_exchanges_per_step": (st.peer_exchanges / R / K) if world > 1 else 0,
             "cache_build_ms": build_ms,
             "breakdown_ms_per_solve": {"total": t_ms, "matvec_spans": matvec_total_ms, "of_which_cache_assembly": build_ms,
-                                       "cg_vector_kernels_and_gaps": t_ms - matvec_total_ms,
+                                       "cg_vector_kernels": st.cg_vector_ms / R, "cg_vector_kernel_ms_each": st.cg_vector_ms / max(int(st.cg_vector_timed), 1),
+                                       "launch_gaps_fill_copies": t_ms - matvec_total_ms - st.cg_vector_ms / R,
                                        "note": "rank 0, CUDA events inside libb200svm around every matvec (sweep + partial-vector reduction / peer push); "
-                                               "the rest is the cooperative CG step kernel (incl. waiting for the peers' slots), launch gaps and the initial fill / copies"},
+                                               "cg_vector_kernels = the fused CG step kernel (several ranks: incl. waiting for the peers' slots); the rest is launch gaps and the initial fill / copies"},
             "roofline": roof,
         }
         if parity is not None:

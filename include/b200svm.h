@@ -140,6 +140,8 @@ typedef struct b200svm_stats {
     double cache_build_ms;        /* device time spent assembling a kernel-matrix cache (dense tiles or sparse S); also inside matvec_ms */
     int64_t dense_cache_bytes;    /* dense tcgen05 path: bytes of kernel-matrix tiles cached on this rank (0 = recomputed every matvec) */
     int64_t sparse_cache_entries; /* CSR paths: stored entries of the cached S matrix on this rank (0 = recomputed on the fly) */
+    double cg_vector_ms;          /* accumulated device time of the O(m) vector kernels of the CG iterations (CUDA events; several ranks: includes waiting for the peers' slots) */
+    int64_t cg_vector_timed;      /* iterations included in cg_vector_ms */
 } b200svm_stats;
 int b200svm_get_stats(b200svm_handle h, b200svm_stats *out);
 int b200svm_reset_stats(b200svm_handle h);

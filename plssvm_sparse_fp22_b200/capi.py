@@ -48,6 +48,8 @@ class Stats(C.Structure):
         ("cache_build_ms", C.c_double),
         ("dense_cache_bytes", C.c_int64),
         ("sparse_cache_entries", C.c_int64),
+        ("cg_vector_ms", C.c_double),
+        ("cg_vector_timed", C.c_int64),
     ]
 
 

@@ -134,6 +134,7 @@ int b200svm_create(b200svm_handle *h, int dtype, int kernel, int degree, double 
         B200_CUDA_CHECK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
         c->stream = c->own_stream;
         for (auto &ev : c->ev) { B200_CUDA_CHECK(cudaEventCreate(&ev)); }
+        for (auto &ev : c->sv) { B200_CUDA_CHECK(cudaEventCreate(&ev)); }
         for (auto &ev : c->cg_ev) { B200_CUDA_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)); }
         for (auto &ev : c->cb_ev) { B200_CUDA_CHECK(cudaEventCreate(&ev)); }
         B200_CUDA_CHECK(cudaMallocHost(&c->pinned, 512));
@@ -165,6 +166,9 @@ int b200svm_destroy(b200svm_handle h) {
         if (ev != nullptr) { cudaEventDestroy(ev); }
     }
     for (auto &ev : c->cg_ev) {
+        if (ev != nullptr) { cudaEventDestroy(ev); }
+    }
+    for (auto &ev : c->sv) {
         if (ev != nullptr) { cudaEventDestroy(ev); }
     }
     for (auto &ev : c->cb_ev) {

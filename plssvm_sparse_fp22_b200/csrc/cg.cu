@@ -6,8 +6,6 @@
 // The host only reads one scalar (delta) per iteration for the stop test `delta <= eps^2 delta0` (csvm.cpp:145).
 #include "device_utils.cuh"
 
-#include <cooperative_groups.h>
-
 #include <algorithm>
 
 namespace b200 {
@@ -183,7 +181,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_cg_direction(T *__restrict__ d,
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// One ordinary CG iteration after the O(m^2) kernel as ONE cooperative kernel (csvm.cpp:121-155 without the refresh branch):
+// One ordinary CG iteration after the O(m^2) kernel as ONE kernel (csvm.cpp:121-155 without the refresh branch):
 //   A  Ad = sum of the partial vectors (+ centring, + d / C), d.Ad          [several ranks: wait for the peers' slots first]
 //   B  alpha_cd = delta / d.Ad ; x += alpha_cd d ; r -= alpha_cd Ad ; delta' = r.r ; stop flag
 //   C  beta = delta' / delta ; d = beta d + r (+ the packed operand of the tile kernels) ; sum d, q.d
@@ -196,7 +194,29 @@ struct step_args {
     finish_args<T> f;   // P / exchange view, d, q, m, inv_cost, qa, target, out = Ad, scal, partials ([4][MAX_PARTIAL_BLOCKS]), mailbox
     T *x, *r, *dvec;
     float4 *pk;
+    unsigned int *bar;  // grid barrier state (two words)
 };
+
+// Grid-wide barrier of a grid whose blocks are all co-resident (at most one per SM, launched alone on the stream): sense-reversing
+// and self-resetting, bar[0] = arrivals, bar[1] = generation.  A plain launch with this barrier measured faster than a
+// cooperative launch with grid.sync() (the cooperative launch itself costs ~30 us per iteration: profiles/r2_summary.md).
+__device__ __forceinline__ void grid_barrier(unsigned int *bar) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        volatile unsigned int *vbar = bar;
+        const unsigned int gen = vbar[1];
+        __threadfence();
+        if (atomicAdd(bar, 1u) == gridDim.x - 1) {
+            vbar[0] = 0u;
+            __threadfence();
+            atomicAdd(bar + 1, 1u);
+        } else {
+            while (vbar[1] == gen) {}
+        }
+        __threadfence();
+    }
+    __syncthreads();
+}
 
 // sum of `count` block partials in a fixed order; result in every thread of the block
 template <typename T>
@@ -215,8 +235,6 @@ __device__ __forceinline__ T total_of(const T *partials, int count, T *red) {
 
 template <typename T>
 __global__ void __launch_bounds__(VEC_THREADS) k_cg_step(const step_args<T> a) {
-    namespace cgx = cooperative_groups;
-    cgx::grid_group grid = cgx::this_grid();
     __shared__ T red[32];
     const finish_args<T> &f = a.f;
     if (f.scal[S_DONE] != T(0)) { return; }  // uniform over the grid: the flag is only written behind the last barrier of such a grid
@@ -243,7 +261,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_cg_step(const step_args<T> a) {
     }
     acc = block_sum(acc, red);
     if (threadIdx.x == 0) { f.partials[blockIdx.x] = acc; }
-    grid.sync();
+    grid_barrier(a.bar);
     const T dAd = total_of(f.partials, nblk, red);
     // ---- B
     const T alpha_cd = delta / dAd;  // csvm.cpp:125
@@ -256,7 +274,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_cg_step(const step_args<T> a) {
     }
     acc = block_sum(acc, red);
     if (threadIdx.x == 0) { f.partials[MAX_PARTIAL_BLOCKS + blockIdx.x] = acc; }
-    grid.sync();
+    grid_barrier(a.bar);
     const T delta_new = total_of(f.partials + MAX_PARTIAL_BLOCKS, nblk, red);
     // ---- C
     const T beta = delta_new / delta;  // csvm.cpp:153
@@ -273,7 +291,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_cg_step(const step_args<T> a) {
         if (threadIdx.x == 0) { f.partials[2 * MAX_PARTIAL_BLOCKS + blockIdx.x] = s0; }
         s1 = block_sum(s1, red);
         if (threadIdx.x == 0) { f.partials[3 * MAX_PARTIAL_BLOCKS + blockIdx.x] = s1; }
-        grid.sync();
+        grid_barrier(a.bar);
         if (blockIdx.x == 0) {
             s0 = total_of(f.partials + 2 * MAX_PARTIAL_BLOCKS, nblk, red);
             s1 = total_of(f.partials + 3 * MAX_PARTIAL_BLOCKS, nblk, red);
@@ -329,9 +347,22 @@ void drain_matvec_events(ctx &c, int64_t upto) {
     }
 }
 
+// account the (start, stop) pairs around the vector kernels of the iterations [sv_tail, upto): known to be complete
+static void drain_vector_events(ctx &c, int64_t upto) {
+    for (; c.sv_tail < upto; ++c.sv_tail) {
+        const int k = (int) (c.sv_tail % ctx::EV_RING);
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, c.sv[2 * k], c.sv[2 * k + 1]) == cudaSuccess) {
+            c.stats.cg_vector_ms += ms;
+            ++c.stats.cg_vector_timed;
+        }
+    }
+}
+
 void sync_stream(ctx &c) {
     B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));
     drain_matvec_events(c, c.ev_head);
+    drain_vector_events(c, c.sv_head);
     if (c.cb_pending) {
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, c.cb_ev[0], c.cb_ev[1]) == cudaSuccess) { c.stats.cache_build_ms += ms; }
@@ -492,10 +523,13 @@ void abar_finish(ctx &c, const kd_result &kd, const T *d, T add, T *out, T targe
     B200_CUDA_CHECK(cudaGetLastError());
 }
 
-// blocks of the cooperative CG step: all of them must be co-resident (at most one per SM is always safe)
-int step_grid(int64_t m) {
+// blocks of the CG step kernel: all of them must be co-resident for its grid barrier (at most one small block per SM always is)
+int step_grid(const ctx &c, int64_t m) {
+    static int sms[64] = {};
+    int &n = sms[c.device & 63];
+    if (n == 0 && cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, c.device) != cudaSuccess) { n = NUM_SMS; }
     const int64_t g = (m + VEC_THREADS * 4 - 1) / (VEC_THREADS * 4);
-    return (int) std::max<int64_t>(1, std::min<int64_t>(g, NUM_SMS));
+    return (int) std::max<int64_t>(1, std::min<int64_t>(g, std::min(n, NUM_SMS)));
 }
 
 template <typename T>
@@ -506,9 +540,8 @@ void cg_step(ctx &c, const kd_result &kd, T *x, T *r, T *d, T *Ad, T target, T *
     a.r = r;
     a.dvec = d;
     a.pk = pk;
-    void *args[] = { &a };
-    B200_CUDA_CHECK(cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(&k_cg_step<T>), dim3((unsigned) step_grid(a.f.m)), dim3(VEC_THREADS), args, 0,
-                                                c.stream));
+    a.bar = c.counters.as<unsigned int>() + 2;
+    k_cg_step<T><<<step_grid(c, a.f.m), VEC_THREADS, 0, c.stream>>>(a);
     count_launch(c);
 }
 
@@ -540,7 +573,7 @@ int64_t cg_solve(ctx &c, const T *b, int64_t imax, T eps, T *x, double *delta_ou
     T *partials = c.partials.as<T>();
     const T *done = scal + S_DONE;
     static const bool unfused = [] {
-        const char *e = std::getenv("B200SVM_CG_UNFUSED");  // A/B switch: three vector kernels per iteration instead of the cooperative step
+        const char *e = std::getenv("B200SVM_CG_UNFUSED");  // A/B switch: three vector kernels per iteration instead of the fused step
         return e != nullptr && e[0] == '1';
     }();
 
@@ -568,12 +601,13 @@ int64_t cg_solve(ctx &c, const T *b, int64_t imax, T eps, T *x, double *delta_ou
     // exchanges and their vector updates — into no-ops: alpha and delta are exactly those of the converged iteration whatever
     // `ahead` is.
     const int64_t ahead = std::min<int64_t>(c.opt_sync_every, ctx::CG_RING - 2);
-    int64_t marks[ctx::CG_RING] = {};
+    int64_t marks[ctx::CG_RING] = {}, vmarks[ctx::CG_RING] = {};
     int64_t converged = -1, polled = 0;
     const auto poll = [&](int64_t it) {
         const int slot = (int) (it % ctx::CG_RING);
         B200_CUDA_CHECK(cudaEventSynchronize(c.cg_ev[slot]));
         drain_matvec_events(c, marks[slot]);
+        drain_vector_events(c, vmarks[slot]);
         delta = *reinterpret_cast<volatile T *>(mailbox + 1 + slot);
         return delta <= target;
     };
@@ -583,6 +617,9 @@ int64_t cg_solve(ctx &c, const T *b, int64_t imax, T eps, T *x, double *delta_ou
             const int slot = (int) (run % ctx::CG_RING);
             // Ad = Abar d (:121-122) and d.Ad
             const kd_result kd = kernel_times_vector<T>(c, d, done, d_described, d_described && pk != nullptr);
+            const bool vtimed = c.sv_head - c.sv_tail < ctx::EV_RING && run % 50 != 49;
+            const int vslot = (int) (c.sv_head % ctx::EV_RING);
+            if (vtimed) { B200_CUDA_CHECK(cudaEventRecord(c.sv[2 * vslot], c.stream)); }
             if (run % 50 == 49) {
                 // x += alpha_cd d ; r = b - Abar x (:130-135)
                 abar_finish<T, 0>(c, kd, d, T(1), Ad);
@@ -602,9 +639,14 @@ int64_t cg_solve(ctx &c, const T *b, int64_t imax, T eps, T *x, double *delta_ou
                 cg_step<T>(c, kd, x, r, d, Ad, target, mailbox + 1 + slot, pk);
             }
             B200_CUDA_CHECK(cudaGetLastError());
+            if (vtimed) {
+                B200_CUDA_CHECK(cudaEventRecord(c.sv[2 * vslot + 1], c.stream));
+                ++c.sv_head;
+            }
             d_described = true;
             B200_CUDA_CHECK(cudaEventRecord(c.cg_ev[slot], c.stream));  // delta of this iteration has reached the mailbox
             marks[slot] = c.ev_head;
+            vmarks[slot] = c.sv_head;
             while (converged < 0 && polled + ahead <= run) {
                 if (poll(polled)) { converged = polled; }
                 ++polled;

@@ -165,6 +165,8 @@ struct ctx {
     static constexpr int EV_RING = 16;
     cudaEvent_t ev[2 * EV_RING]{};  // ring of (start, stop) pairs around the O(m^2) kernel, drained when known to be complete
     int64_t ev_head{ 0 }, ev_tail{ 0 };
+    cudaEvent_t sv[2 * EV_RING]{};  // ring of (start, stop) pairs around the O(m) vector kernels of a CG iteration
+    int64_t sv_head{ 0 }, sv_tail{ 0 };
     cudaEvent_t cb_ev[2]{};         // around the assembly of a kernel-matrix cache (dense tiles / sparse S)
     bool cb_pending{ false };
     static constexpr int CG_RING = 16;

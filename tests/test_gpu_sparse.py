@@ -331,3 +331,47 @@ def test_csr_errors_are_loud():
             h.set_data_csr(rp, np.array([0, 9, 0], np.int32), np.ones(3), 4)
         with pytest.raises(capi.B200Error, match="float handle"):
             h.set_data_csr(rp, None, np.ones(3, np.uint32), 4, value_format=capi.VAL_FP22)
+
+
+@pytest.mark.parametrize("kernel", ["polynomial", "rbf"])
+@pytest.mark.parametrize("shape", [(1100, 300, 0.05, 256), (2500, 200, 0.08, 1024), (3000, 150, 0.1, 0), (130, 60, 0.2, 256)])
+@pytest.mark.parametrize("fp22", [False, True])
+def test_csr_dense_tile_store_of_a_filled_S(kernel, shape, fp22):
+    """Float, S densely filled: S is kept as dense lower-triangle 128 x 256 tiles (B200SVM_OPT_SPARSE_TILES) and swept like the
+    dense kernel-matrix cache.  Against the oracle's CSR restatement and against the indexed cache on the same handle data."""
+    n, F, density, W = shape
+    rp, ci, v, y = make(n, F, density, seed=n + F, dt=np.float32, min_nnz=0)
+    fmt = None
+    if fp22:
+        v = datagen.fp22_round(v)
+        rp_s, v_s = datagen.pack_fp22_csr(rp, ci, v)
+        ci_s, fmt = None, capi.VAL_FP22
+    else:
+        rp_s, ci_s, v_s = rp, ci, v
+    coef0 = 0.5 if kernel == "polynomial" else 0.0
+    rng = np.random.default_rng(n)
+    d = rng.uniform(-1, 2, n - 1).astype(np.float32)
+    res = {}
+    for tiles in (2, 1):
+        with capi.Handle(np.float32, kernel, 3, 1.0 / F, coef0, 1.5) as h:
+            if W:
+                h.set_option(capi.OPT_SPARSE_BLOCK, W)
+            h.set_option(capi.OPT_SPARSE_CACHE, capi.CACHE_REQUIRED)
+            h.set_option(capi.OPT_SPARSE_TILES, tiles)
+            h.set_data_csr(rp_s, ci_s, v_s, F, value_format=fmt)
+            q = h.generate_q()
+            qa = h.kxx_last() + 1.0 / 1.5
+            h.set_q(q, qa)
+            got = h.matvec(d, 1.0)
+            got_b = h.matvec(d, 1.0)   # second matvec: the sweep over the stored tiles / entries
+            st = h.stats()
+            assert (st.dense_cache_bytes > 0) == (tiles == 2), (tiles, st.dense_cache_bytes)
+            assert np.array_equal(got, got_b)
+            alpha, rho, it = h.learn(y, eps=1e-3)
+            res[tiles] = (q, qa, got, alpha, it)
+    q, qa, got, alpha, it = res[2]
+    want = port.csr_matvec(rp, ci, v.astype(np.float64), F, q.astype(np.float64), d.astype(np.float64), qa, 1.0, kernel, 3, 1.0 / F, coef0, 1.5)
+    assert nrm_rel(want, got) < 2e-5, nrm_rel(want, got)
+    assert nrm_rel(res[1][2], got) < 2e-5
+    assert it == res[1][4]
+    assert nrm_rel(res[1][3], alpha) < 1e-3
