@@ -231,7 +231,12 @@ class ClockSampler(threading.Thread):
                         bits = int(self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.dev))
                     except Exception:
                         bits = int(self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.dev))
-                    self.samples.append((sm, self.sm_max, [nm for nm, m in self.masks if bits & m]))
+                    try:
+                        mem = float(self.nv.nvmlDeviceGetClockInfo(self.dev, self.nv.NVML_CLOCK_MEM))
+                        pw = float(self.nv.nvmlDeviceGetPowerUsage(self.dev)) / 1e3
+                    except Exception:
+                        mem, pw = None, None
+                    self.samples.append((sm, self.sm_max, [nm for nm, m in self.masks if bits & m], mem, pw))
                     self.stop_flag.wait(0.005)
                     continue
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
@@ -250,8 +255,11 @@ class ClockSampler(threading.Thread):
         sm = [x[0] for x in s]
         mx = [x[1] for x in s]
         reasons = [nm for nm in self.NAMES if any(nm in x[2] for x in s)]
+        mem = [x[3] for x in s if len(x) > 3 and x[3] is not None]
+        pw = [x[4] for x in s if len(x) > 4 and x[4] is not None]
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(s), "source": self.source}
+                "samples": len(s), "source": self.source, "sm_mhz_min": min(sm) if sm else None, "mem_mhz_min": min(mem) if mem else None,
+                "mem_mhz": float(np.median(mem)) if mem else None, "power_w_median": float(np.median(pw)) if pw else None, "power_w_max": max(pw) if pw else None}
 
 
 def measured_peaks():

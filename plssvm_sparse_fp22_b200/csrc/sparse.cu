@@ -887,6 +887,7 @@ struct sparse_state {
     tile_store *ts{ nullptr };
     bool t_valid{ false }, t_refused{ false };
     int t_rank{ -1 }, t_world{ 0 };
+    int64_t t_m{ -1 };
     ~sparse_state() { tile_store_destroy(ts); }
     // predict staging
     dbuf p_rowptr, p_col, p_val, p_norms, p_u, p_out, p_stats;
@@ -978,9 +979,7 @@ void set_data_typed(ctx &c, const int64_t *rowptr, const int32_t *colidx, const 
     st.c_valid = false;
     st.c_refused = false;
     st.t_valid = false;
-    st.t_refused = false;
-    tile_store_destroy(st.ts);
-    st.ts = nullptr;
+    st.t_refused = false;  // (the tile store itself is kept: a data set of the same size reuses its plan and its buffers)
     c.stats.sparse_cache_entries = 0;
     c.stats.dense_cache_bytes = 0;
     const int64_t entries = rowptr[n];
@@ -1339,12 +1338,13 @@ bool build_tile_store(ctx &c, sparse_state &st) {
         const double fill_est = 1.0 - std::exp(-per_pair);
         const bool want = c.opt_sparse_tiles == 2 || (c.opt_sparse_tiles == 0 && fill_est >= 0.4);
         if (!want || st.W < 256 || m < 1) { return false; }
-        if (st.ts == nullptr || st.t_rank != c.rank || st.t_world != c.world) {
+        if (st.ts == nullptr || st.t_rank != c.rank || st.t_world != c.world || st.t_m != m) {
             tile_store_destroy(st.ts);
             st.ts = nullptr;
             st.ts = tile_store_create(c, m);
             st.t_rank = c.rank;
             st.t_world = c.world;
+            st.t_m = m;
         }
         const size_t need = tile_store_bytes(st.ts);
         size_t free_b = 0, total_b = 0;
