@@ -62,6 +62,7 @@ def parse_args():
     ap.add_argument("--cpu-sample-points", type=int, default=0, help="row subset for the CPU baseline (0 = calibrate)")
     ap.add_argument("--ref-budget-s", type=float, default=900.0, help="--impl reference: CPU seconds the one timed call may take")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ref-cuda", action="store_true", help="skip the reference-CUDA-backend baseline leg (N = 1)")
     ap.add_argument("--seed", type=int, default=43)
     ap.add_argument("--density", type=float, default=0.0,
                     help="> 0: the MAIN line becomes a sparse workload (CSR rows of this density) instead of configs[1]")
@@ -375,6 +376,31 @@ def hbm_roofline(env, nbytes, matvec_ms, kernel, extra=None):
     return roof
 
 
+def reference_cuda_baseline(a, X, b, K):
+    """the UNMODIFIED reference CUDA backend (oracle/_ref/liboracle_ref_cuda.so, built for sm_100 from
+    /root/reference) on the same GPU and the same data: one launch of its device_kernel_* (the matvec) timed with CUDA events, and
+    its host-side CG (gpu_csvm::solver_CG, src/plssvm/backends/gpu_csvm.cpp:185-324) for a few fixed iterations."""
+    from oracle import ref_cuda
+    if not ref_cuda.available():
+        return {"unavailable": "oracle/_ref/liboracle_ref_cuda.so missing (make -C oracle ref_cuda where /root/reference exists)"}
+    try:
+        m = X.shape[0] - 1
+        q = np.zeros(m, X.dtype)
+        d = np.ones(m, X.dtype)
+        _, ms_mean, ms_best = ref_cuda.matvec_ms(X, q, d, 1.0, 1.0, a.kernel, reps=2)
+        steps = min(K, 3)
+        _, it, secs, setup = ref_cuda.solver_cg(X, b, q, 2.0, steps, 0.0, a.kernel)
+        F = X.shape[1]
+        return {"kind": "reference CUDA backend, unmodified, nvcc -arch=sm_100 -O3 --use_fast_math (its Release flags)",
+                "kernel": {"linear": "device_kernel_linear", "polynomial": "device_kernel_poly", "rbf": "device_kernel_radial"}[a.kernel] +
+                          " (src/plssvm/backends/CUDA/svm_kernel.cu)",
+                "ms_per_matvec": ms_mean, "ms_per_matvec_best": ms_best, "alg_tflops": alg_flops_per_matvec(X.shape[0], F) / (ms_mean * 1e-3) / 1e12,
+                "cg": {"value": steps / secs, "unit": UNIT, "steps": steps, "iterations_reported": it, "seconds": secs, "setup_data_on_device_s": setup,
+                       "what": "gpu_csvm::solver_CG with eps = 0: steps + 1 kernel launches, CG vector algebra on the host, 4-5 PCIe copies per iteration"}}
+    except Exception as e:
+        return {"error": f"{type(e).__name__}: {e}"}
+
+
 def run_main_workload(a, env):
     from plssvm_sparse_fp22_b200 import capi, datagen
     torch = env.torch
@@ -553,6 +579,11 @@ def run_main_workload(a, env):
         if world == 1 and not a.no_cpu_baseline and not sparse:
             res = cpu_reference_rate(a, X, 12.0, a.cpu_sample_points)
             line["cpu_baseline"] = {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    if world == 1 and not a.no_ref_cuda and not sparse:
+        h.close()  # free the HBM first
+        ref_cuda = reference_cuda_baseline(a, X, b, K)
+        if line is not None:
+            line["baseline_ref_cuda"] = ref_cuda
     h.close()
     return line
 

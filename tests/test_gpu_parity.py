@@ -322,3 +322,26 @@ def test_multi_gpu_row_and_tile_partition():
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={min(ngpu, 8)}", "--master-addr", "127.0.0.1",
                         "--master-port", "29541", os.path.join(root, "tests", "multi_gpu_check.py")], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("kernel", ["linear", "polynomial", "rbf"])
+@pytest.mark.parametrize("dt", [np.float64, np.float32])
+def test_reference_cuda_backend_agrees(kernel, dt):
+    """the reference's own CUDA kernels (unmodified, built for sm_100: oracle/_ref/liboracle_ref_cuda.so) and
+    libb200svm compute the same ret += add * Abar d on the same device (src/plssvm/backends/CUDA/svm_kernel.cu vs csrc/)."""
+    from oracle import ref_cuda
+    if not ref_cuda.available():
+        pytest.skip("oracle/_ref/liboracle_ref_cuda.so not built")
+    n, F = 700, 90
+    X, _ = datagen.make_dense(n, F, seed=5, problem="planes", dtype=dt)
+    rng = np.random.default_rng(2)
+    d = rng.uniform(-1, 2, n - 1).astype(dt)
+    with capi.Handle(dt, kernel, 3, 1.0 / F, 0.0, 1.5) as h:
+        h.set_data(X)
+        q = h.generate_q()
+        qa = h.kxx_last() + 1.0 / 1.5
+        h.set_q(q, qa)
+        ours = h.matvec(d, 1.0)
+    theirs, _, _ = ref_cuda.matvec_ms(X, q, d, qa, 1.0, kernel, cost=1.5, reps=1)
+    rel = float(np.linalg.norm(ours.astype(np.float64) - theirs) / np.linalg.norm(theirs))
+    assert rel < (1e-12 if dt == np.float64 else 3e-5), rel  # (float: the reference kernel is built with --use_fast_math and sums with atomics)
