@@ -454,7 +454,7 @@ def run_main_workload(a, env):
     QA = h.kxx_last() + 1.0
     warm_steps = warm_up(env, lambda s: h.solver_cg(b, None, QA, s, 0.0), W)
     h.reset_stats()
-    ts, (alpha, iters, delta) = env.repeat_timed(lambda: h.solver_cg(b, None, QA, K, 0.0), lambda: drop_caches(h), a.min_timed_s, 3, 40)
+    ts, (alpha, iters, delta) = env.repeat_timed(lambda: h.solver_cg(b, None, QA, K, 0.0), lambda: drop_caches(h), a.min_timed_s, 3, 120)
     st = h.stats()
     clocks = env.sampler.take()
     assert iters == K, (iters, K)
@@ -515,7 +515,7 @@ def run_main_workload(a, env):
     else:
         e2e_once()  # warm-up (allocations)
         h.reset_stats()
-        te, _ = env.repeat_timed(e2e_once, None, a.min_timed_s, 3, 12)
+        te, _ = env.repeat_timed(e2e_once, None, a.min_timed_s, 3, 40)
         st2 = h.stats()
         clocks_e2e = env.sampler.take()
 

@@ -105,10 +105,17 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         "r"(parity)
         : "memory");
 }
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
-                 "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+// `policy`: L2 eviction priority of the fetched lines (createpolicy): the operand planes are re-read by every tile of a super-tile
+// and must outlive the kernel-value tiles the STORE pass streams through L2 (evict_last against the stores' evict_first)
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1, uint64_t policy) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst),
+                 "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "l"(policy)
                  : "memory");
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -261,6 +268,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
             asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_hi)) : "memory");
             asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_lo)) : "memory");
             if constexpr (FP8X) { asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory"); }
+            const uint64_t keep = l2_policy_evict_last();
             int stage = 0;
             uint32_t phase = 0;
             for (int t = first_tile; t < p.num_tiles; t += tile_step) {
@@ -275,18 +283,18 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
                         mbar_arrive_expect_tx(full, STAGE_BYTES);
                         const uint32_t s0 = sbase + smem_layout::OPERANDS + stage * STAGE_BYTES;
                         if (half == 0) {
-                            tma_load_2d(s0, &map_hi, full, kc, row_a);                          // A_hi  128 rows
-                            tma_load_2d(s0 + A_BYTES, &map_hi, full, kc, row_b);                // B_hi  rows 0..127
-                            tma_load_2d(s0 + 2 * A_BYTES, &map_hi, full, kc, row_b + 128);      // B_hi  rows 128..255
+                            tma_load_2d(s0, &map_hi, full, kc, row_a, keep);                          // A_hi  128 rows
+                            tma_load_2d(s0 + A_BYTES, &map_hi, full, kc, row_b, keep);                // B_hi  rows 0..127
+                            tma_load_2d(s0 + 2 * A_BYTES, &map_hi, full, kc, row_b + 128, keep);      // B_hi  rows 128..255
                         } else if constexpr (FP8X) {
                             const int kc8 = kb * 128;  // bytes: [hi8 | lo8] of this K block
-                            tma_load_2d(s0, &map_lo, full, kc8, row_a);                         // A_8
-                            tma_load_2d(s0 + A_BYTES, &map_b, full, kc8, row_b);                // B_8
-                            tma_load_2d(s0 + 2 * A_BYTES, &map_b, full, kc8, row_b + 128);
+                            tma_load_2d(s0, &map_lo, full, kc8, row_a, keep);                         // A_8
+                            tma_load_2d(s0 + A_BYTES, &map_b, full, kc8, row_b, keep);                // B_8
+                            tma_load_2d(s0 + 2 * A_BYTES, &map_b, full, kc8, row_b + 128, keep);
                         } else {
-                            tma_load_2d(s0, &map_lo, full, kc, row_a);                          // A_lo
-                            tma_load_2d(s0 + A_BYTES, &map_lo, full, kc, row_b);                // B_lo
-                            tma_load_2d(s0 + 2 * A_BYTES, &map_lo, full, kc, row_b + 128);
+                            tma_load_2d(s0, &map_lo, full, kc, row_a, keep);                          // A_lo
+                            tma_load_2d(s0 + A_BYTES, &map_lo, full, kc, row_b, keep);                // B_lo
+                            tma_load_2d(s0 + 2 * A_BYTES, &map_lo, full, kc, row_b + 128, keep);
                         }
                         if (++stage == STAGES) {
                             stage = 0;
