@@ -519,6 +519,7 @@ def run_main_workload(a, env):
         st2 = h.stats()
         clocks_e2e = env.sampler.take()
 
+    fma_peak = h.probe_fma_tflops() if (not sparse and int(st.matvec_path) == 1) else None
     line = None
     if rank == 0:
         peaks = env.peaks
@@ -529,6 +530,16 @@ def run_main_workload(a, env):
                 "peak_source": f"{env.peak_kind} bf16 dense (sustained)", "kernel": {1: "k_kmv_tile (SIMT)", 2: "k_gram_tc (tcgen05 fp16x2-split)", 3: "gemv pair"}.get(path, "?"),
                 "alg_flops_per_launch": flops, "ms_per_launch": matvec_ms, "launches_timed": n_matvecs}
         matvec_gflops = world * flops / (matvec_ms * 1e-3) / 1e9 if matvec_ms > 0 else None
+        if not sparse and path == 1:
+            # SIMT Gram tiles (double precision, or float with --path 1): full square, no symmetry -> 2 F m^2 FMA flops per matvec,
+            # bound by the FP64 / FP32 FMA pipe; the peak is measured on this device by a register-only FMA kernel
+            fl = 2.0 * F * float(n - 1) * float(n - 1) / world
+            ach = fl / (matvec_ms * 1e-3) / 1e12 if matvec_ms > 0 else 0.0
+            roof = {"bound": "fp64-fma" if a.dtype == "f64" else "fp32-fma", "achieved": ach, "peak": fma_peak, "unit": "TFLOP/s", "frac": ach / fma_peak if fma_peak else None,
+                    "traffic": None, "peak_source": "measured on this device: b200svm_probe_fma_tflops (16 independent FMA chains per thread, 2 flops per FMA)",
+                    "kernel": "k_kmv_tile (SIMT register-tiled Gram tiles, full square)", "alg_flops_per_launch": fl,
+                    "alg_flops_symmetric_minimum": flops, "ms_per_launch": matvec_ms, "launches_timed": n_matvecs}
+            matvec_gflops = world * fl / (matvec_ms * 1e-3) / 1e9 if matvec_ms > 0 else None
         if not sparse and path == 2 and dense_cache_bytes > 0:
             # cached kernel matrix: the per-iteration kernel streams the stored lower-triangle tiles once (SURVEY.md §8d "cached dense K")
             asm_tf = flops / (build_ms * 1e-3) / 1e12 if build_ms > 0 else None

@@ -144,6 +144,9 @@ typedef struct b200svm_stats {
     int64_t cg_vector_timed;      /* iterations included in cg_vector_ms */
 } b200svm_stats;
 int b200svm_get_stats(b200svm_handle h, b200svm_stats *out);
+/* Measurement hook: the FP32 / FP64 FMA throughput of the handle's device in TFLOP/s (2 flops per FMA), measured with a register-only
+ * kernel — the roofline denominator of the SIMT Gram-tile kernels (double precision dense polynomial / rbf). */
+int b200svm_probe_fma_tflops(b200svm_handle h, int dtype, double *tflops);
 int b200svm_reset_stats(b200svm_handle h);
 
 #ifdef __cplusplus

@@ -29,7 +29,7 @@ SYMBOLS = [
     "b200svm_set_data_dense", "b200svm_set_data_csr", "b200svm_generate_q", "b200svm_get_kxx_last", "b200svm_set_q",
     "b200svm_matvec", "b200svm_cg_solve", "b200svm_learn", "b200svm_update_w", "b200svm_predict_dense",
     "b200svm_predict_csr", "b200svm_comm_unique_id", "b200svm_comm_init", "b200svm_set_option", "b200svm_get_stats",
-    "b200svm_reset_stats", "b200svm_partition_rows", "b200svm_partition_tiles",
+    "b200svm_reset_stats", "b200svm_partition_rows", "b200svm_partition_tiles", "b200svm_probe_fma_tflops",
 ]
 
 
@@ -95,6 +95,7 @@ def load():
     L.b200svm_set_option.argtypes = [vp, i, i64]
     L.b200svm_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.b200svm_reset_stats.argtypes = [vp]
+    L.b200svm_probe_fma_tflops.argtypes = [vp, i, pd]
     L.b200svm_partition_rows.argtypes = [i64, i, i, pi64, pi64]
     L.b200svm_partition_tiles.argtypes = [i64, i, i, pi64, pi64, pi64]
     _LIB = L
@@ -271,6 +272,13 @@ class Handle:
 
     def reset_stats(self):
         self._chk(self.L.b200svm_reset_stats(self.h))
+
+    def probe_fma_tflops(self, dtype=None):
+        """Measured FMA peak (TFLOP/s) of the handle's device for float32 / float64."""
+        v = C.c_double(0)
+        dt = self.dtype if dtype is None else {np.dtype(np.float32): F32, np.dtype(np.float64): F64}[np.dtype(dtype)]
+        self._chk(self.L.b200svm_probe_fma_tflops(self.h, dt, C.byref(v)))
+        return v.value
 
 
 def partition_rows(m: int, rank: int, world: int):

@@ -252,6 +252,14 @@ int b200svm_set_option(b200svm_handle h, int option, int64_t value) {
     });
 }
 
+int b200svm_probe_fma_tflops(b200svm_handle h, int dtype, double *tflops) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() {
+        B200_REQUIRE(tflops != nullptr && (dtype == B200SVM_F32 || dtype == B200SVM_F64), "bad arguments");
+        *tflops = dtype == B200SVM_F32 ? probe_fma_tflops<float>(*c) : probe_fma_tflops<double>(*c);
+    });
+}
+
 int b200svm_get_stats(b200svm_handle h, b200svm_stats *out) {
     ctx *c = reinterpret_cast<ctx *>(h);
     return guarded(c, [&]() {

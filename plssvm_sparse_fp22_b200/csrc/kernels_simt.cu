@@ -419,4 +419,50 @@ void predict_dense(ctx &c, const T *alpha_dev, T bias, const T *pts_dev, int64_t
 template void predict_dense<float>(ctx &, const float *, float, const float *, int64_t, int64_t, float *);
 template void predict_dense<double>(ctx &, const double *, double, const double *, int64_t, int64_t, double *);
 
+// ---------------------------------------------------------------------------------------------------------------------
+// FMA-pipe probe (measurement hook, b200svm_probe_fma_tflops): the FP32 / FP64 FMA peak of this device, measured — the denominator
+// of the roofline of the SIMT Gram-tile kernel ("must be measured on the box").  16 independent FMA chains per thread.
+// ---------------------------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) k_fma_probe(T *__restrict__ out, int iters, T a, T b) {
+    T acc[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { acc[k] = (T) (threadIdx.x + k); }
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) { acc[k] = fma(acc[k], a, b); }
+    }
+    T s = 0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { s += acc[k]; }
+    if (s == (T) -1.2345) { out[0] = s; }  // never true: keeps the chains alive
+}
+
+template <typename T>
+double probe_fma_tflops(ctx &c) {
+    const int iters = sizeof(T) == 4 ? 8192 : 1024, blocks = NUM_SMS * 8;
+    dbuf sink;
+    sink.reserve(sizeof(T));
+    cudaEvent_t e0, e1;
+    B200_CUDA_CHECK(cudaEventCreate(&e0));
+    B200_CUDA_CHECK(cudaEventCreate(&e1));
+    double best = 0.0;
+    for (int rep = 0; rep < 4; ++rep) {
+        B200_CUDA_CHECK(cudaEventRecord(e0, c.stream));
+        k_fma_probe<T><<<blocks, 256, 0, c.stream>>>(sink.as<T>(), iters, (T) 0.999, (T) 1e-3);
+        B200_CUDA_CHECK(cudaEventRecord(e1, c.stream));
+        B200_CUDA_CHECK(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        B200_CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+        const double tf = 2.0 * 16.0 * iters * 256.0 * blocks / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) { best = tf; }
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    count_launch(c, 4);
+    return best;
+}
+template double probe_fma_tflops<float>(ctx &);
+template double probe_fma_tflops<double>(ctx &);
+
 }  // namespace b200

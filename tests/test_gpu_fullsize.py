@@ -7,6 +7,8 @@ matrix-vector product is checked by
   * agreement of independent device paths (tcgen05 vs SIMT; cached S vs S recomputed on the fly),
   * symmetry  d1 . (Abar d2) == d2 . (Abar d1)  and linearity  Abar (a d1 + b d2) == a Abar d1 + b Abar d2.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -152,11 +154,16 @@ def test_configs0_linear_double_against_the_reference(problem):
     """BASELINE.json configs[0] at its exact size (5000 points x 256 dense features, double, linear, eps = 1e-3): the reference's
     own OpenMP learn() on the host cores against b200svm_learn — identical CG iteration count, alpha within 1e-10 (rho within its cancellation noise),
     bit-identical labels on the training points."""
-    from oracle import port
+    from oracle import port, ref
 
     n, F = 5000, 256
     X, y = datagen.make_dense(n, F, seed=42, problem=problem, dtype=np.float64)
-    a_o, rho_o, it_o = port.learn(X, y, "linear", eps=1e-3, use_rows=True)
+    if ref.available():  # the unmodified reference, one thread (bit-deterministic); ~1-2 minutes on the host
+        ref.set_num_threads(1)
+        a_o, rho_o, it_o, _ = ref.learn(X, y, "linear", eps=1e-3)
+        ref.set_num_threads(os.cpu_count() or 1)
+    else:
+        a_o, rho_o, it_o = port.learn(X, y, "linear", eps=1e-3, use_rows=True)
     with capi.Handle(np.float64, "linear", gamma=1.0 / F) as h:
         h.set_data(X)
         alpha, rho, it = h.learn(y, eps=1e-3)

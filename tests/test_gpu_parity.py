@@ -15,7 +15,7 @@ import numpy as np
 import pytest
 
 from conftest import nrm_rel
-from oracle import port
+from oracle import policy, port
 from plssvm_sparse_fp22_b200 import capi, datagen
 
 pytestmark = pytest.mark.gpu
@@ -128,7 +128,7 @@ def test_learn_synth_golden(golden, case, kernel, eps):
             err_ref = nrm_rel(truth, g[key + "/alpha"])
             err_ours = nrm_rel(truth, alpha)
             assert abs(it - it_ref) <= max(2, abs(it_ref - it_ref8), it_ref // 4), (it, it_ref)
-            assert err_ours <= max(2 * err_ref, 20 * spread, 1e-4), (err_ours, err_ref, spread)
+            assert err_ours <= policy.float_alpha_tolerance(err_ref, spread), (err_ours, err_ref, spread)  # the one float policy (oracle/policy.py)
 
 
 @pytest.mark.parametrize("dt", DTYPES)
