@@ -7,7 +7,10 @@
  * pure virtuals; each declaration cites the reference interface it replaces (paths relative to the reference tree).
  * There is no CPU fallback: every compute entry point fails with B200SVM_ERR_CUDA when no sm_100 device is usable.
  *
- * Host pointers unless a parameter is named *_dev.  `n` = number of data points, `F` = number of features,
+ * Pointers to matrices and vectors of the DENSE entry points (set_data_dense, set_q, matvec, cg_solve, learn, update_w, predict_dense,
+ * generate_q) may be host pointers or device pointers of the handle's GPU — unified addressing tells them apart, device-resident
+ * inputs / outputs cost a device-to-device copy only (plssvm_sparse_fp22_b200/torch_api.py drives the library from torch CUDA tensors
+ * this way).  CSR arrays are host pointers.  `n` = number of data points, `F` = number of features,
  * m = n - 1 = size of the reduced system ("dept" in the reference).  Real type is selected per handle (dtype).
  */
 #ifndef B200SVM_H

@@ -44,23 +44,33 @@ int guarded(ctx *c, Fn &&fn, bool need_handle = true) {
         }                                   \
     } while (0)
 
+// The dense entry points take HOST pointers or DEVICE pointers (unified addressing tells them apart): a caller that already
+// holds its data in HBM — e.g. torch CUDA tensors, plssvm_sparse_fp22_b200/torch_api.py — pays a device-to-device copy only.
+bool on_device(const void *p) {
+    cudaPointerAttributes a{};
+    if (p == nullptr || cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        (void) cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
 void h2d(ctx &c, void *dst, const void *src, size_t bytes) {
     if (bytes == 0) { return; }
-    B200_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c.stream));
-    c.stats.h2d_bytes += (int64_t) bytes;
+    B200_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, c.stream));
+    if (!on_device(src)) { c.stats.h2d_bytes += (int64_t) bytes; }
 }
 void d2h(ctx &c, void *dst, const void *src, size_t bytes) {
     if (bytes == 0) { return; }
-    B200_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c.stream));
-    c.stats.d2h_bytes += (int64_t) bytes;
+    B200_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, c.stream));
+    if (!on_device(dst)) { c.stats.d2h_bytes += (int64_t) bytes; }
 }
 
 // copy a host row-major matrix (rows x F, leading dimension ld) into a zero-padded device matrix (rows x ldd)
 void stage_matrix(ctx &c, void *dst, int64_t ldd, const void *src, int64_t rows, int64_t F, int64_t ld) {
     const size_t es = c.esize();
     B200_CUDA_CHECK(cudaMemsetAsync(dst, 0, (size_t) rows * ldd * es, c.stream));
-    B200_CUDA_CHECK(cudaMemcpy2DAsync(dst, (size_t) ldd * es, src, (size_t) ld * es, (size_t) F * es, (size_t) rows, cudaMemcpyHostToDevice, c.stream));
-    c.stats.h2d_bytes += (int64_t) ((size_t) rows * F * es);
+    B200_CUDA_CHECK(cudaMemcpy2DAsync(dst, (size_t) ldd * es, src, (size_t) ld * es, (size_t) F * es, (size_t) rows, cudaMemcpyDefault, c.stream));
+    if (!on_device(src)) { c.stats.h2d_bytes += (int64_t) ((size_t) rows * F * es); }
 }
 
 void require_data(const ctx &c) { B200_REQUIRE(c.has_data, "no data set: call b200svm_set_data_dense / b200svm_set_data_csr first"); }
@@ -390,6 +400,13 @@ void do_learn(ctx &c, const void *y_host, double eps, void *alpha_out, double *r
     B200_REQUIRE(alpha_out != nullptr && rho_out != nullptr, "null output pointer");
     B200_REQUIRE(c.n >= 2, "at least two data points are required");
     const int64_t n = c.n, m = c.m();
+    std::vector<T> y_copy;
+    if (on_device(y_host)) {  // device-resident labels: n reals come to the host for b = y - y_n and the bias
+        y_copy.resize((size_t) n);
+        B200_CUDA_CHECK(cudaMemcpyAsync(y_copy.data(), y_host, (size_t) n * sizeof(T), cudaMemcpyDefault, c.stream));
+        B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));
+        y_host = y_copy.data();
+    }
     const T *y = static_cast<const T *>(y_host);
     // q = generate_q() ; QA_cost = k(x_n, x_n) + 1 / C   (csvm.cpp:232-243)
     c.q.reserve((size_t) m * sizeof(T));
@@ -418,7 +435,13 @@ void do_learn(ctx &c, const void *y_host, double eps, void *alpha_out, double *r
     sync_stream(c);
     const T sum_alpha = mb[0], q_alpha = mb[1];
     const T bias = y[n - 1] + QA_cost * sum_alpha - q_alpha;
-    static_cast<T *>(alpha_out)[m] = -sum_alpha;
+    const T alpha_n = -sum_alpha;
+    if (on_device(alpha_out)) {
+        B200_CUDA_CHECK(cudaMemcpyAsync(static_cast<T *>(alpha_out) + m, &alpha_n, sizeof(T), cudaMemcpyDefault, c.stream));
+        B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));
+    } else {
+        static_cast<T *>(alpha_out)[m] = alpha_n;
+    }
     *rho_out = -(double) bias;
     if (iters != nullptr) { *iters = it; }
 }

@@ -345,3 +345,29 @@ def test_reference_cuda_backend_agrees(kernel, dt):
     theirs, _, _ = ref_cuda.matvec_ms(X, q, d, qa, 1.0, kernel, cost=1.5, reps=1)
     rel = float(np.linalg.norm(ours.astype(np.float64) - theirs) / np.linalg.norm(theirs))
     assert rel < (1e-12 if dt == np.float64 else 3e-5), rel  # (float: the reference kernel is built with --use_fast_math and sums with atomics)
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("dt", DTYPES)
+def test_torch_device_tensor_api(kernel, dt):
+    """fit / predict on torch CUDA tensors (device pointers through the C ABI) == the host-buffer path."""
+    import torch
+    from plssvm_sparse_fp22_b200.torch_api import LSSVM
+    n, F = 600, 40
+    X, y = datagen.make_dense(n, F, seed=11, problem="planes", dtype=dt)
+    with capi.Handle(dt, kernel) as h:
+        h.set_data(X)
+        alpha, rho, it = h.learn(y, eps=1e-3)
+        dec = h.predict(alpha, rho, X[:100])
+    Xt, yt = torch.from_numpy(X).cuda(), torch.from_numpy(y).cuda()
+    svm = LSSVM(kernel=kernel).fit(Xt, yt)
+    assert svm.iterations == it
+    a_t = svm.alpha.cpu().numpy()
+    assert nrm_rel(alpha, a_t) < (1e-12 if dt == np.float64 else 1e-4)
+    v = svm.decision_function(Xt[:100]).cpu().numpy()
+    assert np.allclose(v, dec, rtol=0, atol=(1e-9 if dt == np.float64 else 2e-3) * max(1.0, np.abs(dec).max()))
+    lab = svm.predict(Xt[:100]).cpu().numpy()
+    assert np.array_equal(lab, capi.Handle.predict_label(v))
+    with pytest.raises(TypeError):
+        LSSVM(kernel=kernel).fit(torch.from_numpy(X), torch.from_numpy(y))  # CPU tensors: no CPU path
+    svm.close()
