@@ -730,19 +730,21 @@ def run_predict(env, tag, svs, F, density, points, seed):
             env.barrier()
             env.sampler.active.clear()
             st = h.stats()
+            atoms_gops = h.probe_smem_atomic_gops()
         t = env.max_over_ranks([t])[0]
         clocks = env.sampler.take()
         total = share * world
         evals = float(total) * svs
         products = evals * F * density * density  # expected sparse Gram products (P n F rho^2)
-        # FP-pipe roofline of the on-the-fly kernel: one multiply-accumulate per product + one ex2 per evaluation; peak = SMs x 128 lanes x clock
-        sm_mhz = clocks.get("sm_mhz") or 1900.0
-        lane_ops = world * 148 * 128 * sm_mhz * 1e6
+        # roofline of the on-the-fly kernel: one 32-bit shared-memory atomic add per Gram product (fixed-point accumulation, DESIGN.md
+        # §4.1); peak = the rate measured on this device by b200svm_probe_smem_atomic_gops, times N GPUs
+        peak = world * atoms_gops
         out.update({"value": total / t, "seconds": t, "kernel_evals_per_s": evals / t, "gram_products_per_s": products / t,
-                    "roofline": {"bound": "fp32-issue", "achieved": (products + evals) / t / 1e12, "peak": lane_ops / 1e12, "unit": "T lane-ops/s",
-                                 "frac": (products + evals) / t / lane_ops, "traffic": None,
-                                 "kernel": "k_sp_kmv (S on the fly: one multiply-accumulate per Gram product into shared-memory fixed point + one ex2 per kernel value)",
-                                 "peak_source": "148 SMs x 128 FP32 lanes x median SM clock under load x N GPUs (one op per lane per cycle); algorithmic ops = products + kernel evaluations",
+                    "roofline": {"bound": "smem-atomic", "achieved": products / t / 1e9, "peak": peak, "unit": "G atomic adds/s",
+                                 "frac": products / t / 1e9 / peak if peak else None, "traffic": None,
+                                 "kernel": "k_sp_kmv (S on the fly: one multiply + one shared-memory atomic add per Gram product, one ex2 per kernel value)",
+                                 "peak_source": "measured on this device: b200svm_probe_smem_atomic_gops (ATOMS.ADD to pseudo-random slots of an 8192-entry accumulator) x N GPUs; "
+                                                "algorithmic ops = expected Gram products P n F rho^2",
                                  "note": "timed through b200svm_predict_csr with host buffers: H2D of the points and D2H of the decision values are inside"},
                     "clocks": clocks,
                     "e2e": {"value": total / t, "unit": "points/s", "h2d_bytes_per_step": int(st.h2d_bytes), "d2h_bytes_per_step": int(st.d2h_bytes)},

@@ -150,6 +150,9 @@ int b200svm_get_stats(b200svm_handle h, b200svm_stats *out);
 /* Measurement hook: the FP32 / FP64 FMA throughput of the handle's device in TFLOP/s (2 flops per FMA), measured with a register-only
  * kernel — the roofline denominator of the SIMT Gram-tile kernels (double precision dense polynomial / rbf). */
 int b200svm_probe_fma_tflops(b200svm_handle h, int dtype, double *tflops);
+/* Measurement hook: rate (1e9 per second) of 32-bit shared-memory atomic adds to spread addresses on the handle's device — the
+ * instruction the on-the-fly sparse kernel issues per Gram product; roofline denominator of b200svm_predict_csr. */
+int b200svm_probe_smem_atomic_gops(b200svm_handle h, double *gops);
 int b200svm_reset_stats(b200svm_handle h);
 
 #ifdef __cplusplus

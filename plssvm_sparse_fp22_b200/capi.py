@@ -29,7 +29,7 @@ SYMBOLS = [
     "b200svm_set_data_dense", "b200svm_set_data_csr", "b200svm_generate_q", "b200svm_get_kxx_last", "b200svm_set_q",
     "b200svm_matvec", "b200svm_cg_solve", "b200svm_learn", "b200svm_update_w", "b200svm_predict_dense",
     "b200svm_predict_csr", "b200svm_comm_unique_id", "b200svm_comm_init", "b200svm_set_option", "b200svm_get_stats",
-    "b200svm_reset_stats", "b200svm_partition_rows", "b200svm_partition_tiles", "b200svm_probe_fma_tflops",
+    "b200svm_reset_stats", "b200svm_partition_rows", "b200svm_partition_tiles", "b200svm_probe_fma_tflops", "b200svm_probe_smem_atomic_gops",
 ]
 
 
@@ -96,6 +96,7 @@ def load():
     L.b200svm_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.b200svm_reset_stats.argtypes = [vp]
     L.b200svm_probe_fma_tflops.argtypes = [vp, i, pd]
+    L.b200svm_probe_smem_atomic_gops.argtypes = [vp, pd]
     L.b200svm_partition_rows.argtypes = [i64, i, i, pi64, pi64]
     L.b200svm_partition_tiles.argtypes = [i64, i, i, pi64, pi64, pi64]
     _LIB = L
@@ -272,6 +273,12 @@ class Handle:
 
     def reset_stats(self):
         self._chk(self.L.b200svm_reset_stats(self.h))
+
+    def probe_smem_atomic_gops(self):
+        """Measured rate (1e9 / s) of 32-bit shared-memory atomic adds to spread addresses on the handle's device."""
+        v = C.c_double(0)
+        self._chk(self.L.b200svm_probe_smem_atomic_gops(self.h, C.byref(v)))
+        return v.value
 
     def probe_fma_tflops(self, dtype=None):
         """Measured FMA peak (TFLOP/s) of the handle's device for float32 / float64."""

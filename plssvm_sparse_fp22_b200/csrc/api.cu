@@ -270,6 +270,14 @@ int b200svm_probe_fma_tflops(b200svm_handle h, int dtype, double *tflops) {
     });
 }
 
+int b200svm_probe_smem_atomic_gops(b200svm_handle h, double *gops) {
+    ctx *c = reinterpret_cast<ctx *>(h);
+    return guarded(c, [&]() {
+        B200_REQUIRE(gops != nullptr, "null output pointer");
+        *gops = probe_smem_atomic_gops(*c);
+    });
+}
+
 int b200svm_get_stats(b200svm_handle h, b200svm_stats *out) {
     ctx *c = reinterpret_cast<ctx *>(h);
     return guarded(c, [&]() {

@@ -191,6 +191,7 @@ template <typename T> int kmv_simt_launch(ctx &c, const T *A, const T *normA, in
 template <typename T> void center_rows(ctx &c, const T *X, int64_t rows, int64_t ld, const T *xlast, T *Z);
 template <typename T> void xt_v(ctx &c, const T *X, int64_t rows, int64_t ld, const T *v, T *w);
 template <typename T> void x_w(ctx &c, const T *X, int64_t rows, int64_t ld, const T *w, T bias, T *out);
+double probe_smem_atomic_gops(ctx &c);                   // measured shared-memory 32-bit atomic-add rate of the device (1e9 / s)
 template <typename T> double probe_fma_tflops(ctx &c);  // measured FMA peak of the device (TFLOP/s, 2 flops per FMA)
 template <typename T> void predict_dense(ctx &c, const T *alpha_dev, T bias, const T *pts_dev, int64_t P, int64_t ld, T *out_dev);
 

@@ -462,6 +462,49 @@ double probe_fma_tflops(ctx &c) {
     count_launch(c, 4);
     return best;
 }
+// Shared-memory integer atomic probe (b200svm_probe_smem_atomic_gops): fire-and-forget 32-bit ATOMS.ADD to pseudo-random slots of an
+// 8192-entry accumulator — the instruction the on-the-fly sparse kernel (k_sp_kmv) issues once per Gram product (float) or twice
+// (double).  Its measured rate is the roofline of that kernel.
+__global__ void __launch_bounds__(256) k_atoms_probe(int *__restrict__ out, int iters) {
+    __shared__ int acc[8192];
+    for (int k = threadIdx.x; k < 8192; k += 256) { acc[k] = 0; }
+    __syncthreads();
+    unsigned int x = threadIdx.x * 2654435761u + blockIdx.x * 40503u + 12345u;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            x = x * 1664525u + 1013904223u;
+            atomicAdd(&acc[(x >> 12) & 8191u], (int) (x & 7u));
+        }
+    }
+    __syncthreads();
+    if (acc[threadIdx.x] == -123456789) { out[0] = 1; }
+}
+
+double probe_smem_atomic_gops(ctx &c) {
+    const int iters = 2048, blocks = NUM_SMS * 16;
+    dbuf sink;
+    sink.reserve(sizeof(int));
+    cudaEvent_t e0, e1;
+    B200_CUDA_CHECK(cudaEventCreate(&e0));
+    B200_CUDA_CHECK(cudaEventCreate(&e1));
+    double best = 0.0;
+    for (int rep = 0; rep < 4; ++rep) {
+        B200_CUDA_CHECK(cudaEventRecord(e0, c.stream));
+        k_atoms_probe<<<blocks, 256, 0, c.stream>>>(sink.as<int>(), iters);
+        B200_CUDA_CHECK(cudaEventRecord(e1, c.stream));
+        B200_CUDA_CHECK(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        B200_CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+        const double g = 8.0 * iters * 256.0 * blocks / (ms * 1e-3) / 1e9;
+        if (rep > 0 && g > best) { best = g; }
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    count_launch(c, 4);
+    return best;
+}
+
 template double probe_fma_tflops<float>(ctx &);
 template double probe_fma_tflops<double>(ctx &);
 
