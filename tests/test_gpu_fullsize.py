@@ -176,3 +176,28 @@ def test_configs0_linear_double_against_the_reference(problem):
     dec_o = port.predict(X, a_o, rho_o, X, "linear")
     safe = np.abs(dec_o) > 1e-9 * np.abs(dec_o).max()
     assert np.array_equal(np.sign(dec[safe]), np.sign(dec_o[safe]))
+
+
+def test_configs1_full_size_cg_iteration_against_the_reference_golden(golden):
+    """BASELINE.json configs[1] at FULL size (65536 x 1024 float rbf): one CG iteration — two applications of the implicit matrix and
+    the vector algebra between them — against the UNMODIFIED reference's solver_CG on the same data (tests/golden/cg_cfg1_full.npz,
+    written by tests/golden/make_golden_cfg1.py from oracle/_ref: 18 minutes on 8 host cores).  Both the cached-matrix mode (STORE pass
+    + sweep) and the recompute mode of the tcgen05 path are held to it."""
+    g = golden("cg_cfg1_full.npz")
+    n, F = int(g["n"]), int(g["F"])
+    X, y = datagen.make_dense(n, F, seed=int(g["seed"]), problem="blobs", dtype=np.float32)
+    b = (y[:-1] - y[-1]).astype(np.float32)
+    for cache in (capi.CACHE_AUTO, capi.CACHE_OFF):
+        with capi.Handle(np.float32, "rbf", 3, 1.0 / F, 0.0, 1.0) as h:
+            h.set_option(capi.OPT_DENSE_CACHE, cache)
+            h.set_data(X)
+            q = h.generate_q()
+            qa = h.kxx_last() + 1.0
+            assert nrm_rel(g["q_head"], q[:4096]) < 2e-6 and abs(float(q.astype(np.float64).sum()) - float(g["q_sum"])) < 2e-6 * abs(float(g["q_sum"]))
+            assert abs(qa - float(g["QA_cost"])) < 1e-6
+            alpha, it, delta = h.solver_cg(b, None, qa, 1, 1e-3)
+            assert h.stats().matvec_path == capi.PATH_TC
+        assert it == int(g["iterations"]) == 1
+        err = nrm_rel(g["alpha"], alpha)
+        # alpha after one step = 1 + alpha_cd d with |alpha_cd d| ~ |1|: float rounding of two 65535-term matvecs on either side
+        assert err < 2e-5, (cache, err)
