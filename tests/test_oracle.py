@@ -1,5 +1,6 @@
 """CPU tests: the oracle (C restatement, oracle/lssvm_oracle.c) against the golden vectors produced by the unmodified
 reference (tests/golden/make_golden.py) and — where oracle/_ref is present — against the reference build itself."""
+import os
 import hashlib
 
 import numpy as np
@@ -145,3 +146,14 @@ def test_fp22_codec_known_answers():
     assert np.array_equal(datagen.fp22_round(r), r)  # idempotent
     for xv in x[:200]:
         assert port.fp22_round(float(xv)) == float(datagen.fp22_round(np.array([xv], np.float32))[0])
+
+
+def test_reference_cuda_backend_library_links():
+    """oracle/_ref/liboracle_ref_cuda.so (the reference's CUDA backend for sm_100) must load without unresolved
+    symbols and export the two driver entry points — checked on the CPU so that a link error is not first seen on the GPU box."""
+    import ctypes
+    from oracle import ref_cuda
+    if not ref_cuda.available():
+        pytest.skip("oracle/_ref/liboracle_ref_cuda.so not built (make -C oracle ref_cuda)")
+    L = ctypes.CDLL(ref_cuda.lib_path(), mode=os.RTLD_NOW)
+    assert L.orefcuda_solver_cg and L.orefcuda_matvec_ms

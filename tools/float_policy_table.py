@@ -30,7 +30,7 @@ for case in ("blobs_257x33_s7", "planes_384x64_s8", "blobs_1000x256_s43"):
             key = f"{case}/f32/{kernel}/{eps:g}"
             truth = g[f"{case}/f64/{kernel}/{eps:g}/alpha"]
             for path in ((0,) if kernel == "linear" else (0, 1)):
-                with capi.Handle(np.float32, kernel) as h:
+                with capi.Handle(np.float32, kernel, gamma=1.0 / F) as h:
                     if path:
                         h.set_option(capi.OPT_MATVEC_PATH, path)
                     h.set_data(X.astype(np.float32))
