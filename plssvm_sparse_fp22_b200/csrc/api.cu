@@ -170,6 +170,7 @@ int b200svm_destroy(b200svm_handle h) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     comm_destroy(*c);
+    tile_store_destroy(c->dts);
     if (c->tc_opaque != nullptr && c->tc_opaque_free != nullptr) { c->tc_opaque_free(c->tc_opaque); }
     if (c->sp_opaque != nullptr && c->sp_opaque_free != nullptr) { c->sp_opaque_free(c->sp_opaque); }
     for (auto &ev : c->ev) {
@@ -237,6 +238,7 @@ int b200svm_set_option(b200svm_handle h, int option, int64_t value) {
                 c->opt_sparse_cache_mb = value;
                 sp_invalidate_cache(*c);
                 tc_invalidate_cache(*c);
+                dense_f64_cache_invalidate(*c);
                 break;
             case B200SVM_OPT_PEER_EXCHANGE:
                 B200_REQUIRE(value >= 0 && value <= 2, "peer exchange mode must be 0 (auto), 1 (NCCL allreduce) or 2 (required)");
@@ -247,6 +249,7 @@ int b200svm_set_option(b200svm_handle h, int option, int64_t value) {
                 B200_REQUIRE(value >= 0 && value <= 2, "dense cache mode must be 0 (auto), 1 (off) or 2 (required)");
                 c->opt_dense_cache = value;
                 tc_invalidate_cache(*c);
+                dense_f64_cache_invalidate(*c);
                 break;
             case B200SVM_OPT_SPARSE_TILES:
                 B200_REQUIRE(value >= 0 && value <= 2, "sparse tile store mode must be 0 (auto), 1 (never) or 2 (always)");
@@ -310,6 +313,7 @@ int b200svm_set_data_dense(b200svm_handle h, const void *X, int64_t n, int64_t F
         c->has_q = false;
         c->has_split = false;
         c->has_Z = false;
+        dense_f64_cache_invalidate(*c);
         c->n = n;
         c->F = F;
         c->ldx = (F + 15) / 16 * 16;

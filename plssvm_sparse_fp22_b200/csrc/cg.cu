@@ -466,6 +466,22 @@ kd_result kernel_times_vector(ctx &c, const T *d, const T *done, bool have_sums 
             }
         }
         c.stats.matvec_path = 2;
+    } else if (sizeof(T) == 8 && dense_f64_cache_ready(c)) {
+        // dense double polynomial / rbf with the kernel matrix cached as lower-triangle tiles: symmetric HBM-bound sweep over this
+        // rank's tiles; several ranks: the partial-vector reduction stores straight into the peers
+        if constexpr (sizeof(T) == 8) {
+            c.P.reserve((size_t) ldP * sizeof(T));
+            xchg_plan plan{};
+            if (c.world > 1) { plan = comm_exchange_begin(c, m, XCHG_SUM); }
+            tile_store_matvec_f64(c, c.dts, c.q.as<double>(), d, c.QA_cost, m, c.P.as<double>(), plan.peer ? &plan.push : nullptr, done);
+            if (plan.peer) {
+                res.x = plan.view;
+                c.stats.collective_bytes += m * (int64_t) sizeof(double) * (int64_t) (c.world - 1);
+            } else if (c.world > 1) {
+                comm_allreduce_sum(c, c.P.p, m);
+            }
+        }
+        c.stats.matvec_path = 1;
     } else {
         // full rows [lo, hi) of the implicit matrix on this rank (all rows when world == 1)
         c.P.reserve((size_t) (MAXS * ldP) * sizeof(T));

@@ -647,17 +647,149 @@ __global__ void __launch_bounds__(256) k_pack(const float *__restrict__ norms, c
     pk[i] = v;
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// The same sweep for DOUBLE tiles (dense double polynomial / rbf): 128 x 256 tiles of 8-byte kernel values in
+// pair-column-major order (double2 of columns (2 cp, 2 cp + 1), row r at cp * 128 + r), 512 threads: warp w owns the 16 columns
+// [16 w, 16 w + 16), lane l the rows l, 32 + l, 64 + l, 96 + l — every load instruction streams 512 contiguous bytes.  Same chunk /
+// run / partial-vector structure as k_tile_sweep.  t_ij = K_ij + QA_cost - q_i - q_j.
+// ---------------------------------------------------------------------------------------------------------------------
+struct sweep_params_f64 {
+    const double *Kc;
+    const int4 *list;
+    int num_tiles;
+    int nchunks;
+    const int *first_slot;
+    const double2 *pk;       // [n_pad] {q_i, w_i}
+    double *Pr;
+    double *Pc;
+    int64_t ldP;
+    double qa;
+    const double *done;
+};
+
+__device__ __forceinline__ double warp_column_sums16(double (&v)[16], int lane) {
+#pragma unroll
+    for (int o = 8; o >= 1; o >>= 1) {
+        const bool up = (lane & o) != 0;
+#pragma unroll
+        for (int k = 0; k < o; ++k) {
+            const double send = up ? v[k] : v[k + o];
+            const double keep = up ? v[k + o] : v[k];
+            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
+    }
+    return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 16);  // both half-warps end with column (lane & 15)
+}
+
+__global__ void __launch_bounds__(512, 1) k_tile_sweep_f64(const sweep_params_f64 p) {
+    if (p.done != nullptr && *p.done != 0.0) { return; }
+    __shared__ double colq[BN], cold[BN];
+    __shared__ double rowpart[2][16][BM];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    for (int c = blockIdx.x; c < p.nchunks; c += gridDim.x) {
+        const int k0 = (int) ((int64_t) p.num_tiles * c / p.nchunks), k1 = (int) ((int64_t) p.num_tiles * (c + 1) / p.nchunks);
+        int curJ = -1, slot = 0;
+        double cs[16];
+        for (int k = k0; k < k1; ++k) {
+            const int4 tile = __ldg(&p.list[k]);
+            const int64_t row0 = static_cast<int64_t>(tile.x) * BM, col0 = static_cast<int64_t>(tile.y) * BN;
+            if (tile.y != curJ) {
+                if (curJ >= 0) {
+                    const double ctot = warp_column_sums16(cs, lane);
+                    if (lane < 16) { p.Pc[static_cast<int64_t>(slot) * p.ldP + static_cast<int64_t>(curJ) * BN + 16 * w + lane] = ctot; }
+                }
+                slot = k == k0 ? __ldg(&p.first_slot[c]) : 0;
+                curJ = tile.y;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) { cs[i] = 0.0; }
+                if (t < BN) {
+                    const double2 v = __ldg(&p.pk[col0 + t]);
+                    colq[t] = v.x;
+                    cold[t] = v.y;
+                }
+                __syncthreads();
+            }
+            const bool diag_tile = row0 < col0 + BN;
+            double ai[4], di[4];
+#pragma unroll
+            for (int rg = 0; rg < 4; ++rg) {
+                const double2 v = __ldg(&p.pk[row0 + rg * 32 + lane]);
+                ai[rg] = p.qa - v.x;
+                di[rg] = v.y;
+            }
+            const double2 *base = reinterpret_cast<const double2 *>(p.Kc) + static_cast<int64_t>(tile.z) * (BM * BN / 2) + static_cast<int64_t>(8 * w) * BM + lane;
+            double rs[4] = { 0.0, 0.0, 0.0, 0.0 };
+#pragma unroll
+            for (int q0 = 0; q0 < 8; q0 += 2) {
+                double2 kv[2][4];
+#pragma unroll
+                for (int kk = 0; kk < 2; ++kk) {
+#pragma unroll
+                    for (int rg = 0; rg < 4; ++rg) { kv[kk][rg] = __ldcs(base + (q0 + kk) * BM + rg * 32); }
+                }
+#pragma unroll
+                for (int kk = 0; kk < 2; ++kk) {
+                    const int cp = 8 * w + q0 + kk;  // column pair inside the tile
+                    const double qj[2] = { colq[2 * cp], colq[2 * cp + 1] };
+                    const double dj[2] = { cold[2 * cp], cold[2 * cp + 1] };
+                    double ca[2] = { 0.0, 0.0 };
+#pragma unroll
+                    for (int rg = 0; rg < 4; ++rg) {
+                        const double e[2] = { kv[kk][rg].x, kv[kk][rg].y };
+                        const int64_t gi = row0 + rg * 32 + lane;
+#pragma unroll
+                        for (int cc = 0; cc < 2; ++cc) {
+                            const int64_t gj = col0 + 2 * cp + cc;
+                            const double tv = e[cc] + (ai[rg] - qj[cc]);
+                            const bool lower = !diag_tile || gi >= gj, strict = !diag_tile || gi > gj;
+                            rs[rg] = lower ? fma(tv, dj[cc], rs[rg]) : rs[rg];
+                            ca[cc] = strict ? fma(tv, di[rg], ca[cc]) : ca[cc];
+                        }
+                    }
+                    cs[(q0 + kk) * 2] += ca[0];
+                    cs[(q0 + kk) * 2 + 1] += ca[1];
+                }
+            }
+            const int buf = (k - k0) & 1;
+#pragma unroll
+            for (int rg = 0; rg < 4; ++rg) { rowpart[buf][w][rg * 32 + lane] = rs[rg]; }
+            __syncthreads();
+            if (t < BM) {
+                const double(*rp)[BM] = rowpart[buf];
+                double s = 0.0;
+#pragma unroll
+                for (int ww = 0; ww < 16; ww += 4) { s += (rp[ww][t] + rp[ww + 1][t]) + (rp[ww + 2][t] + rp[ww + 3][t]); }
+                p.Pr[static_cast<int64_t>(tile.y) * p.ldP + row0 + t] = s;
+            }
+        }
+        if (curJ >= 0) {
+            const double ctot = warp_column_sums16(cs, lane);
+            if (lane < 16) { p.Pc[static_cast<int64_t>(slot) * p.ldP + static_cast<int64_t>(curJ) * BN + 16 * w + lane] = ctot; }
+        }
+    }
+}
+
+// pk[i] = {q_i, w_i} for i < m, zeros above
+__global__ void __launch_bounds__(256) k_pack_f64(const double *__restrict__ q, const double *__restrict__ w, int64_t m, int64_t n_pad, double2 *__restrict__ pk) {
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pad) { return; }
+    pk[i] = i < m ? make_double2(q[i], w[i]) : make_double2(0.0, 0.0);
+}
+
 // Sum of the partial vectors of element i -> out[i], or (several ranks, peer exchange) straight into slot `rank` of every
 // peer's exchange buffer over NVLink: the reduction kernel IS the producer of the exchange (xchg.cuh).
-struct reduce_dst {
-    float *out;
+template <typename T>
+struct reduce_dst_t {
+    T *out;
     xchg_push push;
     int remote;  // 0: out, 1: peers
 };
-__device__ __forceinline__ void reduce_emit(const reduce_dst &dst, unsigned long long seq, int64_t i, float v) {
+using reduce_dst = reduce_dst_t<float>;
+template <typename T>
+__device__ __forceinline__ void reduce_emit(const reduce_dst_t<T> &dst, unsigned long long seq, int64_t i, T v) {
     if (dst.remote) {
 #pragma unroll 1
-        for (int r = 0; r < dst.push.world; ++r) { xchg_slot<float>(dst.push, r, seq, dst.push.rank)[i] = v; }
+        for (int r = 0; r < dst.push.world; ++r) { xchg_slot<T>(dst.push, r, seq, dst.push.rank)[i] = v; }
     } else {
         dst.out[i] = v;
     }
@@ -695,32 +827,33 @@ __global__ void __launch_bounds__(256) k_tc_reduce(const float *__restrict__ Pr,
 // column partials of the runs of strip J_i.  One CTA per 32 consecutive elements: warp w sums the w-th eighth of the strip list
 // (four interleaved accumulators) and every eighth run, the eight warp partials are combined through shared memory in a fixed
 // tree — 8 x shorter dependent load chains than one thread per element (58 -> ~10 us at 65536 points), fixed order => reproducible.
-__global__ void __launch_bounds__(256) k_sweep_reduce(const float *__restrict__ Pr, const float *__restrict__ Pc, int64_t ldP, int64_t m,
+template <typename T>
+__global__ void __launch_bounds__(256) k_sweep_reduce(const T *__restrict__ Pr, const T *__restrict__ Pc, int64_t ldP, int64_t m,
                                                       const int *__restrict__ jptr, const int *__restrict__ jlist, const int *__restrict__ nruns,
-                                                      const reduce_dst dst, const float *__restrict__ done) {
+                                                      const reduce_dst_t<T> dst, const T *__restrict__ done) {
     __shared__ bool is_last;
-    __shared__ float part[8][32];
-    if (done != nullptr && *done != 0.f) { return; }
+    __shared__ T part[8][32];
+    if (done != nullptr && *done != T(0)) { return; }
     const unsigned long long seq = dst.remote ? xchg_next_seq(dst.push) : 0ull;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int64_t i = (int64_t) blockIdx.x * 32 + lane;
-    float tot = 0.f;
+    T tot = T(0);
     if (i < m) {
         const int Ii = (int) (i / BM), Ji = (int) (i / BN);  // (the same for the 32 elements of the CTA)
         const int j0 = __ldg(&jptr[Ii]), len = __ldg(&jptr[Ii + 1]) - j0;
         const int ka = j0 + (int) ((int64_t) len * w / 8), kb = j0 + (int) ((int64_t) len * (w + 1) / 8);
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        T s0 = T(0), s1 = T(0), s2 = T(0), s3 = T(0);
         int k = ka;
         for (; k + 4 <= kb; k += 4) {
             const int Ja = __ldg(&jlist[k]), Jb = __ldg(&jlist[k + 1]), Jc = __ldg(&jlist[k + 2]), Jd = __ldg(&jlist[k + 3]);
-            const float a0 = Pr[(int64_t) Ja * ldP + i], a1 = Pr[(int64_t) Jb * ldP + i], a2 = Pr[(int64_t) Jc * ldP + i], a3 = Pr[(int64_t) Jd * ldP + i];
+            const T a0 = Pr[(int64_t) Ja * ldP + i], a1 = Pr[(int64_t) Jb * ldP + i], a2 = Pr[(int64_t) Jc * ldP + i], a3 = Pr[(int64_t) Jd * ldP + i];
             s0 += a0;
             s1 += a1;
             s2 += a2;
             s3 += a3;
         }
         for (; k < kb; ++k) { s0 += Pr[(int64_t) __ldg(&jlist[k]) * ldP + i]; }
-        float c = 0.f;
+        T c = T(0);
         const int nr = __ldg(&nruns[Ji]);
         for (int r = w; r < nr; r += 8) { c += Pc[(int64_t) r * ldP + i]; }
         tot = ((s0 + s1) + (s2 + s3)) + c;
@@ -1120,7 +1253,7 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out, bool packed, const xch
         sp.qa = p.qa;
         sp.done = done;
         tc::k_tile_sweep<true><<<st.sweep.nchunks, 256, 0, c.stream>>>(sp);
-        tc::k_sweep_reduce<<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(p.Pr, p.Pc, p.ldP, m, st.sweep.jptr.as<int>(), st.sweep.jlist.as<int>(),
+        tc::k_sweep_reduce<float><<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(p.Pr, p.Pc, p.ldP, m, st.sweep.jptr.as<int>(), st.sweep.jlist.as<int>(),
                                                                               st.sweep.nruns.as<int>(), dst, done);
     } else {
         if (!st.kc_valid) { launch_gram<false>(c, st, p); }
@@ -1140,6 +1273,7 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out, bool packed, const xch
 struct tile_store {
     sweep_plan sweep;
     dbuf pk, Pr, Pc, Kc;
+    size_t esize{ 4 };   // 4: float tiles (sparse S), 8: double tiles (dense double kernel matrix)
     int T_r{ 0 }, T_c{ 0 };
     int I_lo{ 0 }, I_hi{ 0 };
     int64_t n_pad{ 0 }, ldP{ 0 };
@@ -1176,8 +1310,9 @@ void tile_store_range(int64_t m, int rank, int world, int *I_lo, int *I_hi) {
     *I_hi = bound(rank + 1);
 }
 
-tile_store *tile_store_create(ctx &c, int64_t m) {
+tile_store *tile_store_create(ctx &c, int64_t m, size_t esize) {
     tile_store *ts = new tile_store();
+    ts->esize = esize;
     ts->n_pad = (m + tc::BN - 1) / tc::BN * tc::BN;
     ts->T_r = (int) (ts->n_pad / tc::BM);
     ts->T_c = (int) (ts->n_pad / tc::BN);
@@ -1190,9 +1325,9 @@ tile_store *tile_store_create(ctx &c, int64_t m) {
     ts->num_tiles = (int) tiles.size();
     try {
         build_sweep_plan(c, ts->sweep, tiles, ts->T_r, ts->T_c);
-        ts->pk.reserve((size_t) ts->n_pad * sizeof(float4));
-        ts->Pr.reserve((size_t) ts->T_c * ts->ldP * sizeof(float));
-        ts->Pc.reserve((size_t) std::max(ts->sweep.max_runs, 1) * ts->ldP * sizeof(float));
+        ts->pk.reserve((size_t) ts->n_pad * 16);  // float4 {-, -, w, -} or double2 {q, w}
+        ts->Pr.reserve((size_t) ts->T_c * ts->ldP * esize);
+        ts->Pc.reserve((size_t) std::max(ts->sweep.max_runs, 1) * ts->ldP * esize);
         B200_CUDA_CHECK(cudaMemsetAsync(ts->Pr.p, 0, ts->Pr.bytes, c.stream));
         B200_CUDA_CHECK(cudaMemsetAsync(ts->Pc.p, 0, ts->Pc.bytes, c.stream));
     } catch (...) {
@@ -1204,15 +1339,15 @@ tile_store *tile_store_create(ctx &c, int64_t m) {
 
 void tile_store_destroy(tile_store *ts) { delete ts; }
 int64_t tile_store_tiles(const tile_store *ts) { return ts->num_tiles; }
-size_t tile_store_bytes(const tile_store *ts) { return (size_t) ts->num_tiles * tc::BM * tc::BN * sizeof(float); }
+size_t tile_store_bytes(const tile_store *ts) { return (size_t) ts->num_tiles * tc::BM * tc::BN * ts->esize; }
 void tile_store_rows(const tile_store *ts, int64_t *row_lo, int64_t *row_hi, int64_t *first_tile) {
     *row_lo = (int64_t) ts->I_lo * tc::BM;
     *row_hi = (int64_t) ts->I_hi * tc::BM;
     *first_tile = tile_store_cum(ts->I_lo);
 }
-float *tile_store_alloc(tile_store *ts) {
+void *tile_store_alloc(tile_store *ts) {
     ts->Kc.reserve(std::max<size_t>(tile_store_bytes(ts), 16));
-    return ts->Kc.as<float>();
+    return ts->Kc.p;
 }
 
 // out[i] = sum_j S_ij w_j over the tiles of this rank (a full-length partial vector when world > 1)
@@ -1234,8 +1369,35 @@ void tile_store_matvec(ctx &c, tile_store *ts, const float *w, int64_t m, float 
     tc::reduce_dst dst{};
     dst.out = out;
     dst.remote = 0;
-    tc::k_sweep_reduce<<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(sp.Pr, sp.Pc, sp.ldP, m, ts->sweep.jptr.as<int>(), ts->sweep.jlist.as<int>(),
+    tc::k_sweep_reduce<float><<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(sp.Pr, sp.Pc, sp.ldP, m, ts->sweep.jptr.as<int>(), ts->sweep.jlist.as<int>(),
                                                                           ts->sweep.nruns.as<int>(), dst, done);
+    count_launch(c, 3);
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+
+// out[i] = sum_j (K_ij + QA_cost - q_i - q_j) w_j over the double tiles of this rank; push != nullptr: straight into the peers
+void tile_store_matvec_f64(ctx &c, tile_store *ts, const double *q, const double *w, double qa, int64_t m, double *out, const xchg_push *push,
+                           const double *done) {
+    tc::k_pack_f64<<<(unsigned) ((ts->n_pad + 255) / 256), 256, 0, c.stream>>>(q, w, m, ts->n_pad, ts->pk.as<double2>());
+    tc::sweep_params_f64 sp{};
+    sp.Kc = ts->Kc.as<double>();
+    sp.list = ts->sweep.list.as<int4>();
+    sp.num_tiles = ts->num_tiles;
+    sp.nchunks = ts->sweep.nchunks;
+    sp.first_slot = ts->sweep.first_slot.as<int>();
+    sp.pk = ts->pk.as<double2>();
+    sp.Pr = ts->Pr.as<double>();
+    sp.Pc = ts->Pc.as<double>();
+    sp.ldP = ts->ldP;
+    sp.qa = qa;
+    sp.done = done;
+    if (ts->num_tiles > 0) { tc::k_tile_sweep_f64<<<std::min(ts->sweep.nchunks, 2 * NUM_SMS), 512, 0, c.stream>>>(sp); }
+    tc::reduce_dst_t<double> dst{};
+    dst.out = out;
+    dst.remote = push != nullptr ? 1 : 0;
+    if (push != nullptr) { dst.push = *push; }
+    tc::k_sweep_reduce<double><<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(sp.Pr, sp.Pc, sp.ldP, m, ts->sweep.jptr.as<int>(), ts->sweep.jlist.as<int>(),
+                                                                                ts->sweep.nruns.as<int>(), dst, done);
     count_launch(c, 3);
     B200_CUDA_CHECK(cudaGetLastError());
 }

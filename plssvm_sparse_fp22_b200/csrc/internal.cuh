@@ -91,6 +91,7 @@ enum scal_index : int {
 };
 
 struct comm_state;  // NCCL communicator wrapper (comm.cu)
+struct tile_store;  // symmetric tile store (gram_tc.cu)
 
 struct ctx {
     // configuration
@@ -151,6 +152,10 @@ struct ctx {
     dbuf pts, pts_norms, pred_out, alpha_dev;  // predict staging
     void *pinned{ nullptr };                   // small pinned host mailbox (scalars / flags)
 
+    struct tile_store *dts{ nullptr };          // dense double polynomial / rbf: cached kernel-matrix tiles (kernels_simt.cu)
+    bool dts_valid{ false }, dts_refused{ false };
+    int dts_rank{ -1 }, dts_world{ 0 };
+    int64_t dts_m{ -1 };
     void *tc_opaque{ nullptr };                 // tcgen05 path state (gram_tc.cu)
     void (*tc_opaque_free)(void *){ nullptr };
     void *sp_opaque{ nullptr };                 // sparse path state (sparse.cu)
@@ -204,16 +209,19 @@ void tc_invalidate_cache(ctx &c);  // drop the cached kernel-matrix tiles (optio
 void tc_kernel_matvec(ctx &c, const float *d, float *out_Kd, bool packed, const xchg_push *push, const float *done);
 void *tc_pack_buffer(ctx &c);                                     // float4 pk[n_pad] of the tcgen05 path (nullptr when not prepared)
 
-// symmetric tile store (gram_tc.cu): a densely filled S of a CSR data set as dense lower-triangle tiles, swept like the dense cache
-struct tile_store;
-tile_store *tile_store_create(ctx &c, int64_t m);          // plan for c.rank / c.world (contiguous row-block ranges of equal tile count)
+// symmetric tile store (gram_tc.cu): a densely filled S of a CSR data set (float) or the kernel matrix of dense double data as dense
+// lower-triangle tiles, swept like the dense float cache
+bool dense_f64_cache_ready(ctx &c);        // dense double polynomial / rbf: tiles assembled (on first use) and valid?
+void dense_f64_cache_invalidate(ctx &c);
+tile_store *tile_store_create(ctx &c, int64_t m, size_t esize = 4);  // plan for c.rank / c.world (contiguous row-block ranges of equal tile count); esize 4 / 8
 void tile_store_destroy(tile_store *ts);
 int64_t tile_store_tiles(const tile_store *ts);
 size_t tile_store_bytes(const tile_store *ts);             // bytes of the stored tiles of this rank
 void tile_store_rows(const tile_store *ts, int64_t *row_lo, int64_t *row_hi, int64_t *first_tile);  // rows of this rank (multiples of 128), storage offset
 int64_t tile_store_cum(int64_t I);                         // tiles of the row blocks < I; tile (I, J) is stored at cum(I) - first_tile + J
-float *tile_store_alloc(tile_store *ts);                   // [tiles][64 column quads][128 rows] float4 (kc_quad_index layout)
+void *tile_store_alloc(tile_store *ts);                    // float: [tiles][64 column quads][128 rows] float4 (kc_quad_index); double: [tiles][128 column pairs][128 rows] double2
 void tile_store_matvec(ctx &c, tile_store *ts, const float *w, int64_t m, float *out, const float *done);
+void tile_store_matvec_f64(ctx &c, tile_store *ts, const double *q, const double *w, double qa, int64_t m, double *out, const xchg_push *push, const double *done);
 
 // sparse path (sparse.cu)
 void sp_invalidate_cache(ctx &c);  // drop the cached S (options changed); rebuilt on the next matvec

@@ -99,14 +99,18 @@ struct vec16<double> {
     static constexpr int N = 2;
 };
 
-template <typename T, int KERNEL, int TM, int TN, bool CENTER>
+// STORE (double): instead of reducing against v, the kernel values k(A_i, B_j) of the lower block triangle go to the
+// symmetric tile store (128 x 256 tiles, pair-column-major double2; tile (I, J) at tile_cum(I) - tile0 + J): P = the tiles, ldP = tile0,
+// qa = global index of A's first row; a CTA covers the 64-column tiles below the end of its row block's diagonal strip only.
+template <typename T, int KERNEL, int TM, int TN, bool CENTER, bool STORE = false>
 __global__ void __launch_bounds__(256)
     k_kmv_tile(const T *__restrict__ A, const T *__restrict__ normA, int64_t rowsA, int64_t ldA, const T *__restrict__ B,
                const T *__restrict__ normB, int64_t rowsB, int64_t ldB, int64_t K, const T *__restrict__ v, int degree, T gamma, T coef0,
                const T *__restrict__ qrow, const T *__restrict__ qcol, T qa, T *__restrict__ P, int64_t ldP, int col_tiles,
                const T *__restrict__ done) {
     constexpr int BM = 16 * TM, BN = 16 * TN;
-    if (*done != T(0)) { return; }  // CG convergence flag (scal[S_DONE]); uniform over the grid
+    static_assert(!STORE || (sizeof(T) == 8 && TM == 4 && TN == 4 && !CENTER), "the tile-store epilogue is written for the 64 x 64 double tile");
+    if (done != nullptr && *done != T(0)) { return; }  // CG convergence flag (scal[S_DONE]); uniform over the grid
     using V = typename vec16<T>::type;
     constexpr int VN = vec16<T>::N;
     constexpr int EA = BM * BK / 256, TPRA = BK / EA;  // elements per thread / threads per row when loading the A slice
@@ -118,6 +122,11 @@ __global__ void __launch_bounds__(256)
 
     const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
     const int64_t row0 = (int64_t) blockIdx.x * BM;
+    int64_t grow0 = 0;  // STORE: global index of the CTA's first row
+    if constexpr (STORE) {
+        grow0 = (int64_t) qa + row0;
+        col_tiles = (int) (256 * ((grow0 >> 8) + 1) / BN);  // columns below the end of the diagonal strip of row block grow0 / 128
+    }
     const int ct0 = (int) ((int64_t) blockIdx.y * col_tiles / gridDim.y);
     const int ct1 = (int) ((int64_t) (blockIdx.y + 1) * col_tiles / gridDim.y);
 
@@ -206,6 +215,26 @@ __global__ void __launch_bounds__(256)
             __syncthreads();
         }
 
+        if constexpr (STORE) {
+            // kernel values of this thread's 4 x 4 block -> two column pairs x four consecutive rows = two 64-byte runs of the tile
+            const int64_t grow = grow0 + ty * 4, col = col0 + tx * 4;
+            const int64_t Ib = grow >> 7, kk2 = Ib >> 1;
+            const int64_t cum = (Ib & 1) ? (kk2 + 1) * (kk2 + 1) : kk2 * (kk2 + 1);  // = tile_store_cum(Ib)
+            double2 *tb = reinterpret_cast<double2 *>(P) + (cum - ldP + (col >> 8)) * (int64_t) (128 * 256 / 2) + ((col & 255) >> 1) * 128 + (grow & 127);
+#pragma unroll
+            for (int r = 0; r < TM; ++r) {
+                if (row0 + ty * 4 + r < rowsA) {
+                    T kv[TN];
+#pragma unroll
+                    for (int cc = 0; cc < TN; ++cc) {
+                        const bool valid = col + cc < rowsB;
+                        kv[cc] = valid ? kernel_value<T, KERNEL>(acc[r][cc], na[r], normB[valid ? col + cc : 0], degree, gamma, coef0) : T(0);
+                    }
+                    tb[r] = make_double2(kv[0], kv[1]);
+                    tb[128 + r] = make_double2(kv[2], kv[3]);
+                }
+            }
+        } else {
         // epilogue of this Gram tile: kernel function, times v_j, row reduction in registers
 #pragma unroll
         for (int cc = 0; cc < TN; ++cc) {
@@ -222,16 +251,19 @@ __global__ void __launch_bounds__(256)
                 rowsum[r] = valid ? fma(kv, vj, rowsum[r]) : rowsum[r];
             }
         }
+        }
     }
 
-    // reduce over the 16 threads (tx) sharing a row; lanes of one row group are contiguous within a half-warp
+    if constexpr (!STORE) {
+        // reduce over the 16 threads (tx) sharing a row; lanes of one row group are contiguous within a half-warp
 #pragma unroll
-    for (int r = 0; r < TM; ++r) {
-        T s = rowsum[r];
+        for (int r = 0; r < TM; ++r) {
+            T s = rowsum[r];
 #pragma unroll
-        for (int o = 8; o > 0; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); }
-        const int64_t row = row0 + (r >> 2) * 64 + ty * 4 + (r & 3);
-        if (tx == 0 && row < rowsA) { P[(int64_t) blockIdx.y * ldP + row] = s; }
+            for (int o = 8; o > 0; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); }
+            const int64_t row = row0 + (r >> 2) * 64 + ty * 4 + (r & 3);
+            if (tx == 0 && row < rowsA) { P[(int64_t) blockIdx.y * ldP + row] = s; }
+        }
     }
 }
 
@@ -282,6 +314,71 @@ template int kmv_simt_launch<float>(ctx &, const float *, const float *, int64_t
                                     const float *, float *, int64_t, int, const float *, const float *, float);
 template int kmv_simt_launch<double>(ctx &, const double *, const double *, int64_t, int64_t, const double *, const double *, int64_t, int64_t,
                                      const double *, double *, int64_t, int, const double *, const double *, double);
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Dense double polynomial / rbf: cached kernel matrix.  The reference keeps the matrix implicit because its devices
+// cannot hold it; 65536 points in double are 17 GB of lower-triangle tiles on a B200.  First matvec after set_data: one pass of the
+// SIMT Gram kernel in STORE mode (FP64 FMA pipe bound, the same O(m^2 F) work as one implicit matvec, lower triangle only); every
+// later matvec: the HBM-bound symmetric sweep k_tile_sweep_f64.  Row blocks are dealt to the ranks by equal tile count.
+// ---------------------------------------------------------------------------------------------------------------------
+bool dense_f64_cache_ready(ctx &c) {
+    if (c.dtype != B200SVM_F64 || c.is_csr || c.kernel == B200SVM_LINEAR || c.opt_dense_cache == 1 || c.m() < 1) { return false; }
+    const int64_t m = c.m();
+    if (c.dts_valid && c.dts_rank == c.rank && c.dts_world == c.world && c.dts_m == m) { return true; }
+    if (c.dts_refused) { return false; }
+    c.dts_valid = false;
+    if (c.dts == nullptr || c.dts_rank != c.rank || c.dts_world != c.world || c.dts_m != m) {
+        tile_store_destroy(c.dts);
+        c.dts = nullptr;
+        c.dts = tile_store_create(c, m, sizeof(double));
+        c.dts_rank = c.rank;
+        c.dts_world = c.world;
+        c.dts_m = m;
+    }
+    const size_t need = tile_store_bytes(c.dts);
+    size_t free_b = 0, total_b = 0;
+    B200_CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
+    const double budget = c.opt_sparse_cache_mb > 0 ? (double) c.opt_sparse_cache_mb * 1048576.0 : 0.85 * (double) free_b;
+    if ((double) need > budget) {
+        B200_REQUIRE(c.opt_dense_cache != 2, "the cached kernel-matrix tiles do not fit the device memory budget");
+        c.dts_refused = true;
+        return false;
+    }
+    double *Kc = static_cast<double *>(tile_store_alloc(c.dts));
+    int64_t row_lo = 0, row_hi = 0, tile0 = 0;
+    tile_store_rows(c.dts, &row_lo, &row_hi, &tile0);
+    row_hi = std::min(row_hi, m);
+    if (c.cb_pending) { sync_stream(c); }
+    B200_CUDA_CHECK(cudaEventRecord(c.cb_ev[0], c.stream));
+    B200_CUDA_CHECK(cudaMemsetAsync(Kc, 0, need, c.stream));  // rows / columns >= m of the padded tiles
+    if (row_hi > row_lo) {
+        const int64_t rows = row_hi - row_lo;
+        const dim3 grid((unsigned) ((rows + 63) / 64), 8);
+        const double *A = c.X.as<double>() + row_lo * c.ldx;
+        const double *nA = c.norms.as<double>() + row_lo;
+        if (c.kernel == B200SVM_RBF) {
+            k_kmv_tile<double, B200SVM_RBF, 4, 4, false, true><<<grid, 256, 0, c.stream>>>(A, nA, rows, c.ldx, c.X.as<double>(), c.norms.as<double>(), m, c.ldx, c.ldx, nullptr,
+                                                                                       c.degree, c.gamma, c.coef0, nullptr, nullptr, (double) row_lo, Kc, tile0, 0, nullptr);
+        } else {
+            k_kmv_tile<double, B200SVM_POLYNOMIAL, 4, 4, false, true><<<grid, 256, 0, c.stream>>>(A, nA, rows, c.ldx, c.X.as<double>(), c.norms.as<double>(), m, c.ldx, c.ldx,
+                                                                                              nullptr, c.degree, c.gamma, c.coef0, nullptr, nullptr, (double) row_lo, Kc, tile0,
+                                                                                              0, nullptr);
+        }
+        count_launch(c);
+        B200_CUDA_CHECK(cudaGetLastError());
+    }
+    B200_CUDA_CHECK(cudaEventRecord(c.cb_ev[1], c.stream));
+    c.cb_pending = true;
+    c.dts_valid = true;
+    c.stats.dense_cache_bytes = (int64_t) need;
+    return true;
+}
+
+void dense_f64_cache_invalidate(ctx &c) {
+    c.dts_valid = false;
+    c.dts_refused = false;
+    if (c.dtype == B200SVM_F64 && !c.is_csr) { c.stats.dense_cache_bytes = 0; }
+}
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Linear kernel: K d = X (X^T d) — two HBM-bound GEMVs instead of an O(m^2 F) pairwise pass.

@@ -1354,7 +1354,7 @@ bool build_tile_store(ctx &c, sparse_state &st) {
             st.t_refused = true;
             return false;
         }
-        float *Kc = tile_store_alloc(st.ts);
+        float *Kc = static_cast<float *>(tile_store_alloc(st.ts));
         int64_t row_lo = 0, row_hi = 0, tile0 = 0;
         tile_store_rows(st.ts, &row_lo, &row_hi, &tile0);
         if (c.cb_pending) { sync_stream(c); }

@@ -371,3 +371,34 @@ def test_torch_device_tensor_api(kernel, dt):
     with pytest.raises(TypeError):
         LSSVM(kernel=kernel).fit(torch.from_numpy(X), torch.from_numpy(y))  # CPU tensors: no CPU path
     svm.close()
+
+
+@pytest.mark.parametrize("kernel", ["polynomial", "rbf"])
+@pytest.mark.parametrize("shape", [(130, 20), (700, 33), (1500, 96), (2600, 40)])
+def test_dense_double_tile_cache(kernel, shape):
+    """Dense double polynomial / rbf: the kernel matrix cached as lower-triangle 128 x 256 tiles (STORE pass of the SIMT Gram kernel +
+    symmetric sweep) against the implicit SIMT path on the same handle data and against the oracle."""
+    n, F = shape
+    X, y = datagen.make_dense(n, F, seed=n, problem="planes", dtype=np.float64)
+    d = np.random.default_rng(n).uniform(-1, 2, n - 1)
+    res = {}
+    for cache in (capi.CACHE_REQUIRED, capi.CACHE_OFF):
+        with capi.Handle(np.float64, kernel, gamma=1.0 / F) as h:
+            h.set_option(capi.OPT_DENSE_CACHE, cache)
+            h.set_data(X)
+            q = h.generate_q()
+            qa = h.kxx_last() + 1.0
+            h.set_q(q, qa)
+            mv = h.matvec(d, 1.0)
+            assert np.array_equal(mv, h.matvec(d, 1.0))
+            st = h.stats()
+            assert (st.dense_cache_bytes > 0) == (cache == capi.CACHE_REQUIRED)
+            alpha, rho, it = h.learn(y, eps=1e-3)
+            res[cache] = (mv, alpha, it, q, qa)
+    mv, alpha, it, q, qa = res[capi.CACHE_REQUIRED]
+    want = port.matvec(X, q, d, qa, 1.0, kernel, rows=(0, n - 1))
+    assert nrm_rel(want, mv) < 1e-12
+    assert nrm_rel(res[capi.CACHE_OFF][0], mv) < 1e-12
+    a_o, rho_o, it_o = port.learn(X, y, kernel, eps=1e-3, use_rows=True)
+    assert it == it_o == res[capi.CACHE_OFF][2]
+    assert nrm_rel(a_o, alpha) < 1e-10
