@@ -7,7 +7,9 @@ against the reference's own FLOAT noise on the same problem:
 
     err(ours vs f64 truth)  <=  max( FLOAT_FLOOR, FLOAT_K * max( err(reference float vs f64 truth), reference 1-vs-N-thread float spread ) )
 
-with FLOAT_FLOOR = 1e-5 (north_star's figure) and FLOAT_K = 4 (profiles/r2_float_policy_table.md has every golden case).
+with FLOAT_FLOOR = 1e-5 (north_star's figure) and FLOAT_K = 1: a float result of this library is never allowed to be further from the
+double truth than the reference's own float run is (profiles/r2_float_policy_table.md: measured on every golden case the ratio is
+0.01 ... 0.65).
 Double precision has no policy: 1e-10 norm-wise and identical iteration counts, as north_star states.
 """
 from __future__ import annotations
@@ -17,7 +19,7 @@ import os
 import numpy as np
 
 FLOAT_FLOOR = 1e-5
-FLOAT_K = 4.0
+FLOAT_K = 1.0
 
 
 def nrm_rel(want, got) -> float:

@@ -75,10 +75,6 @@ struct params {
     int degree;
     int kernel;
     float *Kc;          // STORE mode: kernel values of every tile, [num_tiles][BN / 4][BM] float4 (kc_quad_index)
-    // L2 prefetch of the NEXT super-tile's operand rows, dealt over the tiles of the current one: per tile
-    // {first A row, A rows, first B row, B rows}; a row = 2 num_k_blocks lines of 128 bytes (fp16 hi plane + cross-term plane)
-    const int4 *pf;
-    const uint8_t *plane_hi, *plane_xa, *plane_xb;
     const float *done;  // CG convergence flag (scal[S_DONE]): a launch queued behind the converged iteration returns at once
 };
 
@@ -379,23 +375,6 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
             const uint32_t use = static_cast<uint32_t>(it >> 1);
             const int2 tile = p.tiles[t];
             const int64_t row0 = static_cast<int64_t>(tile.x) * BM, col0 = static_cast<int64_t>(tile.y) * BN;
-            if (p.pf != nullptr) {
-                // this tile's share of the next super-tile's operand rows -> L2 (its first wave would otherwise run at DRAM latency:
-                // every super-tile touches 32 MB of operand rows for the first time)
-                const int4 pf = __ldg(&p.pf[t]);
-                const int lines_per_plane = p.num_k_blocks;          // 128-byte lines of one row of one plane
-                const int per_row = 2 * lines_per_plane;
-                const int total = (pf.y + pf.w) * per_row;
-                const int64_t row_bytes = static_cast<int64_t>(lines_per_plane) * 128;
-                for (int idx = et; idx < total; idx += EPI_WARPS * 32) {
-                    const int rr = idx / per_row, sub = idx - rr * per_row;
-                    const bool is_a = rr < pf.y;
-                    const int64_t grow = is_a ? pf.x + rr : pf.z + (rr - pf.y);
-                    const uint8_t *plane = sub < lines_per_plane ? p.plane_hi : (is_a ? p.plane_xa : p.plane_xb);
-                    const uint8_t *addr = plane + grow * row_bytes + static_cast<int64_t>(sub < lines_per_plane ? sub : sub - lines_per_plane) * 128;
-                    asm volatile("prefetch.global.L2::evict_last [%0];" ::"l"(addr));
-                }
-            }
             // stage the per-column data of this tile
             colbuf[buf * BN + et] = __ldg(&p.pk[col0 + et]);
             const int r = q * 32 + lane;
@@ -926,7 +905,7 @@ namespace {
 
 struct tc_state {
     CUtensorMap map_hi{}, map_lo{}, map_a8{}, map_b8{};
-    dbuf tiles, pk, Pr, Pc, amax, P8a, P8b, own, Kc, pf;
+    dbuf tiles, pk, Pr, Pc, amax, P8a, P8b, own, Kc;
     sweep_plan sweep;
     bool has_own{ false };
     bool kc_valid{ false }, kc_refused{ false };  // cached kernel-matrix tiles of this rank
@@ -974,58 +953,20 @@ void make_map(CUtensorMap *map, void *base, int64_t rows, int64_t ld_elems, bool
 }
 
 // lower block triangle, grouped in super-tiles of GI x GJ block tiles so that one wave of CTAs shares its operands in L2
-std::vector<int2> build_tiles(int T_r, int T_c, int rank, int world, std::vector<int> *group = nullptr) {
+std::vector<int2> build_tiles(int T_r, int T_c, int rank, int world) {
     constexpr int GI = 32, GJ = 16;
     std::vector<int2> all;
-    std::vector<int> gid;
-    int g = 0;
     for (int sj = 0; sj < T_c; sj += GJ) {
-        for (int si = 2 * sj; si < T_r; si += GI, ++g) {
+        for (int si = 2 * sj; si < T_r; si += GI) {
             for (int j = sj; j < std::min(sj + GJ, T_c); ++j) {
-                for (int i = std::max(si, 2 * j); i < std::min(si + GI, T_r); ++i) {
-                    all.push_back(make_int2(i, j));
-                    gid.push_back(g);
-                }
+                for (int i = std::max(si, 2 * j); i < std::min(si + GI, T_r); ++i) { all.push_back(make_int2(i, j)); }
             }
         }
     }
+    if (world <= 1) { return all; }
     // contiguous slice of the (uniform-cost) tile list per rank: balanced to within one tile
-    const size_t lo = world <= 1 ? 0 : all.size() * (size_t) rank / (size_t) world;
-    const size_t hi = world <= 1 ? all.size() : all.size() * (size_t) (rank + 1) / (size_t) world;
-    if (group != nullptr) { group->assign(gid.begin() + (std::ptrdiff_t) lo, gid.begin() + (std::ptrdiff_t) hi); }
+    const size_t lo = all.size() * (size_t) rank / (size_t) world, hi = all.size() * (size_t) (rank + 1) / (size_t) world;
     return std::vector<int2>(all.begin() + (std::ptrdiff_t) lo, all.begin() + (std::ptrdiff_t) hi);
-}
-
-// per tile: its share of the operand rows of the super-tile that follows its own in this rank's list (L2 prefetch, k_gram_tc)
-std::vector<int4> build_prefetch(const std::vector<int2> &tiles, const std::vector<int> &group) {
-    const size_t nt = tiles.size();
-    std::vector<int4> pf(nt, make_int4(0, 0, 0, 0));
-    size_t g0 = 0;
-    while (g0 < nt) {
-        size_t g1 = g0;
-        while (g1 < nt && group[g1] == group[g0]) { ++g1; }
-        size_t g2 = g1;
-        while (g2 < nt && group[g2] == group[g1 < nt ? g1 : g0]) { ++g2; }
-        if (g1 < nt) {
-            int imin = tiles[g1].x, imax = tiles[g1].x, jmin = tiles[g1].y, jmax = tiles[g1].y;
-            for (size_t t = g1; t < g2; ++t) {
-                imin = std::min(imin, tiles[t].x);
-                imax = std::max(imax, tiles[t].x);
-                jmin = std::min(jmin, tiles[t].y);
-                jmax = std::max(jmax, tiles[t].y);
-            }
-            const int a0 = imin * tc::BM, na = (imax + 1 - imin) * tc::BM, b0 = jmin * tc::BN, nb = (jmax + 1 - jmin) * tc::BN;
-            const int64_t L = (int64_t) na + nb, cnt = (int64_t) (g1 - g0);
-            for (size_t t = g0; t < g1; ++t) {
-                const int64_t r0 = L * (int64_t) (t - g0) / cnt, r1 = L * (int64_t) (t - g0 + 1) / cnt;  // rows [r0, r1) of the A rows followed by the B rows
-                const int64_t ar0 = std::min<int64_t>(r0, na), ar1 = std::min<int64_t>(r1, na);
-                const int64_t br0 = std::max<int64_t>(r0, na) - na, br1 = std::max<int64_t>(r1, na) - na;
-                pf[t] = make_int4(a0 + (int) ar0, (int) (ar1 - ar0), b0 + (int) br0, (int) (br1 - br0));
-            }
-        }
-        g0 = g1;
-    }
-    return pf;
 }
 
 }  // namespace
@@ -1085,14 +1026,10 @@ void tc_prepare_split(ctx &c) {
     st.T_r = (int) (c.n_pad / tc::BM);
     st.T_c = (int) (c.n_pad / tc::BN);
     st.ldP = c.n_pad;
-    std::vector<int> group;
-    const std::vector<int2> tiles = build_tiles(st.T_r, st.T_c, c.rank, c.world, &group);
+    const std::vector<int2> tiles = build_tiles(st.T_r, st.T_c, c.rank, c.world);
     st.num_tiles = (int) tiles.size();
     st.tiles.reserve(std::max<size_t>(tiles.size(), 1) * sizeof(int2));
     B200_CUDA_CHECK(cudaMemcpyAsync(st.tiles.p, tiles.data(), tiles.size() * sizeof(int2), cudaMemcpyHostToDevice, c.stream));
-    const std::vector<int4> pf = build_prefetch(tiles, group);
-    st.pf.reserve(std::max<size_t>(pf.size(), 1) * sizeof(int4));
-    B200_CUDA_CHECK(cudaMemcpyAsync(st.pf.p, pf.data(), pf.size() * sizeof(int4), cudaMemcpyHostToDevice, c.stream));
     std::vector<uint8_t> own_map;
     st.has_own = c.world > 1;
     if (st.has_own) {
@@ -1185,14 +1122,6 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out, bool packed, const xch
     p.kernel = c.kernel;
     p.Kc = nullptr;
     p.done = done;
-    static const bool no_prefetch = [] {
-        const char *e = std::getenv("B200SVM_TC_NO_PREFETCH");  // A/B switch
-        return e != nullptr && e[0] == '1';
-    }();
-    p.pf = no_prefetch ? nullptr : st.pf.as<int4>();
-    p.plane_hi = c.Xh_hi.as<uint8_t>();
-    p.plane_xa = st.fp8x ? st.P8a.as<uint8_t>() : c.Xh_lo.as<uint8_t>();
-    p.plane_xb = st.fp8x ? st.P8b.as<uint8_t>() : c.Xh_lo.as<uint8_t>();
     float cscale = 0.f;
     if (c.kernel == B200SVM_RBF) {
         p.w = (float) (2.0 * c.gamma * (double) LOG2E / (double) s2);
@@ -1345,6 +1274,7 @@ void tile_store_rows(const tile_store *ts, int64_t *row_lo, int64_t *row_hi, int
     *row_hi = (int64_t) ts->I_hi * tc::BM;
     *first_tile = tile_store_cum(ts->I_lo);
 }
+size_t tile_store_allocated(const tile_store *ts) { return ts->Kc.bytes; }  // bytes already held for the tiles (reused by the next assembly)
 void *tile_store_alloc(tile_store *ts) {
     ts->Kc.reserve(std::max<size_t>(tile_store_bytes(ts), 16));
     return ts->Kc.p;

@@ -217,6 +217,7 @@ tile_store *tile_store_create(ctx &c, int64_t m, size_t esize = 4);  // plan for
 void tile_store_destroy(tile_store *ts);
 int64_t tile_store_tiles(const tile_store *ts);
 size_t tile_store_bytes(const tile_store *ts);             // bytes of the stored tiles of this rank
+size_t tile_store_allocated(const tile_store *ts);         // bytes already allocated for them (a re-assembly reuses the buffer)
 void tile_store_rows(const tile_store *ts, int64_t *row_lo, int64_t *row_hi, int64_t *first_tile);  // rows of this rank (multiples of 128), storage offset
 int64_t tile_store_cum(int64_t I);                         // tiles of the row blocks < I; tile (I, J) is stored at cum(I) - first_tile + J
 void *tile_store_alloc(tile_store *ts);                    // float: [tiles][64 column quads][128 rows] float4 (kc_quad_index); double: [tiles][128 column pairs][128 rows] double2

@@ -338,6 +338,7 @@ bool dense_f64_cache_ready(ctx &c) {
     const size_t need = tile_store_bytes(c.dts);
     size_t free_b = 0, total_b = 0;
     B200_CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
+    free_b += tile_store_allocated(c.dts);  // the buffer of a previous assembly is reused
     const double budget = c.opt_sparse_cache_mb > 0 ? (double) c.opt_sparse_cache_mb * 1048576.0 : 0.85 * (double) free_b;
     if ((double) need > budget) {
         B200_REQUIRE(c.opt_dense_cache != 2, "the cached kernel-matrix tiles do not fit the device memory budget");

@@ -1349,6 +1349,7 @@ bool build_tile_store(ctx &c, sparse_state &st) {
         const size_t need = tile_store_bytes(st.ts);
         size_t free_b = 0, total_b = 0;
         B200_CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
+        free_b += tile_store_allocated(st.ts);  // the buffer of a previous assembly is reused
         const double budget = c.opt_sparse_cache_mb > 0 ? (double) c.opt_sparse_cache_mb * 1048576.0 : 0.85 * (double) free_b;
         if ((double) need > budget) {
             st.t_refused = true;
