@@ -465,7 +465,7 @@ def run_main_workload(a, env):
     dense_cache_bytes = int(st.dense_cache_bytes)
     # the matvec that assembles a cache is timed as a whole: take the assembly out to get the steady-state launch duration
     n_matvecs = int(st.matvecs_timed)
-    if not sparse and dense_cache_bytes > 0 and build_ms > 0:
+    if not sparse and dense_cache_bytes > 0 and build_ms > 0 and int(st.matvec_path) == 2:
         n_matvecs -= R  # dense tiles: the STORE pass of the tcgen05 kernel also serves the matvec that triggered it (no sweep in that one)
     matvec_ms = (st.matvec_ms - st.cache_build_ms) / max(n_matvecs, 1)
     matvec_total_ms = st.matvec_ms / R  # per solve, assembly included
@@ -530,7 +530,16 @@ def run_main_workload(a, env):
                 "peak_source": f"{env.peak_kind} bf16 dense (sustained)", "kernel": {1: "k_kmv_tile (SIMT)", 2: "k_gram_tc (tcgen05 fp16x2-split)", 3: "gemv pair"}.get(path, "?"),
                 "alg_flops_per_launch": flops, "ms_per_launch": matvec_ms, "launches_timed": n_matvecs}
         matvec_gflops = world * flops / (matvec_ms * 1e-3) / 1e9 if matvec_ms > 0 else None
-        if not sparse and path == 1:
+        if not sparse and path == 1 and dense_cache_bytes > 0:
+            # dense double polynomial / rbf with the kernel matrix cached as double lower-triangle tiles
+            fl_asm = float(F) * float(n - 1) * float(n) / world  # the STORE pass evaluates the lower triangle once: F m (m + 1) flops
+            roof = hbm_roofline(env, dense_cache_bytes, matvec_ms, "k_tile_sweep_f64 (sweep over the stored double kernel-matrix tiles; k_sweep_reduce inside the timed span)",
+                                {"launches_timed": n_matvecs,
+                                 "assembly": {"kernel": "k_kmv_tile<double, STORE> (SIMT Gram tiles on the FP64 FMA pipe, once per data set, inside the timed region)",
+                                              "ms": build_ms, "alg_flops": fl_asm, "achieved_tflops": fl_asm / (build_ms * 1e-3) / 1e12 if build_ms > 0 else None,
+                                              "fp64_fma_peak_tflops_measured": fma_peak}})
+            matvec_gflops = world * float(dense_cache_bytes) / 8.0 * 4.0 / (matvec_ms * 1e-3) / 1e9 if matvec_ms > 0 else None
+        elif not sparse and path == 1:
             # SIMT Gram tiles (double precision, or float with --path 1): full square, no symmetry -> 2 F m^2 FMA flops per matvec,
             # bound by the FP64 / FP32 FMA pipe; the peak is measured on this device by a register-only FMA kernel
             fl = 2.0 * F * float(n - 1) * float(n - 1) / world
