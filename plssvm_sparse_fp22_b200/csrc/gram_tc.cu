@@ -712,17 +712,29 @@ __global__ void __launch_bounds__(512, 1) k_tile_sweep_f64(const sweep_params_f6
                     const double qj[2] = { colq[2 * cp], colq[2 * cp + 1] };
                     const double dj[2] = { cold[2 * cp], cold[2 * cp + 1] };
                     double ca[2] = { 0.0, 0.0 };
+                    if (!diag_tile) {
 #pragma unroll
-                    for (int rg = 0; rg < 4; ++rg) {
-                        const double e[2] = { kv[kk][rg].x, kv[kk][rg].y };
-                        const int64_t gi = row0 + rg * 32 + lane;
+                        for (int rg = 0; rg < 4; ++rg) {
+                            const double e[2] = { kv[kk][rg].x, kv[kk][rg].y };
 #pragma unroll
-                        for (int cc = 0; cc < 2; ++cc) {
-                            const int64_t gj = col0 + 2 * cp + cc;
-                            const double tv = e[cc] + (ai[rg] - qj[cc]);
-                            const bool lower = !diag_tile || gi >= gj, strict = !diag_tile || gi > gj;
-                            rs[rg] = lower ? fma(tv, dj[cc], rs[rg]) : rs[rg];
-                            ca[cc] = strict ? fma(tv, di[rg], ca[cc]) : ca[cc];
+                            for (int cc = 0; cc < 2; ++cc) {
+                                const double tv = e[cc] + (ai[rg] - qj[cc]);
+                                rs[rg] = fma(tv, dj[cc], rs[rg]);
+                                ca[cc] = fma(tv, di[rg], ca[cc]);
+                            }
+                        }
+                    } else {
+                        const int off = (int) (col0 - row0);  // row i of the tile is below column j  <=>  i - j > off
+#pragma unroll
+                        for (int rg = 0; rg < 4; ++rg) {
+                            const double e[2] = { kv[kk][rg].x, kv[kk][rg].y };
+#pragma unroll
+                            for (int cc = 0; cc < 2; ++cc) {
+                                const int dif = rg * 32 + lane - (2 * cp + cc);
+                                const double tv = e[cc] + (ai[rg] - qj[cc]);
+                                rs[rg] = dif >= off ? fma(tv, dj[cc], rs[rg]) : rs[rg];  // lower triangle incl. diagonal -> row i
+                                ca[cc] = dif > off ? fma(tv, di[rg], ca[cc]) : ca[cc];   // strictly lower -> mirrored into column j
+                            }
                         }
                     }
                     cs[(q0 + kk) * 2] += ca[0];
