@@ -479,6 +479,7 @@ def run_main_workload(a, env):
     #      reaches the float noise floor after 2-3 iterations — so their alpha is rounding noise and is not compared.)
     parity = None
     if world > 1:
+        drop_caches(h)  # like the fresh single-GPU handle below, the solve starts with the assembly (STORE) pass
         aN, itN, _ = h.solver_cg(b, None, QA, F, 1e-3)
         t_alpha = torch.from_numpy(aN.astype(np.float64)).cuda()
         ref_alpha = t_alpha.clone()
@@ -502,7 +503,7 @@ def run_main_workload(a, env):
         parity = {"alpha_bit_identical_across_ranks": bool(int(same[0]) == 1), "alpha_of_the_timed_solve_bit_identical_across_ranks": bool(int(same_k[0]) == 1),
                   "iterations": int(itN), "iterations_single_gpu": it1, "alpha_relerr_vs_single_gpu": dist1,
                   "note": "solve at the configured eps = 1e-3 (imax = F) on N ranks vs one rank: norm-wise ||alpha_N - alpha_1|| / ||alpha_1|| "
-                          "(float: the summation order of the partial vectors differs with N)"}
+                          "(0 = bit-identical: the tile paths sum their partial vectors over eight canonical tile groups in a fixed tree for 1, 2, 4 and 8 GPUs)"}
 
     # ---- e2e leg: host buffers through the C ABI ----
     def e2e_once():

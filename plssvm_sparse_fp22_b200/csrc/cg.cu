@@ -47,6 +47,8 @@ __global__ void __launch_bounds__(VEC_THREADS) k_sums2(const T *__restrict__ v, 
 // CENTER 0: P already holds the per-entry centred sums (dense tile kernels)
 //        1: dense linear Z Z^T form: + sum(d) / C
 //        2: P holds the un-centred K d (sparse paths): + (QA_cost - q_i) sum(d) - q.d   (the rank-1 part of svm_kernel.cpp:32)
+//        3: P holds the raw S v of the sparse dense-tile path: K d = u_i (sum v + S v) (rbf) or c0^deg sum v + S v (polynomial) is
+//           formed here, AFTER the partial vectors of the ranks have been combined, then as 2
 // Several ranks: P / splits describe the slots of the peer exchange (xchg.cuh); the kernel waits for every source first.
 template <typename T>
 struct finish_args {
@@ -64,14 +66,34 @@ struct finish_args {
     T *partials;
     unsigned int *ticket;
     T *mailbox;        // pinned host slot that receives delta (MODE 1), or nullptr
+    const T *u;        // CENTER 3: u_i = exp(-gamma |x_i|^2) (rbf)
+    T c0pow;           // CENTER 3: coef0^degree (polynomial)
+    int rbf;
 };
+
+// CENTER 2 / 3: the un-centred K d of element i -> + the rank-1 centring
+template <typename T>
+__device__ __forceinline__ T centre_sparse(const finish_args<T> &a, T kd, int64_t i, T sum_d, T q_d, T sum_v) {
+    if (a.center == 3) { kd = a.rbf ? a.u[i] * (sum_v + kd) : fma(a.c0pow, sum_v, kd); }
+    return kd + fma(a.qa - a.q[i], sum_d, -q_d);
+}
 
 // (K d)_i from the partial vectors
 template <typename T>
 __device__ __forceinline__ T gather_kd(const T *__restrict__ P, int64_t ldP, int splits, bool remote, int64_t i) {
     T kd = T(0);
     if (remote) {
-        for (int s = 0; s < splits; ++s) { kd += __ldcg(&P[(int64_t) s * ldP + i]); }  // rank order: identical on every rank; past L1 (peer-written)
+        // the ranks' slots, read past L1 (peer-written), combined in a fixed order that is identical on every rank: the balanced tree
+        // of group_tree (gram_tc.cu) for 2 / 4 / 8 ranks — with the tile paths' canonical groups the sum is then bit-identical to the
+        // one a single GPU forms — else rank order
+        if (splits == 2 || splits == 4 || splits == 8) {
+            T v[8];
+#pragma unroll
+            for (int s = 0; s < 8; ++s) { v[s] = s < splits ? __ldcg(&P[(int64_t) s * ldP + i]) : T(0); }
+            kd = splits == 8 ? ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7])) : (splits == 4 ? (v[0] + v[1]) + (v[2] + v[3]) : v[0] + v[1]);
+        } else {
+            for (int s = 0; s < splits; ++s) { kd += __ldcg(&P[(int64_t) s * ldP + i]); }
+        }
     } else {
         for (int s = 0; s < splits; ++s) { kd += P[(int64_t) s * ldP + i]; }
     }
@@ -89,13 +111,14 @@ __global__ void __launch_bounds__(VEC_THREADS) k_abar_finish(const finish_args<T
     const int64_t ldP = remote ? a.x.ld : a.ldP;
     const int splits = remote ? a.x.slots : a.splits;
     const T sum_d = a.center != 0 ? a.scal[S_SUM_D] : T(0);
-    const T q_d = a.center == 2 ? a.scal[S_Q_D] : T(0);
+    const T q_d = a.center >= 2 ? a.scal[S_Q_D] : T(0);
+    const T sum_v = a.center == 3 ? a.scal[S_TMP0] : T(0);
     const T rank1 = a.center == 1 ? sum_d * a.inv_cost : T(0);
     T acc[1] = { T(0) };
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < a.m; i += (int64_t) gridDim.x * blockDim.x) {
         T kd = gather_kd<T>(P, ldP, splits, remote, i);
         const T di = a.d[i];
-        if (a.center == 2) { kd += fma(a.qa - a.q[i], sum_d, -q_d); }
+        if (a.center >= 2) { kd = centre_sparse(a, kd, i, sum_d, q_d, sum_v); }
         const T val = kd + rank1 + di * a.inv_cost;
         if constexpr (MODE == 0) {
             a.out[i] = val;
@@ -244,7 +267,8 @@ __global__ void __launch_bounds__(VEC_THREADS) k_cg_step(const step_args<T> a) {
     const int splits = remote ? f.x.slots : f.splits;
     const T delta = f.scal[S_DELTA];
     const T sum_d = f.center != 0 ? f.scal[S_SUM_D] : T(0);
-    const T q_d = f.center == 2 ? f.scal[S_Q_D] : T(0);
+    const T q_d = f.center >= 2 ? f.scal[S_Q_D] : T(0);
+    const T sum_v = f.center == 3 ? f.scal[S_TMP0] : T(0);
     const T rank1 = f.center == 1 ? sum_d * f.inv_cost : T(0);
     const int64_t first = (int64_t) blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t) gridDim.x * blockDim.x;
     const int nblk = (int) gridDim.x;
@@ -254,7 +278,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_cg_step(const step_args<T> a) {
     for (int64_t i = first; i < f.m; i += stride) {
         T kd = gather_kd<T>(P, ldP, splits, remote, i);
         const T di = a.dvec[i];
-        if (f.center == 2) { kd += fma(f.qa - f.q[i], sum_d, -q_d); }
+        if (f.center >= 2) { kd = centre_sparse(f, kd, i, sum_d, q_d, sum_v); }
         const T val = kd + rank1 + di * f.inv_cost;
         Ad[i] = val;
         acc = fma(di, val, acc);
@@ -387,6 +411,9 @@ struct kd_result {
     int64_t ldP;
     int splits;
     int center;  // see k_abar_finish
+    const void *u{ nullptr };  // CENTER 3
+    double c0pow{ 0 };
+    int rbf{ 0 };
     xchg_view x; // several ranks, peer exchange: where the partial vectors of all ranks arrive (base == nullptr: c.P holds the sum)
 };
 
@@ -408,7 +435,10 @@ kd_result kernel_times_vector(ctx &c, const T *d, const T *done, bool have_sums 
     const int64_t m = c.m();
     const int64_t ldP = (m + 255) / 256 * 256;
     constexpr int MAXS = 64;
-    kd_result res{ ldP, 1, 0, xchg_view{} };
+    kd_result res{};
+    res.ldP = ldP;
+    res.splits = 1;
+    res.center = 0;
     const bool timed = c.ev_head - c.ev_tail < ctx::EV_RING;
     const int ev_slot = (int) (c.ev_head % ctx::EV_RING);
     if (timed) { B200_CUDA_CHECK(cudaEventRecord(c.ev[2 * ev_slot], c.stream)); }
@@ -431,9 +461,12 @@ kd_result kernel_times_vector(ctx &c, const T *d, const T *done, bool have_sums 
         c.P.reserve((size_t) ldP * sizeof(T));
         if (!have_sums) { sums2<T>(c, d, S_SUM_D, S_Q_D); }
         const bool zero_rest = c.world > 1 && !comm_peer_mode(c, m);
-        // (false: dense-tile S cache — tile-partitioned partial vectors of full length, summed over the ranks)
-        exchange(sp_kernel_matvec<T>(c, d, c.P.as<T>(), zero_rest, done) ? XCHG_GATHER : XCHG_SUM);
-        res.center = 2;
+        // (false: dense-tile S cache — tile-partitioned RAW partial vectors S v of full length, summed over the ranks; K d is formed
+        //  from the sum by the O(m) epilogue, centre mode 3)
+        const bool rows = sp_kernel_matvec<T>(c, d, c.P.as<T>(), zero_rest, done);
+        exchange(rows ? XCHG_GATHER : XCHG_SUM);
+        res.center = rows ? 2 : 3;
+        if (!rows) { sp_finish_params(c, &res.u, &res.c0pow, &res.rbf); }
         c.stats.matvec_path = 4;
     } else if (c.kernel == B200SVM_LINEAR) {
         // centred linear kernel: sum_j (K_ij + K_nn - K_in - K_nj) d_j = Z (Z^T d), Z = X - 1 x_n^T : two GEMVs (HBM bound);
@@ -528,6 +561,9 @@ finish_args<T> make_finish_args(ctx &c, const kd_result &kd, const T *d, T add, 
     a.partials = c.partials.as<T>();
     a.ticket = c.counters.as<unsigned int>();
     a.mailbox = mailbox;
+    a.u = static_cast<const T *>(kd.u);
+    a.c0pow = (T) kd.c0pow;
+    a.rbf = kd.rbf;
     return a;
 }
 

@@ -472,10 +472,10 @@ struct sweep_params {
     const int4 *list;        // tiles of this rank sorted by (J, I): {I, J, storage index, 0}
     int num_tiles;
     int nchunks;
-    const int *first_slot;   // [nchunks] run index (within its strip) of the first run of a chunk
+    const int4 *chunks;      // [nchunks] {first tile, end tile, partial-vector slot of the chunk's first run, first slot of the chunk's group}
     const float4 *pk;        // [n_pad] {-, q_i, w_i, -}
     float *Pr;               // [T_c][ldP]
-    float *Pc;               // [max_runs][ldP]
+    float *Pc;               // [slots][ldP]: one per (group, run of a strip)
     int64_t ldP;
     float qa;
     const float *done;
@@ -489,7 +489,8 @@ __global__ void __launch_bounds__(256, 2) k_tile_sweep(const sweep_params p) {
     __shared__ float rowpart[2][8][BM];  // per warp: totals of the 128 rows over its 32 columns (double-buffered over the tiles)
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
     for (int c = blockIdx.x; c < p.nchunks; c += gridDim.x) {
-        const int k0 = (int) ((int64_t) p.num_tiles * c / p.nchunks), k1 = (int) ((int64_t) p.num_tiles * (c + 1) / p.nchunks);
+        const int4 chunk = __ldg(&p.chunks[c]);
+        const int k0 = chunk.x, k1 = chunk.y;
         int curJ = -1, slot = 0;
         float cs[32];
         for (int k = k0; k < k1; ++k) {
@@ -500,7 +501,7 @@ __global__ void __launch_bounds__(256, 2) k_tile_sweep(const sweep_params p) {
                     const float ctot = warp_column_sums(cs, lane);  // lane j: column 32 w + j over the rows of the run
                     p.Pc[static_cast<int64_t>(slot) * p.ldP + static_cast<int64_t>(curJ) * BN + 32 * w + lane] = ctot;
                 }
-                slot = k == k0 ? __ldg(&p.first_slot[c]) : 0;
+                slot = k == k0 ? chunk.z : chunk.w;  // (a run that starts inside a chunk starts its strip within the group)
                 curJ = tile.y;
 #pragma unroll
                 for (int i = 0; i < 32; ++i) { cs[i] = 0.f; }
@@ -637,7 +638,7 @@ struct sweep_params_f64 {
     const int4 *list;
     int num_tiles;
     int nchunks;
-    const int *first_slot;
+    const int4 *chunks;
     const double2 *pk;       // [n_pad] {q_i, w_i}
     double *Pr;
     double *Pc;
@@ -666,7 +667,8 @@ __global__ void __launch_bounds__(512, 1) k_tile_sweep_f64(const sweep_params_f6
     __shared__ double rowpart[2][16][BM];
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
     for (int c = blockIdx.x; c < p.nchunks; c += gridDim.x) {
-        const int k0 = (int) ((int64_t) p.num_tiles * c / p.nchunks), k1 = (int) ((int64_t) p.num_tiles * (c + 1) / p.nchunks);
+        const int4 chunk = __ldg(&p.chunks[c]);
+        const int k0 = chunk.x, k1 = chunk.y;
         int curJ = -1, slot = 0;
         double cs[16];
         for (int k = k0; k < k1; ++k) {
@@ -677,7 +679,7 @@ __global__ void __launch_bounds__(512, 1) k_tile_sweep_f64(const sweep_params_f6
                     const double ctot = warp_column_sums16(cs, lane);
                     if (lane < 16) { p.Pc[static_cast<int64_t>(slot) * p.ldP + static_cast<int64_t>(curJ) * BN + 16 * w + lane] = ctot; }
                 }
-                slot = k == k0 ? __ldg(&p.first_slot[c]) : 0;
+                slot = k == k0 ? chunk.z : chunk.w;  // (a run that starts inside a chunk starts its strip within the group)
                 curJ = tile.y;
 #pragma unroll
                 for (int i = 0; i < 16; ++i) { cs[i] = 0.0; }
@@ -786,42 +788,30 @@ __device__ __forceinline__ void reduce_emit(const reduce_dst_t<T> &dst, unsigned
     }
 }
 
-// Partial vectors of the Gram kernel (one per tile row / tile column):
-// out[i] = sum_{J <= I_i / 2} Pr[J][i] + sum_{I' >= 2 J_i} Pc[I'][i]   (fixed order; slots of tiles owned by other ranks are skipped)
-// own (multi-GPU): byte map [T_r][T_c] of the tiles this rank computes
-__global__ void __launch_bounds__(256) k_tc_reduce(const float *__restrict__ Pr, const float *__restrict__ Pc, int64_t ldP, int64_t m, int T_r,
-                                                   int T_c, const uint8_t *__restrict__ own, const reduce_dst dst, const float *__restrict__ done) {
-    __shared__ bool is_last;
-    if (done != nullptr && *done != 0.f) { return; }
-    const unsigned long long seq = dst.remote ? xchg_next_seq(dst.push) : 0ull;
-    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < m) {
-        const int Ii = (int) (i / BM), Ji = (int) (i / BN);
-        float s0 = 0.f, s1 = 0.f;
-        if (own == nullptr) {
-            for (int J = 0; J <= Ii / 2; ++J) { s0 += Pr[(int64_t) J * ldP + i]; }
-            for (int I = 2 * Ji; I < T_r; ++I) { s1 += Pc[(int64_t) I * ldP + i]; }
-        } else {  // the map entries are warp-uniform (32 consecutive i share Ii and Ji)
-            for (int J = 0; J <= Ii / 2; ++J) {
-                if (own[Ii * T_c + J] != 0) { s0 += Pr[(int64_t) J * ldP + i]; }
-            }
-            for (int I = 2 * Ji; I < T_r; ++I) {
-                if (own[I * T_c + Ji] != 0) { s1 += Pc[(int64_t) I * ldP + i]; }
-            }
+// Fixed summation tree over the partial sums of up to eight tile GROUPS (DESIGN.md §6 "N-independent results"): the tiles are dealt
+// to eight canonical groups; a rank of a world of 1 / 2 / 4 / 8 owns 8 / 4 / 2 / 1 consecutive groups, sums each group's partial
+// vectors in the group's own fixed order, combines its groups by the balanced tree below, and the consumer combines the ranks' slots
+// by the same tree — the value of every element is bit-identical for 1, 2, 4 and 8 GPUs.
+template <typename T>
+__device__ __forceinline__ T group_tree(const T (&p)[8], int n) {
+    switch (n) {
+        case 8: return ((p[0] + p[1]) + (p[2] + p[3])) + ((p[4] + p[5]) + (p[6] + p[7]));
+        case 4: return (p[0] + p[1]) + (p[2] + p[3]);
+        case 2: return p[0] + p[1];
+        default: {
+            T s = p[0];
+            for (int g = 1; g < n; ++g) { s += p[g]; }
+            return s;
         }
-        reduce_emit(dst, seq, i, s0 + s1);
     }
-    if (dst.remote) { xchg_publish(dst.push, seq, &is_last); }
 }
 
-// Partial vectors of the sweep: row partials of the column strips this rank owns in row block I_i (jlist[jptr[I] .. jptr[I + 1])),
-// column partials of the runs of strip J_i.  One CTA per 32 consecutive elements: warp w sums the w-th eighth of the strip list
-// (four interleaved accumulators) and every eighth run, the eight warp partials are combined through shared memory in a fixed
-// tree — 8 x shorter dependent load chains than one thread per element (58 -> ~10 us at 65536 points), fixed order => reproducible.
+// Partial vectors of the Gram kernel (one per tile): out[i] = sum over the tiles (I_i, J) of Pr[J][i] + sum over the tiles (I, J_i) of
+// Pc[I][i], per group (gmap[I][J] = local group of the tile, 255 = not this rank's) in ascending J, then ascending I; one warp per
+// group, 32 elements per CTA.
 template <typename T>
-__global__ void __launch_bounds__(256) k_sweep_reduce(const T *__restrict__ Pr, const T *__restrict__ Pc, int64_t ldP, int64_t m,
-                                                      const int *__restrict__ jptr, const int *__restrict__ jlist, const int *__restrict__ nruns,
-                                                      const reduce_dst_t<T> dst, const T *__restrict__ done) {
+__global__ void __launch_bounds__(256) k_tc_reduce(const T *__restrict__ Pr, const T *__restrict__ Pc, int64_t ldP, int64_t m, int T_r, int T_c,
+                                                   const uint8_t *__restrict__ gmap, int groups, const reduce_dst_t<T> dst, const T *__restrict__ done) {
     __shared__ bool is_last;
     __shared__ T part[8][32];
     if (done != nullptr && *done != T(0)) { return; }
@@ -829,10 +819,45 @@ __global__ void __launch_bounds__(256) k_sweep_reduce(const T *__restrict__ Pr, 
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int64_t i = (int64_t) blockIdx.x * 32 + lane;
     T tot = T(0);
-    if (i < m) {
+    if (i < m && w < groups) {
+        const int Ii = (int) (i / BM), Ji = (int) (i / BN);  // (the same for the 32 elements of the CTA: the map reads are warp-uniform)
+        T s0 = T(0), s1 = T(0);
+        for (int J = 0; J <= Ii / 2; ++J) {
+            if (gmap[Ii * T_c + J] == w) { s0 += Pr[(int64_t) J * ldP + i]; }
+        }
+        for (int I = 2 * Ji; I < T_r; ++I) {
+            if (gmap[I * T_c + Ji] == w) { s1 += Pc[(int64_t) I * ldP + i]; }
+        }
+        tot = s0 + s1;
+    }
+    part[w][lane] = tot;
+    __syncthreads();
+    if (w == 0 && i < m) {
+        T pg[8];
+#pragma unroll
+        for (int g = 0; g < 8; ++g) { pg[g] = part[g][lane]; }
+        reduce_emit(dst, seq, i, group_tree(pg, groups));
+    }
+    if (dst.remote) { xchg_publish(dst.push, seq, &is_last); }
+}
+
+// Partial vectors of the sweep: per group g, the row partials of the group's column strips in row block I_i
+// (jlist[jptr[I (G + 1) + g] .. jptr[I (G + 1) + g + 1])) with four interleaved accumulators, then the column partials of the group's
+// runs of strip J_i (slots slot_base[g] .. + nruns[g T_c + J]).  One warp per group, 32 elements per CTA, groups combined by group_tree.
+template <typename T>
+__global__ void __launch_bounds__(256) k_sweep_reduce(const T *__restrict__ Pr, const T *__restrict__ Pc, int64_t ldP, int64_t m, int T_c,
+                                                      const int *__restrict__ jptr, const int *__restrict__ jlist, const int *__restrict__ nruns,
+                                                      const int *__restrict__ slot_base, int groups, const reduce_dst_t<T> dst, const T *__restrict__ done) {
+    __shared__ bool is_last;
+    __shared__ T part[8][32];
+    if (done != nullptr && *done != T(0)) { return; }
+    const unsigned long long seq = dst.remote ? xchg_next_seq(dst.push) : 0ull;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t i = (int64_t) blockIdx.x * 32 + lane;
+    T tot = T(0);
+    if (i < m && w < groups) {
         const int Ii = (int) (i / BM), Ji = (int) (i / BN);  // (the same for the 32 elements of the CTA)
-        const int j0 = __ldg(&jptr[Ii]), len = __ldg(&jptr[Ii + 1]) - j0;
-        const int ka = j0 + (int) ((int64_t) len * w / 8), kb = j0 + (int) ((int64_t) len * (w + 1) / 8);
+        const int ka = __ldg(&jptr[Ii * (groups + 1) + w]), kb = __ldg(&jptr[Ii * (groups + 1) + w + 1]);
         T s0 = T(0), s1 = T(0), s2 = T(0), s3 = T(0);
         int k = ka;
         for (; k + 4 <= kb; k += 4) {
@@ -845,14 +870,17 @@ __global__ void __launch_bounds__(256) k_sweep_reduce(const T *__restrict__ Pr, 
         }
         for (; k < kb; ++k) { s0 += Pr[(int64_t) __ldg(&jlist[k]) * ldP + i]; }
         T c = T(0);
-        const int nr = __ldg(&nruns[Ji]);
-        for (int r = w; r < nr; r += 8) { c += Pc[(int64_t) r * ldP + i]; }
+        const int nr = __ldg(&nruns[w * T_c + Ji]), sb = __ldg(&slot_base[w]);
+        for (int r = 0; r < nr; ++r) { c += Pc[(int64_t) (sb + r) * ldP + i]; }
         tot = ((s0 + s1) + (s2 + s3)) + c;
     }
     part[w][lane] = tot;
     __syncthreads();
     if (w == 0 && i < m) {
-        reduce_emit(dst, seq, i, ((part[0][lane] + part[1][lane]) + (part[2][lane] + part[3][lane])) + ((part[4][lane] + part[5][lane]) + (part[6][lane] + part[7][lane])));
+        T pg[8];
+#pragma unroll
+        for (int g = 0; g < 8; ++g) { pg[g] = part[g][lane]; }
+        reduce_emit(dst, seq, i, group_tree(pg, groups));
     }
     if (dst.remote) { xchg_publish(dst.push, seq, &is_last); }
 }
@@ -865,49 +893,81 @@ __global__ void __launch_bounds__(256) k_sweep_reduce(const T *__restrict__ Pr, 
 // sweep over stored tiles: the rank's tiles sorted by (strip, row block), cut into chunks (one per CTA), and what the reduction
 // kernel needs to find the partial vectors (k_tile_sweep / k_sweep_reduce)
 struct sweep_plan {
-    dbuf list, first_slot, nruns, jptr, jlist;
+    dbuf list, chunks, nruns, slot_base, jptr, jlist;
     int nchunks{ 0 };
-    int max_runs{ 0 };
+    int groups{ 1 };
+    int slots{ 1 };  // column partial vectors (rows of Pc) in use
 };
 
-void build_sweep_plan(ctx &c, sweep_plan &sw, const std::vector<int2> &tiles, int T_r, int T_c) {
+// canonical tile groups (k_sweep_reduce / group_tree): 8 when the world divides 8, else one per rank (no cross-world reproducibility)
+int canonical_groups(int world) { return world >= 1 && 8 % world == 0 ? 8 : world; }
+
+// tiles: this rank's tiles in storage order; grp[k] = local group of tile k (non-decreasing, 0 .. groups - 1)
+void build_sweep_plan(ctx &c, sweep_plan &sw, const std::vector<int2> &tiles, const std::vector<int> &grp, int groups, int T_r, int T_c) {
     const int nt = (int) tiles.size();
+    sw.groups = groups;
     std::vector<int4> list((size_t) nt);
-    for (int t = 0; t < nt; ++t) { list[(size_t) t] = make_int4(tiles[(size_t) t].x, tiles[(size_t) t].y, t, 0); }
-    std::sort(list.begin(), list.end(), [](const int4 &a, const int4 &b) { return a.y != b.y ? a.y < b.y : a.x < b.x; });
-    sw.nchunks = std::max(1, std::min(nt, 4 * NUM_SMS));
-    std::vector<int> first_slot((size_t) sw.nchunks, 0), nruns((size_t) T_c, 0);
-    for (int ch = 0; ch < sw.nchunks; ++ch) {
-        const int k0 = (int) ((int64_t) nt * ch / sw.nchunks), k1 = (int) ((int64_t) nt * (ch + 1) / sw.nchunks);
-        int curJ = -1;
-        for (int k = k0; k < k1; ++k) {
-            const int J = list[(size_t) k].y;
-            if (J != curJ) {
-                if (k == k0) { first_slot[(size_t) ch] = nruns[(size_t) J]; }  // (a run that starts inside a chunk starts its strip: slot 0)
-                ++nruns[(size_t) J];
-                curJ = J;
+    for (int t = 0; t < nt; ++t) { list[(size_t) t] = make_int4(tiles[(size_t) t].x, tiles[(size_t) t].y, t, grp[(size_t) t]); }
+    std::sort(list.begin(), list.end(), [](const int4 &a, const int4 &b) { return a.w != b.w ? a.w < b.w : (a.y != b.y ? a.y < b.y : a.x < b.x); });
+    // chunks: every group is cut into the same number of equal chunks whatever the world size is (one CTA per chunk; 296 = one wave
+    // of two CTAs per SM for a rank that owns a single group)
+    constexpr int CHUNKS_PER_GROUP = 2 * NUM_SMS;
+    std::vector<int4> chunks;
+    std::vector<int> nruns((size_t) groups * (size_t) T_c, 0), slot_base((size_t) groups, 0);
+    int g0 = 0, slots = 0;
+    for (int g = 0; g < groups; ++g) {
+        int g1 = g0;
+        while (g1 < nt && list[(size_t) g1].w == g) { ++g1; }
+        const int ng = g1 - g0, nch = std::max(1, std::min(ng, CHUNKS_PER_GROUP));
+        slot_base[(size_t) g] = slots;
+        int max_runs = 0;
+        for (int ch = 0; ch < nch && ng > 0; ++ch) {
+            const int k0 = g0 + (int) ((int64_t) ng * ch / nch), k1 = g0 + (int) ((int64_t) ng * (ch + 1) / nch);
+            int curJ = -1, first = 0;
+            for (int k = k0; k < k1; ++k) {
+                const int J = list[(size_t) k].y;
+                if (J != curJ) {
+                    int &cnt = nruns[(size_t) g * (size_t) T_c + (size_t) J];
+                    if (k == k0) { first = cnt; }
+                    ++cnt;
+                    max_runs = std::max(max_runs, cnt);
+                    curJ = J;
+                }
             }
+            chunks.push_back(make_int4(k0, k1, slots + first, slots));
         }
+        slots += std::max(max_runs, 1);
+        g0 = g1;
     }
-    sw.max_runs = 1;
-    for (const int r : nruns) { sw.max_runs = std::max(sw.max_runs, r); }
-    // owned column strips per row block, ascending
-    std::vector<std::vector<int>> per_row((size_t) T_r);
-    for (const int4 &e : list) { per_row[(size_t) e.x].push_back(e.y); }  // list is sorted by J: every per_row list comes out ascending
-    std::vector<int> jptr((size_t) T_r + 1, 0), jlist;
+    sw.nchunks = (int) chunks.size();
+    sw.slots = std::max(slots, 1);
+    for (int4 &e : list) { e.w = 0; }
+    // column strips per (row block, group), ascending
+    std::vector<std::vector<int>> per((size_t) T_r * (size_t) groups);
+    {
+        std::vector<int4> bygroup((size_t) nt);
+        for (int t = 0; t < nt; ++t) { bygroup[(size_t) t] = make_int4(tiles[(size_t) t].x, tiles[(size_t) t].y, grp[(size_t) t], 0); }
+        std::sort(bygroup.begin(), bygroup.end(), [](const int4 &a, const int4 &b) { return a.y < b.y; });
+        for (const int4 &e : bygroup) { per[(size_t) e.x * (size_t) groups + (size_t) e.z].push_back(e.y); }
+    }
+    std::vector<int> jptr((size_t) T_r * (size_t) (groups + 1), 0), jlist;
     jlist.reserve((size_t) nt);
     for (int I = 0; I < T_r; ++I) {
-        jptr[(size_t) I] = (int) jlist.size();
-        jlist.insert(jlist.end(), per_row[(size_t) I].begin(), per_row[(size_t) I].end());
+        for (int g = 0; g < groups; ++g) {
+            jptr[(size_t) I * (size_t) (groups + 1) + (size_t) g] = (int) jlist.size();
+            const std::vector<int> &v = per[(size_t) I * (size_t) groups + (size_t) g];
+            jlist.insert(jlist.end(), v.begin(), v.end());
+        }
+        jptr[(size_t) I * (size_t) (groups + 1) + (size_t) groups] = (int) jlist.size();
     }
-    jptr[(size_t) T_r] = (int) jlist.size();
     const auto up = [&](dbuf &dst, const void *src, size_t bytes) {
         dst.reserve(std::max<size_t>(bytes, 16));
         if (bytes != 0) { B200_CUDA_CHECK(cudaMemcpyAsync(dst.p, src, bytes, cudaMemcpyHostToDevice, c.stream)); }
     };
     up(sw.list, list.data(), list.size() * sizeof(int4));
-    up(sw.first_slot, first_slot.data(), first_slot.size() * sizeof(int));
+    up(sw.chunks, chunks.data(), chunks.size() * sizeof(int4));
     up(sw.nruns, nruns.data(), nruns.size() * sizeof(int));
+    up(sw.slot_base, slot_base.data(), slot_base.size() * sizeof(int));
     up(sw.jptr, jptr.data(), jptr.size() * sizeof(int));
     up(sw.jlist, jlist.data(), jlist.size() * sizeof(int));
     B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));  // the host vectors must outlive the copies
@@ -919,7 +979,7 @@ struct tc_state {
     CUtensorMap map_hi{}, map_lo{}, map_a8{}, map_b8{};
     dbuf tiles, pk, Pr, Pc, amax, P8a, P8b, own, Kc;
     sweep_plan sweep;
-    bool has_own{ false };
+    int groups{ 1 };  // canonical tile groups of this rank (group_tree)
     bool kc_valid{ false }, kc_refused{ false };  // cached kernel-matrix tiles of this rank
     bool fp8x{ false };
     int num_tiles{ 0 };
@@ -965,7 +1025,9 @@ void make_map(CUtensorMap *map, void *base, int64_t rows, int64_t ld_elems, bool
 }
 
 // lower block triangle, grouped in super-tiles of GI x GJ block tiles so that one wave of CTAs shares its operands in L2
-std::vector<int2> build_tiles(int T_r, int T_c, int rank, int world) {
+// grp (optional): local canonical group of every returned tile (canonical_groups(world) equal slices of the full list; a rank owns
+// canonical_groups / world consecutive ones — for world = 1, 2, 4, 8 the eight groups are the same sets of tiles)
+std::vector<int2> build_tiles(int T_r, int T_c, int rank, int world, std::vector<int> *grp = nullptr) {
     constexpr int GI = 32, GJ = 16;
     std::vector<int2> all;
     for (int sj = 0; sj < T_c; sj += GJ) {
@@ -975,9 +1037,17 @@ std::vector<int2> build_tiles(int T_r, int T_c, int rank, int world) {
             }
         }
     }
-    if (world <= 1) { return all; }
     // contiguous slice of the (uniform-cost) tile list per rank: balanced to within one tile
     const size_t lo = all.size() * (size_t) rank / (size_t) world, hi = all.size() * (size_t) (rank + 1) / (size_t) world;
+    if (grp != nullptr) {
+        const int G = canonical_groups(world), per_rank = G / world;
+        grp->assign(hi - lo, 0);
+        int g = rank * per_rank;
+        for (size_t t = lo; t < hi; ++t) {
+            while (g + 1 < (rank + 1) * per_rank && t >= all.size() * (size_t) (g + 1) / (size_t) G) { ++g; }
+            (*grp)[t - lo] = g - rank * per_rank;
+        }
+    }
     return std::vector<int2>(all.begin() + (std::ptrdiff_t) lo, all.begin() + (std::ptrdiff_t) hi);
 }
 
@@ -1038,24 +1108,24 @@ void tc_prepare_split(ctx &c) {
     st.T_r = (int) (c.n_pad / tc::BM);
     st.T_c = (int) (c.n_pad / tc::BN);
     st.ldP = c.n_pad;
-    const std::vector<int2> tiles = build_tiles(st.T_r, st.T_c, c.rank, c.world);
+    std::vector<int> grp;
+    const std::vector<int2> tiles = build_tiles(st.T_r, st.T_c, c.rank, c.world, &grp);
+    st.groups = canonical_groups(c.world) / c.world;
     st.num_tiles = (int) tiles.size();
     st.tiles.reserve(std::max<size_t>(tiles.size(), 1) * sizeof(int2));
     B200_CUDA_CHECK(cudaMemcpyAsync(st.tiles.p, tiles.data(), tiles.size() * sizeof(int2), cudaMemcpyHostToDevice, c.stream));
-    std::vector<uint8_t> own_map;
-    st.has_own = c.world > 1;
-    if (st.has_own) {
-        own_map.assign((size_t) st.T_r * (size_t) st.T_c, 0);
-        for (const int2 &t : tiles) { own_map[(size_t) t.x * (size_t) st.T_c + (size_t) t.y] = 1; }
-        st.own.reserve(own_map.size());
-        B200_CUDA_CHECK(cudaMemcpyAsync(st.own.p, own_map.data(), own_map.size(), cudaMemcpyHostToDevice, c.stream));
-    }
-    build_sweep_plan(c, st.sweep, tiles, st.T_r, st.T_c);
+    // tile -> local group of this rank (255: another rank's tile), for the reduction of the Gram kernel's per-tile partial vectors
+    std::vector<uint8_t> own_map((size_t) st.T_r * (size_t) st.T_c, (uint8_t) 255);
+    for (size_t t = 0; t < tiles.size(); ++t) { own_map[(size_t) tiles[t].x * (size_t) st.T_c + (size_t) tiles[t].y] = (uint8_t) grp[t]; }
+    st.own.reserve(own_map.size());
+    B200_CUDA_CHECK(cudaMemcpyAsync(st.own.p, own_map.data(), own_map.size(), cudaMemcpyHostToDevice, c.stream));
+    build_sweep_plan(c, st.sweep, tiles, grp, st.groups, st.T_r, st.T_c);
     st.pk.reserve((size_t) c.n_pad * sizeof(float4));
     st.Pr.reserve((size_t) st.T_c * st.ldP * sizeof(float));
-    st.Pc.reserve((size_t) st.T_r * st.ldP * sizeof(float));
+    const size_t pc_rows = (size_t) std::max(st.T_r, st.sweep.slots);  // Gram kernel: one per tile row; sweep: one per (group, run)
+    st.Pc.reserve(pc_rows * st.ldP * sizeof(float));
     B200_CUDA_CHECK(cudaMemsetAsync(st.Pr.p, 0, (size_t) st.T_c * st.ldP * sizeof(float), c.stream));
-    B200_CUDA_CHECK(cudaMemsetAsync(st.Pc.p, 0, (size_t) st.T_r * st.ldP * sizeof(float), c.stream));
+    B200_CUDA_CHECK(cudaMemsetAsync(st.Pc.p, 0, pc_rows * st.ldP * sizeof(float), c.stream));
     B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));  // `tiles` (host vector) must outlive the copy
     static bool attr_set = false;
     if (!attr_set) {
@@ -1178,7 +1248,6 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out, bool packed, const xch
     dst.out = out;
     dst.remote = push != nullptr ? 1 : 0;
     if (push != nullptr) { dst.push = *push; }
-    const unsigned rgrid = (unsigned) ((m + 255) / 256);
     const bool swept = st.kc_valid && !assembled_now;  // (the STORE pass has already filled Pr / Pc for this d)
     if (swept) {
         tc::sweep_params sp{};
@@ -1186,7 +1255,7 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out, bool packed, const xch
         sp.list = st.sweep.list.as<int4>();
         sp.num_tiles = st.num_tiles;
         sp.nchunks = st.sweep.nchunks;
-        sp.first_slot = st.sweep.first_slot.as<int>();
+        sp.chunks = st.sweep.chunks.as<int4>();
         sp.pk = p.pk;
         sp.Pr = p.Pr;
         sp.Pc = p.Pc;
@@ -1194,11 +1263,11 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out, bool packed, const xch
         sp.qa = p.qa;
         sp.done = done;
         tc::k_tile_sweep<true><<<st.sweep.nchunks, 256, 0, c.stream>>>(sp);
-        tc::k_sweep_reduce<float><<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(p.Pr, p.Pc, p.ldP, m, st.sweep.jptr.as<int>(), st.sweep.jlist.as<int>(),
-                                                                              st.sweep.nruns.as<int>(), dst, done);
+        tc::k_sweep_reduce<float><<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(p.Pr, p.Pc, p.ldP, m, st.T_c, st.sweep.jptr.as<int>(), st.sweep.jlist.as<int>(),
+                                                                              st.sweep.nruns.as<int>(), st.sweep.slot_base.as<int>(), st.sweep.groups, dst, done);
     } else {
         if (!st.kc_valid) { launch_gram<false>(c, st, p); }
-        tc::k_tc_reduce<<<rgrid, 256, 0, c.stream>>>(p.Pr, p.Pc, p.ldP, m, st.T_r, st.T_c, st.has_own ? st.own.as<uint8_t>() : nullptr, dst, done);
+        tc::k_tc_reduce<float><<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(p.Pr, p.Pc, p.ldP, m, st.T_r, st.T_c, st.own.as<uint8_t>(), st.groups, dst, done);
     }
     count_launch(c, swept ? 2 : 1);
     B200_CUDA_CHECK(cudaGetLastError());
@@ -1235,20 +1304,23 @@ int64_t tile_store_cum(int64_t I) {  // tiles (I', J), 2 J <= I', of the row blo
     return (I & 1) ? (k + 1) * (k + 1) : k * (k + 1);
 }
 
+// row-block boundary of the `part`-th of `parts` equal shares of the tiles (by cumulative tile count)
+static int tile_store_bound(int T_r, int part, int parts) {
+    if (part <= 0) { return 0; }
+    if (part >= parts) { return T_r; }
+    const int64_t want = tile_store_cum(T_r) * part / parts;
+    int I = 0;
+    while (I < T_r && tile_store_cum(I) < want) { ++I; }
+    return I;
+}
+
+// rows of a rank = its canonical_groups / world consecutive groups of row blocks (the same eight groups for world = 1, 2, 4, 8)
 void tile_store_range(int64_t m, int rank, int world, int *I_lo, int *I_hi) {
     const int64_t n_pad = (m + tc::BN - 1) / tc::BN * tc::BN;
     const int T_r = (int) (n_pad / tc::BM);
-    const int64_t total = tile_store_cum(T_r);
-    const auto bound = [&](int r) {  // first row block whose cumulative tile count reaches r / world of the total
-        if (r <= 0) { return 0; }
-        if (r >= world) { return T_r; }
-        const int64_t want = total * r / world;
-        int I = 0;
-        while (I < T_r && tile_store_cum(I) < want) { ++I; }
-        return I;
-    };
-    *I_lo = bound(rank);
-    *I_hi = bound(rank + 1);
+    const int G = canonical_groups(world), per_rank = G / world;
+    *I_lo = tile_store_bound(T_r, rank * per_rank, G);
+    *I_hi = tile_store_bound(T_r, (rank + 1) * per_rank, G);
 }
 
 tile_store *tile_store_create(ctx &c, int64_t m, size_t esize) {
@@ -1260,15 +1332,23 @@ tile_store *tile_store_create(ctx &c, int64_t m, size_t esize) {
     ts->ldP = ts->n_pad;
     tile_store_range(m, c.rank, c.world, &ts->I_lo, &ts->I_hi);
     std::vector<int2> tiles;
-    for (int I = ts->I_lo; I < ts->I_hi; ++I) {
-        for (int J = 0; 2 * J <= I; ++J) { tiles.push_back(make_int2(I, J)); }
+    std::vector<int> grp;
+    const int G = canonical_groups(c.world), per_rank = G / c.world;
+    for (int g = 0; g < per_rank; ++g) {
+        const int Ia = tile_store_bound(ts->T_r, c.rank * per_rank + g, G), Ib = tile_store_bound(ts->T_r, c.rank * per_rank + g + 1, G);
+        for (int I = Ia; I < Ib; ++I) {
+            for (int J = 0; 2 * J <= I; ++J) {
+                tiles.push_back(make_int2(I, J));
+                grp.push_back(g);
+            }
+        }
     }
     ts->num_tiles = (int) tiles.size();
     try {
-        build_sweep_plan(c, ts->sweep, tiles, ts->T_r, ts->T_c);
+        build_sweep_plan(c, ts->sweep, tiles, grp, per_rank, ts->T_r, ts->T_c);
         ts->pk.reserve((size_t) ts->n_pad * 16);  // float4 {-, -, w, -} or double2 {q, w}
         ts->Pr.reserve((size_t) ts->T_c * ts->ldP * esize);
-        ts->Pc.reserve((size_t) std::max(ts->sweep.max_runs, 1) * ts->ldP * esize);
+        ts->Pc.reserve((size_t) ts->sweep.slots * ts->ldP * esize);
         B200_CUDA_CHECK(cudaMemsetAsync(ts->Pr.p, 0, ts->Pr.bytes, c.stream));
         B200_CUDA_CHECK(cudaMemsetAsync(ts->Pc.p, 0, ts->Pc.bytes, c.stream));
     } catch (...) {
@@ -1300,7 +1380,7 @@ void tile_store_matvec(ctx &c, tile_store *ts, const float *w, int64_t m, float 
     sp.list = ts->sweep.list.as<int4>();
     sp.num_tiles = ts->num_tiles;
     sp.nchunks = ts->sweep.nchunks;
-    sp.first_slot = ts->sweep.first_slot.as<int>();
+    sp.chunks = ts->sweep.chunks.as<int4>();
     sp.pk = ts->pk.as<float4>();
     sp.Pr = ts->Pr.as<float>();
     sp.Pc = ts->Pc.as<float>();
@@ -1311,8 +1391,8 @@ void tile_store_matvec(ctx &c, tile_store *ts, const float *w, int64_t m, float 
     tc::reduce_dst dst{};
     dst.out = out;
     dst.remote = 0;
-    tc::k_sweep_reduce<float><<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(sp.Pr, sp.Pc, sp.ldP, m, ts->sweep.jptr.as<int>(), ts->sweep.jlist.as<int>(),
-                                                                          ts->sweep.nruns.as<int>(), dst, done);
+    tc::k_sweep_reduce<float><<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(sp.Pr, sp.Pc, sp.ldP, m, ts->T_c, ts->sweep.jptr.as<int>(), ts->sweep.jlist.as<int>(),
+                                                                          ts->sweep.nruns.as<int>(), ts->sweep.slot_base.as<int>(), ts->sweep.groups, dst, done);
     count_launch(c, 3);
     B200_CUDA_CHECK(cudaGetLastError());
 }
@@ -1326,7 +1406,7 @@ void tile_store_matvec_f64(ctx &c, tile_store *ts, const double *q, const double
     sp.list = ts->sweep.list.as<int4>();
     sp.num_tiles = ts->num_tiles;
     sp.nchunks = ts->sweep.nchunks;
-    sp.first_slot = ts->sweep.first_slot.as<int>();
+    sp.chunks = ts->sweep.chunks.as<int4>();
     sp.pk = ts->pk.as<double2>();
     sp.Pr = ts->Pr.as<double>();
     sp.Pc = ts->Pc.as<double>();
@@ -1338,8 +1418,8 @@ void tile_store_matvec_f64(ctx &c, tile_store *ts, const double *q, const double
     dst.out = out;
     dst.remote = push != nullptr ? 1 : 0;
     if (push != nullptr) { dst.push = *push; }
-    tc::k_sweep_reduce<double><<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(sp.Pr, sp.Pc, sp.ldP, m, ts->sweep.jptr.as<int>(), ts->sweep.jlist.as<int>(),
-                                                                                ts->sweep.nruns.as<int>(), dst, done);
+    tc::k_sweep_reduce<double><<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(sp.Pr, sp.Pc, sp.ldP, m, ts->T_c, ts->sweep.jptr.as<int>(), ts->sweep.jlist.as<int>(),
+                                                                                ts->sweep.nruns.as<int>(), ts->sweep.slot_base.as<int>(), ts->sweep.groups, dst, done);
     count_launch(c, 3);
     B200_CUDA_CHECK(cudaGetLastError());
 }

@@ -229,8 +229,10 @@ void sp_invalidate_cache(ctx &c);  // drop the cached S (options changed); rebui
 void sp_set_data(ctx &c, const int64_t *rowptr, const int32_t *colidx, const void *values, int64_t n, int64_t F, int64_t nnz, int fmt);
 template <typename T> void sp_generate_q(ctx &c);
 // out = K d (un-centred).  Returns true: rows [lo, hi) of this rank are in out[lo, hi) (the rest is zeroed when zero_rest);
-// false: out holds a full-length partial vector over this rank's TILES of a densely filled S (to be summed over the ranks)
+// false: out holds the RAW partial vector S v over this rank's TILES of a densely filled S (to be summed over the ranks, then turned
+// into K d by the O(m) epilogue: sp_finish_params)
 template <typename T> bool sp_kernel_matvec(ctx &c, const T *d, T *out, bool zero_rest, const T *done);
+void sp_finish_params(ctx &c, const void **u, double *c0pow, int *rbf);  // what the O(m) epilogue needs to turn a raw S v into K d (centre mode 3)
 template <typename T> void sp_update_w(ctx &c, const T *alpha_dev, T *w_dev);
 template <typename T> void sp_predict(ctx &c, const T *alpha_dev, T bias, const int64_t *rowptr, const int32_t *colidx, const void *values, int64_t P,
                                       int64_t nnz, int fmt, T *out_host);

@@ -1463,6 +1463,13 @@ template void sp_generate_q<double>(ctx &);
 
 // out[lo..hi) = K d over the reduced system for the rows owned by this rank (zero elsewhere when zero_rest); un-centred:
 // the caller adds (QA_cost - q_i) sum(d) - q.d + d_i / C (k_abar_finish, centre mode 2).
+void sp_finish_params(ctx &c, const void **u, double *c0pow, int *rbf) {
+    sparse_state &st = state_of(c);
+    *u = st.u.p;
+    *c0pow = make_kfun(c).c0pow;
+    *rbf = c.kernel == B200SVM_RBF ? 1 : 0;
+}
+
 template <typename T>
 bool sp_kernel_matvec(ctx &c, const T *d, T *out, bool zero_rest, const T *done) {
     sparse_state &st = state_of(c);
@@ -1495,13 +1502,7 @@ bool sp_kernel_matvec(ctx &c, const T *d, T *out, bool zero_rest, const T *done)
     }
     if (st.t_valid) {
         if constexpr (sizeof(T) == 4) { tile_store_matvec(c, st.ts, v, m, out, done_flag); }
-        const sp::kfun kft = make_kfun(c);
-        const int64_t gt = std::max<int64_t>(1, std::min<int64_t>((m + 1023) / 1024, 8 * NUM_SMS));
-        sp::k_sp_finish<T><<<(unsigned) gt, 256, 0, c.stream>>>(out, st.u.as<T>(), m, 0, m, rbf ? 1 : 0, (T) kft.c0pow, c.scal.as<T>(), S_TMP0, T(0), 0,
-                                                                c.rank == 0 ? 1 : 0);
-        count_launch(c);
-        B200_CUDA_CHECK(cudaGetLastError());
-        return false;
+        return false;  // raw S v of this rank's tiles: K d is formed after the ranks' partial vectors have been combined (cg.cu, centre mode 3)
     }
     // S is cached on first use when it fits the memory budget (then the matvec is an HBM-bound SpMV), else recomputed on the fly
     if (c.opt_sparse_cache != 1 && hi > lo) {
