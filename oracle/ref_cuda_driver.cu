@@ -42,6 +42,7 @@ class exposed_cuda_csvm : public plssvm::cuda::csvm<T> {
     using base_type::setup_data_on_device;
     using base_type::solver_CG;
     void set_QA_cost(const T v) { base_type::QA_cost_ = v; }
+    std::size_t num_devices() const { return base_type::devices_.size(); }
     std::size_t dept() const { return base_type::dept_; }
     std::size_t boundary() const { return base_type::boundary_size_; }
 };
@@ -153,23 +154,38 @@ int do_matvec_ms(int kernel, int degree, double gamma, double coef0, double cost
         svm.set_QA_cost(static_cast<T>(QA_cost));
         using dptr = typename exposed_cuda_csvm<T>::device_ptr_type;
         const std::size_t len = svm.dept() + svm.boundary();
-        dptr q_d{ len, 0 }, r_d{ len, 0 }, x_d{ len, 0 };
-        q_d.memset(0);
-        r_d.memset(0);
-        x_d.memset(0);
-        q_d.memcpy_to_device(static_cast<const T *>(q_in), 0, m);
-        x_d.memcpy_to_device(static_cast<const T *>(d_in), 0, m);
-        r_d.memcpy_to_device(static_cast<const T *>(ret_inout), 0, m);
-        svm.run_device_kernel(0, q_d, r_d, x_d, static_cast<T>(add));  // the call whose result is returned
-        cudaDeviceSynchronize();
-        r_d.memcpy_to_host(static_cast<T *>(ret_inout), 0, m);
+        // the linear kernel splits the FEATURES over all visible devices (src/plssvm/backends/gpu_csvm.cpp:129-157); every device adds
+        // its share into its own copy of ret, the copies are summed on the host like gpu_csvm::device_reduction (:365-386)
+        const std::size_t nd = svm.num_devices();
+        std::vector<dptr> q_d(nd), r_d(nd), x_d(nd);
+        for (std::size_t dev = 0; dev < nd; ++dev) {
+            q_d[dev] = dptr{ len, static_cast<int>(dev) };
+            r_d[dev] = dptr{ len, static_cast<int>(dev) };
+            x_d[dev] = dptr{ len, static_cast<int>(dev) };
+            q_d[dev].memset(0);
+            r_d[dev].memset(0);
+            x_d[dev].memset(0);
+            q_d[dev].memcpy_to_device(static_cast<const T *>(q_in), 0, m);
+            x_d[dev].memcpy_to_device(static_cast<const T *>(d_in), 0, m);
+        }
+        r_d[0].memcpy_to_device(static_cast<const T *>(ret_inout), 0, m);
+        for (std::size_t dev = 0; dev < nd; ++dev) { svm.run_device_kernel(dev, q_d[dev], r_d[dev], x_d[dev], static_cast<T>(add)); }  // the call whose result is returned
+        std::vector<T> acc(static_cast<std::size_t>(m), T(0)), part(static_cast<std::size_t>(m));
+        for (std::size_t dev = 0; dev < nd; ++dev) {
+            cudaSetDevice(static_cast<int>(dev));
+            cudaDeviceSynchronize();
+            r_d[dev].memcpy_to_host(part.data(), 0, m);
+            for (long i = 0; i < m; ++i) { acc[static_cast<std::size_t>(i)] += part[static_cast<std::size_t>(i)]; }
+        }
+        std::memcpy(ret_inout, acc.data(), static_cast<std::size_t>(m) * sizeof(T));
+        cudaSetDevice(0);
         cudaEvent_t e0, e1;
         cudaEventCreate(&e0);
         cudaEventCreate(&e1);
         double best = 1e30, sum = 0;
-        for (int k = 0; k < reps; ++k) {
+        for (int k = 0; k < reps; ++k) {  // timing: device 0's share (the whole kernel for polynomial / rbf, which the reference runs on one device)
             cudaEventRecord(e0, 0);
-            svm.run_device_kernel(0, q_d, r_d, x_d, static_cast<T>(add));
+            svm.run_device_kernel(0, q_d[0], r_d[0], x_d[0], static_cast<T>(add));
             cudaEventRecord(e1, 0);
             cudaEventSynchronize(e1);
             float ms = 0.f;

@@ -788,6 +788,12 @@ __device__ __forceinline__ void reduce_emit(const reduce_dst_t<T> &dst, unsigned
     }
 }
 
+// CTAs of a reduction kernel: 32 * 8 / groups elements each (see k_sweep_reduce)
+inline unsigned reduce_grid(int64_t m, int groups) {
+    const int64_t per = 32 * (8 / groups);
+    return (unsigned) ((m + per - 1) / per);
+}
+
 // Fixed summation tree over the partial sums of up to eight tile GROUPS (DESIGN.md §6 "N-independent results"): the tiles are dealt
 // to eight canonical groups; a rank of a world of 1 / 2 / 4 / 8 owns 8 / 4 / 2 / 1 consecutive groups, sums each group's partial
 // vectors in the group's own fixed order, combines its groups by the balanced tree below, and the consumer combines the ranks' slots
@@ -816,11 +822,12 @@ __global__ void __launch_bounds__(256) k_tc_reduce(const T *__restrict__ Pr, con
     __shared__ T part[8][32];
     if (done != nullptr && *done != T(0)) { return; }
     const unsigned long long seq = dst.remote ? xchg_next_seq(dst.push) : 0ull;
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int64_t i = (int64_t) blockIdx.x * 32 + lane;
+    // groups in {1, 2, 4, 8}: the eight warps serve 8 / groups sets of 32 consecutive elements, one warp per (set, group)
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, w = wid % groups, set = wid / groups;
+    const int64_t i = ((int64_t) blockIdx.x * (8 / groups) + set) * 32 + lane;
     T tot = T(0);
-    if (i < m && w < groups) {
-        const int Ii = (int) (i / BM), Ji = (int) (i / BN);  // (the same for the 32 elements of the CTA: the map reads are warp-uniform)
+    if (i < m) {
+        const int Ii = (int) (i / BM), Ji = (int) (i / BN);  // (the same for the 32 elements of the warp: the map reads are warp-uniform)
         T s0 = T(0), s1 = T(0);
         for (int J = 0; J <= Ii / 2; ++J) {
             if (gmap[Ii * T_c + J] == w) { s0 += Pr[(int64_t) J * ldP + i]; }
@@ -830,12 +837,12 @@ __global__ void __launch_bounds__(256) k_tc_reduce(const T *__restrict__ Pr, con
         }
         tot = s0 + s1;
     }
-    part[w][lane] = tot;
+    part[wid][lane] = tot;
     __syncthreads();
     if (w == 0 && i < m) {
         T pg[8];
 #pragma unroll
-        for (int g = 0; g < 8; ++g) { pg[g] = part[g][lane]; }
+        for (int g = 0; g < 8; ++g) { pg[g] = g < groups ? part[set * groups + g][lane] : T(0); }
         reduce_emit(dst, seq, i, group_tree(pg, groups));
     }
     if (dst.remote) { xchg_publish(dst.push, seq, &is_last); }
@@ -852,11 +859,12 @@ __global__ void __launch_bounds__(256) k_sweep_reduce(const T *__restrict__ Pr, 
     __shared__ T part[8][32];
     if (done != nullptr && *done != T(0)) { return; }
     const unsigned long long seq = dst.remote ? xchg_next_seq(dst.push) : 0ull;
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int64_t i = (int64_t) blockIdx.x * 32 + lane;
+    // groups in {1, 2, 4, 8}: the eight warps serve 8 / groups sets of 32 consecutive elements, one warp per (set, group)
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, w = wid % groups, set = wid / groups;
+    const int64_t i = ((int64_t) blockIdx.x * (8 / groups) + set) * 32 + lane;
     T tot = T(0);
-    if (i < m && w < groups) {
-        const int Ii = (int) (i / BM), Ji = (int) (i / BN);  // (the same for the 32 elements of the CTA)
+    if (i < m) {
+        const int Ii = (int) (i / BM), Ji = (int) (i / BN);  // (the same for the 32 elements of the warp)
         const int ka = __ldg(&jptr[Ii * (groups + 1) + w]), kb = __ldg(&jptr[Ii * (groups + 1) + w + 1]);
         T s0 = T(0), s1 = T(0), s2 = T(0), s3 = T(0);
         int k = ka;
@@ -874,12 +882,12 @@ __global__ void __launch_bounds__(256) k_sweep_reduce(const T *__restrict__ Pr, 
         for (int r = 0; r < nr; ++r) { c += Pc[(int64_t) (sb + r) * ldP + i]; }
         tot = ((s0 + s1) + (s2 + s3)) + c;
     }
-    part[w][lane] = tot;
+    part[wid][lane] = tot;
     __syncthreads();
     if (w == 0 && i < m) {
         T pg[8];
 #pragma unroll
-        for (int g = 0; g < 8; ++g) { pg[g] = part[g][lane]; }
+        for (int g = 0; g < 8; ++g) { pg[g] = g < groups ? part[set * groups + g][lane] : T(0); }
         reduce_emit(dst, seq, i, group_tree(pg, groups));
     }
     if (dst.remote) { xchg_publish(dst.push, seq, &is_last); }
@@ -911,7 +919,11 @@ void build_sweep_plan(ctx &c, sweep_plan &sw, const std::vector<int2> &tiles, co
     std::sort(list.begin(), list.end(), [](const int4 &a, const int4 &b) { return a.w != b.w ? a.w < b.w : (a.y != b.y ? a.y < b.y : a.x < b.x); });
     // chunks: every group is cut into the same number of equal chunks whatever the world size is (one CTA per chunk; 296 = one wave
     // of two CTAs per SM for a rank that owns a single group)
-    constexpr int CHUNKS_PER_GROUP = 2 * NUM_SMS;
+    static const int CHUNKS_PER_GROUP = [] {
+        const char *e = std::getenv("B200SVM_SWEEP_CHUNKS");  // experiment switch; results are comparable across world sizes only for equal values
+        const int v = e != nullptr ? std::atoi(e) : 0;
+        return v > 0 ? v : 2 * NUM_SMS;
+    }();
     std::vector<int4> chunks;
     std::vector<int> nruns((size_t) groups * (size_t) T_c, 0), slot_base((size_t) groups, 0);
     int g0 = 0, slots = 0;
@@ -1263,11 +1275,11 @@ void tc_kernel_matvec(ctx &c, const float *d, float *out, bool packed, const xch
         sp.qa = p.qa;
         sp.done = done;
         tc::k_tile_sweep<true><<<st.sweep.nchunks, 256, 0, c.stream>>>(sp);
-        tc::k_sweep_reduce<float><<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(p.Pr, p.Pc, p.ldP, m, st.T_c, st.sweep.jptr.as<int>(), st.sweep.jlist.as<int>(),
+        tc::k_sweep_reduce<float><<<tc::reduce_grid(m, st.sweep.groups), 256, 0, c.stream>>>(p.Pr, p.Pc, p.ldP, m, st.T_c, st.sweep.jptr.as<int>(), st.sweep.jlist.as<int>(),
                                                                               st.sweep.nruns.as<int>(), st.sweep.slot_base.as<int>(), st.sweep.groups, dst, done);
     } else {
         if (!st.kc_valid) { launch_gram<false>(c, st, p); }
-        tc::k_tc_reduce<float><<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(p.Pr, p.Pc, p.ldP, m, st.T_r, st.T_c, st.own.as<uint8_t>(), st.groups, dst, done);
+        tc::k_tc_reduce<float><<<tc::reduce_grid(m, st.groups), 256, 0, c.stream>>>(p.Pr, p.Pc, p.ldP, m, st.T_r, st.T_c, st.own.as<uint8_t>(), st.groups, dst, done);
     }
     count_launch(c, swept ? 2 : 1);
     B200_CUDA_CHECK(cudaGetLastError());
@@ -1391,7 +1403,7 @@ void tile_store_matvec(ctx &c, tile_store *ts, const float *w, int64_t m, float 
     tc::reduce_dst dst{};
     dst.out = out;
     dst.remote = 0;
-    tc::k_sweep_reduce<float><<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(sp.Pr, sp.Pc, sp.ldP, m, ts->T_c, ts->sweep.jptr.as<int>(), ts->sweep.jlist.as<int>(),
+    tc::k_sweep_reduce<float><<<tc::reduce_grid(m, ts->sweep.groups), 256, 0, c.stream>>>(sp.Pr, sp.Pc, sp.ldP, m, ts->T_c, ts->sweep.jptr.as<int>(), ts->sweep.jlist.as<int>(),
                                                                           ts->sweep.nruns.as<int>(), ts->sweep.slot_base.as<int>(), ts->sweep.groups, dst, done);
     count_launch(c, 3);
     B200_CUDA_CHECK(cudaGetLastError());
@@ -1418,7 +1430,7 @@ void tile_store_matvec_f64(ctx &c, tile_store *ts, const double *q, const double
     dst.out = out;
     dst.remote = push != nullptr ? 1 : 0;
     if (push != nullptr) { dst.push = *push; }
-    tc::k_sweep_reduce<double><<<(unsigned) ((m + 31) / 32), 256, 0, c.stream>>>(sp.Pr, sp.Pc, sp.ldP, m, ts->T_c, ts->sweep.jptr.as<int>(), ts->sweep.jlist.as<int>(),
+    tc::k_sweep_reduce<double><<<tc::reduce_grid(m, ts->sweep.groups), 256, 0, c.stream>>>(sp.Pr, sp.Pc, sp.ldP, m, ts->T_c, ts->sweep.jptr.as<int>(), ts->sweep.jlist.as<int>(),
                                                                                 ts->sweep.nruns.as<int>(), ts->sweep.slot_base.as<int>(), ts->sweep.groups, dst, done);
     count_launch(c, 3);
     B200_CUDA_CHECK(cudaGetLastError());
