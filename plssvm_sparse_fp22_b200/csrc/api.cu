@@ -1,6 +1,7 @@
 // C ABI of libb200svm.so (see include/b200svm.h for the contract and the reference interfaces each entry replaces).
 #include "internal.cuh"
 
+#include <algorithm>
 #include <cstring>
 #include <exception>
 #include <new>
@@ -317,9 +318,25 @@ int b200svm_set_data_dense(b200svm_handle h, const void *X, int64_t n, int64_t F
         c->n = n;
         c->F = F;
         c->ldx = (F + 15) / 16 * 16;
-        c->X.reserve((size_t) n * c->ldx * es);
         c->norms.reserve((size_t) n * es);
-        stage_matrix(*c, c->X.p, c->ldx, X, n, F, ld);
+        static const bool full_upload = [] {
+            const char *e = std::getenv("B200SVM_FULL_UPLOAD");  // A/B switch: every rank uploads the whole matrix over PCIe
+            return e != nullptr && e[0] == '1';
+        }();
+        if (c->world > 1 && c->comm != nullptr && !full_upload && !on_device(X)) {
+            // several ranks (every rank is handed the same matrix): upload 1 / world of the rows over PCIe, fetch the rest from the
+            // peers over NVLink (in-place ncclAllGather) — the host-to-device copy is the largest part of a multi-GPU set_data
+            const int64_t per = (n + c->world - 1) / c->world;
+            c->X.reserve((size_t) per * c->world * c->ldx * es);
+            const int64_t lo = std::min<int64_t>(n, per * c->rank), hi = std::min<int64_t>(n, per * (c->rank + 1));
+            char *share = static_cast<char *>(c->X.p) + (size_t) per * c->rank * c->ldx * es;
+            B200_CUDA_CHECK(cudaMemsetAsync(share, 0, (size_t) per * c->ldx * es, c->stream));
+            if (hi > lo) { stage_matrix(*c, share, c->ldx, static_cast<const char *>(X) + (size_t) lo * ld * es, hi - lo, F, ld); }
+            comm_allgather_inplace(*c, c->X.p, (size_t) per * c->ldx * es);
+        } else {
+            c->X.reserve((size_t) n * c->ldx * es);
+            stage_matrix(*c, c->X.p, c->ldx, X, n, F, ld);
+        }
         DISPATCH_T(c, compute_norms<T>(*c, c->X.as<T>(), n, c->ldx, F, c->norms.as<T>()), compute_norms<T>(*c, c->X.as<T>(), n, c->ldx, F, c->norms.as<T>()));
         c->has_data = true;
         if (c->dtype == B200SVM_F32 && c->kernel != B200SVM_LINEAR && c->opt_matvec_path != 1) { tc_prepare_split(*c); }

@@ -314,6 +314,17 @@ void comm_allreduce_sum(ctx &c, void *buf, int64_t count) {
     c.stats.collective_bytes += count * (int64_t) c.esize();
 }
 
+// in-place all-gather over NVLink: rank r's `bytes_per_rank` bytes already sit at buf + r * bytes_per_rank; afterwards every rank holds all
+// shares (set_data: every rank uploads 1 / world of the training matrix over PCIe and fetches the rest from its peers)
+void comm_allgather_inplace(ctx &c, void *buf, size_t bytes_per_rank) {
+    if (c.world <= 1 || bytes_per_rank == 0) { return; }
+    if (c.comm == nullptr || c.comm->comm == nullptr) { fail(B200SVM_ERR_NCCL, "NCCL communicator not initialised"); }
+    nccl_check(api().AllGather(static_cast<char *>(buf) + (size_t) c.rank * bytes_per_rank, buf, bytes_per_rank, /* ncclUint8 */ 1, c.comm->comm, c.stream),
+               "ncclAllGather");
+    ++c.stats.collectives;
+    c.stats.collective_bytes += (int64_t) bytes_per_rank * (int64_t) (c.world - 1);
+}
+
 // Row range [lo, hi) of the m rows of the implicit matrix owned by `rank` (full-row paths: equal row counts)
 void partition_rows(int64_t m, int rank, int world, int64_t *lo, int64_t *hi) {
     if (world <= 1) {

@@ -240,6 +240,7 @@ template <typename T> void sp_predict(ctx &c, const T *alpha_dev, T bias, const 
 // multi-GPU (comm.cu)
 void comm_destroy(ctx &c);
 void comm_allreduce_sum(ctx &c, void *buf, int64_t count);  // in place, real type of the handle
+void comm_allgather_inplace(ctx &c, void *buf, size_t bytes_per_rank);  // rank r's share sits at buf + r * bytes_per_rank
 // peer-memory exchange (protocol and device helpers: xchg.cuh)
 enum xchg_mode : int { XCHG_SUM = 0, XCHG_GATHER = 1 };
 struct xchg_plan {
