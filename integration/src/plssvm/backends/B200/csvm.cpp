@@ -34,7 +34,7 @@ b200svm_handle as_handle(void *p) { return static_cast<b200svm_handle>(p); }
 // rows are stored sparsely on the device when at most this fraction of the entries is non-zero (and no row is too long for the
 // sparse kernels); the reference itself always densifies (src/plssvm/parameter.cpp:41-116)
 constexpr double sparse_density_threshold = 0.05;
-constexpr std::size_t sparse_max_row = 1024;
+constexpr std::size_t sparse_max_row = 4096;  // the sparse kernels stage one row in shared memory: longer rows go dense (libb200svm rejects them)
 
 }  // namespace
 
@@ -85,6 +85,10 @@ void csvm<T>::setup_data_on_device() {
         longest = std::max(longest, c);
     }
     sparse_rows_ = static_cast<double>(nnz) <= sparse_density_threshold * static_cast<double>(n) * static_cast<double>(F) && longest <= sparse_max_row;
+    if (print_info_) {
+        fmt::print("B200 backend: {} x {} data set, {:.3g} % non-zero, longest row {} entries -> stored {} on the device.\n", n, F,
+                   100.0 * static_cast<double>(nnz) / std::max(1.0, static_cast<double>(n) * static_cast<double>(F)), longest, sparse_rows_ ? "as CSR rows" : "dense");
+    }
     if (sparse_rows_) {
         std::vector<std::int64_t> rowptr(n + 1, 0);
         std::vector<std::int32_t> colidx;
