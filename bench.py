@@ -741,6 +741,7 @@ def run_predict(env, tag, svs, F, density, points, seed):
             env.sampler.active.clear()
             st = h.stats()
             atoms_gops = h.probe_smem_atomic_gops()
+            fma_tflops = h.probe_fma_tflops(np.float32)
         t = env.max_over_ranks([t])[0]
         clocks = env.sampler.take()
         total = share * world
@@ -755,7 +756,10 @@ def run_predict(env, tag, svs, F, density, points, seed):
                                  "kernel": "k_sp_kmv (S on the fly: one multiply + one shared-memory atomic add per Gram product, one ex2 per kernel value)",
                                  "peak_source": "measured on this device: b200svm_probe_smem_atomic_gops (ATOMS.ADD to pseudo-random slots of an 8192-entry accumulator) x N GPUs; "
                                                 "algorithmic ops = expected Gram products P n F rho^2",
-                                 "note": "timed through b200svm_predict_csr with host buffers: H2D of the points and D2H of the decision values are inside"},
+                                 "note": "timed through b200svm_predict_csr with host buffers: H2D of the points and D2H of the decision values are inside",
+                                 "frac_of_fp32_fma_peak": (2.0 * products + 8.0 * evals) / t / 1e12 / (world * fma_tflops) if fma_tflops else None,
+                                 "fp32_fma_peak_tflops_measured": fma_tflops,
+                                 "fp32_note": "2 flops per Gram product + ~8 per kernel evaluation (exponent, ex2, weight) against the measured FP32 FMA peak x N"},
                     "clocks": clocks,
                     "e2e": {"value": total / t, "unit": "points/s", "h2d_bytes_per_step": int(st.h2d_bytes), "d2h_bytes_per_step": int(st.d2h_bytes)},
                     "gpu_launches": int(st.kernel_launches), "positive_labels_rank0": int((dec > 0).sum())})
