@@ -104,7 +104,11 @@ int b200svm_predict_csr(b200svm_handle h, const void *alpha, double rho, const i
 /* Multi-GPU (one process per GPU): rows/tiles of the implicit matrix are partitioned over `world` ranks; the CG loop
  * exchanges with NCCL on the handle's stream.  The unique id (128 bytes) is created on rank 0 and distributed by the
  * caller (e.g. torch.distributed broadcast).  Replaces the reference's host-staged device_reduction
- * (src/plssvm/backends/gpu_csvm.cpp:365-386). */
+ * (src/plssvm/backends/gpu_csvm.cpp:365-386).  With a communicator the following calls are COLLECTIVE (every rank makes them in the same
+ * order, with the same data): b200svm_set_data_dense (each rank uploads 1 / world of the rows and all-gathers the rest over NVLink),
+ * b200svm_matvec / b200svm_cg_solve / b200svm_learn (one exchange of the matvec result per application of the implicit matrix through
+ * CUDA-IPC mapped peer buffers), b200svm_comm_init and b200svm_destroy (barrier before the exchange buffers are released).  Results are
+ * bit-identical on every rank and, on the tile-partitioned paths, bit-identical for 1, 2, 4 and 8 ranks. */
 int b200svm_comm_unique_id(void *id128);
 int b200svm_comm_init(b200svm_handle h, const void *id128, int rank, int world);
 /* Host-only helpers (no device needed): the ownership rules the ranks use, exposed so that the sharding can be tested on
