@@ -329,13 +329,21 @@ class Env:
         """Repeat fn until min_total_s of device time (max over ranks) have been timed; the repeat count is agreed over the ranks.
         Returns (per-repetition ms as max over ranks, last result)."""
         t0, out = self.timed(fn, before)
-        t0 = self.max_over_ranks([t0])[0]
-        reps = int(min(rmax, max(rmin, math.ceil(min_total_s * 1e3 / max(t0, 1e-3)))))
-        ts = []
-        for _ in range(reps - 1):
-            t, out = self.timed(fn, before)
-            ts.append(t)
-        return [t0] + (self.max_over_ranks(ts) if ts else []), out
+        all_ts = [self.max_over_ranks([t0])[0]]
+        # batches of repetitions until enough device time has been timed (the first repetition can be an outlier, so the count is
+        # re-estimated from the median after every batch); every decision uses values that are identical on all ranks
+        while len(all_ts) < rmax:
+            total = sum(all_ts)
+            if len(all_ts) >= rmin and total >= min_total_s * 1e3:
+                break
+            est = float(np.median(all_ts))
+            more = int(min(rmax - len(all_ts), max(rmin - len(all_ts), math.ceil(max(min_total_s * 1e3 - total, 0.0) / max(est, 1e-3)), 1)))
+            ts = []
+            for _ in range(more):
+                t, out = self.timed(fn, before)
+                ts.append(t)
+            all_ts += self.max_over_ranks(ts)
+        return all_ts, out
 
     def close(self):
         self.sampler.stop_flag.set()
@@ -454,7 +462,7 @@ def run_main_workload(a, env):
     QA = h.kxx_last() + 1.0
     warm_steps = warm_up(env, lambda s: h.solver_cg(b, None, QA, s, 0.0), W)
     h.reset_stats()
-    ts, (alpha, iters, delta) = env.repeat_timed(lambda: h.solver_cg(b, None, QA, K, 0.0), lambda: drop_caches(h), a.min_timed_s, 3, 120)
+    ts, (alpha, iters, delta) = env.repeat_timed(lambda: h.solver_cg(b, None, QA, K, 0.0), lambda: drop_caches(h), a.min_timed_s, 3, 200)
     st = h.stats()
     clocks = env.sampler.take()
     assert iters == K, (iters, K)

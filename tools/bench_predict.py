@@ -32,6 +32,7 @@ def main():
     ap.add_argument("--storage", default="native", choices=["native", "fp22"])
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--seed", type=int, default=46)
+    ap.add_argument("--sweep", default="", help="geometry sweep on one GPU: semicolon list of block,threads,lanes (0 = default), e.g. '0,0,0;16384,256,0'")
     a = ap.parse_args()
 
     import torch
@@ -61,6 +62,23 @@ def main():
     t_gen = time.time() - t0
     rng = np.random.default_rng(a.seed)
     alpha = (rng.standard_normal(a.svs) * 0.1).astype(dt)  # alpha ~ N(0, 1e-2), rho = 0.1 (SURVEY.md §8d cfg 5)
+    for cfg in [c for c in a.sweep.split(";") if c]:
+        blk, thr, lanes = (int(x) for x in cfg.split(","))
+        with capi.Handle(dt, a.kernel, 3, 1.0 / F, 0.0, 1.0, device=local) as h:
+            if blk:
+                h.set_option(capi.OPT_SPARSE_BLOCK, blk)
+            if thr:
+                h.set_option(capi.OPT_SPARSE_THREADS, thr)
+            if lanes:
+                h.set_option(capi.OPT_SPARSE_LANES, lanes)
+            h.set_data_csr(rp, ci, v, F, value_format=fmt)
+            h.predict_csr(alpha, 0.1, prp[:2], None if pci is None else pci[: prp[1]], pv[: prp[1]], value_format=fmt)
+            ts = []
+            for _ in range(a.reps):
+                t0 = time.perf_counter()
+                dec = h.predict_csr(alpha, 0.1, prp, pci, pv, value_format=fmt)
+                ts.append(time.perf_counter() - t0)
+            print(json.dumps({"sweep": cfg, "seconds": min(ts), "points_per_s": share / min(ts), "checksum": float(np.abs(dec).sum())}), flush=True)
     with capi.Handle(dt, a.kernel, 3, 1.0 / F, 0.0, 1.0, device=local) as h:
         h.set_data_csr(rp, ci, v, F, value_format=fmt)
         dec = h.predict_csr(alpha, 0.1, prp[:2], None if pci is None else pci[: prp[1]], pv[: prp[1]], value_format=fmt)  # warm-up (one point)
