@@ -116,6 +116,12 @@ int b200svm_comm_init(b200svm_handle h, const void *id128, int rank, int world);
  * [first, first + count) of the `total` lower-triangle 128 x 256 tiles of an n-point problem (tcgen05 path). */
 int b200svm_partition_rows(int64_t m, int rank, int world, int64_t *lo, int64_t *hi);
 int b200svm_partition_tiles(int64_t n, int rank, int world, int64_t *first, int64_t *count, int64_t *total);
+/* Row-block ranges of the symmetric tile stores (double dense tiles, dense-tile S of CSR data): rows [row_lo, row_hi) (multiples of 128) of
+ * rank `rank`, contiguous ranges of equal tile count.  b200svm_canonical_groups(world) = number of canonical tile groups (8 when world
+ * divides 8): a rank owns groups / world consecutive ones, so the group boundaries are the same for 1, 2, 4 and 8 ranks — the basis of
+ * the bit-identical results across GPU counts. */
+int b200svm_partition_tile_rows(int64_t m, int rank, int world, int64_t *row_lo, int64_t *row_hi);
+int b200svm_canonical_groups(int world);
 
 /* Tuning / introspection. */
 #define B200SVM_OPT_MATVEC_PATH 1 /* 0 = auto, 1 = SIMT full-square, 2 = tcgen05 symmetric tiles (f32 dense only) */

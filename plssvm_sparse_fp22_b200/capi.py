@@ -29,7 +29,7 @@ SYMBOLS = [
     "b200svm_set_data_dense", "b200svm_set_data_csr", "b200svm_generate_q", "b200svm_get_kxx_last", "b200svm_set_q",
     "b200svm_matvec", "b200svm_cg_solve", "b200svm_learn", "b200svm_update_w", "b200svm_predict_dense",
     "b200svm_predict_csr", "b200svm_comm_unique_id", "b200svm_comm_init", "b200svm_set_option", "b200svm_get_stats",
-    "b200svm_reset_stats", "b200svm_partition_rows", "b200svm_partition_tiles", "b200svm_probe_fma_tflops", "b200svm_probe_smem_atomic_gops",
+    "b200svm_reset_stats", "b200svm_partition_rows", "b200svm_partition_tiles", "b200svm_probe_fma_tflops", "b200svm_probe_smem_atomic_gops", "b200svm_partition_tile_rows", "b200svm_canonical_groups",
 ]
 
 
@@ -99,6 +99,8 @@ def load():
     L.b200svm_probe_smem_atomic_gops.argtypes = [vp, pd]
     L.b200svm_partition_rows.argtypes = [i64, i, i, pi64, pi64]
     L.b200svm_partition_tiles.argtypes = [i64, i, i, pi64, pi64, pi64]
+    L.b200svm_partition_tile_rows.argtypes = [i64, i, i, pi64, pi64]
+    L.b200svm_canonical_groups.argtypes = [i]
     _LIB = L
     return L
 
@@ -302,6 +304,18 @@ def partition_tiles(n: int, rank: int, world: int):
     if rc != 0:
         raise B200Error(rc, "invalid partition request")
     return first.value, count.value, total.value
+
+
+def partition_tile_rows(m: int, rank: int, world: int):
+    lo, hi = C.c_int64(0), C.c_int64(0)
+    rc = load().b200svm_partition_tile_rows(m, rank, world, C.byref(lo), C.byref(hi))
+    if rc != 0:
+        raise B200Error(rc, "invalid partition request")
+    return lo.value, hi.value
+
+
+def canonical_groups(world: int) -> int:
+    return load().b200svm_canonical_groups(world)
 
 
 def comm_unique_id() -> bytes:

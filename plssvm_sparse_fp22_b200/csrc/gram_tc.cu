@@ -1449,3 +1449,14 @@ extern "C" int b200svm_partition_tiles(int64_t n, int rank, int world, int64_t *
     *total = (int64_t) all;
     return B200SVM_OK;
 }
+
+extern "C" int b200svm_canonical_groups(int world) { return world >= 1 ? b200::canonical_groups(world) : 0; }
+
+extern "C" int b200svm_partition_tile_rows(int64_t m, int rank, int world, int64_t *row_lo, int64_t *row_hi) {
+    if (row_lo == nullptr || row_hi == nullptr || world < 1 || rank < 0 || rank >= world || m < 1) { return B200SVM_ERR_INVALID; }
+    int I_lo = 0, I_hi = 0;
+    b200::tile_store_range(m, rank, world, &I_lo, &I_hi);
+    *row_lo = (int64_t) I_lo * b200::tc::BM;
+    *row_hi = (int64_t) I_hi * b200::tc::BM;
+    return B200SVM_OK;
+}

@@ -104,3 +104,35 @@ def test_partition_tiles_cover(n, world):
     n_pad = (n + 255) // 256 * 256
     T_r, T_c = n_pad // 128, n_pad // 256
     assert total == sum(T_r - 2 * j for j in range(T_c))
+
+
+def test_canonical_groups_are_nested_across_world_sizes():
+    """The tile-partitioned paths return bit-identical results on 1, 2, 4 and 8 GPUs because every rank owns whole CANONICAL groups
+    (DESIGN.md §6): the slice / row-block boundaries of 2, 4 and 8 ranks must be a subset of those of 8 ranks, for both partitions."""
+    assert [capi.canonical_groups(w) for w in (1, 2, 4, 8)] == [8, 8, 8, 8]
+    assert [capi.canonical_groups(w) for w in (3, 5, 6, 7, 16)] == [3, 5, 6, 7, 16]
+    for n in (257, 5000, 65536, 262144):
+        tile_edges, row_edges = {}, {}
+        for w in (1, 2, 4, 8):
+            te, re_ = {0}, {0}
+            prev = 0
+            for r in range(w):
+                first, count, total = capi.partition_tiles(n, r, w)
+                te.add(first + count)
+                lo, hi = capi.partition_tile_rows(n - 1, r, w)
+                assert lo == prev and hi >= lo and lo % 128 == 0
+                prev = hi
+                re_.add(hi)
+            n_pad = (n - 1 + 255) // 256 * 256
+            assert prev == n_pad and max(te) == total
+            tile_edges[w], row_edges[w] = te, re_
+        for w in (1, 2, 4):
+            assert tile_edges[w] <= tile_edges[8]
+            assert row_edges[w] <= row_edges[8]
+    # equal tile counts: the row-block ranges of 8 ranks hold the same number of tiles to within one row block's worth
+    n = 65536
+    counts = []
+    for r in range(8):
+        lo, hi = capi.partition_tile_rows(n - 1, r, 8)
+        counts.append(sum(I // 2 + 1 for I in range(lo // 128, hi // 128)))
+    assert max(counts) - min(counts) <= 256 + 1
