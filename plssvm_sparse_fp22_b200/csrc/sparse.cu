@@ -1016,7 +1016,12 @@ void set_data_typed(ctx &c, const int64_t *rowptr, const int32_t *colidx, const 
         }
     }
     // block width (rows of X per accumulator pass): option or default (8192: 50 KB float / 84 KB double per CTA => 4 / 2 CTAs per SM)
-    const int W = c.opt_sparse_block > 0 ? (int) c.opt_sparse_block : 8192;
+    // Float rows whose S will be densely filled (two rows share nnz^2 / (n^2 F) features at least — Cauchy-Schwarz on the column counts):
+    // blocks of 16384 with 512 threads — half the (row, block) visits; measured on the configs[4] geometry (predict, 65536 points x
+    // 262144 support vectors, one B200): 820 k points/s against 699 k with 8192 / 256 (profiles/r2_summary.md)
+    const double shared_lb = (double) entries * (double) entries / std::max(1.0, (double) n * (double) n * (double) F);
+    const bool wide = sizeof(T) == 4 && shared_lb >= 0.5 && n >= 32768;
+    const int W = c.opt_sparse_block > 0 ? (int) c.opt_sparse_block : (wide ? 16384 : 8192);
     B200_REQUIRE(W >= 128 && W <= 32768 && (W & (W - 1)) == 0, "sparse block width must be a power of two in [128, 32768]");
     B200_REQUIRE(kmv_smem_bytes<T>(W, 1024) <= (size_t) 200 * 1024, "sparse block width too large for the shared memory of one SM");
     st.W = W;
@@ -1095,7 +1100,7 @@ void set_data_typed(ctx &c, const int64_t *rowptr, const int32_t *colidx, const 
     st.G = (int) std::max(1.0, std::min((double) st.nb, 48.0e6 / std::max(1.0, bytes_per_block)));
     if (c.opt_sparse_group > 0) { st.G = (int) std::min<int64_t>(c.opt_sparse_group, st.nb); }
     st.ng = (st.nb + st.G - 1) / st.G;
-    st.threads = sizeof(T) == 4 ? 256 : 512;
+    st.threads = sizeof(T) == 4 && W < 16384 ? 256 : 512;
     st.v.reserve((size_t) st.nb * W * sizeof(T));
     st.xl.reserve((size_t) F * sizeof(T));
     st.wvec.reserve((size_t) F * sizeof(T));
