@@ -95,6 +95,22 @@ int b200svm_learn(b200svm_handle h, const void *y, double eps, void *alpha_out, 
  * over the data set by set_data_*; alpha: n reals; w_out: F reals. */
 int b200svm_update_w(b200svm_handle h, const void *alpha, void *w_out);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  The same computation as b200svm_update_w — w[f] = sum_i alpha_i
+ * X[i][f], i < n, f < F — without a handle and without any allocation: it calls no cudaMalloc / cudaFree / allocating library routine.
+ * The chunk partials of the first kernel live in a file-scope static __device__ array of B200SVM_NOALLOC_SCRATCH_BYTES that every GPU
+ * loading libb200svm.so holds until the process exits.  X_dev (n rows, leading dimension ld >= F reals), alpha_dev (n reals) and
+ * w_out_dev (F reals) are DEVICE pointers of one GPU; dtype = B200SVM_F32 / B200SVM_F64; cuda_stream = cudaStream_t of that GPU (NULL =
+ * the default stream); the call only enqueues two kernels and does not synchronise.  Limit: chunks * ld * sizeof(real) <=
+ * B200SVM_NOALLOC_SCRATCH_BYTES with chunks = min(ceil(592 / ceil(ld / 256)), ceil(n / 64)) — which holds for every n when ld <= 524288
+ * doubles or ld <= 1048576 floats; larger sizes are rejected with B200SVM_ERR_INVALID (use b200svm_update_w).  All calls share the one array per GPU and it keeps
+ * the previous call's contents (every element read is written first, so nothing needs clearing): calls that overlap on the same GPU —
+ * different streams, or threads — race; serialise them.  On failure the message is copied into err (err_len bytes incl. the NUL; err may
+ * be NULL). */
+#define B200SVM_NOALLOC_SCRATCH_BYTES (4u << 20)
+int b200svm_update_w_noalloc(int dtype, const void *X_dev, int64_t n, int64_t F, int64_t ld, const void *alpha_dev, void *w_out_dev,
+                             void *cuda_stream, char *err, size_t err_len);
+
 /* Replaces predict(points) (include/plssvm/csvm.hpp:214; src/plssvm/backends/OpenMP/csvm.cpp:191-244): decision values
  * out[p] = -rho + sum_i alpha_i k(x_i, p) over the support vectors set by set_data_* (alpha: n reals). */
 int b200svm_predict_dense(b200svm_handle h, const void *alpha, double rho, const void *points, int64_t P, int64_t ld, void *out);

@@ -19,6 +19,7 @@ VAL_F32, VAL_F64, VAL_FP22 = 0, 1, 2
 OPT_MATVEC_PATH, OPT_SYNC_EVERY, OPT_SPARSE_BLOCK, OPT_SPARSE_GROUP, OPT_SPARSE_LANES, OPT_TC_MODE, OPT_SPARSE_THREADS = 1, 2, 3, 4, 5, 6, 7
 OPT_SPARSE_CACHE, OPT_SPARSE_CACHE_MB, OPT_DENSE_CACHE, OPT_PEER_EXCHANGE = 8, 9, 10, 11
 OPT_SPARSE_TILES = 12
+NOALLOC_SCRATCH_BYTES = 4 << 20  # B200SVM_NOALLOC_SCRATCH_BYTES
 CACHE_AUTO, CACHE_OFF, CACHE_REQUIRED = 0, 1, 2
 TC_F16X3, TC_FP8X = 1, 2
 PATH_AUTO, PATH_SIMT, PATH_TC = 0, 1, 2
@@ -30,6 +31,7 @@ SYMBOLS = [
     "b200svm_matvec", "b200svm_cg_solve", "b200svm_learn", "b200svm_update_w", "b200svm_predict_dense",
     "b200svm_predict_csr", "b200svm_comm_unique_id", "b200svm_comm_init", "b200svm_set_option", "b200svm_get_stats",
     "b200svm_reset_stats", "b200svm_partition_rows", "b200svm_partition_tiles", "b200svm_probe_fma_tflops", "b200svm_probe_smem_atomic_gops", "b200svm_partition_tile_rows", "b200svm_canonical_groups",
+    "b200svm_update_w_noalloc",
 ]
 
 
@@ -101,6 +103,7 @@ def load():
     L.b200svm_partition_tiles.argtypes = [i64, i, i, pi64, pi64, pi64]
     L.b200svm_partition_tile_rows.argtypes = [i64, i, i, pi64, pi64]
     L.b200svm_canonical_groups.argtypes = [i]
+    L.b200svm_update_w_noalloc.argtypes = [i, vp, i64, i64, i64, vp, vp, vp, C.c_char_p, C.c_size_t]
     _LIB = L
     return L
 

@@ -7,6 +7,8 @@
 // (deterministic), rank-1 terms (QA_cost, q) applied in an O(m) epilogue, linear kernel as X (X^T d).
 #include "device_utils.cuh"
 
+#include <cstdarg>
+
 namespace b200 {
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -607,3 +609,113 @@ template double probe_fma_tflops<float>(ctx &);
 template double probe_fma_tflops<double>(ctx &);
 
 }  // namespace b200
+
+// ---------------------------------------------------------------------------------------------------------------------
+// b200svm_update_w_noalloc: w = X^T alpha with the chunk partials of k_xt_v in a file-scope static device array instead of a
+// cudaMalloc'ed buffer (include/b200svm.h).  No counterpart in the reference; added for callers
+// that cannot allocate (CUDA graph capture, serving loops).  Nothing here allocates: no handle, no dbuf, no std::string.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace b200 {
+namespace {
+
+// every GPU that loads libb200svm.so holds these B200SVM_NOALLOC_SCRATCH_BYTES until the process exits
+static __device__ __align__(256) unsigned char g_noalloc_scratch[B200SVM_NOALLOC_SCRATCH_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+void *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};  // device address of g_noalloc_scratch per device (the symbol itself is a host stand-in)
+
+// w[f] = sum_chunk wpart[chunk][f] for the F real features only (k_sum_chunks writes all ld columns of a handle-owned buffer)
+template <typename T>
+__global__ void __launch_bounds__(256) k_sum_chunks_noalloc(const T *__restrict__ wpart, int64_t ld, int64_t F, int chunks, T *__restrict__ w) {
+    const int64_t f = (int64_t) blockIdx.x * 256 + threadIdx.x;
+    if (f >= F) { return; }
+    T s = 0;
+    for (int ch = 0; ch < chunks; ++ch) { s += wpart[(int64_t) ch * ld + f]; }
+    w[f] = s;
+}
+
+int noalloc_fail(char *err, size_t err_len, int code, const char *fmt, ...) {
+    if (err != nullptr && err_len > 0) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(err, err_len, fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+
+// device that owns a device pointer; -1 if it is not device memory
+int noalloc_device_of(const void *p) {
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+        cudaGetLastError();
+        return -1;
+    }
+    return (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged) ? at.device : -1;
+}
+
+template <typename T>
+int update_w_noalloc(const T *X, int64_t n, int64_t F, int64_t ld, const T *alpha, T *w, cudaStream_t stream, void *scratch, char *err, size_t err_len) {
+    // same chunking as xt_v above, so the result equals b200svm_update_w's when the leading dimensions agree
+    const int64_t fblocks = (ld + 255) / 256;
+    int64_t chunks = (4 * NUM_SMS + fblocks - 1) / fblocks;
+    if (chunks > (n + 63) / 64) { chunks = (n + 63) / 64; }
+    if (chunks < 1) { chunks = 1; }
+    const int64_t rpc = (n + chunks - 1) / chunks;
+    chunks = (n + rpc - 1) / rpc;
+    const unsigned long long need = (unsigned long long) chunks * (unsigned long long) ld * sizeof(T);
+    if (need > (unsigned long long) B200SVM_NOALLOC_SCRATCH_BYTES) {
+        return noalloc_fail(err, err_len, B200SVM_ERR_INVALID,
+                            "b200svm_update_w_noalloc: %lld chunks x ld %lld x %zu bytes = %llu bytes of scratch exceed the static array of %llu bytes "
+                            "(B200SVM_NOALLOC_SCRATCH_BYTES); use b200svm_update_w for this size",
+                            (long long) chunks, (long long) ld, sizeof(T), need, (unsigned long long) B200SVM_NOALLOC_SCRATCH_BYTES);
+    }
+    if (fblocks > 2147483647LL || chunks > 65535) { return noalloc_fail(err, err_len, B200SVM_ERR_INVALID, "b200svm_update_w_noalloc: grid too large"); }
+    // every (chunk, f < ld) element that k_sum_chunks_noalloc reads is written by k_xt_v first: nothing of the previous call's
+    // contents survives into the result, so nothing has to be cleared
+    T *wpart = static_cast<T *>(scratch);
+    k_xt_v<T><<<dim3((unsigned) fblocks, (unsigned) chunks), 256, 0, stream>>>(X, n, ld, alpha, wpart, rpc);
+    k_sum_chunks_noalloc<T><<<(unsigned) ((F + 255) / 256), 256, 0, stream>>>(wpart, ld, F, (int) chunks, w);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { return noalloc_fail(err, err_len, B200SVM_ERR_CUDA, "b200svm_update_w_noalloc: kernel launch failed: %s", cudaGetErrorString(e)); }
+    return B200SVM_OK;
+}
+
+}  // namespace
+}  // namespace b200
+
+extern "C" int b200svm_update_w_noalloc(int dtype, const void *X_dev, int64_t n, int64_t F, int64_t ld, const void *alpha_dev, void *w_out_dev,
+                                        void *cuda_stream, char *err, size_t err_len) {
+    using namespace b200;
+    if (err != nullptr && err_len > 0) { err[0] = '\0'; }
+    if (dtype != B200SVM_F32 && dtype != B200SVM_F64) { return noalloc_fail(err, err_len, B200SVM_ERR_INVALID, "b200svm_update_w_noalloc: dtype must be B200SVM_F32 or B200SVM_F64"); }
+    if (X_dev == nullptr || alpha_dev == nullptr || w_out_dev == nullptr) { return noalloc_fail(err, err_len, B200SVM_ERR_INVALID, "b200svm_update_w_noalloc: null pointer"); }
+    if (n < 1 || F < 1 || ld < F) { return noalloc_fail(err, err_len, B200SVM_ERR_INVALID, "b200svm_update_w_noalloc: need n >= 1, F >= 1 and ld >= F (got n %lld, F %lld, ld %lld)", (long long) n, (long long) F, (long long) ld); }
+    const int dev = noalloc_device_of(X_dev);
+    if (dev < 0 || noalloc_device_of(alpha_dev) != dev || noalloc_device_of(w_out_dev) != dev) {
+        return noalloc_fail(err, err_len, B200SVM_ERR_INVALID, "b200svm_update_w_noalloc: X, alpha and w_out must be device pointers of one GPU (there is no CPU fallback and no staging copy)");
+    }
+    if (dev >= NOALLOC_MAX_DEVICES) { return noalloc_fail(err, err_len, B200SVM_ERR_INVALID, "b200svm_update_w_noalloc: device ordinal %d >= %d", dev, NOALLOC_MAX_DEVICES); }
+    int prev = -1;
+    cudaError_t e = cudaGetDevice(&prev);
+    if (e == cudaSuccess && prev != dev) { e = cudaSetDevice(dev); }
+    if (e != cudaSuccess) { return noalloc_fail(err, err_len, B200SVM_ERR_CUDA, "b200svm_update_w_noalloc: cannot select device %d: %s", dev, cudaGetErrorString(e)); }
+    int rc = B200SVM_OK;
+    // once per device, with that device current: the device address of the static array (racing first calls store the same value)
+    void *scratch = __atomic_load_n(&g_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+    if (scratch == nullptr) {
+        e = cudaGetSymbolAddress(&scratch, g_noalloc_scratch);
+        if (e != cudaSuccess || scratch == nullptr) {
+            rc = noalloc_fail(err, err_len, B200SVM_ERR_CUDA, "b200svm_update_w_noalloc: cudaGetSymbolAddress of the static scratch array failed on device %d: %s", dev, cudaGetErrorString(e));
+        } else {
+            __atomic_store_n(&g_noalloc_ptr[dev], scratch, __ATOMIC_RELEASE);
+        }
+    }
+    if (rc == B200SVM_OK) {
+        cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+        rc = dtype == B200SVM_F32 ? update_w_noalloc<float>(static_cast<const float *>(X_dev), n, F, ld, static_cast<const float *>(alpha_dev), static_cast<float *>(w_out_dev), stream, scratch, err, err_len)
+                                  : update_w_noalloc<double>(static_cast<const double *>(X_dev), n, F, ld, static_cast<const double *>(alpha_dev), static_cast<double *>(w_out_dev), stream, scratch, err, err_len);
+    }
+    if (prev >= 0 && prev != dev) { cudaSetDevice(prev); }
+    return rc;
+}
