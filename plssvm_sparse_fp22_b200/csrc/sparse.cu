@@ -187,28 +187,26 @@ __global__ void __launch_bounds__(256) k_sp_xt_v(csc_view B, const T *__restrict
 // ---------------------------------------------------------------------------------------------------------------------
 // S(g): the part of the kernel value that vanishes when two rows share no feature
 // ---------------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ double expm1_fast(double z) {
-    if (fabs(z) < 0x1p-7) {  // Taylor to z^7: truncation z^7 / 5040 -> relative 2^-42 / 5040 < 1e-16
-        double p = fma(z, 1.0 / 7.0, 1.0);
-        p = fma(z * (1.0 / 6.0), p, 1.0);
-        p = fma(z * (1.0 / 5.0), p, 1.0);
-        p = fma(z * (1.0 / 4.0), p, 1.0);
-        p = fma(z * (1.0 / 3.0), p, 1.0);
-        p = fma(z * (1.0 / 2.0), p, 1.0);
-        return z * p;
-    }
-    return expm1(z);
+__device__ __forceinline__ double expm1_taylor(double z) {  // |z| < 2^-7, to z^7: truncation z^7 / 5040 -> relative 2^-42 / 5040 < 1e-16
+    double p = fma(z, 1.0 / 5040.0, 1.0 / 720.0);
+    p = fma(p, z, 1.0 / 120.0);
+    p = fma(p, z, 1.0 / 24.0);
+    p = fma(p, z, 1.0 / 6.0);
+    p = fma(p, z, 0.5);
+    p = fma(p, z, 1.0);
+    return z * p;
 }
-__device__ __forceinline__ float expm1_fast(float z) {
-    if (fabsf(z) < 0x1p-4f) {  // Taylor to z^5: truncation relative z^5 / 720 < 2e-9
-        float p = fmaf(z, 1.f / 5.f, 1.f);
-        p = fmaf(z * (1.f / 4.f), p, 1.f);
-        p = fmaf(z * (1.f / 3.f), p, 1.f);
-        p = fmaf(z * (1.f / 2.f), p, 1.f);
-        return z * p;
-    }
-    return expm1f(z);
+__device__ __forceinline__ float expm1_taylor(float z) {  // |z| < 2^-4, to z^5: truncation relative z^5 / 720 < 2e-9
+    float p = fmaf(z, 1.f / 120.f, 1.f / 24.f);
+    p = fmaf(p, z, 1.f / 6.f);
+    p = fmaf(p, z, 0.5f);
+    p = fmaf(p, z, 1.f);
+    return z * p;
 }
+__device__ __forceinline__ bool expm1_small(double z) { return fabs(z) < 0x1p-7; }
+__device__ __forceinline__ bool expm1_small(float z) { return fabsf(z) < 0x1p-4f; }
+__device__ __forceinline__ double expm1_fast(double z) { return expm1_small(z) ? expm1_taylor(z) : expm1(z); }
+__device__ __forceinline__ float expm1_fast(float z) { return expm1_small(z) ? expm1_taylor(z) : expm1f(z); }
 
 struct kfun {
     int degree;
@@ -219,12 +217,25 @@ struct kfun {
     int lb;                   // double: bit at which q is split into limbs
 };
 
+// kernel constants in the handle's type, hoisted out of the slot loops.  za = a 2^-s folds the fixed-point scale into the factor of
+// the Gram value: a (q 2^-s) and (a 2^-s) q are the same real number and 2^-s is a power of two, so both round identically.
+template <typename T>
+struct kconst {
+    T za, coef0, c0pow;
+    int degree;
+};
+template <typename T>
+__device__ __forceinline__ kconst<T> make_kconst(const kfun &k) {
+    return kconst<T>{ (T) k.a * (T) k.fx_inv, (T) k.coef0, (T) k.c0pow, k.degree };
+}
+
+// S of the fixed-point Gram sum q (converted to T): rbf expm1(2 gamma G), polynomial (gamma G + c0)^deg - c0^deg
 template <typename T, int KERNEL>
-__device__ __forceinline__ T s_value(T g, const kfun &k) {
+__device__ __forceinline__ T s_of_q(T q, const kconst<T> &k) {
     if constexpr (KERNEL == B200SVM_RBF) {
-        return expm1_fast((T) k.a * g);
+        return expm1_fast(k.za * q);
     } else {
-        const T base = fma((T) k.a, g, (T) k.coef0);
+        const T base = fma(k.za, q, k.coef0);
         T r;
         switch (k.degree) {  // warp-uniform
             case 1: r = base; break;
@@ -233,7 +244,26 @@ __device__ __forceinline__ T s_value(T g, const kfun &k) {
             case 4: r = (base * base) * (base * base); break;
             default: r = ipow(base, k.degree); break;
         }
-        return r - (T) k.c0pow;
+        return r - k.c0pow;
+    }
+}
+// four slots at once: one branch for the whole quad on the rbf fast path (every |z| small, which is the rule: z = 2 gamma G)
+template <typename T, int KERNEL>
+__device__ __forceinline__ void s_of_q4(const T (&q)[4], const kconst<T> &k, T (&sv)[4]) {
+    if constexpr (KERNEL == B200SVM_RBF) {
+        T z[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { z[u] = k.za * q[u]; }
+        if (expm1_small(fmax(fmax(fabs(z[0]), fabs(z[1])), fmax(fabs(z[2]), fabs(z[3]))))) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { sv[u] = expm1_taylor(z[u]); }
+        } else {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { sv[u] = expm1_fast(z[u]); }
+        }
+    } else {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { sv[u] = s_of_q<T, KERNEL>(q[u], k); }
     }
 }
 
@@ -257,37 +287,126 @@ __device__ __forceinline__ T s_value(T g, const kfun &k) {
 //   double: q is split at bit `lb` into an unsigned low limb (32 - lb bits of head-room: up to 2^(32-lb) additions per slot
 //           without a carry) and a signed high limb; lb + 30 significant bits (52 for rows of up to 1024 stored entries)
 // The sum is exact on the fixed-point grid and independent of the order of the additions.
+// The accumulator is addressed through its 32-bit shared-memory address (computed once per kernel) with explicit ld / st / red
+// instructions: the address arithmetic of a generic pointer into dynamic shared memory is otherwise redone for every access.
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void red_s32(uint32_t a, int q) { asm volatile("red.shared.add.s32 [%0], %1;" ::"r"(a), "r"(q) : "memory"); }
+__device__ __forceinline__ void red_u32(uint32_t a, uint32_t q) { asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a), "r"(q) : "memory"); }
+__device__ __forceinline__ void red_s32_if(bool p, uint32_t a, int q) {
+    asm volatile("{\n\t.reg .pred pp;\n\tsetp.ne.b32 pp, %2, 0;\n\t@pp red.shared.add.s32 [%0], %1;\n\t}" ::"r"(a), "r"(q), "r"((int) p) : "memory");
+}
+__device__ __forceinline__ void red_u32_if(bool p, uint32_t a, uint32_t q) {
+    asm volatile("{\n\t.reg .pred pp;\n\tsetp.ne.b32 pp, %2, 0;\n\t@pp red.shared.add.u32 [%0], %1;\n\t}" ::"r"(a), "r"(q), "r"((int) p) : "memory");
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ uint4 lds_v4(uint32_t a) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_v4_zero(uint32_t a) { asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(a), "r"(0u) : "memory"); }
+
+__device__ __forceinline__ void load4(const float *p, float (&v)[4]) {
+    const float4 w = __ldg(reinterpret_cast<const float4 *>(p));
+    v[0] = w.x, v[1] = w.y, v[2] = w.z, v[3] = w.w;
+}
+__device__ __forceinline__ void load4(const double *p, double (&v)[4]) {
+    const double2 a = __ldg(reinterpret_cast<const double2 *>(p)), b = __ldg(reinterpret_cast<const double2 *>(p) + 1);
+    v[0] = a.x, v[1] = a.y, v[2] = b.x, v[3] = b.y;
+}
+
+// add(): p is the product ALREADY scaled by 2^s (the row value is scaled once when the row is loaded: a power of two commutes with
+// the rounding of the product).  take_q(): the accumulated integer converted to T (NOT scaled back: 2^-s is folded into the kernel
+// constant, kconst::za) with the slot cleared for the next visit; take_q4(): four consecutive slots (jl a multiple of 4).
 template <typename T>
 struct fixp;
 template <>
 struct fixp<float> {
     static constexpr int LIMBS = 1;
-    static __device__ __forceinline__ void add(uint32_t *acc, int, int jl, float p, float scale, int) {
-        atomicAdd(reinterpret_cast<int *>(&acc[jl]), __float2int_rn(p * scale));
+    static __device__ __forceinline__ void add(uint32_t acc_s, int, int jl, float p, int) { red_s32(acc_s + 4u * (uint32_t) jl, __float2int_rn(p)); }
+    static __device__ __forceinline__ void add_if(bool on, uint32_t acc_s, int, int jl, float p, int) {
+        red_s32_if(on, acc_s + 4u * (uint32_t) jl, __float2int_rn(p));
     }
-    static __device__ __forceinline__ float take(uint32_t *acc, int, int jl, double inv_scale, int) {
-        const int q = (int) acc[jl];
-        acc[jl] = 0u;
-        return (float) q * (float) inv_scale;  // 2^-s: exact scaling, one rounding of q to 24 bits
+    static __device__ __forceinline__ float take_q(uint32_t acc_s, int, int jl, int) {
+        const uint32_t a = acc_s + 4u * (uint32_t) jl;
+        const int q = (int) lds_u32(a);
+        sts_u32(a, 0u);
+        return (float) q;  // one rounding of q to 24 bits
+    }
+    static __device__ __forceinline__ void take_q4(uint32_t acc_s, int, int jl, int, float (&q)[4]) {
+        const uint32_t a = acc_s + 4u * (uint32_t) jl;
+        const uint4 v = lds_v4(a);
+        sts_v4_zero(a);
+        q[0] = (float) (int) v.x;
+        q[1] = (float) (int) v.y;
+        q[2] = (float) (int) v.z;
+        q[3] = (float) (int) v.w;
     }
 };
 template <>
 struct fixp<double> {
     static constexpr int LIMBS = 2;
-    static __device__ __forceinline__ void add(uint32_t *acc, int W, int jl, double p, double scale, int lb) {
-        const long long q = __double2ll_rn(p * scale);
-        atomicAdd(&acc[jl], (uint32_t) (q & ((1ll << lb) - 1ll)));
-        atomicAdd(reinterpret_cast<int *>(&acc[W + jl]), (int) (q >> lb));
+    static __device__ __forceinline__ void add(uint32_t acc_s, int W, int jl, double p, int lb) {
+        const long long q = __double2ll_rn(p);
+        const uint32_t a = acc_s + 4u * (uint32_t) jl;
+        red_u32(a, (uint32_t) (q & ((1ll << lb) - 1ll)));
+        red_s32(a + 4u * (uint32_t) W, (int) (q >> lb));
     }
-    static __device__ __forceinline__ double take(uint32_t *acc, int W, int jl, double inv_scale, int lb) {
-        const uint32_t lo = acc[jl];
-        const int hi = (int) acc[W + jl];
-        acc[jl] = 0u;
-        acc[W + jl] = 0u;
-        const long long q = ((long long) hi << lb) + (long long) lo;
-        return (double) q * inv_scale;
+    static __device__ __forceinline__ void add_if(bool on, uint32_t acc_s, int W, int jl, double p, int lb) {
+        const long long q = __double2ll_rn(p);
+        const uint32_t a = acc_s + 4u * (uint32_t) jl;
+        red_u32_if(on, a, (uint32_t) (q & ((1ll << lb) - 1ll)));
+        red_s32_if(on, a + 4u * (uint32_t) W, (int) (q >> lb));
+    }
+    static __device__ __forceinline__ double join(uint32_t lo, uint32_t hi, int lb) { return (double) (((long long) (int) hi << lb) + (long long) lo); }
+    static __device__ __forceinline__ double take_q(uint32_t acc_s, int W, int jl, int lb) {
+        const uint32_t a = acc_s + 4u * (uint32_t) jl, ah = a + 4u * (uint32_t) W;
+        const uint32_t lo = lds_u32(a), hi = lds_u32(ah);
+        sts_u32(a, 0u);
+        sts_u32(ah, 0u);
+        return join(lo, hi, lb);
+    }
+    static __device__ __forceinline__ void take_q4(uint32_t acc_s, int W, int jl, int lb, double (&q)[4]) {
+        const uint32_t a = acc_s + 4u * (uint32_t) jl, ah = a + 4u * (uint32_t) W;
+        const uint4 lo = lds_v4(a), hi = lds_v4(ah);
+        sts_v4_zero(a);
+        sts_v4_zero(ah);
+        q[0] = join(lo.x, hi.x, lb);
+        q[1] = join(lo.y, hi.y, lb);
+        q[2] = join(lo.z, hi.z, lb);
+        q[3] = join(lo.w, hi.w, lb);
     }
 };
+
+// N rounds of 32 consecutive entries of one (feature, block) segment of the transpose: lane l takes entries l, l + 32, ...; x = row
+// value 2^s.  GUARD: round u only if 32 u < left (left = entries from this lane on).
+template <typename T>
+constexpr int SEG_ROUNDS = sizeof(T) == 4 ? 6 : 2;  // registers: a double round costs three (index, value pair)
+template <typename T, int N, bool COMPACT, bool GUARD>
+__device__ __forceinline__ void seg_rounds(const uint16_t *__restrict__ pj, const T *__restrict__ pv, int left, T x, uint32_t acc_s, int W, int lb,
+                                           uint32_t *bits) {
+    int ja[N];
+    T va[N];
+#pragma unroll
+    for (int u = 0; u < N; ++u) {
+        if (!GUARD || 32 * u < left) {
+            ja[u] = (int) __ldg(pj + 32 * u);
+            va[u] = __ldg(pv + 32 * u);
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < N; ++u) {
+        if (!GUARD || 32 * u < left) {
+            fixp<T>::add(acc_s, W, ja[u], x * va[u], lb);
+            if constexpr (COMPACT) { atomicOr(&bits[ja[u] >> 5], 1u << (ja[u] & 31)); }
+        }
+    }
+}
 
 constexpr int SP_MAX_OWN = 4;  // stored entries of a row per thread: rows of up to 4 * blockDim.x entries
 
@@ -342,8 +461,9 @@ __global__ void __launch_bounds__(1024)
     uint16_t *list = longk + rmax;
     for (int k = t; k < W * FX::LIMBS + words; k += TT) { acc[k] = 0u; }
     if (t == 0) { nlong_s = 0; }
+    const uint32_t acc_s = smem_u32(acc);
     const T fx_scale = (T) kf.fx_scale;
-    const double fx_inv = kf.fx_inv;
+    const kconst<T> kc = make_kconst<T>(kf);
     const int lb = kf.lb;
     const int GS = 1 << gs_log2, NG = TT >> gs_log2, gid = t >> gs_log2, gl = t & (GS - 1);
     const int b0 = g * B.G, b1 = min(B.nb, b0 + B.G);
@@ -359,7 +479,7 @@ __global__ void __launch_bounds__(1024)
         const int64_t jmax = MODE == 4 ? 256 * ((row >> 8) + 1) : 0;
         const int b1r = MODE == 4 ? (int) min((int64_t) b1, (jmax + W - 1) / W) : b1;
         if (MODE == 4 ? b0 >= b1r : R == 0) { continue; }  // block-uniform
-        // ---- the row: (feature, value) of every stored entry; entry k is owned by thread k % TT
+        // ---- the row: (feature, value 2^s) of every stored entry; entry k is owned by thread k % TT
         if constexpr (FP22) {
             int carry = 0;
             for (int base = 0; base < R; base += TT) {
@@ -376,7 +496,7 @@ __global__ void __launch_bounds__(1024)
                 }
                 if (k < R) {
                     const T x = (T) fp22_value(w);
-                    xs[k] = x;
+                    xs[k] = x * fx_scale;
                     feat[k] = x != T(0) ? carry + off + incl : -1;
                 }
                 carry += tot;
@@ -385,7 +505,7 @@ __global__ void __launch_bounds__(1024)
         } else {
             for (int k = t; k < R; k += TT) {
                 const T x = __ldg(static_cast<const T *>(A.val) + p0 + k);
-                xs[k] = x;
+                xs[k] = x * fx_scale;  // the fixed-point scale 2^s rides on the row value
                 feat[k] = x != T(0) ? __ldg(A.col + p0 + k) : -1;
             }
         }
@@ -423,53 +543,72 @@ __global__ void __launch_bounds__(1024)
                     if (f >= 0 && b + 1 < b1r) { nxt[q] = __ldg(B.ptrT + (int64_t) f * ldp + b + 2); }
                 }
             }
-            // ---- 2. products: GS lanes per segment; four segments x two entries in flight per lane and round
-            for (int k0 = gid; k0 < R; k0 += 4 * NG) {
-                uint32_t e[4], e1[4];
-                T x[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int k = k0 + u * NG;
-                    e[u] = 0u;
-                    e1[u] = 0u;
-                    x[u] = T(0);
-                    if (k < R) {
-                        const uint32_t a0 = s0[k], a1 = s1[k];
-                        if ((int) (a1 - a0) <= thr) {
-                            e[u] = a0 + (uint32_t) gl;
-                            e1[u] = a1;
-                            x[u] = xs[k];
-                        }
+            // ---- 2. products
+            if (gs_log2 == 5) {
+                // one warp per segment, in chunks of SEG_ROUNDS rounds of 32 entries: every load of a chunk is in flight before its
+                // first product, so a typical segment exposes the L2 latency once; full chunks (warp-uniform test) run unpredicated
+                for (int k = warp; k < R; k += nwarps) {
+                    const uint32_t a0 = s0[k];
+                    const int len = (int) (s1[k] - a0);
+                    if (len <= 0 || len > thr) { continue; }
+                    const T x = xs[k];
+                    const uint16_t *pj = Bj + a0 + lane;
+                    const T *pv = Bv + a0 + lane;
+                    int rest = len;
+                    for (; rest >= 32 * SEG_ROUNDS<T>; rest -= 32 * SEG_ROUNDS<T>, pj += 32 * SEG_ROUNDS<T>, pv += 32 * SEG_ROUNDS<T>) {
+                        seg_rounds<T, SEG_ROUNDS<T>, COMPACT, false>(pj, pv, 0, x, acc_s, W, lb, bits);
                     }
+                    if (rest > 0) { seg_rounds<T, SEG_ROUNDS<T>, COMPACT, true>(pj, pv, rest - lane, x, acc_s, W, lb, bits); }
                 }
-                bool more = (e[0] < e1[0]) | (e[1] < e1[1]) | (e[2] < e1[2]) | (e[3] < e1[3]);
-                while (more) {
-                    int ja[4], jb[4];
-                    T va[4], vb2[4];
+            } else {
+                // GS < 32 lanes per segment; four segments x two entries in flight per lane and round
+                for (int k0 = gid; k0 < R; k0 += 4 * NG) {
+                    uint32_t e[4], e1[4];
+                    T x[4];
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
-                        if (e[u] < e1[u]) {
-                            ja[u] = (int) __ldg(Bj + e[u]);
-                            va[u] = __ldg(Bv + e[u]);
-                        }
-                        if (e[u] + (uint32_t) GS < e1[u]) {
-                            jb[u] = (int) __ldg(Bj + e[u] + GS);
-                            vb2[u] = __ldg(Bv + e[u] + GS);
+                        const int k = k0 + u * NG;
+                        e[u] = 0u;
+                        e1[u] = 0u;
+                        x[u] = T(0);
+                        if (k < R) {
+                            const uint32_t a0 = s0[k], a1 = s1[k];
+                            if ((int) (a1 - a0) <= thr) {
+                                e[u] = a0 + (uint32_t) gl;
+                                e1[u] = a1;
+                                x[u] = xs[k];
+                            }
                         }
                     }
-                    more = false;
+                    bool more = (e[0] < e1[0]) | (e[1] < e1[1]) | (e[2] < e1[2]) | (e[3] < e1[3]);
+                    while (more) {
+                        int ja[4], jb[4];
+                        T va[4], vb2[4];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        if (e[u] < e1[u]) {
-                            FX::add(acc, W, ja[u], x[u] * va[u], fx_scale, lb);
-                            if constexpr (COMPACT) { atomicOr(&bits[ja[u] >> 5], 1u << (ja[u] & 31)); }
+                        for (int u = 0; u < 4; ++u) {
+                            if (e[u] < e1[u]) {
+                                ja[u] = (int) __ldg(Bj + e[u]);
+                                va[u] = __ldg(Bv + e[u]);
+                            }
+                            if (e[u] + (uint32_t) GS < e1[u]) {
+                                jb[u] = (int) __ldg(Bj + e[u] + GS);
+                                vb2[u] = __ldg(Bv + e[u] + GS);
+                            }
                         }
-                        if (e[u] + (uint32_t) GS < e1[u]) {
-                            FX::add(acc, W, jb[u], x[u] * vb2[u], fx_scale, lb);
-                            if constexpr (COMPACT) { atomicOr(&bits[jb[u] >> 5], 1u << (jb[u] & 31)); }
+                        more = false;
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            if (e[u] < e1[u]) {
+                                FX::add(acc_s, W, ja[u], x[u] * va[u], lb);
+                                if constexpr (COMPACT) { atomicOr(&bits[ja[u] >> 5], 1u << (ja[u] & 31)); }
+                            }
+                            if (e[u] + (uint32_t) GS < e1[u]) {
+                                FX::add(acc_s, W, jb[u], x[u] * vb2[u], lb);
+                                if constexpr (COMPACT) { atomicOr(&bits[jb[u] >> 5], 1u << (jb[u] & 31)); }
+                            }
+                            e[u] = min(e[u] + 2u * (uint32_t) GS, e1[u]);
+                            more |= e[u] < e1[u];
                         }
-                        e[u] = min(e[u] + 2u * (uint32_t) GS, e1[u]);
-                        more |= e[u] < e1[u];
                     }
                 }
             }
@@ -481,7 +620,7 @@ __global__ void __launch_bounds__(1024)
                     const T x = xs[k];
                     for (uint32_t e = s0[k] + (uint32_t) t, e1 = s1[k]; e < e1; e += (uint32_t) TT) {
                         const int ja = (int) __ldg(Bj + e);
-                        FX::add(acc, W, ja, x * __ldg(Bv + e), fx_scale, lb);
+                        FX::add(acc_s, W, ja, x * __ldg(Bv + e), lb);
                         if constexpr (COMPACT) { atomicOr(&bits[ja >> 5], 1u << (ja & 31)); }
                     }
                 }
@@ -527,8 +666,7 @@ __global__ void __launch_bounds__(1024)
                 if constexpr (MODE == 0) {
                     for (int i = t; i < cnt; i += TT) {
                         const int jl = list[i];
-                        const T gv = FX::take(acc, W, jl, fx_inv, lb);
-                        rowsum = fma(s_value<T, KERNEL>(gv, kf), __ldg(vb + jl), rowsum);
+                        rowsum = fma(s_of_q<T, KERNEL>(FX::take_q(acc_s, W, jl, lb), kc), __ldg(vb + jl), rowsum);
                     }
                 } else {
                     const int64_t visit = (int64_t) b * cache.rows + (row - row_lo);
@@ -538,7 +676,7 @@ __global__ void __launch_bounds__(1024)
                             cache.ptr[visit] = cnt4;
                             cache.cnt[visit] = cnt4;
                         }
-                        for (int i = t; i < cnt; i += TT) { (void) FX::take(acc, W, list[i], fx_inv, lb); }
+                        for (int i = t; i < cnt; i += TT) { (void) FX::take_q(acc_s, W, list[i], lb); }
                     } else {
                         int64_t base;
                         if constexpr (MODE == 2) {
@@ -557,7 +695,7 @@ __global__ void __launch_bounds__(1024)
                             __syncthreads();
                             base = base_s;
                             if (base < 0) {  // block-uniform: out of capacity, the host falls back to the two-pass assembly
-                                for (int i = t; i < cnt; i += TT) { (void) FX::take(acc, W, list[i], fx_inv, lb); }
+                                for (int i = t; i < cnt; i += TT) { (void) FX::take_q(acc_s, W, list[i], lb); }
                                 __syncthreads();
                                 continue;
                             }
@@ -565,9 +703,8 @@ __global__ void __launch_bounds__(1024)
                         T *sval = static_cast<T *>(cache.val);
                         for (int i = t; i < cnt; i += TT) {
                             const int jl = list[i];
-                            const T gv = FX::take(acc, W, jl, fx_inv, lb);
                             cache.j[base + i] = (uint16_t) jl;
-                            sval[base + i] = s_value<T, KERNEL>(gv, kf);
+                            sval[base + i] = s_of_q<T, KERNEL>(FX::take_q(acc_s, W, jl, lb), kc);
                         }
                         for (int i = cnt + t; i < ((cnt + 3) & ~3); i += TT) {
                             cache.j[base + i] = (uint16_t) 0;
@@ -582,29 +719,36 @@ __global__ void __launch_bounds__(1024)
                 float4 *tiles = reinterpret_cast<float4 *>(cache.Kc) + (tile_cum(row >> 7) - cache.tile0) * (int64_t) (128 * 256 / 4);
                 for (int q4 = t; q4 < (ncols >> 2); q4 += TT) {
                     const int jl = q4 << 2;
-                    float sv[4];
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) { sv[u] = s_value<T, KERNEL>(FX::take(acc, W, jl + u, fx_inv, lb), kf); }
+                    T qv[4], sv[4];
+                    FX::take_q4(acc_s, W, jl, lb, qv);
+                    s_of_q4<T, KERNEL>(qv, kc, sv);
                     const int64_t col = col_base + jl;
                     // consecutive rows (other CTAs, same time) fill the neighbouring 16 bytes: the sectors merge in L2
                     __stcg(tiles + (col >> 8) * (int64_t) (128 * 256 / 4) + (int64_t) (((int) (col & 255)) >> 2) * 128 + rr, make_float4(sv[0], sv[1], sv[2], sv[3]));
                 }
-                for (int jl = ncols + t; jl < W; jl += TT) { (void) FX::take(acc, W, jl, fx_inv, lb); }  // slots above the diagonal strip
+                for (int jl = ncols + 4 * t; jl < W; jl += 4 * TT) {  // slots above the diagonal strip
+                    T qv[4];
+                    FX::take_q4(acc_s, W, jl, lb, qv);
+                }
             } else {
-                for (int jl0 = t; jl0 < W; jl0 += 4 * TT) {  // four slots per thread in flight (the weights come from L2)
-                    T gv[4], vv[4];
+                // two quads of consecutive slots per thread and round; the weights (L1 / L2) of both are requested first
+                constexpr int QUADS = sizeof(T) == 4 ? 2 : 1;  // registers
+                for (int jl = 4 * t; jl < W; jl += 4 * QUADS * TT) {
+                    const int jl2 = jl + 4 * TT;
+                    const bool two = QUADS == 2 && jl2 < W;
+                    T qv[4], sv[4], va[4], vb4[4];
+                    load4(vb + jl, va);
+                    if (two) { load4(vb + jl2, vb4); }
+                    FX::take_q4(acc_s, W, jl, lb, qv);
+                    s_of_q4<T, KERNEL>(qv, kc, sv);
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const int jl = jl0 + u * TT;
-                        gv[u] = T(0);
-                        vv[u] = T(0);
-                        if (jl < W) {
-                            gv[u] = FX::take(acc, W, jl, fx_inv, lb);
-                            vv[u] = __ldg(vb + jl);
-                        }
+                    for (int u = 0; u < 4; ++u) { rowsum = fma(sv[u], va[u], rowsum); }
+                    if (two) {
+                        FX::take_q4(acc_s, W, jl2, lb, qv);
+                        s_of_q4<T, KERNEL>(qv, kc, sv);
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) { rowsum = fma(sv[u], vb4[u], rowsum); }
                     }
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) { rowsum = fma(s_value<T, KERNEL>(gv[u], kf), vv[u], rowsum); }
                 }
             }
             __syncthreads();
@@ -927,8 +1071,8 @@ void upload(ctx &c, dbuf &dst, const void *src, size_t bytes) {
 
 // shared memory of one k_sp_kmv CTA: accumulator limbs | bitmap | row (value, feature, segment start / end, long list) | slot list
 template <typename T>
-size_t kmv_smem_bytes(int W, int rmax) {
-    return (size_t) W * 4 * sp::fixp<T>::LIMBS + (size_t) W / 8 + (size_t) rmax * (sizeof(T) + 4 + 4 + 4 + 2) + (size_t) W * 2;
+size_t kmv_smem_bytes(int W, int rmax, bool compact = true) {  // the slot list (last region) is used by the compacting variants only
+    return (size_t) W * 4 * sp::fixp<T>::LIMBS + (size_t) W / 8 + (size_t) rmax * (sizeof(T) + 4 + 4 + 4 + 2) + (compact ? (size_t) W * 2 : 0);
 }
 
 template <typename T, int KERNEL, bool FP22>
@@ -1201,12 +1345,12 @@ void launch_kmv_variant(ctx &c, const sparse_state &st, const sp::csr_view &A, i
     int threads = c.opt_sparse_threads > 0 ? (int) c.opt_sparse_threads : st.threads;
     while ((int64_t) threads * sp::SP_MAX_OWN < max_row) { threads *= 2; }
     const int rmax = (int) std::max<int64_t>(32, (max_row + 31) / 32 * 32);
-    const size_t smem = kmv_smem_bytes<T>(st.W, rmax);
+    const bool compact = (mode != 0 && mode != 4) || (mode == 0 && st.fill < 0.5);
+    const size_t smem = kmv_smem_bytes<T>(st.W, rmax, compact);
     B200_REQUIRE(smem <= (size_t) 227 * 1024, "sparse block width and row length exceed the shared memory of one SM");
-    set_kmv_attributes<T>(smem);
+    set_kmv_attributes<T>(kmv_smem_bytes<T>(st.W, rmax));
     const int per_sm = (int) std::max<size_t>(1, std::min<size_t>((size_t) 2048 / (size_t) threads, (size_t) (227 * 1024) / (smem + 1024)));
     const int grid = (int) std::min<int64_t>((int64_t) NUM_SMS * per_sm, rows);
-    const bool compact = (mode != 0 && mode != 4) || (mode == 0 && st.fill < 0.5);
     // lanes per (feature, block) segment: the power of two next to the mean segment length (option: fixed)
     int gs_log2 = 0;
     if (c.opt_sparse_lanes > 0) {
