@@ -1032,9 +1032,17 @@ struct sparse_state {
     bool t_valid{ false }, t_refused{ false };
     int t_rank{ -1 }, t_world{ 0 };
     int64_t t_m{ -1 };
-    ~sparse_state() { tile_store_destroy(ts); }
-    // predict staging
-    dbuf p_rowptr, p_col, p_val, p_norms, p_u, p_out, p_stats;
+    ~sparse_state() {
+        tile_store_destroy(ts);
+        if (p_stream != nullptr) { cudaStreamDestroy(p_stream); }
+    }
+    // predict staging: two sets (upload + norms of chunk i + 1 on p_stream while chunk i computes); p_stats is also the set-up scratch
+    struct pstage {
+        dbuf rowptr, col, val, norms, u, out, stats;
+    };
+    pstage ps[2];
+    dbuf p_stats;
+    cudaStream_t p_stream{ nullptr };
 };
 
 sparse_state &state_of(ctx &c) {
@@ -1700,72 +1708,109 @@ void sp_predict(ctx &c, const T *alpha_dev, T bias, const int64_t *rowptr, const
     } else {
         weights<T>(c, alpha_dev, rbf ? st.u.as<T>() : static_cast<const T *>(nullptr), st.n, nbW, st.v.as<T>());  // sum v -> scal[S_TMP0]
     }
-    // stage the points in chunks of at most ~2^27 stored entries; values already in the handle's type (and FP22 words) are
-    // uploaded straight from the caller's arrays, validated on the device together with the row norms
-    const int64_t max_entries = int64_t(1) << 27;
+    // The points are staged in chunks of at most ~2^24 stored entries through two sets of buffers: while the kernels of chunk i run
+    // on the handle's stream, the host uploads chunk i + 1 on a second stream (values already in the handle's type, and FP22 words,
+    // straight from the caller's arrays) and one kernel there computes its norms, u, the largest norm (bound of the fixed-point
+    // scale, needed on the host before the launch) and validates the column indices.
+    int64_t max_entries = int64_t(1) << 24;
+    if (const char *e = std::getenv("B200SVM_PREDICT_CHUNK")) {  // test hook: stored entries per chunk
+        const long long v = std::atoll(e);
+        if (v > 0) { max_entries = v; }
+    }
     const bool same_type = st.fp22 || (fmt == B200SVM_VAL_F32 ? sizeof(T) == 4 : sizeof(T) == 8);
+    if (st.p_stream == nullptr) { B200_CUDA_CHECK(cudaStreamCreateWithFlags(&st.p_stream, cudaStreamNonBlocking)); }
     std::vector<int64_t> rp;
     std::vector<T> vals;
-    st.p_stats.reserve(2 * sizeof(unsigned long long));
     unsigned long long *mailbox = static_cast<unsigned long long *>(c.pinned);
-    for (int64_t r0 = 0; r0 < P;) {
+    struct chunk {
+        int64_t r0{ 0 }, rows{ 0 }, max_row{ 0 };
+        double norm2{ 0 };
+    };
+    const auto chunk_end = [&](int64_t r0) {
         int64_t r1 = r0 + 1;
         while (r1 < P && rowptr[r1 + 1] - rowptr[r0] <= max_entries) { ++r1; }
-        const int64_t rows = r1 - r0, e0 = rowptr[r0], entries = rowptr[r1] - e0;
+        return r1;
+    };
+    // upload + norms of the chunk starting at r0 into set `s` on the staging stream; returns after both are complete
+    const auto prepare = [&](int64_t r0, int s) {
+        sparse_state::pstage &ps = st.ps[s];
+        chunk ch;
+        ch.r0 = r0;
+        const int64_t r1 = chunk_end(r0);
+        ch.rows = r1 - r0;
+        const int64_t rows = ch.rows, e0 = rowptr[r0], entries = rowptr[r1] - e0;
         rp.resize((size_t) rows + 1);
-        int64_t max_row = 0;
         for (int64_t i = 0; i <= rows; ++i) {
             rp[(size_t) i] = rowptr[r0 + i] - e0;
             if (i > 0) {
                 B200_REQUIRE(rp[(size_t) i] >= rp[(size_t) i - 1], "CSR row pointers must be non-decreasing");
-                max_row = std::max(max_row, rp[(size_t) i] - rp[(size_t) i - 1]);
+                ch.max_row = std::max(ch.max_row, rp[(size_t) i] - rp[(size_t) i - 1]);
             }
         }
-        upload(c, st.p_rowptr, rp.data(), rp.size() * sizeof(int64_t));
-        if (st.fp22) {
-            upload(c, st.p_val, static_cast<const uint32_t *>(values) + e0, (size_t) entries * sizeof(uint32_t));
-            st.p_col.reserve(16);
-        } else {
-            B200_REQUIRE(colidx != nullptr || entries == 0, "null column index array");
-            upload(c, st.p_col, colidx + e0, (size_t) entries * sizeof(int32_t));
-            if (same_type) {
-                upload(c, st.p_val, static_cast<const T *>(values) + e0, (size_t) entries * sizeof(T));
+        cudaStream_t keep = c.stream;
+        c.stream = st.p_stream;  // upload() and norms_and_u() launch on the handle's current stream
+        try {
+            upload(c, ps.rowptr, rp.data(), rp.size() * sizeof(int64_t));
+            if (st.fp22) {
+                upload(c, ps.val, static_cast<const uint32_t *>(values) + e0, (size_t) entries * sizeof(uint32_t));
+                ps.col.reserve(16);
             } else {
-                vals.resize((size_t) entries);
-                for (int64_t p = 0; p < entries; ++p) {
-                    vals[(size_t) p] = fmt == B200SVM_VAL_F32 ? (T) static_cast<const float *>(values)[e0 + p] : (T) static_cast<const double *>(values)[e0 + p];
+                B200_REQUIRE(colidx != nullptr || entries == 0, "null column index array");
+                upload(c, ps.col, colidx + e0, (size_t) entries * sizeof(int32_t));
+                if (same_type) {
+                    upload(c, ps.val, static_cast<const T *>(values) + e0, (size_t) entries * sizeof(T));
+                } else {
+                    vals.resize((size_t) entries);
+                    for (int64_t q = 0; q < entries; ++q) {
+                        vals[(size_t) q] = fmt == B200SVM_VAL_F32 ? (T) static_cast<const float *>(values)[e0 + q] : (T) static_cast<const double *>(values)[e0 + q];
+                    }
+                    upload(c, ps.val, vals.data(), vals.size() * sizeof(T));
                 }
-                upload(c, st.p_val, vals.data(), vals.size() * sizeof(T));
             }
+            ps.out.reserve((size_t) rows * sizeof(T));
+            ps.norms.reserve((size_t) rows * sizeof(T));
+            ps.u.reserve((size_t) rows * sizeof(T));
+            ps.stats.reserve(2 * sizeof(unsigned long long));
+            const sp::csr_view A{ ps.rowptr.as<int64_t>(), ps.col.as<int32_t>(), ps.val.p, rows };
+            B200_CUDA_CHECK(cudaMemsetAsync(ps.stats.p, 0, 2 * sizeof(unsigned long long), c.stream));
+            norms_and_u<T>(c, st, A, ps.norms.as<T>(), ps.u.as<T>(), ps.stats.as<unsigned long long>());
+            B200_CUDA_CHECK(cudaMemcpyAsync(mailbox + 2 * s, ps.stats.p, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
+            B200_CUDA_CHECK(cudaStreamSynchronize(c.stream));
+        } catch (...) {
+            c.stream = keep;
+            throw;
         }
-        st.p_out.reserve((size_t) rows * sizeof(T));
-        st.p_norms.reserve((size_t) rows * sizeof(T));
-        st.p_u.reserve((size_t) rows * sizeof(T));
-        const sp::csr_view A{ st.p_rowptr.as<int64_t>(), st.p_col.as<int32_t>(), st.p_val.p, rows };
-        // norms, u and the validation of the column indices in one pass; two scalars come back
-        B200_CUDA_CHECK(cudaMemsetAsync(st.p_stats.p, 0, 2 * sizeof(unsigned long long), c.stream));
-        norms_and_u<T>(c, st, A, st.p_norms.as<T>(), st.p_u.as<T>(), st.p_stats.as<unsigned long long>());
-        B200_CUDA_CHECK(cudaMemcpyAsync(mailbox, st.p_stats.p, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
-        sync_stream(c);
-        B200_REQUIRE(mailbox[1] == 0ull, "Number of features per data point must match the number of features per predict point!");
-        double pts_norm2 = 0;
-        std::memcpy(&pts_norm2, &mailbox[0], sizeof(double));
+        c.stream = keep;
+        B200_REQUIRE(mailbox[2 * s + 1] == 0ull, "Number of features per data point must match the number of features per predict point!");
+        std::memcpy(&ch.norm2, &mailbox[2 * s], sizeof(double));
+        return ch;
+    };
+    sync_stream(c);  // the weights are complete and the staging sets are free before the second stream touches anything
+    chunk cur = prepare(0, 0);
+    for (int i = 0;; ++i) {
+        sparse_state::pstage &ps = st.ps[i & 1];
+        const int64_t rows = cur.rows;
+        const sp::csr_view A{ ps.rowptr.as<int64_t>(), ps.col.as<int32_t>(), ps.val.p, rows };
         if (linear) {
-            row_dot<T>(c, st, A, st.wvec.as<T>(), bias, st.p_out.as<T>());
+            row_dot<T>(c, st, A, st.wvec.as<T>(), bias, ps.out.as<T>());
         } else {
-            B200_CUDA_CHECK(cudaMemsetAsync(st.p_out.p, 0, (size_t) rows * sizeof(T), c.stream));
-            launch_kmv<T>(c, st, A, 0, rows, max_row, std::max(st.max_norm2, pts_norm2), st.v.as<T>(), st.p_out.as<T>());
+            B200_CUDA_CHECK(cudaMemsetAsync(ps.out.p, 0, (size_t) rows * sizeof(T), c.stream));
+            launch_kmv<T>(c, st, A, 0, rows, cur.max_row, std::max(st.max_norm2, cur.norm2), st.v.as<T>(), ps.out.as<T>());
             const sp::kfun kf = make_kfun(c);
             int64_t g = std::max<int64_t>(1, std::min<int64_t>((rows + 1023) / 1024, 8 * NUM_SMS));
-            sp::k_sp_finish<T><<<(unsigned) g, 256, 0, c.stream>>>(st.p_out.as<T>(), st.p_u.as<T>(), rows, 0, rows, rbf ? 1 : 0, (T) kf.c0pow,
+            sp::k_sp_finish<T><<<(unsigned) g, 256, 0, c.stream>>>(ps.out.as<T>(), ps.u.as<T>(), rows, 0, rows, rbf ? 1 : 0, (T) kf.c0pow,
                                                                    c.scal.as<T>(), S_TMP0, bias, 0, 1);
             count_launch(c);
             B200_CUDA_CHECK(cudaGetLastError());
         }
-        B200_CUDA_CHECK(cudaMemcpyAsync(out_host + r0, st.p_out.p, (size_t) rows * sizeof(T), cudaMemcpyDeviceToHost, c.stream));
+        const int64_t next = cur.r0 + rows;
+        chunk nxt;
+        if (next < P) { nxt = prepare(next, (i + 1) & 1); }  // overlaps the kernels queued above; the other set was drained by the copy below
+        B200_CUDA_CHECK(cudaMemcpyAsync(out_host + cur.r0, ps.out.p, (size_t) rows * sizeof(T), cudaMemcpyDeviceToHost, c.stream));
         c.stats.d2h_bytes += (int64_t) ((size_t) rows * sizeof(T));
-        sync_stream(c);  // staging vectors are reused by the next chunk
-        r0 = r1;
+        sync_stream(c);
+        if (next >= P) { break; }
+        cur = nxt;
     }
 }
 template void sp_predict<float>(ctx &, const float *, float, const int64_t *, const int32_t *, const void *, int64_t, int64_t, int, float *);

@@ -156,6 +156,28 @@ def test_csr_predict_and_update_w(kernel, dt):
             assert nrm_rel(w_o, w) < (1e-13 if dt == np.float64 else 1e-5)
 
 
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_csr_predict_chunk_pipeline(kernel, monkeypatch):
+    """The points are staged in chunks over two buffer sets (upload + norms of chunk i + 1 on a second stream while chunk i computes):
+    many small chunks (test hook B200SVM_PREDICT_CHUNK = stored entries per chunk) must give exactly the one-chunk result."""
+    n, F, P = 500, 600, 2100
+    dt = np.float32
+    rp, ci, v, y = make(n, F, 0.03, seed=41, dt=dt)
+    prp, pci, pv, _ = make(P, F, 0.03, seed=42, dt=dt, min_nnz=0)
+    alpha = (np.random.default_rng(8).standard_normal(n) * 0.1).astype(dt)
+    with capi.Handle(dt, kernel, gamma=1.0 / F) as h:
+        h.set_option(capi.OPT_SPARSE_BLOCK, 256)
+        h.set_data_csr(rp, ci, v, F)
+        one = h.predict_csr(alpha, 0.1, prp, pci, pv)
+        for chunk in (1, 700, 5000):  # one row per chunk; ~40 rows; ~280 rows
+            monkeypatch.setenv("B200SVM_PREDICT_CHUNK", str(chunk))
+            many = h.predict_csr(alpha, 0.1, prp, pci, pv)
+            # the fixed-point scale follows the largest norm of a CHUNK: the Gram sums round on a (slightly) different grid
+            assert nrm_rel(one, many) < 2e-6, chunk
+        monkeypatch.delenv("B200SVM_PREDICT_CHUNK")
+        assert np.array_equal(one, h.predict_csr(alpha, 0.1, prp, pci, pv))
+
+
 @pytest.mark.parametrize("dt", [np.float64, np.float32])
 @pytest.mark.parametrize("kernel", ["polynomial", "rbf"])
 @pytest.mark.parametrize("shape", [(300, 2000, 0.1, 128, 1), (200, 1500, 0.4, 128, 1), (900, 500, 0.05, 128, 2), (1000, 3000, 0.01, 256, 1)])
