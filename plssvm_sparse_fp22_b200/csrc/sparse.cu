@@ -561,12 +561,13 @@ __global__ void __launch_bounds__(1024)
                     if (rest > 0) { seg_rounds<T, SEG_ROUNDS<T>, COMPACT, true>(pj, pv, rest - lane, x, acc_s, W, lb, bits); }
                 }
             } else {
-                // GS < 32 lanes per segment; four segments x two entries in flight per lane and round
-                for (int k0 = gid; k0 < R; k0 += 4 * NG) {
-                    uint32_t e[4], e1[4];
-                    T x[4];
+                // GS < 32 lanes per segment (short segments: the visit is bound by its instruction count, not by the load latency):
+                // a group of GS lanes walks two segments at once, one entry of each per lane and round
+                for (int k0 = gid; k0 < R; k0 += 2 * NG) {
+                    uint32_t e[2], e1[2];
+                    T x[2];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
+                    for (int u = 0; u < 2; ++u) {
                         const int k = k0 + u * NG;
                         e[u] = 0u;
                         e1[u] = 0u;
@@ -580,34 +581,23 @@ __global__ void __launch_bounds__(1024)
                             }
                         }
                     }
-                    bool more = (e[0] < e1[0]) | (e[1] < e1[1]) | (e[2] < e1[2]) | (e[3] < e1[3]);
-                    while (more) {
-                        int ja[4], jb[4];
-                        T va[4], vb2[4];
+                    while ((e[0] < e1[0]) | (e[1] < e1[1])) {
+                        int ja[2];
+                        T va[2];
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) {
+                        for (int u = 0; u < 2; ++u) {
                             if (e[u] < e1[u]) {
                                 ja[u] = (int) __ldg(Bj + e[u]);
                                 va[u] = __ldg(Bv + e[u]);
                             }
-                            if (e[u] + (uint32_t) GS < e1[u]) {
-                                jb[u] = (int) __ldg(Bj + e[u] + GS);
-                                vb2[u] = __ldg(Bv + e[u] + GS);
-                            }
                         }
-                        more = false;
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) {
+                        for (int u = 0; u < 2; ++u) {
                             if (e[u] < e1[u]) {
                                 FX::add(acc_s, W, ja[u], x[u] * va[u], lb);
                                 if constexpr (COMPACT) { atomicOr(&bits[ja[u] >> 5], 1u << (ja[u] & 31)); }
+                                e[u] += (uint32_t) GS;
                             }
-                            if (e[u] + (uint32_t) GS < e1[u]) {
-                                FX::add(acc_s, W, jb[u], x[u] * vb2[u], lb);
-                                if constexpr (COMPACT) { atomicOr(&bits[jb[u] >> 5], 1u << (jb[u] & 31)); }
-                            }
-                            e[u] = min(e[u] + 2u * (uint32_t) GS, e1[u]);
-                            more |= e[u] < e1[u];
                         }
                     }
                 }
@@ -648,12 +638,10 @@ __global__ void __launch_bounds__(1024)
                     const int incl = warp_incl_scan(c, lane);
                     if (lane == 31) { wtot[warp] = incl; }
                     __syncthreads();
-                    int off = 0, tot = 0;
-                    for (int w2 = 0; w2 < nwarps; ++w2) {
-                        const int cw = wtot[w2];
-                        off += w2 < warp ? cw : 0;
-                        tot += cw;
-                    }
+                    const int cw = lane < nwarps ? wtot[lane] : 0;  // every warp scans the (at most 32) warp totals
+                    const int incl2 = warp_incl_scan(cw, lane);
+                    const int off = __shfl_sync(0xffffffffu, incl2 - cw, warp);
+                    const int tot = __shfl_sync(0xffffffffu, incl2, 31);
                     int pos = cnt + off + incl - c;
                     while (word != 0u) {
                         const int bit = __ffs((int) word) - 1;
