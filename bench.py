@@ -373,6 +373,24 @@ def warm_up(env, solve, W):
     return (2 + reps) * steps
 
 
+def ncu_traffic(csv_name, kernel_prefix):
+    """dram__bytes_read.sum + dram__bytes_write.sum (bytes, one launch) of the first launch of `kernel_prefix` in a committed
+    `ncu --set full ... --page raw --csv` export under profiles/; None when the file or the kernel is missing."""
+    import csv
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    try:
+        with open(os.path.join(ROOT, "profiles", csv_name), newline="") as f:
+            rows = list(csv.reader(f))
+        hdr, units = rows[0], rows[1]
+        ik, ir, iw = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        for r in rows[2:]:
+            if kernel_prefix in r[ik]:
+                return float(r[ir].replace(",", "")) * scale[units[ir]] + float(r[iw].replace(",", "")) * scale[units[iw]]
+    except Exception:
+        return None
+    return None
+
+
 def hbm_roofline(env, nbytes, matvec_ms, kernel, extra=None):
     hb = float(env.peaks.get("hbm_gbs", 6650.0))
     ach = nbytes / (matvec_ms * 1e-3) / 1e9 if matvec_ms > 0 else 0.0
@@ -585,6 +603,15 @@ def run_main_workload(a, env):
                                  "assembly": {"kernel": "k_gram_tc<STORE> (tcgen05 fp16x2-split, once per data set, inside the timed region; it also serves the first matvec)",
                                               "ms": build_ms, "alg_flops": flops, "achieved_tflops": asm_tf, "frac_of_bf16_sustained": asm_tf / peak if asm_tf else None,
                                               "frac_issued": 2.0 * asm_tf / peak if asm_tf else None}})
+            # DRAM traffic of one k_tile_sweep launch: from the committed ncu capture of this kernel when the run has the shape the
+            # capture was taken on (configs[1] on one GPU: the same tiles, the same bytes); null otherwise — never a typed-in literal
+            if world == 1 and a.points == 65536 and a.features == 1024 and a.kernel == "rbf" and a.dtype == "f32":
+                tr = ncu_traffic("r2_tile_sweep_ncu_full_raw.csv", "k_tile_sweep")
+                if tr is not None:
+                    roof["traffic"] = tr
+                    roof["traffic_over_algorithmic"] = tr / float(dense_cache_bytes)
+                    roof["traffic_note"] = ("bytes per launch = dram__bytes_read.sum + dram__bytes_write.sum of k_tile_sweep in profiles/r2_tile_sweep_ncu_full_raw.csv "
+                                            "(ncu --set full of this command at this shape, read at run time; not re-measured by this run)")
             # the sweep multiplies every stored entry twice (row part and mirrored column part): 4 flops per stored entry — NOT the
             # F m (m+1) of a recompute
             matvec_gflops = world * float(dense_cache_bytes) / (matvec_ms * 1e-3) / 1e9 if matvec_ms > 0 else None
